@@ -1,0 +1,81 @@
+"""ctypes binding of libpdec.so (the C-ABI CUDA library declared in include/pdec.h).
+
+There is NO CPU fallback: if the library is missing or a call fails, a PdecError is raised.
+"""
+import ctypes
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libpdec.so")
+
+MODE_CONSTANT, MODE_REPLICATE, MODE_CIRCULAR = 0, 1, 2
+EFFECT_NONE, EFFECT_GROW, EFFECT_ADD = 0, 1, 2
+
+# field extrapolation name -> resample/pad mode (reference: PF/physics/field/grid.py:240-249)
+MODE_OF_EXTRAPOLATION = {"constant": MODE_CONSTANT, "boundary": MODE_REPLICATE, "periodic": MODE_CIRCULAR}
+
+
+class PdecError(RuntimeError):
+    def __init__(self, code, where):
+        self.code = code
+        msg = _lib().pdec_error_string(code).decode() if _LIB is not None else "library not loaded"
+        RuntimeError.__init__(self, "%s failed: %s (code %d)" % (where, msg, code))
+
+
+_LIB = None
+
+_c = ctypes
+_P = _c.c_void_p
+_SIGNATURES = {
+    "pdec_version": (_c.c_int, []),
+    "pdec_error_string": (_c.c_char_p, [_c.c_int]),
+    "pdec_device_count": (_c.c_int, []),
+    "pdec_burgers_trajectory_fwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double,
+                                                _c.c_double, _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_int, _P]),
+    "pdec_burgers_trajectory_bwd": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
+                                                _c.c_double, _c.c_double, _c.c_float, _c.c_float, _c.c_int, _c.c_int,
+                                                _c.c_int, _P]),
+    "pdec_burgers_pair_loss_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int]),
+    "pdec_burgers_pair_loss": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _c.c_double,
+                                           _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_float, _c.c_float, _P,
+                                           _c.c_size_t, _P]),
+}
+
+
+def exported_symbols():
+    """Names of every entry point include/pdec.h declares (used by the CPU symbol test)."""
+    return sorted(_SIGNATURES)
+
+
+def _lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libpdec.so is not built (%s). Run `python -m pde_control_b200.build`. "
+                               "There is no CPU fallback." % LIB_PATH)
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError if the symbol is missing: fail loudly
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = lib
+    return _LIB
+
+
+def lib():
+    return _lib()
+
+
+def check(code, where):
+    if code != 0:
+        raise PdecError(code, where)
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (None -> NULL)."""
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def stream_ptr():
+    import torch
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)

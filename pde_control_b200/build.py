@@ -1,0 +1,65 @@
+"""Builds libpdec.so (the C-ABI CUDA library) in-tree with nvcc for sm_100a.
+
+Usage: python -m pde_control_b200.build [--force]
+The .so is git-ignored but travels to the GPU box with the gpurun snapshot.
+"""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libpdec.so")
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+
+COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+          "-Xcompiler", "-fPIC", "--use_fast_math=false"]
+# per-file extra flags: the physics kernels reproduce the reference's fp32 operation order -> no FMA contraction
+SOURCES = {
+    "abi.cu": [],
+    "burgers.cu": ["-fmad=false"],
+    "fluid.cu": ["-fmad=false"],
+    "cg.cu": [],
+    "host_pipeline.cu": [],
+}
+
+
+def _sources():
+    return [(os.path.join(CSRC, f), flags) for f, flags in SOURCES.items() if os.path.exists(os.path.join(CSRC, f))]
+
+
+def _stale():
+    if not os.path.exists(LIB):
+        return True
+    t = os.path.getmtime(LIB)
+    deps = [s for s, _ in _sources()] + [os.path.join(CSRC, "pdec_common.cuh"),
+                                         os.path.join(HERE, "..", "include", "pdec.h"), __file__]
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build(force=False, verbose=False):
+    if not force and not _stale():
+        return LIB
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+    objs = []
+    for src, flags in _sources():
+        obj = os.path.join(objdir, os.path.basename(src) + ".o")
+        cmd = [NVCC] + [f for f in COMMON if f != "--use_fast_math=false"] + flags + ["-c", src, "-o", obj]
+        if verbose:
+            cmd.insert(1, "-Xptxas=-v")
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))
+        if verbose:
+            print(r.stderr)
+        objs.append(obj)
+    cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-lcudart"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
