@@ -1,0 +1,89 @@
+"""TEST INFRASTRUCTURE ONLY -- fluid golden vectors from the UNMODIFIED reference NumPy backend
+(oracle/ref_shim.py).  Called by oracle/make_golden.py.  Build container only."""
+import os
+
+import numpy as np
+
+
+def _smooth(rng, shape, scale, passes=6):
+    a = rng.randn(*shape)
+    for _ in range(passes):
+        a = (a + np.roll(a, 1, -1) + np.roll(a, -1, -1) + np.roll(a, 1, -2) + np.roll(a, -1, -2)) / 5
+    return (a / np.abs(a).max() * scale).astype(np.float32)
+
+
+def random_staggered(rng, B, ny, nx, scale):
+    return _smooth(rng, (B, ny + 1, nx), scale), _smooth(rng, (B, ny, nx + 1), scale)
+
+
+def staggered_tensor(vy, vx):
+    """[B, ny+1, nx+1, 2] staggered tensor (staggered_grid.py:41-46)."""
+    B, ny1, nx = vy.shape
+    t = np.zeros((B, ny1, nx + 1, 2), np.float32)
+    t[:, :, :nx, 0] = vy
+    t[:, :ny1 - 1, :, 1] = vx
+    return t
+
+
+def fluid_step_case(pf, ny, nx, B, boundary, seed, steps, dt, solver="direct"):
+    rng = np.random.RandomState(seed)
+    rho = np.abs(_smooth(rng, (B, ny, nx), 1.0))
+    vy, vx = random_staggered(rng, B, ny, nx, 1.5)
+    material = pf.OPEN if boundary == "open" else pf.CLOSED
+    dom = pf.Domain([ny, nx], boundaries=material)
+    fluid = pf.Fluid(dom, density=rho[..., None].copy(), velocity=staggered_tensor(vy, vx), batch_size=B)
+    psolver = pf.SparseSciPy() if solver == "direct" else pf.SparseCG(accuracy=1e-7, max_iterations=5000)
+    phys = pf.IncompressibleFlow(pressure_solver=psolver)
+    out = dict(rho0=rho, vy0=vy, vx0=vx, dt=dt, boundary=boundary, steps=steps)
+    for s in range(steps):
+        fluid = phys.step(fluid, dt)
+        out["rho%d" % (s + 1)] = np.asarray(fluid.density.data[..., 0], np.float32)
+        out["vy%d" % (s + 1)] = np.asarray(fluid.velocity.data[0].data[..., 0], np.float32)
+        out["vx%d" % (s + 1)] = np.asarray(fluid.velocity.data[1].data[..., 0], np.float32)
+        out["p%d" % (s + 1)] = np.asarray(fluid.solve_info["pressure"].data[..., 0], np.float32)
+        out["div%d" % (s + 1)] = np.asarray(fluid.solve_info["divergence"].data[..., 0], np.float32)
+        out["avy%d" % (s + 1)] = np.asarray(fluid.solve_info["advected_velocity"].data[0].data[..., 0], np.float32)
+        out["avx%d" % (s + 1)] = np.asarray(fluid.solve_info["advected_velocity"].data[1].data[..., 0], np.float32)
+    return out
+
+
+def controlled_case(pf, ny, nx, B, seed, dt):
+    """Notebook variant: curl of a potential ('constant' extrapolation, like the U-Net output) advects the
+    density; staggered self-advection of that velocity (force loss)."""
+    rng = np.random.RandomState(seed)
+    rho = np.abs(_smooth(rng, (B, ny, nx), 1.0))
+    phi = _smooth(rng, (B, ny, nx), 6.0)
+    dom = pf.Domain([ny, nx])
+    density = pf.CenteredGrid.sample(0, dom, batch_size=B).copied_with(data=rho[..., None].copy())
+    pot = pf.CenteredGrid(phi[..., None].copy(), box=dom.box, extrapolation="constant")
+    vel = pf.staggered_curl_2d(pot)
+    nxt = pf.advect.semi_lagrangian(density, vel, dt)
+    adv = pf.advect.semi_lagrangian(vel, vel, dt)
+    return dict(rho=rho, phi=phi, dt=dt, vy=np.asarray(vel.data[0].data[..., 0], np.float32),
+                vx=np.asarray(vel.data[1].data[..., 0], np.float32), rho_next=np.asarray(nxt.data[..., 0], np.float32),
+                avy=np.asarray(adv.data[0].data[..., 0], np.float32), avx=np.asarray(adv.data[1].data[..., 0], np.float32),
+                density_extrapolation=str(density.extrapolation), velocity_extrapolation=str(vel.extrapolation))
+
+
+def poisson_cases(pf):
+    """PhiFlow/tests/test_poisson_solve.py:14-23 fixed right-hand sides + random 40x32 on OPEN/CLOSED."""
+    out = {}
+    rng = np.random.RandomState(4)
+    for name, material in (("open", pf.OPEN), ("closed", pf.CLOSED)):
+        dom = pf.Domain([40, 32], boundaries=material)
+        rhs = rng.randn(3, 40, 32).astype(np.float32)
+        if name == "closed":
+            rhs -= rhs.mean((1, 2), keepdims=True)
+        field = pf.CenteredGrid(rhs[..., None].copy(), box=dom.box)
+        p, _ = pf.poisson_solve(field, dom, solver=pf.SparseCG(accuracy=1e-6, max_iterations=5000))
+        out["rhs_" + name] = rhs
+        out["p_" + name] = np.asarray(p.data[..., 0], np.float32)
+    return out
+
+
+def main(pf, out_dir):
+    np.savez_compressed(os.path.join(out_dir, "fluid_open_32.npz"), **fluid_step_case(pf, 32, 32, 2, "open", 3, 3, 1.0))
+    np.savez_compressed(os.path.join(out_dir, "fluid_closed_32x24.npz"), **fluid_step_case(pf, 32, 24, 2, "closed", 5, 3, 0.7))
+    np.savez_compressed(os.path.join(out_dir, "fluid_open_128.npz"), **fluid_step_case(pf, 128, 128, 1, "open", 7, 1, 1.0))
+    np.savez_compressed(os.path.join(out_dir, "fluid_controlled_64.npz"), **controlled_case(pf, 64, 64, 2, 9, 1.0))
+    np.savez_compressed(os.path.join(out_dir, "poisson_40x32.npz"), **poisson_cases(pf))

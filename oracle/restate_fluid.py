@@ -1,0 +1,338 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU restatement (PyTorch-CPU) of the reference's 2-D incompressible-flow hot
+path (PhiFlow 1.4.0, TF-1.14 semantics): SURVEY rows F1-F8.  Autograd over this op graph is the gradient
+oracle; the pressure solve carries the reference's registered gradient (a second solve, A symmetric:
+PF/physics/pressuresolver/sparse.py:93-94).
+
+Parity pinning: forwards validated against the UNMODIFIED reference NumPy backend (oracle/ref_shim.py) by
+tests/test_oracle_fluid.py (build container) and against tests/golden/fluid_*.npz (generated from the real
+reference by oracle/make_golden_fluid.py).  The pressure is pinned as the *solution* of A p = div (direct
+sparse solve in fp64), not as a CG iterate sequence.
+
+Layouts (channel dropped): rho[B,ny,nx], vy[B,ny+1,nx], vx[B,ny,nx+1]; axis 0 = y, axis 1 = x
+(PF/physics/field/staggered_grid.py:33-39).  PF/ = /root/reference/PhiFlow/phi/.
+"""
+import numpy as np
+import torch
+
+from .restate import CONSTANT, REPLICATE, CIRCULAR, resample, pad_axis, l2_loss  # noqa: F401
+
+OPEN, CLOSED = "open", "closed"
+
+
+class Geometry:
+    """Domain box + derived staggered component boxes (PF/physics/field/staggered_grid.py:49-53)."""
+
+    def __init__(self, ny, nx, lower=(0.0, 0.0), size=None):
+        self.res = (ny, nx)
+        size = (float(ny), float(nx)) if size is None else size
+        self.lower = np.asarray(lower, np.float32)
+        self.size = np.asarray(size, np.float32)
+        self.dx = self.size.astype(np.float64) / np.asarray(self.res, np.float64)     # grid.py:77-79
+
+    def component(self, axis):
+        """(resolution, lower, size) of staggered component `axis` as a CenteredGrid."""
+        res = list(self.res)
+        res[axis] += 1
+        unit = np.zeros(2)
+        unit[axis] = self.dx[axis]
+        lower = (self.lower.astype(np.float64) - unit / 2).astype(np.float32)
+        upper = (self.lower.astype(np.float64) + self.size.astype(np.float64) + unit / 2).astype(np.float32)
+        return tuple(res), lower, (upper - lower).astype(np.float32)
+
+
+def _points(res, lower, size, dtype):
+    """CenteredGrid.getpoints (grid.py:176-181): float64 linspace cast to float32, then local_to_global."""
+    out = []
+    for d in range(2):
+        loc = torch.from_numpy(np.linspace(0.5 / res[d], 1 - 0.5 / res[d], res[d]).astype(np.float32)).to(dtype)
+        out.append(loc * torch.tensor(float(size[d]), dtype=dtype) + torch.tensor(float(lower[d]), dtype=dtype))
+    return out  # [y coords (res0), x coords (res1)]
+
+
+def _index_coords(x, lower, size, res, axis, dtype):
+    """sample_at: local = (x - lower)/size (geom/_box.py:50-52); idx = local*res - 0.5 (grid.py:104-105)."""
+    local = (x - torch.tensor(float(lower[axis]), dtype=dtype)) / torch.tensor(float(size[axis]), dtype=dtype)
+    return local * torch.tensor(float(res[axis]), dtype=dtype) - 0.5
+
+
+def _half_weights(self_lower, self_size, self_res, other_lower, axis, dtype):
+    """CenteredGrid.at fast path (grid.py:112-120): upper_weight = origin_in_local % 1.0 where
+    origin_in_local = global_to_local(other.lower) * resolution; lower_weight = 1 - upper_weight
+    (math/nd.py:386).  Computed like the reference (float32 box arithmetic, float64 product)."""
+    origin = (np.float32(other_lower[axis]) - np.float32(self_lower[axis])) / np.float32(self_size[axis])
+    origin = np.float64(origin) * self_res[axis]
+    wu = origin % 1.0
+    return (torch.tensor(float(np.float32(wu)), dtype=dtype), torch.tensor(float(np.float32(1 - wu)), dtype=dtype))
+
+
+def curl_2d(phi, mode=CONSTANT):
+    """F3: staggered_curl_2d (PF/physics/field/util.py:60-67): phi padded [1,2]x[1,2] with its own mode, 3x3
+    'valid' correlation -> vy[i,j] = phi[i,j]-phi[i,j+1] ([ny+1,nx]), vx[i,j] = phi[i+1,j]-phi[i,j] ([ny,nx+1])."""
+    p = pad_axis(pad_axis(phi, 1, 1, 2, mode), 2, 1, 2, mode)       # p[a,b] = phi[a-1,b-1]
+    ny, nx = phi.shape[1:]
+    vy = p[:, 1:ny + 2, 1:nx + 1] - p[:, 1:ny + 2, 2:nx + 2]
+    vx = p[:, 2:ny + 2, 1:nx + 2] - p[:, 1:ny + 1, 1:nx + 2]
+    return vy, vx
+
+
+def velocity_at_centers(vy, vx, geo):
+    """StaggeredGrid.at(centered points) (staggered_grid.py:126-137) -> per component CenteredGrid.at fast path:
+    crop + interpolate_linear along the staggered axis (math/nd.py:378-392): upper*wu + lower*wl."""
+    dt_ = vy.dtype
+    (_, ly, sy), (_, lx, sx) = geo.component(0), geo.component(1)
+    ry, rx = geo.component(0)[0], geo.component(1)[0]
+    wu, wl = _half_weights(ly, sy, ry, geo.lower, 0, dt_)
+    cy = vy[:, 1:, :] * wu + vy[:, :-1, :] * wl
+    wu, wl = _half_weights(lx, sx, rx, geo.lower, 1, dt_)
+    cx = vx[:, :, 1:] * wu + vx[:, :, :-1] * wl
+    return cy, cx
+
+
+def advect_centered(rho, vy, vx, dt, geo, mode):
+    """F1: semi_lagrangian(density, velocity, dt) (PF/physics/field/advect.py:24-37)."""
+    dtp = rho.dtype
+    ny, nx = geo.res
+    py, px = _points(geo.res, geo.lower, geo.size, dtp)
+    cy, cx = velocity_at_centers(vy, vx, geo)
+    dt_ = torch.tensor(dt, dtype=dtp)
+    y = py[None, :, None] - cy * dt_
+    x = px[None, None, :] - cx * dt_
+    iy = _index_coords(y, geo.lower, geo.size, geo.res, 0, dtp)
+    ix = _index_coords(x, geo.lower, geo.size, geo.res, 1, dtp)
+    return resample(rho, torch.stack([iy, ix], -1), mode)
+
+
+def _other_component_at(v_other, other_axis, geo, mode, dtp):
+    """Component `other_axis` brought to the face centres of the OTHER staggered component
+    (grid.py:112-123): pad 1 cell along the target's axis with the field's mode, then crop +
+    interpolate_linear over both axes (axis order y then x)."""
+    target_axis = 1 - other_axis
+    res_o, lo_o, sz_o = geo.component(other_axis)
+    res_t, lo_t, sz_t = geo.component(target_axis)
+    padded = pad_axis(v_other, 1 + target_axis, 1, 1, mode)
+    # padded box: lower - dx along target axis
+    lo_p = lo_o.astype(np.float64).copy()
+    lo_p[target_axis] -= geo.dx[target_axis]
+    sz_p = sz_o.astype(np.float64).copy()
+    sz_p[target_axis] += 2 * geo.dx[target_axis]
+    res_p = list(res_o)
+    res_p[target_axis] += 2
+    lo_p = lo_p.astype(np.float32)
+    sz_p = sz_p.astype(np.float32)
+    t = padded
+    for axis in (0, 1):
+        wu, wl = _half_weights(lo_p, sz_p, res_p, lo_t, axis, dtp)
+        if axis == 0:
+            t = t[:, 1:, :] * wu + t[:, :-1, :] * wl
+        else:
+            t = t[:, :, 1:] * wu + t[:, :, :-1] * wl
+    return t
+
+
+def advect_staggered(vy, vx, dt, geo, mode):
+    """F2: semi_lagrangian(v, v, dt) on a StaggeredGrid (advect.py:38-40 recursion per component)."""
+    dtp = vy.dtype
+    dt_ = torch.tensor(dt, dtype=dtp)
+    out = []
+    for c, vc in ((0, vy), (1, vx)):
+        res_c, lo_c, sz_c = geo.component(c)
+        py, px = _points(res_c, lo_c, sz_c, dtp)
+        other = _other_component_at(vx if c == 0 else vy, 1 - c, geo, mode, dtp)
+        uy, ux = (vc, other) if c == 0 else (other, vc)
+        y = py[None, :, None] - uy * dt_
+        x = px[None, None, :] - ux * dt_
+        iy = _index_coords(y, lo_c, sz_c, res_c, 0, dtp)
+        ix = _index_coords(x, lo_c, sz_c, res_c, 1, dtp)
+        out.append(resample(vc, torch.stack([iy, ix], -1), mode))
+    return out[0], out[1]
+
+
+def hard_boundary_mask(vy, vx, boundary):
+    """F4: PoissonDomain.with_hard_boundary_conditions (solver_api.py:111-121), no obstacles: faces on a solid
+    domain boundary are multiplied by 0, all others by 1."""
+    if boundary == OPEN:
+        return vy, vx
+    my = torch.ones_like(vy)
+    my[:, 0, :] = 0
+    my[:, -1, :] = 0
+    mx = torch.ones_like(vx)
+    mx[:, :, 0] = 0
+    mx[:, :, -1] = 0
+    return vy * my, vx * mx
+
+
+def divergence(vy, vx):
+    """F4: StaggeredGrid.divergence(physical_units=False) (staggered_grid.py:201-209)."""
+    return (vy[:, 1:, :] - vy[:, :-1, :]) + (vx[:, :, 1:] - vx[:, :, :-1])
+
+
+def laplace_apply(p, boundary):
+    """F5 matrix (sparse.py:114-154 / 157-221), no obstacles: off-diagonal 1 towards in-domain neighbours,
+    diagonal -(number of accessible neighbours) clamped <= -1: OPEN -4; CLOSED -(in-domain neighbours)."""
+    z = pad_axis(pad_axis(p, 1, 1, 1, CONSTANT), 2, 1, 1, CONSTANT)
+    nb = z[:, 2:, 1:-1] + z[:, :-2, 1:-1] + z[:, 1:-1, 2:] + z[:, 1:-1, :-2]
+    if boundary == OPEN:
+        diag = torch.full_like(p[0], -4.0)
+    else:
+        o = pad_axis(pad_axis(torch.ones_like(p[:1]), 1, 1, 1, CONSTANT), 2, 1, 1, CONSTANT)
+        diag = -(o[:, 2:, 1:-1] + o[:, :-2, 1:-1] + o[:, 1:-1, 2:] + o[:, 1:-1, :-2])[0]
+        diag = torch.minimum(diag, torch.tensor(-1.0, dtype=p.dtype))
+    return nb + diag[None] * p
+
+
+def conjugate_gradient(div, boundary, accuracy=1e-5, max_iterations=2000, guess=None):
+    """F5: conjugate_gradient with TF (immutable tensor) semantics, PF/math/blas.py:5-64.
+    Returns (x, iterations).  Stop rule: max|r| over the WHOLE batch < accuracy."""
+    k = div
+    if guess is None:
+        x = torch.zeros_like(k)
+        m = k
+    else:
+        x = guess
+        m = k - laplace_apply(x, boundary)
+    r = m
+    Am = laplace_apply(m, boundary)
+    it = 0
+
+    def nn(a, b):   # divide_no_nan
+        return torch.where(b == 0, torch.zeros_like(a), a / torch.where(b == 0, torch.ones_like(b), b))
+
+    while it < max_iterations and (accuracy is None or float(r.abs().max()) >= accuracy):
+        tmp = (m * Am).sum((1, 2), keepdim=True)
+        a = nn((m * r).sum((1, 2), keepdim=True), tmp)
+        x = x + a * m
+        r = r - a * Am
+        m = r - nn((r * Am).sum((1, 2), keepdim=True) * m, tmp)
+        Am = laplace_apply(m, boundary)
+        it += 1
+    return x, it
+
+
+_LU = {}
+
+
+def _direct_factor(ny, nx, boundary):
+    """fp64 sparse LU of the restated matrix.  CLOSED is singular (constants): bordered with the mean-zero
+    constraint, which is the solution CG converges to from a zero guess."""
+    key = (ny, nx, boundary)
+    if key not in _LU:
+        import scipy.sparse as sp
+        import scipy.sparse.linalg as spl
+        N = ny * nx
+        idx = np.arange(N).reshape(ny, nx)
+        rows, cols, vals = [], [], []
+        deg = np.zeros((ny, nx))
+        for sl_a, sl_b in ((np.s_[1:, :], np.s_[:-1, :]), (np.s_[:, 1:], np.s_[:, :-1])):
+            a, b = idx[sl_a].ravel(), idx[sl_b].ravel()
+            rows += [a, b]
+            cols += [b, a]
+            vals += [np.ones(a.size), np.ones(a.size)]
+            deg[sl_a] += 1
+            deg[sl_b] += 1
+        diag = -4.0 * np.ones(N) if boundary == OPEN else np.minimum(-deg.ravel(), -1.0)
+        rows.append(idx.ravel())
+        cols.append(idx.ravel())
+        vals.append(diag)
+        A = sp.csc_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))), shape=(N, N))
+        if boundary == CLOSED:
+            one = sp.csc_matrix(np.ones((N, 1)))
+            A = sp.bmat([[A, one], [one.T, None]], format="csc")
+        _LU[key] = spl.splu(A)
+    return _LU[key]
+
+
+def _direct_solve_np(rhs, boundary):
+    B, ny, nx = rhs.shape
+    lu = _direct_factor(ny, nx, boundary)
+    out = np.empty((B, ny, nx))
+    for b in range(B):
+        v = rhs[b].astype(np.float64).ravel()
+        if boundary == CLOSED:
+            v = np.concatenate([v, [0.0]])
+        out[b] = lu.solve(v)[:ny * nx].reshape(ny, nx)
+    return out
+
+
+class _PressureSolve(torch.autograd.Function):
+    """p = A^-1 div (converged CG), gradient dL/ddiv = A^-1 dL/dp (sparse.py:93-94, A symmetric)."""
+
+    @staticmethod
+    def forward(ctx, div, boundary):
+        ctx.boundary = boundary
+        return torch.from_numpy(_direct_solve_np(div.detach().numpy(), boundary)).to(div.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        return torch.from_numpy(_direct_solve_np(g.detach().numpy(), ctx.boundary)).to(g.dtype), None
+
+
+def pressure_solve(div, boundary):
+    return _PressureSolve.apply(div, boundary)
+
+
+def subtract_pressure_gradient(vy, vx, p, geo, boundary):
+    """F6: divergence_free tail (PF/physics/fluid.py:240-242): p *= dx[0]; StaggeredGrid.gradient with
+    replicate padding (staggered_grid.py:219-231) -> boundary-face gradients are 0;
+    v -= mask * grad."""
+    dtp = p.dtype
+    p = p * torch.tensor(float(geo.dx[0]), dtype=dtp)
+    py = pad_axis(p, 1, 1, 1, REPLICATE)
+    px = pad_axis(p, 2, 1, 1, REPLICATE)
+    gy = (py[:, 1:, :] - py[:, :-1, :]) / torch.tensor(float(geo.dx[0]), dtype=dtp)
+    gx = (px[:, :, 1:] - px[:, :, :-1]) / torch.tensor(float(geo.dx[1]), dtype=dtp)
+    gy, gx = hard_boundary_mask(gy, gx, boundary)
+    return vy - gy, vx - gx
+
+
+def divergence_free(vy, vx, geo, boundary, solver=pressure_solve):
+    """F4-F6: divergence_free (PF/physics/fluid.py:214-243), no obstacles."""
+    vy, vx = hard_boundary_mask(vy, vx, boundary)
+    div = divergence(vy, vx)
+    p = solver(div, boundary)
+    vy2, vx2 = subtract_pressure_gradient(vy, vx, p, geo, boundary)
+    return vy2, vx2, p, div
+
+
+def normalize_to(target, source, epsilon=1e-5):
+    """CenteredGrid.normalized -> math.normalize_to (PF/math/nd.py:28-40)."""
+    tt = target.sum((1, 2), keepdim=True)
+    den = torch.maximum(tt, torch.tensor(epsilon, dtype=target.dtype))
+    st = source.sum((1, 2), keepdim=True)
+    return target * (st / den)
+
+
+def modes_of(boundary):
+    """(density mode, velocity mode): Material.extrapolation_mode / vector_extrapolation_mode
+    (PF/physics/material.py:66-98): OPEN -> constant/constant; CLOSED (friction 0) -> boundary/boundary."""
+    return (CONSTANT, CONSTANT) if boundary == OPEN else (REPLICATE, REPLICATE)
+
+
+def incompressible_step(rho, vy, vx, dt, geo, boundary, solver=pressure_solve):
+    """F8: IncompressibleFlow.step (PF/physics/fluid.py:90-114) with default flags, no obstacles, no effects,
+    buoyancy_factor 0."""
+    rmode, vmode = modes_of(boundary)
+    rho2 = advect_centered(rho, vy, vx, dt, geo, rmode)
+    ay, ax = advect_staggered(vy, vx, dt, geo, vmode)
+    if boundary == CLOSED:                       # conserve_density and all boundaries solid (fluid.py:100-101)
+        rho2 = normalize_to(rho2, rho)
+    vy2, vx2, p, div = divergence_free(ay, ax, geo, boundary, solver)
+    return rho2, vy2, vx2, p
+
+
+def controlled_step(rho, phi, dt, geo, rho_mode=CONSTANT, phi_mode=CONSTANT):
+    """Notebook variant: ControlledIncompressibleFlow.step (src/control/pde/incompressible_flow.py:53-59):
+    v = staggered_curl_2d(potential); density advected by v.  Returns (rho', vy, vx)."""
+    vy, vx = curl_2d(phi, phi_mode)
+    return advect_centered(rho, vy, vx, dt, geo, rho_mode), vy, vx
+
+
+def force_loss(vys, vxs, dt, geo, mode=REPLICATE):
+    """IncompressibleFluidPDE.total_force_loss (src/control/pde/incompressible_flow.py:31-43): mean over
+    consecutive pairs of l2_loss(semi_lagrangian(v1, v1) - v2).  l2_loss of a StaggeredGrid difference =
+    l2 over the staggered tensor (sum over both components)."""
+    loss = 0
+    n = len(vys) - 1
+    for t in range(n):
+        ay, ax = advect_staggered(vys[t], vxs[t], dt, geo, mode)
+        loss = loss + l2_loss(ay - vys[t + 1]) + l2_loss(ax - vxs[t + 1])
+    return loss / n
