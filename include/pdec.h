@@ -95,6 +95,81 @@ int pdec_burgers_pair_loss(const float* s, float* grad_s, float* losses, int T, 
                            double viscosity, float box_lower, float box_size, int substeps, int resubstep,
                            float gl2, float gl1, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * 2-D incompressible flow  
+ * Layouts: rho[B,ny,nx], vy[B,ny+1,nx], vx[B,ny,nx+1] (PF/physics/field/staggered_grid.py:33-39), axis 0 = y.
+ * Box arguments: lower/size of the DOMAIN box per axis (PF/geom/_box.py); the staggered component boxes are
+ * derived as in staggered_grid.py:49-53.  `mode` = PDEC_MODE_* of the sampled field
+ * (Material.extrapolation_mode / vector_extrapolation_mode, PF/physics/material.py:66-98).
+ * Adjoint entry points take the forward INPUTS (nothing else is saved) and a caller-owned workspace.
+ * `accumulate` != 0 adds into the velocity-gradient outputs instead of overwriting them.
+ * ------------------------------------------------------------------------------------------------ */
+
+/* staggered_curl_2d, PF/physics/field/util.py:60-67: vy[i,j] = phi(i,j)-phi(i,j+1), vx[i,j] = phi(i+1,j)-phi(i,j),
+ * phi extended by `mode`.  bwd: transpose (replaces TF conv2d gradient). */
+int pdec_curl_2d_fwd(const float* phi, float* vy, float* vx, int B, int ny, int nx, int mode, void* stream);
+int pdec_curl_2d_bwd(const float* g_vy, const float* g_vx, float* g_phi, int B, int ny, int nx, int mode, void* stream);
+
+/* advect.semi_lagrangian(density, velocity, dt), PF/physics/field/advect.py:24-37 with StaggeredGrid.at(centres)
+ * staggered_grid.py:126-137 and CenteredGrid.sample_at grid.py:101-107 (-> tf_backend.resample :145-154; native twin
+ * Resample, PF/tf/cuda/src/resample.cu.cc:112-141). */
+int pdec_advect_centered_2d_fwd(const float* rho, const float* vy, const float* vx, float* rho_out, int B, int ny, int nx,
+                                int mode, double dt, float lower_y, float lower_x, float size_y, float size_x, void* stream);
+/* advect.semi_lagrangian(v, v, dt) on a StaggeredGrid (advect.py:38-40; grid.py:112-123). */
+int pdec_advect_staggered_2d_fwd(const float* vy, const float* vx, float* ay, float* ax, int B, int ny, int nx, int mode,
+                                 double dt, float lower_y, float lower_x, float size_y, float size_x, void* stream);
+/* adjoints (replace TF autodiff of gather_nd; native twin ResampleGradient, resample_gradient.cu.cc:138-226, which uses
+ * float atomics): deterministic gather-transpose over a window bounded by the per-element maximum displacement.
+ * g_rho / g_vy / g_vx of the centred variant may be NULL (not wanted). */
+size_t pdec_advect_2d_workspace_bytes(int B, int ny, int nx);
+int pdec_advect_centered_2d_bwd(const float* rho, const float* vy, const float* vx, const float* g_out, float* g_rho,
+                                float* g_vy, float* g_vx, int accumulate_v, int B, int ny, int nx, int mode, double dt,
+                                float lower_y, float lower_x, float size_y, float size_x, void* workspace,
+                                size_t workspace_bytes, void* stream);
+int pdec_advect_staggered_2d_bwd(const float* vy, const float* vx, const float* g_ay, const float* g_ax, float* g_vy,
+                                 float* g_vx, int accumulate, int B, int ny, int nx, int mode, double dt, float lower_y,
+                                 float lower_x, float size_y, float size_x, void* workspace, size_t workspace_bytes,
+                                 void* stream);
+
+/* PoissonDomain.with_hard_boundary_conditions (PF/physics/pressuresolver/solver_api.py:111-121, no obstacles: faces on a
+ * solid domain boundary are zeroed when closed != 0) fused with StaggeredGrid.divergence(physical_units=False)
+ * (staggered_grid.py:201-209). */
+int pdec_mask_divergence_2d_fwd(const float* vy, const float* vx, float* div, int B, int ny, int nx, int closed, void* stream);
+int pdec_mask_divergence_2d_bwd(const float* g_div, float* g_vy, float* g_vx, int accumulate, int B, int ny, int nx, int closed,
+                                void* stream);
+
+/* divergence_free tail, PF/physics/fluid.py:237-242: v_out = mask*v - mask*grad(p*dx0)/dx with replicate-padded
+ * gradient (staggered_grid.py:219-231: boundary-face gradient 0).  bwd outputs may be NULL. */
+int pdec_subtract_pressure_gradient_2d_fwd(const float* vy, const float* vx, const float* p, float* vy_out, float* vx_out, int B,
+                                           int ny, int nx, int closed, float size_y, float size_x, void* stream);
+int pdec_subtract_pressure_gradient_2d_bwd(const float* g_vy_out, const float* g_vx_out, float* g_vy, float* g_vx, float* g_p,
+                                           int accumulate_v, int B, int ny, int nx, int closed, float size_y, float size_x,
+                                           void* stream);
+
+/* CenteredGrid.normalized -> math.normalize_to (PF/physics/field/grid.py:205-209, PF/math/nd.py:28-40):
+ * out = target * (sum(source) / max(sum(target), epsilon)) per batch element; deterministic two-stage sums. */
+size_t pdec_normalize_2d_workspace_bytes(int B, int ny, int nx);
+int pdec_normalize_2d_fwd(const float* target, const float* source, float* out, int B, int ny, int nx, float epsilon,
+                          void* workspace, size_t workspace_bytes, void* stream);
+int pdec_normalize_2d_bwd(const float* target, const float* source, const float* g_out, float* g_target, float* g_source, int B,
+                          int ny, int nx, float epsilon, void* workspace, size_t workspace_bytes, void* stream);
+
+/* poisson_solve with SparseCG (PF/physics/pressuresolver/solver_api.py:132-158, sparse.py:73-111) = conjugate_gradient
+ * (PF/math/blas.py:5-64) on the matrix-free 5-point operator of sparse.py:114-221 without obstacles (off-diagonals 1 towards
+ * in-domain neighbours; diagonal -4 when open, -(in-domain neighbours) when closed).  Native twin: PressureSolve,
+ * PF/tf/cuda/src/pressure_solve_op.cu.cc:19-227.  The SAME entry serves the adjoint: dL/d(rhs) = solve(dL/dp)
+ * (sparse.py:93-94; tf_cuda_pressuresolver.py:43-50).
+ * rhs, p [B,ny,nx]; guess [B,ny,nx] or NULL (zero); iterations [B] int32 (device) or NULL; residual [B] (device, final
+ * max|r| per element) or NULL.  accuracy <= 0: run exactly max_iterations.
+ * stop_mode PDEC_CG_STOP_PER_ELEMENT: every batch element stops on its own max|r| < accuracy;
+ * PDEC_CG_STOP_WHOLE_BATCH: all elements iterate until the batch-wide max|r| < accuracy (blas.py:33-35). */
+#define PDEC_CG_STOP_PER_ELEMENT 0
+#define PDEC_CG_STOP_WHOLE_BATCH 1
+size_t pdec_cg_poisson_2d_workspace_bytes(int B, int ny, int nx);
+int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
+                       int closed, float accuracy, int max_iterations, int stop_mode, void* workspace, size_t workspace_bytes,
+                       void* stream);
+
 #ifdef __cplusplus
 }
 #endif

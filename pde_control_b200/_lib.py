@@ -39,6 +39,30 @@ _SIGNATURES = {
     "pdec_burgers_pair_loss": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _c.c_double,
                                            _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_float, _c.c_float, _P,
                                            _c.c_size_t, _P]),
+    # ---- 2-D incompressible flow ----
+    "pdec_curl_2d_fwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),
+    "pdec_curl_2d_bwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),
+    "pdec_advect_centered_2d_fwd": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double,
+                                                _c.c_float, _c.c_float, _c.c_float, _c.c_float, _P]),
+    "pdec_advect_staggered_2d_fwd": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double,
+                                                 _c.c_float, _c.c_float, _c.c_float, _c.c_float, _P]),
+    "pdec_advect_2d_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int]),
+    "pdec_advect_centered_2d_bwd": (_c.c_int, [_P, _P, _P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
+                                                _c.c_double, _c.c_float, _c.c_float, _c.c_float, _c.c_float, _P, _c.c_size_t, _P]),
+    "pdec_advect_staggered_2d_bwd": (_c.c_int, [_P, _P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
+                                                 _c.c_double, _c.c_float, _c.c_float, _c.c_float, _c.c_float, _P, _c.c_size_t, _P]),
+    "pdec_mask_divergence_2d_fwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),
+    "pdec_mask_divergence_2d_bwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),
+    "pdec_subtract_pressure_gradient_2d_fwd": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
+                                                           _c.c_float, _c.c_float, _P]),
+    "pdec_subtract_pressure_gradient_2d_bwd": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
+                                                           _c.c_float, _c.c_float, _P]),
+    "pdec_normalize_2d_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int]),
+    "pdec_normalize_2d_fwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _P, _c.c_size_t, _P]),
+    "pdec_normalize_2d_bwd": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _P, _c.c_size_t, _P]),
+    "pdec_cg_poisson_2d_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int]),
+    "pdec_cg_poisson_2d": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _c.c_int, _c.c_int,
+                                       _P, _c.c_size_t, _P]),
 }
 
 
@@ -79,3 +103,18 @@ def ptr(t):
 def stream_ptr():
     import torch
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+_WORKSPACES = {}
+
+
+def workspace(device, nbytes):
+    """Caller-owned scratch for the C-ABI calls: one grow-only byte tensor per (device, stream).  Work on one
+    stream is ordered, so consecutive ops may share it."""
+    import torch
+    key = (device.index if device.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(device).cuda_stream)
+    ws = _WORKSPACES.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
+        _WORKSPACES[key] = ws
+    return ws

@@ -1,0 +1,425 @@
+// cg.cu -- conjugate-gradient Poisson pressure solve for sm_100a (F7 adjoint reuses it).
+//
+// Operator (PF/physics/pressuresolver/sparse.py:114-221, no obstacles): (A p)[i,j] = sum of in-domain neighbours
+// + diag * p[i,j], diag = -4 (open) or -(number of in-domain neighbours) clamped <= -1 (closed).
+// Recurrence (PF/math/blas.py:37-55):  t = m.Am;  a = (m.r)/t;  x += a m;  r -= a Am;  m = r - ((r.Am) m)/t;  Am = A m,
+// with divide_no_nan, stop when max|r| < accuracy.
+//
+// Two kernels:
+//  * cg_smem_kernel: ONE CTA PER BATCH ELEMENT, persistent over all iterations (grids up to 16384 cells, e.g. 128x128).
+//    x, r, Am live in registers (16 cells per thread), the search direction m lives in shared memory (the only vector the
+//    5-point stencil reads across threads).  Per iteration: matvec + three dots + three axpys with NO global-memory traffic,
+//    two warp-shuffle block reductions ((m.Am, m.r) and (r.Am, max|r|)) and three __syncthreads.  HBM is touched once
+//    (rhs in, p out).  The iteration count is decided on the device -> CUDA-graph capturable.
+//  * cg_global_kernel: cooperative persistent kernel for large grids (vectors in global memory / L2), two passes per
+//    iteration (matvec fused with the dots of pass 1; axpys fused with the dot of pass 2; the m-update is folded into the
+//    next matvec), grid-wide barriers between passes, deterministic two-stage reductions.
+#include "pdec_common.cuh"
+#include <cooperative_groups.h>
+
+namespace cg = cooperative_groups;
+
+namespace pdec {
+
+__device__ __forceinline__ float div_no_nan(float a, float b) { return b == 0.0f ? 0.0f : a / b; }
+
+// neighbour-availability nibble: bit0 up (i-1), bit1 down (i+1), bit2 left (j-1), bit3 right (j+1)
+__device__ __forceinline__ unsigned cell_nibble(int i, int j, int ny, int nx) {
+    return (i > 0 ? 1u : 0u) | (i < ny - 1 ? 2u : 0u) | (j > 0 ? 4u : 0u) | (j < nx - 1 ? 8u : 0u);
+}
+__device__ __forceinline__ float cell_diag(unsigned nib, int closed) {
+    if (!closed) return -4.0f;
+    const float d = -(float)__popc(nib);
+    return fminf(d, -1.0f);
+}
+// sum in the column order of the sorted sparse row (sparse.py:173-176): i-1, j-1, centre, j+1, i+1
+__device__ __forceinline__ float stencil_apply(const float* m, int idx, int nx, unsigned nib, float diag) {
+    float s = 0.0f;
+    if (nib & 1u) s += m[idx - nx];
+    if (nib & 4u) s += m[idx - 1];
+    s += diag * m[idx];
+    if (nib & 8u) s += m[idx + 1];
+    if (nib & 2u) s += m[idx + nx];
+    return s;
+}
+
+template <int THREADS>
+__device__ __forceinline__ void block_reduce2(float& a, float& b, float (*red)[32], bool second_is_max) {
+    constexpr int NW = THREADS / 32;
+    a = warp_sum(a);
+    b = second_is_max ? warp_max(b) : warp_sum(b);
+    if (NW == 1) return;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { red[0][w] = a; red[1][w] = b; }
+    __syncthreads();
+    a = lane < NW ? red[0][lane] : 0.0f;
+    b = lane < NW ? red[1][lane] : 0.0f;
+    a = warp_sum(a);
+    b = second_is_max ? warp_max(b) : warp_sum(b);
+}
+
+template <int THREADS, int CPT>
+__global__ void __launch_bounds__(THREADS, 1) cg_smem_kernel(const float* __restrict__ rhs, const float* __restrict__ guess, float* __restrict__ out,
+                                                             int* __restrict__ iters, float* __restrict__ resid, int ny, int nx, int closed,
+                                                             float accuracy, int max_it) {
+    extern __shared__ __align__(16) float sm_m[];
+    __shared__ float redA[2][32], redB[2][32];
+    const int N = ny * nx, tid = threadIdx.x;
+    const size_t base = (size_t)blockIdx.x * N;
+    float x[CPT], r[CPT], am[CPT];
+    unsigned long long nibs[(CPT + 15) / 16];
+#pragma unroll
+    for (int k = 0; k < (CPT + 15) / 16; ++k) nibs[k] = 0ull;
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+        const int idx = tid + k * THREADS;
+        x[k] = 0.0f; r[k] = 0.0f; am[k] = 0.0f;
+        if (idx < N) {
+            const int i = idx / nx, j = idx - i * nx;
+            nibs[k >> 4] |= (unsigned long long)cell_nibble(i, j, ny, nx) << (4 * (k & 15));
+            r[k] = rhs[base + idx];
+            if (guess != nullptr) { x[k] = guess[base + idx]; sm_m[idx] = x[k]; }
+        }
+    }
+    if (guess != nullptr) {                 // momentum = k - A x0   (blas.py:24-26)
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < CPT; ++k) {
+            const int idx = tid + k * THREADS;
+            if (idx < N) {
+                const unsigned nib = (unsigned)(nibs[k >> 4] >> (4 * (k & 15))) & 15u;
+                r[k] -= stencil_apply(sm_m, idx, nx, nib, cell_diag(nib, closed));
+            }
+        }
+        __syncthreads();
+    }
+    float rmax = 0.0f, dummy = 0.0f;
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+        const int idx = tid + k * THREADS;
+        if (idx < N) { sm_m[idx] = r[k]; rmax = fmaxf(rmax, fabsf(r[k])); }
+    }
+    block_reduce2<THREADS>(dummy, rmax, redB, true);   // contains a __syncthreads when THREADS > 32
+    if (THREADS == 32) __syncwarp();
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+        const int idx = tid + k * THREADS;
+        if (idx < N) {
+            const unsigned nib = (unsigned)(nibs[k >> 4] >> (4 * (k & 15))) & 15u;
+            am[k] = stencil_apply(sm_m, idx, nx, nib, cell_diag(nib, closed));
+        }
+    }
+    int it = 0;
+    while (it < max_it && (accuracy <= 0.0f || rmax >= accuracy)) {
+        float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+        for (int k = 0; k < CPT; ++k) {
+            const int idx = tid + k * THREADS;
+            if (idx < N) { const float m = sm_m[idx]; s1 += m * am[k]; s2 += m * r[k]; }
+        }
+        block_reduce2<THREADS>(s1, s2, redA, false);
+        const float tmp = s1, a = div_no_nan(s2, tmp);
+        float s3 = 0.0f, mx = 0.0f;
+#pragma unroll
+        for (int k = 0; k < CPT; ++k) {
+            const int idx = tid + k * THREADS;
+            if (idx < N) {
+                const float m = sm_m[idx];
+                x[k] += a * m;
+                r[k] -= a * am[k];
+                s3 += r[k] * am[k];
+                mx = fmaxf(mx, fabsf(r[k]));
+            }
+        }
+        block_reduce2<THREADS>(s3, mx, redB, true);
+        // every thread has read its own m above; cross-thread (stencil) reads of the old m finished before reduction A
+#pragma unroll
+        for (int k = 0; k < CPT; ++k) {
+            const int idx = tid + k * THREADS;
+            if (idx < N) sm_m[idx] = r[k] - div_no_nan(s3 * sm_m[idx], tmp);
+        }
+        if (THREADS == 32) __syncwarp(); else __syncthreads();
+#pragma unroll
+        for (int k = 0; k < CPT; ++k) {
+            const int idx = tid + k * THREADS;
+            if (idx < N) {
+                const unsigned nib = (unsigned)(nibs[k >> 4] >> (4 * (k & 15))) & 15u;
+                am[k] = stencil_apply(sm_m, idx, nx, nib, cell_diag(nib, closed));
+            }
+        }
+        rmax = mx;
+        ++it;
+    }
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+        const int idx = tid + k * THREADS;
+        if (idx < N) out[base + idx] = x[k];
+    }
+    if (tid == 0) {
+        if (iters) iters[blockIdx.x] = it;
+        if (resid) resid[blockIdx.x] = rmax;
+    }
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// Large grids: cooperative persistent kernel, vectors in global memory (L2 resident up to ~20 MB per vector).
+// Unit of work = (batch element b, chunk c of consecutive cells); blocks take units grid-stride.
+// Per iteration TWO passes separated by grid-wide barriers:
+//   pass 1: m_new = r - (s3 m_old)/t_prev (folded m-update, recomputed for the 4 neighbours; m ping-pongs between two
+//           buffers), Am = A m_new, partials of m.Am and m.r
+//   pass 2: x += a m, r -= a Am, partials of r.Am and max|r|
+// Reductions are two-stage and deterministic: one partial per unit (fixed intra-block tree), then every block re-reduces
+// the partials of its element in a fixed order.  All partial slots ping-pong on the iteration parity, so no block can
+// overwrite a value another block still reads.  An element that has converged stops updating; its max|r| is carried.
+// -------------------------------------------------------------------------------------------------------------
+struct CgGlobal {
+    const float* rhs; const float* guess; float* x; float* r; float* m[2]; float* am; float* part;
+    int* iters; float* resid; int* count;
+    int B, ny, nx, closed, chunks, max_it;
+    float accuracy;
+};
+
+enum { S_MAM = 0, S_MR = 1, S_RAM = 2, S_MAX = 3, S_SLOTS = 4 };
+
+__device__ __forceinline__ float* part_ptr(const CgGlobal& P, int parity, int slot, int b) {
+    return P.part + (((size_t)parity * S_SLOTS + slot) * P.B + b) * P.chunks;
+}
+__device__ __forceinline__ float block_sum(float v, float* sh) {
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float t = (threadIdx.x & 31) < (blockDim.x >> 5) ? sh[threadIdx.x & 31] : 0.0f;
+    t = warp_sum(t);
+    __syncthreads();
+    return t;
+}
+__device__ __forceinline__ float block_max(float v, float* sh) {
+    v = warp_max(v);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float t = (threadIdx.x & 31) < (blockDim.x >> 5) ? sh[threadIdx.x & 31] : 0.0f;
+    t = warp_max(t);
+    __syncthreads();
+    return t;
+}
+// fixed-order sum / max over the `chunks` partials of one element (every block gets the same bits)
+__device__ __forceinline__ float reduce_chunks_sum(const float* p, int chunks, float* sh) {
+    float s = 0.0f;
+    for (int c = threadIdx.x; c < chunks; c += blockDim.x) s += __ldcg(p + c);
+    return block_sum(s, sh);
+}
+__device__ __forceinline__ float reduce_chunks_max(const float* p, int chunks, float* sh) {
+    float s = 0.0f;
+    for (int c = threadIdx.x; c < chunks; c += blockDim.x) s = fmaxf(s, __ldcg(p + c));
+    return block_max(s, sh);
+}
+
+__global__ void __launch_bounds__(256) cg_global_kernel(CgGlobal P) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ float sh[32];
+    const int N = P.ny * P.nx, nx = P.nx, ny = P.ny;
+    const int units = P.B * P.chunks;
+    const int per = (N + P.chunks - 1) / P.chunks;
+    // ---- init: x = guess | 0, r = rhs - A x; max|r| -> parity 1 (read by iteration 0) ----
+    for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        const int b = u / P.chunks, c = u - b * P.chunks;
+        const size_t base = (size_t)b * N;
+        const int lo = c * per, hi = min(N, lo + per);
+        float mx = 0.0f;
+        for (int idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
+            float rr = P.rhs[base + idx], xx = 0.0f;
+            if (P.guess) {
+                xx = P.guess[base + idx];
+                const int i = idx / nx, j = idx - i * nx;
+                const unsigned nib = cell_nibble(i, j, ny, nx);
+                rr -= stencil_apply(P.guess + base, idx, nx, nib, cell_diag(nib, P.closed));
+            }
+            P.x[base + idx] = xx;
+            P.r[base + idx] = rr;
+            P.m[1][base + idx] = 0.0f;        // "old" direction of iteration 0 (beta = 0)
+            mx = fmaxf(mx, fabsf(rr));
+        }
+        mx = block_max(mx, sh);
+        if (threadIdx.x == 0) {
+            part_ptr(P, 1, S_MAX, b)[c] = mx;
+            part_ptr(P, 1, S_RAM, b)[c] = 0.0f;
+            part_ptr(P, 1, S_MAM, b)[c] = 0.0f;
+            if (c == 0) P.count[b] = 0;
+        }
+    }
+    grid.sync();
+    for (int it = 0; it < P.max_it; ++it) {
+        const int cur = it & 1, prev = cur ^ 1;
+        // uniform exit test: is any element still above the accuracy?  (max >= acc  <=>  some chunk partial >= acc)
+        if (P.accuracy > 0.0f) {
+            int above = 0;
+            const float* mxp = part_ptr(P, prev, S_MAX, 0);
+            for (int k = threadIdx.x; k < units; k += blockDim.x) above |= (__ldcg(mxp + k) >= P.accuracy) ? 1 : 0;
+            if (!__syncthreads_or(above)) break;
+        }
+        const float* m_old = P.m[prev];
+        float* m_new = P.m[cur];
+        // ---- pass 1 ----
+        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+            const int b = u / P.chunks, c = u - b * P.chunks;
+            const float rmax = reduce_chunks_max(part_ptr(P, prev, S_MAX, b), P.chunks, sh);
+            if (P.accuracy > 0.0f && rmax < P.accuracy) continue;
+            const float t_prev = reduce_chunks_sum(part_ptr(P, prev, S_MAM, b), P.chunks, sh);
+            const float s3 = reduce_chunks_sum(part_ptr(P, prev, S_RAM, b), P.chunks, sh);
+            const size_t base = (size_t)b * N;
+            const float* rb = P.r + base;
+            const float* mo = m_old + base;
+            auto mval = [&](int q) -> float { return __ldcg(rb + q) - div_no_nan(s3 * __ldcg(mo + q), t_prev); };
+            const int lo = c * per, hi = min(N, lo + per);
+            float s1 = 0.0f, s2 = 0.0f;
+            for (int idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
+                const int i = idx / nx, j = idx - i * nx;
+                const unsigned nib = cell_nibble(i, j, ny, nx);
+                const float mm = mval(idx);
+                float a_m = 0.0f;
+                if (nib & 1u) a_m += mval(idx - nx);
+                if (nib & 4u) a_m += mval(idx - 1);
+                a_m += cell_diag(nib, P.closed) * mm;
+                if (nib & 8u) a_m += mval(idx + 1);
+                if (nib & 2u) a_m += mval(idx + nx);
+                m_new[base + idx] = mm;
+                P.am[base + idx] = a_m;
+                s1 += mm * a_m;
+                s2 += mm * __ldcg(rb + idx);
+            }
+            s1 = block_sum(s1, sh);
+            s2 = block_sum(s2, sh);
+            if (threadIdx.x == 0) {
+                part_ptr(P, cur, S_MAM, b)[c] = s1;
+                part_ptr(P, cur, S_MR, b)[c] = s2;
+            }
+        }
+        grid.sync();
+        // ---- pass 2 ----
+        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+            const int b = u / P.chunks, c = u - b * P.chunks;
+            const float rmax = reduce_chunks_max(part_ptr(P, prev, S_MAX, b), P.chunks, sh);
+            if (P.accuracy > 0.0f && rmax < P.accuracy) {       // converged earlier: carry its state forward
+                if (threadIdx.x == 0) {
+                    part_ptr(P, cur, S_MAX, b)[c] = part_ptr(P, prev, S_MAX, b)[c];
+                    part_ptr(P, cur, S_MAM, b)[c] = 0.0f;
+                    part_ptr(P, cur, S_RAM, b)[c] = 0.0f;
+                }
+                continue;
+            }
+            const float tmp = reduce_chunks_sum(part_ptr(P, cur, S_MAM, b), P.chunks, sh);
+            const float mr = reduce_chunks_sum(part_ptr(P, cur, S_MR, b), P.chunks, sh);
+            const float a = div_no_nan(mr, tmp);
+            const size_t base = (size_t)b * N;
+            const int lo = c * per, hi = min(N, lo + per);
+            float s3 = 0.0f, mx = 0.0f;
+            for (int idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
+                const float mm = m_new[base + idx], a_m = P.am[base + idx];
+                P.x[base + idx] += a * mm;
+                const float rr = P.r[base + idx] - a * a_m;
+                P.r[base + idx] = rr;
+                s3 += rr * a_m;
+                mx = fmaxf(mx, fabsf(rr));
+            }
+            s3 = block_sum(s3, sh);
+            mx = block_max(mx, sh);
+            if (threadIdx.x == 0) {
+                part_ptr(P, cur, S_RAM, b)[c] = s3;
+                part_ptr(P, cur, S_MAX, b)[c] = mx;
+                if (c == 0) P.count[b] = it + 1;
+            }
+        }
+        grid.sync();
+    }
+    // the last written parity holds the final max|r|: it is the one NOT equal to the parity of the next iteration.
+    // Both parities agree for converged elements; for elements stopped by max_it use the larger iteration's slot.
+    for (int b = blockIdx.x; b < P.B; b += gridDim.x) {
+        const int n_it = P.count[b];
+        const int par = (n_it == 0) ? 1 : ((n_it - 1) & 1);
+        const float rmax = reduce_chunks_max(part_ptr(P, par, S_MAX, b), P.chunks, sh);
+        if (threadIdx.x == 0) {
+            if (P.iters) P.iters[b] = n_it;
+            if (P.resid) P.resid[b] = rmax;
+        }
+    }
+}
+
+}  // namespace pdec
+
+using namespace pdec;
+
+#define PDEC_CG_SMEM_MAX_CELLS 16384
+
+static int global_chunks(int N) {
+    int c = (N + 8191) / 8192;
+    return c < 1 ? 1 : (c > 1024 ? 1024 : c);
+}
+
+extern "C" size_t pdec_cg_poisson_2d_workspace_bytes(int B, int ny, int nx) {
+    const size_t N = (size_t)ny * nx, b = B > 0 ? B : 1;
+    if (N <= PDEC_CG_SMEM_MAX_CELLS) return 256;
+    // r, m[2], Am + 2 parities x 4 partial slots + iteration counters
+    return 4 * b * N * sizeof(float) + 8 * b * global_chunks((int)N) * sizeof(float) + b * sizeof(int) + 1024;
+}
+
+template <int THREADS, int CPT = 16>
+static int launch_smem(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
+                       int closed, float accuracy, int max_iterations, cudaStream_t st) {
+    const size_t smem = (size_t)ny * nx * sizeof(float);
+    auto kernel = cg_smem_kernel<THREADS, CPT>;
+    if (smem > 48 * 1024 && cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return PDEC_ERR_CUDA_LAUNCH;
+    kernel<<<B, THREADS, smem, st>>>(rhs, guess, p, iterations, residual, ny, nx, closed, accuracy, max_iterations);
+    return PDEC_OK;
+}
+
+extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
+                                  int closed, float accuracy, int max_iterations, int stop_mode, void* workspace, size_t workspace_bytes,
+                                  void* stream) {
+    if (B < 0 || ny < 2 || nx < 2 || max_iterations < 0) return PDEC_ERR_INVALID_ARGUMENT;
+    const int variant = (stop_mode >> 8) & 0xff;      // experimental kernel-shape selector (benchmarks only)
+    stop_mode &= 0xff;
+    if (stop_mode != PDEC_CG_STOP_PER_ELEMENT && stop_mode != PDEC_CG_STOP_WHOLE_BATCH) return PDEC_ERR_INVALID_ARGUMENT;
+    if (stop_mode == PDEC_CG_STOP_WHOLE_BATCH && accuracy > 0.0f && B > 1) return PDEC_ERR_UNSUPPORTED_SIZE;
+    if (B == 0) return PDEC_OK;
+    if (!rhs || !p) return PDEC_ERR_INVALID_ARGUMENT;
+    if (workspace_bytes < pdec_cg_poisson_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+    cudaStream_t st = (cudaStream_t)stream;
+    closed = closed ? 1 : 0;
+    const long long N = (long long)ny * nx;
+    int rc = PDEC_OK;
+    if (N <= PDEC_CG_SMEM_MAX_CELLS) {
+        if (N > 8192 && variant == 1) rc = launch_smem<512, 32>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+        else if (N > 8192) rc = launch_smem<1024>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+        else if (N > 4096) rc = launch_smem<512>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+        else if (N > 2048) rc = launch_smem<256>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+        else if (N > 1024) rc = launch_smem<128>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+        else if (N > 512) rc = launch_smem<64>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+        else rc = launch_smem<32>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+        if (rc != PDEC_OK) return rc;
+        PDEC_CHECK_LAUNCH();
+        return PDEC_OK;
+    }
+    if (N > 0x7fffffffLL || !workspace) return PDEC_ERR_UNSUPPORTED_SIZE;
+    CgGlobal P;
+    const size_t n = (size_t)B * N;
+    float* w = reinterpret_cast<float*>(workspace);
+    P.rhs = rhs; P.guess = guess; P.x = p; P.r = w; P.m[0] = w + n; P.m[1] = w + 2 * n; P.am = w + 3 * n; P.part = w + 4 * n;
+    P.chunks = global_chunks((int)N);
+    P.count = reinterpret_cast<int*>(P.part + (size_t)8 * B * P.chunks);
+    P.iters = iterations; P.resid = residual;
+    P.B = B; P.ny = ny; P.nx = nx; P.closed = closed; P.max_it = max_iterations; P.accuracy = accuracy;
+    int dev = 0, sms = 148, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cg_global_kernel, 256, 0) != cudaSuccess || per_sm < 1) return PDEC_ERR_CUDA_LAUNCH;
+    long long grid = (long long)sms * per_sm;
+    const long long units = (long long)B * P.chunks;
+    if (grid > units) grid = units;
+    void* args[] = {&P};
+    if (cudaLaunchCooperativeKernel((void*)cg_global_kernel, dim3((unsigned)grid), dim3(256), args, 0, st) != cudaSuccess) {
+        cudaGetLastError();
+        return PDEC_ERR_CUDA_LAUNCH;
+    }
+    return PDEC_OK;
+}

@@ -1,0 +1,789 @@
+// fluid.cu -- 2-D incompressible-flow stencil / gather kernels for sm_100a:
+// staggered curl, semi-Lagrangian advection of a centred field and of the staggered velocity, masked
+// divergence, pressure-gradient subtraction, density normalisation, and the reverse-mode adjoint of each.
+//
+// Compile with -fmad=false: back-traced sample coordinates follow the reference's fp32 operation order
+// (the 'constant' extrapolation rule is discontinuous in the coordinate).
+//
+// Layouts (channel dropped, contiguous fp32): rho[B,ny,nx], vy[B,ny+1,nx], vx[B,ny,nx+1]; axis 0 = y.
+// Thread mapping: one thread per output sample, blockDim (32, 8), grid (x tiles, y tiles, batch): every warp
+// reads/writes 128 contiguous bytes of a row; gathers go through the read-only L1 path (__ldg) -- at the
+// configured sizes all fields are L2 resident (128x128 x 64 = 4 MiB per field, L2 = 126 MB).
+//
+// Adjoint of the bilinear gather = deterministic GATHER-TRANSPOSE (no float atomics): pass A stores every
+// source sample's back-traced index coordinates (xi_y, xi_x) and its coordinate gradients, and reduces the
+// per-batch-element maximum displacement R (integer atomicMax: order independent); pass B lets every
+// DESTINATION cell collect  sum_s g[s] * hat(xi_y[s]-i) * hat(xi_x[s]-j)  over the window |s-d| <= R in a fixed
+// order.  hat(t) = max(0, 1-|t|) is the bilinear weight; extrapolation modes act on xi.
+#include "pdec_common.cuh"
+
+namespace pdec {
+
+struct FluidGeo {
+    int ny, nx;
+    float lo[2], sz[2];          // domain box (centred grids)
+    float clo[2][2], csz[2][2];  // staggered component boxes [component][axis]  (staggered_grid.py:49-53)
+    float c_wu[2], c_wl[2];      // component c -> cell centres along axis c      (grid.py:112-120)
+    float s_wu[2][2], s_wl[2][2];// component 1-c -> face centres of component c, [c][axis]
+    float dt;
+};
+
+enum { V_CENTERED = 0, V_COMP_Y = 1, V_COMP_X = 2 };
+
+template <int MODE>
+__device__ __forceinline__ int map_index(int i, int n) {   // pad-mode index map; -1 = outside ('constant')
+    if (MODE == PDEC_MODE_CONSTANT) return (i < 0 || i >= n) ? -1 : i;
+    if (MODE == PDEC_MODE_REPLICATE) return min(max(i, 0), n - 1);
+    int m = i % n;
+    return m < 0 ? m + n : m;
+}
+template <int MODE>
+__device__ __forceinline__ float load_mapped(const float* __restrict__ f, int i, int j, int ny, int nx) {
+    const int a = map_index<MODE>(i, ny), b = map_index<MODE>(j, nx);
+    if (MODE == PDEC_MODE_CONSTANT && (a < 0 || b < 0)) return 0.0f;
+    return __ldg(f + (size_t)a * nx + b);
+}
+
+__device__ __forceinline__ float point_coord(int i, int n, float lower, float size) {
+    return cell_center_local(i, n) * size + lower;      // box.local_to_global (geom/_box.py:54-56)
+}
+__device__ __forceinline__ float index_coord(float x, float lower, float size, float resf) {
+    return ((x - lower) / size) * resf - 0.5f;          // _box.py:50-52, grid.py:104-105
+}
+
+// Resolution of the grid a VARIANT advects (= samples from and writes to).
+template <int VARIANT>
+__device__ __host__ __forceinline__ void variant_res(int ny, int nx, int& ry, int& rx) {
+    ry = ny + (VARIANT == V_COMP_Y ? 1 : 0);
+    rx = nx + (VARIANT == V_COMP_X ? 1 : 0);
+}
+
+// Velocity (uy, ux) at sample point (i, j) of the VARIANT's grid.  VMODE = extrapolation of the velocity field.
+template <int VARIANT, int VMODE>
+__device__ __forceinline__ void velocity_at(const FluidGeo& g, const float* __restrict__ vy, const float* __restrict__ vx,
+                                            int i, int j, float& uy, float& ux) {
+    const int ny = g.ny, nx = g.nx;
+    if (VARIANT == V_CENTERED) {            // StaggeredGrid.at(centres): upper*wu + lower*wl per component
+        uy = __ldg(vy + (size_t)(i + 1) * nx + j) * g.c_wu[0] + __ldg(vy + (size_t)i * nx + j) * g.c_wl[0];
+        ux = __ldg(vx + (size_t)i * (nx + 1) + j + 1) * g.c_wu[1] + __ldg(vx + (size_t)i * (nx + 1) + j) * g.c_wl[1];
+    } else if (VARIANT == V_COMP_Y) {       // vy faces: uy = vy; ux = vx padded along y, lerp y then x
+        uy = __ldg(vy + (size_t)i * nx + j);
+        const float a0 = load_mapped<VMODE>(vx, i, j, ny, nx + 1) * g.s_wu[0][0] + load_mapped<VMODE>(vx, i - 1, j, ny, nx + 1) * g.s_wl[0][0];
+        const float a1 = load_mapped<VMODE>(vx, i, j + 1, ny, nx + 1) * g.s_wu[0][0] + load_mapped<VMODE>(vx, i - 1, j + 1, ny, nx + 1) * g.s_wl[0][0];
+        ux = a1 * g.s_wu[0][1] + a0 * g.s_wl[0][1];
+    } else {                                // vx faces: ux = vx; uy = vy padded along x, lerp y then x
+        ux = __ldg(vx + (size_t)i * (nx + 1) + j);
+        const float a0 = load_mapped<VMODE>(vy, i + 1, j - 1, ny + 1, nx) * g.s_wu[1][0] + load_mapped<VMODE>(vy, i, j - 1, ny + 1, nx) * g.s_wl[1][0];
+        const float a1 = load_mapped<VMODE>(vy, i + 1, j, ny + 1, nx) * g.s_wu[1][0] + load_mapped<VMODE>(vy, i, j, ny + 1, nx) * g.s_wl[1][0];
+        uy = a1 * g.s_wu[1][1] + a0 * g.s_wl[1][1];
+    }
+}
+
+// Back-traced index coordinates of sample (i, j) of the VARIANT's grid.
+template <int VARIANT, int VMODE>
+__device__ __forceinline__ void backtrace(const FluidGeo& g, const float* __restrict__ vy, const float* __restrict__ vx,
+                                          int i, int j, int ry, int rx, float& xiy, float& xix) {
+    float uy, ux;
+    velocity_at<VARIANT, VMODE>(g, vy, vx, i, j, uy, ux);
+    const float *lo = (VARIANT == V_CENTERED) ? g.lo : g.clo[VARIANT - 1];
+    const float *sz = (VARIANT == V_CENTERED) ? g.sz : g.csz[VARIANT - 1];
+    const float y = point_coord(i, ry, lo[0], sz[0]) - uy * g.dt;    // advect.py:35
+    const float x = point_coord(j, rx, lo[1], sz[1]) - ux * g.dt;
+    xiy = index_coord(y, lo[0], sz[0], (float)ry);
+    xix = index_coord(x, lo[1], sz[1], (float)rx);
+}
+
+// Bilinear sample, TF op order (tf_backend.py:491-497): combine over y first, then x.
+// Optionally returns d/dxi_y and d/dxi_x.
+template <int MODE, bool DERIV>
+__device__ __forceinline__ float sample2d(const float* __restrict__ f, int ry, int rx, float xiy, float xix, float& dy, float& dx) {
+    int fy, cy, fx, cx;
+    float w0y, w1y, w0x, w1x;
+    interp_setup<MODE>(xiy, ry, fy, cy, w0y, w1y);
+    interp_setup<MODE>(xix, rx, fx, cx, w0x, w1x);
+    const float s00 = __ldg(f + (size_t)fy * rx + fx), s01 = __ldg(f + (size_t)fy * rx + cx);
+    const float s10 = __ldg(f + (size_t)cy * rx + fx), s11 = __ldg(f + (size_t)cy * rx + cx);
+    const float f0 = s00 * w1y + s10 * w0y;
+    const float f1 = s01 * w1y + s11 * w0y;
+    if (DERIV) {
+        dy = (s10 - s00) * w1x + (s11 - s01) * w0x;
+        dx = f1 - f0;
+    }
+    return f0 * w1x + f1 * w0x;
+}
+
+// ---- forward advection ---------------------------------------------------------------------------
+template <int VARIANT, int FMODE, int VMODE>
+__global__ void __launch_bounds__(256) advect_fwd_kernel(FluidGeo g, const float* __restrict__ field, const float* __restrict__ vy,
+                                                         const float* __restrict__ vx, float* __restrict__ out) {
+    int ry, rx;
+    variant_res<VARIANT>(g.ny, g.nx, ry, rx);
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    if (i >= ry || j >= rx) return;
+    const size_t sy = (size_t)(g.ny + 1) * g.nx, sx = (size_t)g.ny * (g.nx + 1), sf = (size_t)ry * rx;
+    float xiy, xix, d0, d1;
+    backtrace<VARIANT, VMODE>(g, vy + b * sy, vx + b * sx, i, j, ry, rx, xiy, xix);
+    out[b * sf + (size_t)i * rx + j] = sample2d<FMODE, false>(field + b * sf, ry, rx, xiy, xix, d0, d1);
+}
+
+// ---- adjoint pass A: coordinates, coordinate gradients, displacement bound ----------------------------
+// Effective coordinate for the transpose: 'constant' -> NaN marks "contributes nothing"; 'replicate' -> clamped.
+template <int MODE>
+__device__ __forceinline__ float effective_coord(float xi, int n) {
+    if (MODE == PDEC_MODE_CONSTANT) return (xi >= 0.0f && xi < (float)(n - 1)) ? xi : __int_as_float(0x7fc00000);
+    if (MODE == PDEC_MODE_REPLICATE) return fminf(fmaxf(xi, 0.0f), (float)(n - 1));
+    return xi;
+}
+
+template <int VARIANT, int FMODE, int VMODE>
+__global__ void __launch_bounds__(256) advect_bwd_prep_kernel(FluidGeo g, const float* __restrict__ field, const float* __restrict__ vy,
+                                                              const float* __restrict__ vx, const float* __restrict__ gout,
+                                                              float* __restrict__ XY, float* __restrict__ XX, float* __restrict__ GY,
+                                                              float* __restrict__ GX, int* __restrict__ rmax) {
+    int ry, rx;
+    variant_res<VARIANT>(g.ny, g.nx, ry, rx);
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    const size_t sy = (size_t)(g.ny + 1) * g.nx, sx = (size_t)g.ny * (g.nx + 1), sf = (size_t)ry * rx;
+    int dispy = 0, dispx = 0;
+    if (i < ry && j < rx) {
+        float xiy, xix, dy, dx;
+        backtrace<VARIANT, VMODE>(g, vy + b * sy, vx + b * sx, i, j, ry, rx, xiy, xix);
+        sample2d<FMODE, true>(field + b * sf, ry, rx, xiy, xix, dy, dx);
+        const float go = gout[b * sf + (size_t)i * rx + j];
+        const float *sz = (VARIANT == V_CENTERED) ? g.sz : g.csz[VARIANT - 1];
+        const size_t o = b * sf + (size_t)i * rx + j;
+        float ey = effective_coord<FMODE>(xiy, ry), ex = effective_coord<FMODE>(xix, rx);
+        if (FMODE == PDEC_MODE_CONSTANT && (ey != ey || ex != ex)) ey = ex = __int_as_float(0x7fc00000);
+        XY[o] = ey;
+        XX[o] = ex;
+        GY[o] = go * dy * (-(g.dt * (float)ry) / sz[0]);     // through xi = ((p - u*dt - lower)/size)*res - 0.5
+        GX[o] = go * dx * (-(g.dt * (float)rx) / sz[1]);
+        if (ey == ey) {
+            float ty = fabsf(ey - (float)i), tx = fabsf(ex - (float)j);
+            if (FMODE == PDEC_MODE_CIRCULAR) { ty = fminf(ty, (float)ry * 0.5f); tx = fminf(tx, (float)rx * 0.5f); }
+            dispy = (int)fminf(ty, 1.0e6f) + 1;               // window half-width that covers floor and ceil
+            dispx = (int)fminf(tx, 1.0e6f) + 1;
+        }
+    }
+    // block max -> one integer atomicMax per block (max is order independent: deterministic)
+    __shared__ int sm[2][8];
+    for (int o = 16; o > 0; o >>= 1) {
+        dispy = max(dispy, __shfl_xor_sync(PDEC_FULL_MASK, dispy, o));
+        dispx = max(dispx, __shfl_xor_sync(PDEC_FULL_MASK, dispx, o));
+    }
+    if (threadIdx.x == 0) { sm[0][threadIdx.y] = dispy; sm[1][threadIdx.y] = dispx; }
+    __syncthreads();
+    if (threadIdx.y == 0 && threadIdx.x < 8) {
+        dispy = sm[0][threadIdx.x];
+        dispx = sm[1][threadIdx.x];
+        for (int o = 4; o > 0; o >>= 1) {
+            dispy = max(dispy, __shfl_xor_sync(0xffu, dispy, o));
+            dispx = max(dispx, __shfl_xor_sync(0xffu, dispx, o));
+        }
+        if (threadIdx.x == 0) {
+            atomicMax(rmax + 2 * b, dispy);
+            atomicMax(rmax + 2 * b + 1, dispx);
+        }
+    }
+}
+
+__device__ __forceinline__ float hat(float t) { return fmaxf(0.0f, 1.0f - fabsf(t)); }
+
+// ---- adjoint pass B: gather-transpose of g over the bounded window ---------------------------------
+template <int MODE>
+__device__ __forceinline__ float gather_transpose(const float* __restrict__ XY, const float* __restrict__ XX, const float* __restrict__ G,
+                                                  int ry, int rx, int i, int j, int Ry, int Rx) {
+    float acc = 0.0f;
+    if (MODE == PDEC_MODE_CIRCULAR) {
+        Ry = min(Ry, ry / 2); Rx = min(Rx, rx / 2);
+        for (int di = -Ry; di <= Ry; ++di) {
+            const int a = map_index<MODE>(i + di, ry);
+            for (int dj = -Rx; dj <= Rx; ++dj) {
+                const int c = map_index<MODE>(j + dj, rx);
+                const size_t o = (size_t)a * rx + c;
+                float ty = __ldg(XY + o) - (float)i, tx = __ldg(XX + o) - (float)j;
+                ty -= (float)ry * rintf(ty / (float)ry);
+                tx -= (float)rx * rintf(tx / (float)rx);
+                acc += __ldg(G + o) * (hat(ty) * hat(tx));
+            }
+        }
+        return acc;
+    }
+    const int a0 = max(i - Ry, 0), a1 = min(i + Ry, ry - 1), c0 = max(j - Rx, 0), c1 = min(j + Rx, rx - 1);
+    for (int a = a0; a <= a1; ++a) {
+        for (int c = c0; c <= c1; ++c) {
+            const size_t o = (size_t)a * rx + c;
+            const float wy = hat(__ldg(XY + o) - (float)i);      // NaN ('constant', outside) -> fmaxf(0, NaN) = 0
+            if (wy > 0.0f) {
+                const float wx = hat(__ldg(XX + o) - (float)j);
+                if (wx > 0.0f) acc += __ldg(G + o) * (wy * wx);
+            }
+        }
+    }
+    return acc;
+}
+
+// transpose of "component brought to the other component's faces" (two nested 2-point lerps with pad mode)
+// G0X: coordinate gradient d/d(ux) at vy faces [ny+1, nx]  ->  contribution to g_vx[r, c]  (vx is [ny, nx+1])
+template <int VMODE>
+__device__ __forceinline__ float cross_to_vx(const FluidGeo& g, const float* __restrict__ G0X, int r, int c) {
+    const int ny = g.ny, nx = g.nx;
+    // g_t[i, c] = wu_x * G0X[i, c-1] + wl_x * G0X[i, c]   (i in [0, ny], c in [0, nx])
+    auto gt = [&](int i) -> float {
+        float v = 0.0f;
+        if (c >= 1) v += g.s_wu[0][1] * __ldg(G0X + (size_t)i * nx + c - 1);
+        if (c <= nx - 1) v += g.s_wl[0][1] * __ldg(G0X + (size_t)i * nx + c);
+        return v;
+    };
+    // t[i, c] = vx(i, c) * wu_y + vx(i-1, c) * wl_y with the row index mapped by VMODE
+    float acc = 0.0f;
+    if (VMODE == PDEC_MODE_CIRCULAR) {
+        acc = g.s_wu[0][0] * gt(r) + g.s_wl[0][0] * gt(r + 1);
+        if (r == 0) acc += g.s_wu[0][0] * gt(ny);          // i = ny reads vx(ny) -> row 0
+        if (r == ny - 1) acc += g.s_wl[0][0] * gt(0);      // i = 0 reads vx(-1) -> row ny-1
+        return acc;
+    }
+    acc = g.s_wu[0][0] * gt(r) + g.s_wl[0][0] * gt(r + 1);
+    if (VMODE == PDEC_MODE_REPLICATE) {
+        if (r == 0) acc += g.s_wl[0][0] * gt(0);           // vx(-1) -> row 0
+        if (r == ny - 1) acc += g.s_wu[0][0] * gt(ny);     // vx(ny) -> row ny-1
+    }
+    return acc;
+}
+// G1Y: coordinate gradient d/d(uy) at vx faces [ny, nx+1]  ->  contribution to g_vy[r, c]  (vy is [ny+1, nx])
+template <int VMODE>
+__device__ __forceinline__ float cross_to_vy(const FluidGeo& g, const float* __restrict__ G1Y, int r, int c) {
+    const int ny = g.ny, nx = g.nx;
+    // uy(i, j) = T(i, j) * wu_x + T(i, j-1) * wl_x,  T(i, c) = vy[i+1, c] * wu_y + vy[i, c] * wl_y, column mapped by VMODE
+    // g_T[i, c] = wu_x * G1Y[i, c] + wl_x * G1Y[i, c+1] (+ mode terms)
+    auto gT = [&](int i) -> float {
+        float v = g.s_wu[1][1] * __ldg(G1Y + (size_t)i * (nx + 1) + c) + g.s_wl[1][1] * __ldg(G1Y + (size_t)i * (nx + 1) + c + 1);
+        if (VMODE == PDEC_MODE_REPLICATE) {
+            if (c == 0) v += g.s_wl[1][1] * __ldg(G1Y + (size_t)i * (nx + 1));               // j = 0 reads T(i, -1) -> col 0
+            if (c == nx - 1) v += g.s_wu[1][1] * __ldg(G1Y + (size_t)i * (nx + 1) + nx);     // j = nx reads T(i, nx) -> col nx-1
+        } else if (VMODE == PDEC_MODE_CIRCULAR) {
+            if (c == nx - 1) v += g.s_wl[1][1] * __ldg(G1Y + (size_t)i * (nx + 1));          // j = 0 reads T(i, -1) -> col nx-1
+            if (c == 0) v += g.s_wu[1][1] * __ldg(G1Y + (size_t)i * (nx + 1) + nx);          // j = nx reads T(i, nx) -> col 0
+        }
+        return v;
+    };
+    float acc = 0.0f;
+    if (r >= 1) acc += g.s_wu[1][0] * gT(r - 1);
+    if (r <= ny - 1) acc += g.s_wl[1][0] * gT(r);
+    return acc;
+}
+
+// centred advection, pass B: g_rho (transpose), and the velocity gradient from the coordinate gradients
+template <int FMODE>
+__global__ void __launch_bounds__(256) advect_centered_bwd_kernel(FluidGeo g, const float* __restrict__ XY, const float* __restrict__ XX,
+                                                                  const float* __restrict__ GY, const float* __restrict__ GX,
+                                                                  const float* __restrict__ gout, const int* __restrict__ rmax,
+                                                                  float* __restrict__ g_rho, float* __restrict__ g_vy,
+                                                                  float* __restrict__ g_vx, int accumulate) {
+    const int ny = g.ny, nx = g.nx;
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    const size_t sf = (size_t)ny * nx;
+    if (i < ny && j < nx && g_rho != nullptr)
+        g_rho[b * sf + (size_t)i * nx + j] = gather_transpose<FMODE>(XY + b * sf, XX + b * sf, gout + b * sf, ny, nx, i, j, rmax[2 * b], rmax[2 * b + 1]);
+    // velocity at centres = vy[i+1]*wu + vy[i]*wl  ->  g_vy[i] = wu * GY[i-1] + wl * GY[i]
+    if (g_vy != nullptr && i <= ny && j < nx) {
+        float v = 0.0f;
+        if (i >= 1) v += g.c_wu[0] * __ldg(GY + b * sf + (size_t)(i - 1) * nx + j);
+        if (i <= ny - 1) v += g.c_wl[0] * __ldg(GY + b * sf + (size_t)i * nx + j);
+        float* p = g_vy + b * (size_t)(ny + 1) * nx + (size_t)i * nx + j;
+        *p = accumulate ? *p + v : v;
+    }
+    if (g_vx != nullptr && i < ny && j <= nx) {
+        float v = 0.0f;
+        if (j >= 1) v += g.c_wu[1] * __ldg(GX + b * sf + (size_t)i * nx + j - 1);
+        if (j <= nx - 1) v += g.c_wl[1] * __ldg(GX + b * sf + (size_t)i * nx + j);
+        float* p = g_vx + b * (size_t)ny * (nx + 1) + (size_t)i * (nx + 1) + j;
+        *p = accumulate ? *p + v : v;
+    }
+}
+
+// staggered self-advection, pass B.  W0 = {XY,XX,GY,GX} of the vy grid, W1 of the vx grid.
+template <int VMODE>
+__global__ void __launch_bounds__(256) advect_staggered_bwd_kernel(FluidGeo g, const float* __restrict__ W0, const float* __restrict__ W1,
+                                                                   const float* __restrict__ g_ay, const float* __restrict__ g_ax,
+                                                                   const int* __restrict__ rmax0, const int* __restrict__ rmax1,
+                                                                   float* __restrict__ g_vy, float* __restrict__ g_vx, int accumulate,
+                                                                   int B) {
+    const int ny = g.ny, nx = g.nx;
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    const size_t sy = (size_t)(ny + 1) * nx, sx = (size_t)ny * (nx + 1);
+    const float *XY0 = W0 + b * sy, *XX0 = W0 + (size_t)B * sy + b * sy, *GY0 = W0 + 2 * (size_t)B * sy + b * sy, *GX0 = W0 + 3 * (size_t)B * sy + b * sy;
+    const float *XY1 = W1 + b * sx, *XX1 = W1 + (size_t)B * sx + b * sx, *GY1 = W1 + 2 * (size_t)B * sx + b * sx, *GX1 = W1 + 3 * (size_t)B * sx + b * sx;
+    if (i <= ny && j < nx) {
+        float v = gather_transpose<VMODE>(XY0, XX0, g_ay + b * sy, ny + 1, nx, i, j, rmax0[2 * b], rmax0[2 * b + 1]);
+        v += __ldg(GY0 + (size_t)i * nx + j);               // uy = vy itself at vy faces
+        v += cross_to_vy<VMODE>(g, GY1, i, j);              // vy averaged to vx faces
+        float* p = g_vy + b * sy + (size_t)i * nx + j;
+        *p = accumulate ? *p + v : v;
+    }
+    if (i < ny && j <= nx) {
+        float v = gather_transpose<VMODE>(XY1, XX1, g_ax + b * sx, ny, nx + 1, i, j, rmax1[2 * b], rmax1[2 * b + 1]);
+        v += __ldg(GX1 + (size_t)i * (nx + 1) + j);
+        v += cross_to_vx<VMODE>(g, GX0, i, j);
+        float* p = g_vx + b * sx + (size_t)i * (nx + 1) + j;
+        *p = accumulate ? *p + v : v;
+    }
+}
+
+// ---- staggered curl (util.py:60-67) -------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(256) curl_fwd_kernel(const float* __restrict__ phi, float* __restrict__ vy, float* __restrict__ vx, int ny, int nx) {
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    if (i > ny || j > nx) return;
+    const float* f = phi + (size_t)b * ny * nx;
+    const float c = load_mapped<MODE>(f, i, j, ny, nx);
+    if (j < nx) vy[(size_t)b * (ny + 1) * nx + (size_t)i * nx + j] = c - load_mapped<MODE>(f, i, j + 1, ny, nx);
+    if (i < ny) vx[(size_t)b * ny * (nx + 1) + (size_t)i * (nx + 1) + j] = load_mapped<MODE>(f, i + 1, j, ny, nx) - c;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) curl_bwd_kernel(const float* __restrict__ g_vy, const float* __restrict__ g_vx, float* __restrict__ g_phi, int ny, int nx) {
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    if (i >= ny || j >= nx) return;
+    const float* gy = g_vy + (size_t)b * (ny + 1) * nx;
+    const float* gx = g_vx + (size_t)b * ny * (nx + 1);
+    // vy[a, c] = phi(m(a), m(c)) - phi(m(a), m(c+1)),  a in [0, ny], c in [0, nx-1]
+    // vx[a, c] = phi(m(a+1), m(c)) - phi(m(a), m(c)),  a in [0, ny-1], c in [0, nx]
+    float acc = 0.0f;
+    for (int pass = 0; pass < 2; ++pass) {
+        // rows a of vy whose mapped row is i: a == i always; a == ny if replicate and i == ny-1 / circular and i == 0
+        int a = i;
+        if (pass == 1) {
+            if ((MODE == PDEC_MODE_REPLICATE && i == ny - 1) || (MODE == PDEC_MODE_CIRCULAR && i == 0)) a = ny; else break;
+        }
+        acc += __ldg(gy + (size_t)a * nx + j);                                                          // + term, c = j
+        if (j >= 1) acc -= __ldg(gy + (size_t)a * nx + j - 1);                                          // - term, c + 1 = j
+        if (MODE == PDEC_MODE_REPLICATE && j == nx - 1) acc -= __ldg(gy + (size_t)a * nx + nx - 1);     // c + 1 = nx -> nx-1
+        if (MODE == PDEC_MODE_CIRCULAR && j == 0) acc -= __ldg(gy + (size_t)a * nx + nx - 1);           // c + 1 = nx -> 0
+    }
+    for (int pass = 0; pass < 2; ++pass) {
+        // columns c of vx whose mapped column is j: c == j always; c == nx if replicate and j == nx-1 / circular and j == 0
+        int c = j;
+        if (pass == 1) {
+            if ((MODE == PDEC_MODE_REPLICATE && j == nx - 1) || (MODE == PDEC_MODE_CIRCULAR && j == 0)) c = nx; else break;
+        }
+        acc -= __ldg(gx + (size_t)i * (nx + 1) + c);                                // - term, a = i
+        if (i >= 1) acc += __ldg(gx + (size_t)(i - 1) * (nx + 1) + c);              // + term, a + 1 = i
+        if (MODE == PDEC_MODE_REPLICATE && i == ny - 1) acc += __ldg(gx + (size_t)(ny - 1) * (nx + 1) + c);   // a + 1 = ny -> ny-1
+        if (MODE == PDEC_MODE_CIRCULAR && i == 0) acc += __ldg(gx + (size_t)(ny - 1) * (nx + 1) + c);        // a + 1 = ny -> 0
+    }
+    g_phi[(size_t)b * ny * nx + (size_t)i * nx + j] = acc;
+}
+
+// ---- masked divergence (solver_api.py:111-121, staggered_grid.py:201-209) ----------------------------
+__device__ __forceinline__ float face_mask(int idx, int n, int closed) { return (closed && (idx == 0 || idx == n)) ? 0.0f : 1.0f; }
+
+__global__ void __launch_bounds__(256) mask_divergence_fwd_kernel(const float* __restrict__ vy, const float* __restrict__ vx, float* __restrict__ div,
+                                                                  int ny, int nx, int closed) {
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    if (i >= ny || j >= nx) return;
+    const float* y = vy + (size_t)b * (ny + 1) * nx;
+    const float* x = vx + (size_t)b * ny * (nx + 1);
+    const float dy = y[(size_t)(i + 1) * nx + j] * face_mask(i + 1, ny, closed) - y[(size_t)i * nx + j] * face_mask(i, ny, closed);
+    const float dx = x[(size_t)i * (nx + 1) + j + 1] * face_mask(j + 1, nx, closed) - x[(size_t)i * (nx + 1) + j] * face_mask(j, nx, closed);
+    div[(size_t)b * ny * nx + (size_t)i * nx + j] = dy + dx;
+}
+
+__global__ void __launch_bounds__(256) mask_divergence_bwd_kernel(const float* __restrict__ g_div, float* __restrict__ g_vy, float* __restrict__ g_vx,
+                                                                  int ny, int nx, int closed, int accumulate) {
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    const float* d = g_div + (size_t)b * ny * nx;
+    if (i <= ny && j < nx) {
+        const float lo = (i >= 1) ? d[(size_t)(i - 1) * nx + j] : 0.0f, hi = (i < ny) ? d[(size_t)i * nx + j] : 0.0f;
+        const float v = (lo - hi) * face_mask(i, ny, closed);
+        float* p = g_vy + (size_t)b * (ny + 1) * nx + (size_t)i * nx + j;
+        *p = accumulate ? *p + v : v;
+    }
+    if (i < ny && j <= nx) {
+        const float lo = (j >= 1) ? d[(size_t)i * nx + j - 1] : 0.0f, hi = (j < nx) ? d[(size_t)i * nx + j] : 0.0f;
+        const float v = (lo - hi) * face_mask(j, nx, closed);
+        float* p = g_vx + (size_t)b * ny * (nx + 1) + (size_t)i * (nx + 1) + j;
+        *p = accumulate ? *p + v : v;
+    }
+}
+
+// ---- pressure-gradient subtraction (fluid.py:240-242, staggered_grid.py:219-231) ---------------------
+__global__ void __launch_bounds__(256) subtract_gradient_fwd_kernel(const float* __restrict__ vy, const float* __restrict__ vx, const float* __restrict__ p,
+                                                                    float* __restrict__ oy, float* __restrict__ ox, int ny, int nx, int closed,
+                                                                    float dx0, float dxy, float dxx) {
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    const float* q = p + (size_t)b * ny * nx;
+    if (i <= ny && j < nx) {
+        const size_t o = (size_t)b * (ny + 1) * nx + (size_t)i * nx + j;
+        const float m = face_mask(i, ny, closed);
+        float gr = 0.0f;                                   // replicate pad: boundary-face gradient is 0
+        if (i >= 1 && i < ny) gr = (q[(size_t)i * nx + j] * dx0 - q[(size_t)(i - 1) * nx + j] * dx0) / dxy;
+        oy[o] = vy[o] * m - gr * m;
+    }
+    if (i < ny && j <= nx) {
+        const size_t o = (size_t)b * ny * (nx + 1) + (size_t)i * (nx + 1) + j;
+        const float m = face_mask(j, nx, closed);
+        float gr = 0.0f;
+        if (j >= 1 && j < nx) gr = (q[(size_t)i * nx + j] * dx0 - q[(size_t)i * nx + j - 1] * dx0) / dxx;
+        ox[o] = vx[o] * m - gr * m;
+    }
+}
+
+__global__ void __launch_bounds__(256) subtract_gradient_bwd_kernel(const float* __restrict__ g_oy, const float* __restrict__ g_ox, float* __restrict__ g_vy,
+                                                                    float* __restrict__ g_vx, float* __restrict__ g_p, int ny, int nx, int closed,
+                                                                    float dx0, float dxy, float dxx, int accumulate) {
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    const float* gy = g_oy + (size_t)b * (ny + 1) * nx;
+    const float* gx = g_ox + (size_t)b * ny * (nx + 1);
+    if (g_vy != nullptr && i <= ny && j < nx) {
+        const float v = gy[(size_t)i * nx + j] * face_mask(i, ny, closed);
+        float* p = g_vy + (size_t)b * (ny + 1) * nx + (size_t)i * nx + j;
+        *p = accumulate ? *p + v : v;
+    }
+    if (g_vx != nullptr && i < ny && j <= nx) {
+        const float v = gx[(size_t)i * (nx + 1) + j] * face_mask(j, nx, closed);
+        float* p = g_vx + (size_t)b * ny * (nx + 1) + (size_t)i * (nx + 1) + j;
+        *p = accumulate ? *p + v : v;
+    }
+    if (g_p != nullptr && i < ny && j < nx) {
+        // interior faces only: face i (1..ny-1) contributes -g/dx to p[i] and +g/dx to p[i-1]
+        float acc = 0.0f;
+        if (i >= 1) acc -= gy[(size_t)i * nx + j] / dxy;
+        if (i + 1 < ny) acc += gy[(size_t)(i + 1) * nx + j] / dxy;
+        if (j >= 1) acc -= gx[(size_t)i * (nx + 1) + j] / dxx;
+        if (j + 1 < nx) acc += gx[(size_t)i * (nx + 1) + j + 1] / dxx;
+        g_p[(size_t)b * ny * nx + (size_t)i * nx + j] = acc * dx0;
+    }
+}
+
+// ---- density normalisation (grid.py:205-209, nd.py:28-40) ---------------------------------------------
+// stage 1: per (block, b) partial sums of up to three products, fixed order; stage 2 re-reduces the partials.
+__device__ __forceinline__ float block_sum_256(float v, float* sh) {
+    v = warp_sum(v);
+    const int w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) sh[w] = v;
+    __syncthreads();
+    float r = 0.0f;
+    if (threadIdx.x < 32) {
+        r = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.0f;
+        r = warp_sum(r);
+        if (threadIdx.x == 0) sh[0] = r;
+    }
+    __syncthreads();
+    r = sh[0];
+    __syncthreads();
+    return r;
+}
+
+// partials[(k * B + b) * nblk + blk], k = 0: sum a, 1: sum c, 2: sum a*c   (c may be null)
+__global__ void __launch_bounds__(256) sums_kernel(const float* __restrict__ a, const float* __restrict__ c, float* __restrict__ partials, int n, int B) {
+    __shared__ float sh[32];
+    const int b = blockIdx.y, nblk = gridDim.x;
+    const float* pa = a + (size_t)b * n;
+    const float* pc = c ? c + (size_t)b * n : nullptr;
+    float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += nblk * blockDim.x) {
+        const float x = pa[i], y = pc ? pc[i] : 0.0f;
+        s0 += x; s1 += y; s2 += x * y;
+    }
+    s0 = block_sum_256(s0, sh); s1 = block_sum_256(s1, sh); s2 = block_sum_256(s2, sh);
+    if (threadIdx.x == 0) {
+        partials[((size_t)0 * B + b) * nblk + blockIdx.x] = s0;
+        partials[((size_t)1 * B + b) * nblk + blockIdx.x] = s1;
+        partials[((size_t)2 * B + b) * nblk + blockIdx.x] = s2;
+    }
+}
+__device__ __forceinline__ float reduce_partials(const float* __restrict__ partials, int k, int B, int b, int nblk) {
+    float s = 0.0f;
+    for (int i = 0; i < nblk; ++i) s += partials[((size_t)k * B + b) * nblk + i];
+    return s;
+}
+// out = target * (sum(source) / max(sum(target), eps));  partials from sums_kernel(a = target, c = source)
+__global__ void __launch_bounds__(256) normalize_fwd_kernel(const float* __restrict__ target, const float* __restrict__ partials, float* __restrict__ out,
+                                                            int n, int B, int nblk, float eps) {
+    const int b = blockIdx.y;
+    const float T = reduce_partials(partials, 0, B, b, nblk), S = reduce_partials(partials, 1, B, b, nblk);
+    const float scale = S / fmaxf(T, eps);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[(size_t)b * n + i] = target[(size_t)b * n + i] * scale;
+}
+// p1 = sums(target, source) ; p2 = sums(g_out, target)[k=2] = sum(g_out * target)
+__global__ void __launch_bounds__(256) normalize_bwd_kernel(const float* __restrict__ g_out, const float* __restrict__ p1, const float* __restrict__ p2,
+                                                            float* __restrict__ g_target, float* __restrict__ g_source, int n, int B, int nblk, float eps) {
+    const int b = blockIdx.y;
+    const float T = reduce_partials(p1, 0, B, b, nblk), S = reduce_partials(p1, 1, B, b, nblk), D = reduce_partials(p2, 2, B, b, nblk);
+    const float den = fmaxf(T, eps);
+    const float scale = S / den;
+    const float dT = (T > eps) ? -(D * S) / (den * den) : 0.0f;
+    const float dS = D / den;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        if (g_target) g_target[(size_t)b * n + i] = g_out[(size_t)b * n + i] * scale + dT;
+        if (g_source) g_source[(size_t)b * n + i] = dS;
+    }
+}
+
+}  // namespace pdec
+
+// ======================================================================================================
+// host side
+// ======================================================================================================
+using namespace pdec;
+
+// upper_weight of CenteredGrid.at's fast path (grid.py:112-119), computed like the reference:
+// float32 box arithmetic, float64 product with the resolution, % 1.0; weights cast to float32.
+static void half_weights(float self_lower, float self_size, int self_res, float other_lower, float& wu, float& wl) {
+    const float origin32 = (other_lower - self_lower) / self_size;
+    const double origin = (double)origin32 * (double)self_res;
+    double w = fmod(origin, 1.0);
+    if (w < 0) w += 1.0;
+    wu = (float)w;
+    wl = (float)(1.0 - w);
+}
+
+static int make_geo(FluidGeo& g, int B, int ny, int nx, double dt, float lower_y, float lower_x, float size_y, float size_x) {
+    if (B < 0 || ny < 2 || nx < 2 || !(size_y > 0.0f) || !(size_x > 0.0f)) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B > 65535) return PDEC_ERR_UNSUPPORTED_SIZE;
+    g.ny = ny; g.nx = nx; g.dt = (float)dt;
+    g.lo[0] = lower_y; g.lo[1] = lower_x; g.sz[0] = size_y; g.sz[1] = size_x;
+    const int res[2] = {ny, nx};
+    double dx[2];
+    for (int a = 0; a < 2; ++a) dx[a] = (double)g.sz[a] / (double)res[a];
+    for (int c = 0; c < 2; ++c)
+        for (int a = 0; a < 2; ++a) {
+            const double unit = (a == c) ? dx[a] : 0.0;
+            const float up = g.lo[a] + g.sz[a];
+            const float lo_c = (float)((double)g.lo[a] - unit / 2), up_c = (float)((double)up + unit / 2);
+            g.clo[c][a] = lo_c;
+            g.csz[c][a] = up_c - lo_c;
+        }
+    for (int c = 0; c < 2; ++c) half_weights(g.clo[c][c], g.csz[c][c], res[c] + 1, g.lo[c], g.c_wu[c], g.c_wl[c]);
+    for (int c = 0; c < 2; ++c) {
+        const int d = 1 - c;   // the other component, padded by one cell on both sides along axis c
+        for (int a = 0; a < 2; ++a) {
+            float lo_p = g.clo[d][a], sz_p = g.csz[d][a];
+            int res_p = res[a] + (a == d ? 1 : 0);
+            if (a == c) {
+                lo_p = (float)((double)g.clo[d][a] - dx[a]);
+                sz_p = (float)((double)g.csz[d][a] + 2 * dx[a]);
+                res_p += 2;
+            }
+            half_weights(lo_p, sz_p, res_p, g.clo[c][a], g.s_wu[c][a], g.s_wl[c][a]);
+        }
+    }
+    return PDEC_OK;
+}
+
+static dim3 tiles(int ry, int rx, int B) { return dim3((rx + 31) / 32, (ry + 7) / 8, B); }
+static const dim3 kBlock(32, 8, 1);
+
+#define MODE_SWITCH(mode, CALL)                                   \
+    do {                                                          \
+        if ((mode) == PDEC_MODE_CONSTANT) { CALL(PDEC_MODE_CONSTANT); }       \
+        else if ((mode) == PDEC_MODE_REPLICATE) { CALL(PDEC_MODE_REPLICATE); } \
+        else { CALL(PDEC_MODE_CIRCULAR); }                        \
+    } while (0)
+static bool bad_mode(int m) { return m < 0 || m > 2; }
+
+extern "C" int pdec_curl_2d_fwd(const float* phi, float* vy, float* vx, int B, int ny, int nx, int mode, void* stream) {
+    if (B < 0 || ny < 2 || nx < 2 || bad_mode(mode) || B > 65535) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!phi || !vy || !vx) return PDEC_ERR_INVALID_ARGUMENT;
+    cudaStream_t st = (cudaStream_t)stream;
+#define CALL(M) curl_fwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(phi, vy, vx, ny, nx)
+    MODE_SWITCH(mode, CALL);
+#undef CALL
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+extern "C" int pdec_curl_2d_bwd(const float* g_vy, const float* g_vx, float* g_phi, int B, int ny, int nx, int mode, void* stream) {
+    if (B < 0 || ny < 2 || nx < 2 || bad_mode(mode) || B > 65535) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!g_vy || !g_vx || !g_phi) return PDEC_ERR_INVALID_ARGUMENT;
+    cudaStream_t st = (cudaStream_t)stream;
+#define CALL(M) curl_bwd_kernel<M><<<tiles(ny, nx, B), kBlock, 0, st>>>(g_vy, g_vx, g_phi, ny, nx)
+    MODE_SWITCH(mode, CALL);
+#undef CALL
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+extern "C" int pdec_advect_centered_2d_fwd(const float* rho, const float* vy, const float* vx, float* rho_out, int B, int ny, int nx,
+                                           int mode, double dt, float lower_y, float lower_x, float size_y, float size_x, void* stream) {
+    FluidGeo g;
+    int rc = make_geo(g, B, ny, nx, dt, lower_y, lower_x, size_y, size_x);
+    if (rc != PDEC_OK) return rc;
+    if (bad_mode(mode)) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!rho || !vy || !vx || !rho_out) return PDEC_ERR_INVALID_ARGUMENT;
+    cudaStream_t st = (cudaStream_t)stream;
+    // the velocity is never extrapolated for centred sample points -> VMODE irrelevant (use 0)
+#define CALL(M) advect_fwd_kernel<V_CENTERED, M, 0><<<tiles(ny, nx, B), kBlock, 0, st>>>(g, rho, vy, vx, rho_out)
+    MODE_SWITCH(mode, CALL);
+#undef CALL
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+extern "C" int pdec_advect_staggered_2d_fwd(const float* vy, const float* vx, float* ay, float* ax, int B, int ny, int nx, int mode,
+                                            double dt, float lower_y, float lower_x, float size_y, float size_x, void* stream) {
+    FluidGeo g;
+    int rc = make_geo(g, B, ny, nx, dt, lower_y, lower_x, size_y, size_x);
+    if (rc != PDEC_OK) return rc;
+    if (bad_mode(mode)) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!vy || !vx || !ay || !ax) return PDEC_ERR_INVALID_ARGUMENT;
+    cudaStream_t st = (cudaStream_t)stream;
+#define CALL(M)                                                                                              \
+    advect_fwd_kernel<V_COMP_Y, M, M><<<tiles(ny + 1, nx, B), kBlock, 0, st>>>(g, vy, vy, vx, ay);           \
+    advect_fwd_kernel<V_COMP_X, M, M><<<tiles(ny, nx + 1, B), kBlock, 0, st>>>(g, vx, vy, vx, ax)
+    MODE_SWITCH(mode, CALL);
+#undef CALL
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+// workspace layout for the advection adjoints: [ints: 4*B (rmax of two grids)] [pad to 256 B] [W0: 4 arrays B*(ny+1)*nx]
+// [W1: 4 arrays B*ny*(nx+1)]
+static size_t ws_header(int B) { return (((size_t)4 * (B > 0 ? B : 1) * sizeof(int)) + 255) & ~(size_t)255; }
+
+extern "C" size_t pdec_advect_2d_workspace_bytes(int B, int ny, int nx) {
+    const size_t b = B > 0 ? B : 1;
+    return ws_header(B) + 4 * sizeof(float) * b * ((size_t)(ny + 1) * nx + (size_t)ny * (nx + 1));
+}
+
+extern "C" int pdec_advect_centered_2d_bwd(const float* rho, const float* vy, const float* vx, const float* g_out, float* g_rho,
+                                           float* g_vy, float* g_vx, int accumulate_v, int B, int ny, int nx, int mode, double dt,
+                                           float lower_y, float lower_x, float size_y, float size_x, void* workspace,
+                                           size_t workspace_bytes, void* stream) {
+    FluidGeo g;
+    int rc = make_geo(g, B, ny, nx, dt, lower_y, lower_x, size_y, size_x);
+    if (rc != PDEC_OK) return rc;
+    if (bad_mode(mode)) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!rho || !vy || !vx || !g_out || !workspace) return PDEC_ERR_INVALID_ARGUMENT;
+    if (workspace_bytes < pdec_advect_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+    cudaStream_t st = (cudaStream_t)stream;
+    int* rmax = reinterpret_cast<int*>(workspace);
+    float* W = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + ws_header(B));
+    const size_t sf = (size_t)B * ny * nx;
+    if (cudaMemsetAsync(rmax, 0, 4 * (size_t)B * sizeof(int), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+#define CALL(M)                                                                                                                     \
+    advect_bwd_prep_kernel<V_CENTERED, M, 0><<<tiles(ny, nx, B), kBlock, 0, st>>>(g, rho, vy, vx, g_out, W, W + sf, W + 2 * sf, W + 3 * sf, rmax); \
+    advect_centered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, W, W + sf, W + 2 * sf, W + 3 * sf, g_out, rmax, g_rho, g_vy, g_vx, accumulate_v)
+    MODE_SWITCH(mode, CALL);
+#undef CALL
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+extern "C" int pdec_advect_staggered_2d_bwd(const float* vy, const float* vx, const float* g_ay, const float* g_ax, float* g_vy,
+                                            float* g_vx, int accumulate, int B, int ny, int nx, int mode, double dt, float lower_y,
+                                            float lower_x, float size_y, float size_x, void* workspace, size_t workspace_bytes,
+                                            void* stream) {
+    FluidGeo g;
+    int rc = make_geo(g, B, ny, nx, dt, lower_y, lower_x, size_y, size_x);
+    if (rc != PDEC_OK) return rc;
+    if (bad_mode(mode)) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!vy || !vx || !g_ay || !g_ax || !g_vy || !g_vx || !workspace) return PDEC_ERR_INVALID_ARGUMENT;
+    if (workspace_bytes < pdec_advect_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+    cudaStream_t st = (cudaStream_t)stream;
+    int* rmax0 = reinterpret_cast<int*>(workspace);
+    int* rmax1 = rmax0 + 2 * (size_t)B;
+    float* W0 = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + ws_header(B));
+    const size_t sy = (size_t)B * (ny + 1) * nx, sx = (size_t)B * ny * (nx + 1);
+    float* W1 = W0 + 4 * sy;
+    if (cudaMemsetAsync(rmax0, 0, 4 * (size_t)B * sizeof(int), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+#define CALL(M)                                                                                                                              \
+    advect_bwd_prep_kernel<V_COMP_Y, M, M><<<tiles(ny + 1, nx, B), kBlock, 0, st>>>(g, vy, vy, vx, g_ay, W0, W0 + sy, W0 + 2 * sy, W0 + 3 * sy, rmax0); \
+    advect_bwd_prep_kernel<V_COMP_X, M, M><<<tiles(ny, nx + 1, B), kBlock, 0, st>>>(g, vx, vy, vx, g_ax, W1, W1 + sx, W1 + 2 * sx, W1 + 3 * sx, rmax1); \
+    advect_staggered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, W0, W1, g_ay, g_ax, rmax0, rmax1, g_vy, g_vx, accumulate, B)
+    MODE_SWITCH(mode, CALL);
+#undef CALL
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+extern "C" int pdec_mask_divergence_2d_fwd(const float* vy, const float* vx, float* div, int B, int ny, int nx, int closed, void* stream) {
+    if (B < 0 || ny < 2 || nx < 2 || B > 65535) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!vy || !vx || !div) return PDEC_ERR_INVALID_ARGUMENT;
+    mask_divergence_fwd_kernel<<<tiles(ny, nx, B), kBlock, 0, (cudaStream_t)stream>>>(vy, vx, div, ny, nx, closed ? 1 : 0);
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+extern "C" int pdec_mask_divergence_2d_bwd(const float* g_div, float* g_vy, float* g_vx, int accumulate, int B, int ny, int nx, int closed,
+                                           void* stream) {
+    if (B < 0 || ny < 2 || nx < 2 || B > 65535) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!g_div || !g_vy || !g_vx) return PDEC_ERR_INVALID_ARGUMENT;
+    mask_divergence_bwd_kernel<<<tiles(ny + 1, nx + 1, B), kBlock, 0, (cudaStream_t)stream>>>(g_div, g_vy, g_vx, ny, nx, closed ? 1 : 0, accumulate);
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+extern "C" int pdec_subtract_pressure_gradient_2d_fwd(const float* vy, const float* vx, const float* p, float* vy_out, float* vx_out, int B,
+                                                      int ny, int nx, int closed, float size_y, float size_x, void* stream) {
+    if (B < 0 || ny < 2 || nx < 2 || B > 65535 || !(size_y > 0.0f) || !(size_x > 0.0f)) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!vy || !vx || !p || !vy_out || !vx_out) return PDEC_ERR_INVALID_ARGUMENT;
+    const float dxy = (float)((double)size_y / ny), dxx = (float)((double)size_x / nx);
+    subtract_gradient_fwd_kernel<<<tiles(ny + 1, nx + 1, B), kBlock, 0, (cudaStream_t)stream>>>(vy, vx, p, vy_out, vx_out, ny, nx, closed ? 1 : 0,
+                                                                                                 dxy, dxy, dxx);
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+extern "C" int pdec_subtract_pressure_gradient_2d_bwd(const float* g_vy_out, const float* g_vx_out, float* g_vy, float* g_vx, float* g_p,
+                                                      int accumulate_v, int B, int ny, int nx, int closed, float size_y, float size_x,
+                                                      void* stream) {
+    if (B < 0 || ny < 2 || nx < 2 || B > 65535 || !(size_y > 0.0f) || !(size_x > 0.0f)) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!g_vy_out || !g_vx_out) return PDEC_ERR_INVALID_ARGUMENT;
+    const float dxy = (float)((double)size_y / ny), dxx = (float)((double)size_x / nx);
+    subtract_gradient_bwd_kernel<<<tiles(ny + 1, nx + 1, B), kBlock, 0, (cudaStream_t)stream>>>(g_vy_out, g_vx_out, g_vy, g_vx, g_p, ny, nx,
+                                                                                                 closed ? 1 : 0, dxy, dxy, dxx, accumulate_v);
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+static int norm_blocks(int n) {
+    int nb = (n + 256 * 16 - 1) / (256 * 16);
+    return nb < 1 ? 1 : (nb > 64 ? 64 : nb);
+}
+extern "C" size_t pdec_normalize_2d_workspace_bytes(int B, int ny, int nx) {
+    return (size_t)2 * 3 * (B > 0 ? B : 1) * norm_blocks(ny * nx) * sizeof(float);
+}
+
+extern "C" int pdec_normalize_2d_fwd(const float* target, const float* source, float* out, int B, int ny, int nx, float epsilon,
+                                     void* workspace, size_t workspace_bytes, void* stream) {
+    if (B < 0 || ny < 1 || nx < 1 || B > 65535) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!target || !source || !out || !workspace) return PDEC_ERR_INVALID_ARGUMENT;
+    if (workspace_bytes < pdec_normalize_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+    const int n = ny * nx, nb = norm_blocks(n);
+    cudaStream_t st = (cudaStream_t)stream;
+    float* p1 = reinterpret_cast<float*>(workspace);
+    sums_kernel<<<dim3(nb, B), 256, 0, st>>>(target, source, p1, n, B);
+    normalize_fwd_kernel<<<dim3(nb, B), 256, 0, st>>>(target, p1, out, n, B, nb, epsilon);
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+extern "C" int pdec_normalize_2d_bwd(const float* target, const float* source, const float* g_out, float* g_target, float* g_source, int B,
+                                     int ny, int nx, float epsilon, void* workspace, size_t workspace_bytes, void* stream) {
+    if (B < 0 || ny < 1 || nx < 1 || B > 65535) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!target || !source || !g_out || !workspace) return PDEC_ERR_INVALID_ARGUMENT;
+    if (workspace_bytes < pdec_normalize_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+    const int n = ny * nx, nb = norm_blocks(n);
+    cudaStream_t st = (cudaStream_t)stream;
+    float* p1 = reinterpret_cast<float*>(workspace);
+    float* p2 = p1 + (size_t)3 * B * nb;
+    sums_kernel<<<dim3(nb, B), 256, 0, st>>>(target, source, p1, n, B);
+    sums_kernel<<<dim3(nb, B), 256, 0, st>>>(g_out, target, p2, n, B);
+    normalize_bwd_kernel<<<dim3(nb, B), 256, 0, st>>>(g_out, p1, p2, g_target, g_source, n, B, nb, epsilon);
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}

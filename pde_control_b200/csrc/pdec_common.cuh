@@ -99,6 +99,31 @@ __device__ __forceinline__ int wrap_index(float f, int n) {
     return i;
 }
 
+// ---- interpolation set-up: PF/tf/tf_backend.py:462-476 --------------------------------------------
+template <int MODE>
+__device__ __forceinline__ void interp_setup(float xi, int n, int& fi, int& ci, float& w0, float& w1) {
+    const float base = floorf(xi);
+    if (MODE == PDEC_MODE_CONSTANT) {
+        const float hi = (float)(n - 1);
+        const float fc = fminf(fmaxf(base, 0.0f), hi);
+        const float cc = fminf(fmaxf(base + 1.0f, 0.0f), hi);
+        w0 = xi - fc;  // weight of the ceil sample
+        w1 = cc - xi;  // weight of the floor sample
+        fi = (int)fc;
+        ci = (int)cc;
+    } else {
+        w0 = xi - base;
+        w1 = 1.0f - w0;
+        if (MODE == PDEC_MODE_REPLICATE) {
+            fi = clamp_index(base, n);
+            ci = clamp_index(base + 1.0f, n);
+        } else {
+            fi = wrap_index(base, n);
+            ci = wrap_index(base + 1.0f, n);
+        }
+    }
+}
+
 }  // namespace pdec
 
 #define PDEC_CHECK_LAUNCH()                                   \

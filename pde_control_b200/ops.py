@@ -128,3 +128,295 @@ def burgers_pair_loss_raw(s, grad_out, losses_out, workspace, dt, viscosity, low
                                            int(resubstep), float(gl2), float(gl1), _lib.ptr(workspace),
                                            workspace.numel() * workspace.element_size(), _lib.stream_ptr())
     _lib.check(rc, "pdec_burgers_pair_loss")
+
+
+# ------------------------------------------------------------------------------------------------
+# 2-D incompressible flow.  Layouts: rho[B,ny,nx], vy[B,ny+1,nx], vx[B,ny,nx+1]; axis 0 = y.
+# box = (lower_y, lower_x, size_y, size_x) of the domain; None -> AABox(0, resolution) (dx = 1).
+# ------------------------------------------------------------------------------------------------
+
+def _box(box, ny, nx):
+    if box is None:
+        return (0.0, 0.0, float(ny), float(nx))
+    return tuple(float(v) for v in box)
+
+
+def _call(name, *args):
+    rc = getattr(_lib.lib(), name)(*args)
+    _lib.check(rc, name)
+
+
+class _Curl2D(torch.autograd.Function):
+    """staggered_curl_2d (PF/physics/field/util.py:60-67)."""
+
+    @staticmethod
+    def forward(ctx, phi, mode):
+        _req_cuda(phi)
+        phi = _c(phi)
+        B, ny, nx = phi.shape
+        vy = torch.empty((B, ny + 1, nx), device=phi.device, dtype=torch.float32)
+        vx = torch.empty((B, ny, nx + 1), device=phi.device, dtype=torch.float32)
+        with torch.cuda.device(phi.device):
+            _call("pdec_curl_2d_fwd", _lib.ptr(phi), _lib.ptr(vy), _lib.ptr(vx), B, ny, nx, mode, _lib.stream_ptr())
+        ctx.cfg = (B, ny, nx, mode)
+        return vy, vx
+
+    @staticmethod
+    def backward(ctx, g_vy, g_vx):
+        B, ny, nx, mode = ctx.cfg
+        g_vy, g_vx = _c(g_vy), _c(g_vx)
+        g_phi = torch.empty((B, ny, nx), device=g_vy.device, dtype=torch.float32)
+        with torch.cuda.device(g_vy.device):
+            _call("pdec_curl_2d_bwd", _lib.ptr(g_vy), _lib.ptr(g_vx), _lib.ptr(g_phi), B, ny, nx, mode, _lib.stream_ptr())
+        return g_phi, None
+
+
+def curl_2d(phi, mode=MODE_CONSTANT):
+    return _Curl2D.apply(phi, int(mode))
+
+
+class _AdvectCentered(torch.autograd.Function):
+    """advect.semi_lagrangian(density, velocity, dt) (PF/physics/field/advect.py:24-37)."""
+
+    @staticmethod
+    def forward(ctx, rho, vy, vx, dt, mode, box):
+        _req_cuda(rho, vy, vx)
+        rho, vy, vx = _c(rho), _c(vy), _c(vx)
+        B, ny, nx = rho.shape
+        assert vy.shape == (B, ny + 1, nx) and vx.shape == (B, ny, nx + 1), (rho.shape, vy.shape, vx.shape)
+        out = torch.empty_like(rho)
+        with torch.cuda.device(rho.device):
+            _call("pdec_advect_centered_2d_fwd", _lib.ptr(rho), _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(out), B, ny, nx, mode, dt,
+                  *box, _lib.stream_ptr())
+        ctx.save_for_backward(rho, vy, vx)
+        ctx.cfg = (dt, mode, box)
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        rho, vy, vx = ctx.saved_tensors
+        dt, mode, box = ctx.cfg
+        B, ny, nx = rho.shape
+        g_out = _c(g_out)
+        need_v = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        g_rho = torch.empty_like(rho) if ctx.needs_input_grad[0] else None
+        g_vy = torch.empty_like(vy) if need_v else None
+        g_vx = torch.empty_like(vx) if need_v else None
+        L = _lib.lib()
+        nbytes = L.pdec_advect_2d_workspace_bytes(B, ny, nx)
+        ws = _lib.workspace(rho.device, nbytes)
+        with torch.cuda.device(rho.device):
+            _call("pdec_advect_centered_2d_bwd", _lib.ptr(rho), _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(g_out), _lib.ptr(g_rho),
+                  _lib.ptr(g_vy), _lib.ptr(g_vx), 0, B, ny, nx, mode, dt, *box, _lib.ptr(ws), nbytes, _lib.stream_ptr())
+        return g_rho, g_vy, g_vx, None, None, None
+
+
+def advect_centered(rho, vy, vx, dt, mode=MODE_CONSTANT, box=None):
+    return _AdvectCentered.apply(rho, vy, vx, float(dt), int(mode), _box(box, rho.shape[1], rho.shape[2]))
+
+
+class _AdvectStaggered(torch.autograd.Function):
+    """advect.semi_lagrangian(v, v, dt) on a StaggeredGrid (advect.py:38-40)."""
+
+    @staticmethod
+    def forward(ctx, vy, vx, dt, mode, box):
+        _req_cuda(vy, vx)
+        vy, vx = _c(vy), _c(vx)
+        B, ny1, nx = vy.shape
+        ny = ny1 - 1
+        assert vx.shape == (B, ny, nx + 1), (vy.shape, vx.shape)
+        ay, ax = torch.empty_like(vy), torch.empty_like(vx)
+        with torch.cuda.device(vy.device):
+            _call("pdec_advect_staggered_2d_fwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(ay), _lib.ptr(ax), B, ny, nx, mode, dt, *box,
+                  _lib.stream_ptr())
+        ctx.save_for_backward(vy, vx)
+        ctx.cfg = (dt, mode, box)
+        return ay, ax
+
+    @staticmethod
+    def backward(ctx, g_ay, g_ax):
+        vy, vx = ctx.saved_tensors
+        dt, mode, box = ctx.cfg
+        B, ny1, nx = vy.shape
+        ny = ny1 - 1
+        g_ay, g_ax = _c(g_ay), _c(g_ax)
+        g_vy, g_vx = torch.empty_like(vy), torch.empty_like(vx)
+        nbytes = _lib.lib().pdec_advect_2d_workspace_bytes(B, ny, nx)
+        ws = _lib.workspace(vy.device, nbytes)
+        with torch.cuda.device(vy.device):
+            _call("pdec_advect_staggered_2d_bwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(g_ay), _lib.ptr(g_ax), _lib.ptr(g_vy),
+                  _lib.ptr(g_vx), 0, B, ny, nx, mode, dt, *box, _lib.ptr(ws), nbytes, _lib.stream_ptr())
+        return g_vy, g_vx, None, None, None
+
+
+def advect_staggered(vy, vx, dt, mode=MODE_REPLICATE, box=None):
+    return _AdvectStaggered.apply(vy, vx, float(dt), int(mode), _box(box, vx.shape[1], vy.shape[2]))
+
+
+class _MaskDivergence(torch.autograd.Function):
+    """with_hard_boundary_conditions + divergence(physical_units=False) (solver_api.py:111-121, staggered_grid.py:201-209)."""
+
+    @staticmethod
+    def forward(ctx, vy, vx, closed):
+        _req_cuda(vy, vx)
+        vy, vx = _c(vy), _c(vx)
+        B, ny1, nx = vy.shape
+        ny = ny1 - 1
+        div = torch.empty((B, ny, nx), device=vy.device, dtype=torch.float32)
+        with torch.cuda.device(vy.device):
+            _call("pdec_mask_divergence_2d_fwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(div), B, ny, nx, int(closed), _lib.stream_ptr())
+        ctx.cfg = (B, ny, nx, int(closed))
+        return div
+
+    @staticmethod
+    def backward(ctx, g_div):
+        B, ny, nx, closed = ctx.cfg
+        g_div = _c(g_div)
+        g_vy = torch.empty((B, ny + 1, nx), device=g_div.device, dtype=torch.float32)
+        g_vx = torch.empty((B, ny, nx + 1), device=g_div.device, dtype=torch.float32)
+        with torch.cuda.device(g_div.device):
+            _call("pdec_mask_divergence_2d_bwd", _lib.ptr(g_div), _lib.ptr(g_vy), _lib.ptr(g_vx), 0, B, ny, nx, closed, _lib.stream_ptr())
+        return g_vy, g_vx, None
+
+
+def mask_divergence(vy, vx, closed):
+    return _MaskDivergence.apply(vy, vx, bool(closed))
+
+
+CG_STOP_PER_ELEMENT, CG_STOP_WHOLE_BATCH = 0, 1
+
+
+def cg_poisson_raw(rhs, out, closed, accuracy, max_iterations, guess=None, iterations=None, residual=None, stop_mode=0):
+    """Allocation-light form: solves A out = rhs on the current stream."""
+    B, ny, nx = rhs.shape
+    L = _lib.lib()
+    nbytes = L.pdec_cg_poisson_2d_workspace_bytes(B, ny, nx)
+    ws = _lib.workspace(rhs.device, nbytes)
+    with torch.cuda.device(rhs.device):
+        _call("pdec_cg_poisson_2d", _lib.ptr(rhs), _lib.ptr(guess), _lib.ptr(out), _lib.ptr(iterations), _lib.ptr(residual), B, ny, nx,
+              int(closed), float(accuracy if accuracy is not None else 0.0), int(max_iterations), int(stop_mode), _lib.ptr(ws), nbytes,
+              _lib.stream_ptr())
+
+
+class _PressureSolve(torch.autograd.Function):
+    """poisson_solve with SparseCG (solver_api.py:132-158, sparse.py:73-111, math/blas.py:5-64).  Backward = the same
+    CG applied to the incoming gradient (sparse.py:93-94: A is symmetric)."""
+
+    @staticmethod
+    def forward(ctx, div, closed, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations, guess, stop_mode):
+        _req_cuda(div, guess)
+        div = _c(div)
+        B = div.shape[0]
+        p = torch.empty_like(div)
+        iters = torch.zeros(B, device=div.device, dtype=torch.int32)
+        resid = torch.zeros(B, device=div.device, dtype=torch.float32)
+        cg_poisson_raw(div, p, closed, accuracy, max_iterations, _c(guess), iters, resid, stop_mode)
+        ctx.cfg = (closed, gradient_accuracy, max_gradient_iterations, stop_mode)
+        ctx.mark_non_differentiable(iters, resid)
+        return p, iters, resid
+
+    @staticmethod
+    def backward(ctx, g_p, _gi, _gr):
+        closed, accuracy, max_it, stop_mode = ctx.cfg
+        g_p = _c(g_p)
+        g_div = torch.empty_like(g_p)
+        cg_poisson_raw(g_p, g_div, closed, accuracy, max_it, None, None, None, stop_mode)
+        return g_div, None, None, None, None, None, None, None
+
+
+def pressure_solve(div, closed, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None, max_gradient_iterations=None,
+                   guess=None, stop_mode=CG_STOP_PER_ELEMENT):
+    """Returns (pressure, iterations[B] int32, residual[B]); only the pressure is differentiable (w.r.t. div)."""
+    ga = accuracy if gradient_accuracy is None else gradient_accuracy
+    gi = max_iterations if max_gradient_iterations is None else max_gradient_iterations
+    return _PressureSolve.apply(div, bool(closed), accuracy, int(max_iterations), ga, int(gi), guess, int(stop_mode))
+
+
+class _SubtractPressureGradient(torch.autograd.Function):
+    """divergence_free tail (PF/physics/fluid.py:237-242)."""
+
+    @staticmethod
+    def forward(ctx, vy, vx, p, closed, size_y, size_x):
+        _req_cuda(vy, vx, p)
+        vy, vx, p = _c(vy), _c(vx), _c(p)
+        B, ny, nx = p.shape
+        oy, ox = torch.empty_like(vy), torch.empty_like(vx)
+        with torch.cuda.device(p.device):
+            _call("pdec_subtract_pressure_gradient_2d_fwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(p), _lib.ptr(oy), _lib.ptr(ox), B, ny, nx,
+                  int(closed), size_y, size_x, _lib.stream_ptr())
+        ctx.cfg = (B, ny, nx, int(closed), size_y, size_x)
+        return oy, ox
+
+    @staticmethod
+    def backward(ctx, g_oy, g_ox):
+        B, ny, nx, closed, size_y, size_x = ctx.cfg
+        g_oy, g_ox = _c(g_oy), _c(g_ox)
+        g_vy, g_vx = torch.empty_like(g_oy), torch.empty_like(g_ox)
+        g_p = torch.empty((B, ny, nx), device=g_oy.device, dtype=torch.float32)
+        with torch.cuda.device(g_oy.device):
+            _call("pdec_subtract_pressure_gradient_2d_bwd", _lib.ptr(g_oy), _lib.ptr(g_ox), _lib.ptr(g_vy), _lib.ptr(g_vx), _lib.ptr(g_p), 0,
+                  B, ny, nx, closed, size_y, size_x, _lib.stream_ptr())
+        return g_vy, g_vx, g_p, None, None, None
+
+
+def subtract_pressure_gradient(vy, vx, p, closed, box=None):
+    b = _box(box, p.shape[1], p.shape[2])
+    return _SubtractPressureGradient.apply(vy, vx, p, bool(closed), b[2], b[3])
+
+
+class _Normalize(torch.autograd.Function):
+    """CenteredGrid.normalized -> math.normalize_to (grid.py:205-209, nd.py:28-40)."""
+
+    @staticmethod
+    def forward(ctx, target, source, epsilon):
+        _req_cuda(target, source)
+        target, source = _c(target), _c(source)
+        B, ny, nx = target.shape
+        out = torch.empty_like(target)
+        nbytes = _lib.lib().pdec_normalize_2d_workspace_bytes(B, ny, nx)
+        ws = _lib.workspace(target.device, nbytes)
+        with torch.cuda.device(target.device):
+            _call("pdec_normalize_2d_fwd", _lib.ptr(target), _lib.ptr(source), _lib.ptr(out), B, ny, nx, epsilon, _lib.ptr(ws), nbytes,
+                  _lib.stream_ptr())
+        ctx.save_for_backward(target, source)
+        ctx.eps = epsilon
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        target, source = ctx.saved_tensors
+        B, ny, nx = target.shape
+        g_out = _c(g_out)
+        g_t, g_s = torch.empty_like(target), torch.empty_like(source)
+        nbytes = _lib.lib().pdec_normalize_2d_workspace_bytes(B, ny, nx)
+        ws = _lib.workspace(target.device, nbytes)
+        with torch.cuda.device(target.device):
+            _call("pdec_normalize_2d_bwd", _lib.ptr(target), _lib.ptr(source), _lib.ptr(g_out), _lib.ptr(g_t), _lib.ptr(g_s), B, ny, nx,
+                  ctx.eps, _lib.ptr(ws), nbytes, _lib.stream_ptr())
+        return g_t, g_s, None
+
+
+def normalize_to(target, source, epsilon=1e-5):
+    return _Normalize.apply(target, source, float(epsilon))
+
+
+def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
+                    max_gradient_iterations=None, guess=None):
+    """divergence_free (PF/physics/fluid.py:214-243) without obstacles -> (vy', vx', pressure, iterations, divergence)."""
+    div = mask_divergence(vy, vx, closed)
+    p, iters, _ = pressure_solve(div, closed, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations, guess)
+    oy, ox = subtract_pressure_gradient(vy, vx, p, closed, box)
+    return oy, ox, p, iters, div
+
+
+def incompressible_step(rho, vy, vx, dt, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
+                        max_gradient_iterations=None, conserve_density=True):
+    """IncompressibleFlow.step (PF/physics/fluid.py:90-114), default flags, no obstacles / effects / buoyancy.
+    Field modes follow Material.extrapolation_mode / vector_extrapolation_mode: open -> constant, closed -> replicate."""
+    mode = MODE_REPLICATE if closed else MODE_CONSTANT
+    rho2 = advect_centered(rho, vy, vx, dt, mode, box)
+    ay, ax = advect_staggered(vy, vx, dt, mode, box)
+    if closed and conserve_density:
+        rho2 = normalize_to(rho2, rho)
+    oy, ox, p, iters, _ = divergence_free(ay, ax, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations)
+    return rho2, oy, ox, p, iters

@@ -1,0 +1,370 @@
+"""GPU parity: CUDA 2-D fluid kernels (through the C-ABI) vs the oracle (oracle/restate_fluid.py) and the golden
+vectors produced by the real reference.
+
+Tolerances (BASELINE.json north_star): relative 1e-5 per step on states, 1e-4 over a trajectory, 1e-3 on gradients;
+"relative" = max-norm error / max-norm of the reference field.  Steps that contain the CG solve are compared at
+the tolerance the solve was run to (stated per test).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import restate as R
+from oracle import restate_fluid as F
+from conftest import GOLDEN, rel_err
+
+pytestmark = pytest.mark.gpu
+MODES = [R.CONSTANT, R.REPLICATE, R.CIRCULAR]
+
+
+def _ops():
+    from pde_control_b200 import ops
+    return ops
+
+
+def _smooth(rng, shape, scale, passes=4):
+    a = rng.randn(*shape)
+    for _ in range(passes):
+        a = (a + np.roll(a, 1, -1) + np.roll(a, -1, -1) + np.roll(a, 1, -2) + np.roll(a, -1, -2)) / 5
+    return (a / np.abs(a).max() * scale).astype(np.float32)
+
+
+def _fields(rng, B, ny, nx, vscale):
+    return (np.abs(_smooth(rng, (B, ny, nx), 1.0)), _smooth(rng, (B, ny + 1, nx), vscale), _smooth(rng, (B, ny, nx + 1), vscale))
+
+
+def _pair(arrs, grad=True):
+    cpu = [torch.tensor(a, requires_grad=grad) for a in arrs]
+    gpu = [torch.tensor(a, device="cuda", requires_grad=grad) for a in arrs]
+    return cpu, gpu
+
+
+def _backward_weighted(outs, ws):
+    sum((o * w).sum() for o, w in zip(outs, ws)).backward()
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_curl_forward_adjoint_and_divergence_free(mode):
+    ops = _ops()
+    rng = np.random.RandomState(mode)
+    phi = rng.randn(3, 20, 37).astype(np.float32)
+    (po,), (pc,) = _pair([phi])
+    vyo, vxo = F.curl_2d(po, mode)
+    vyc, vxc = ops.curl_2d(pc, mode)
+    assert torch.equal(vyc.detach().cpu(), vyo.detach()) and torch.equal(vxc.detach().cpu(), vxo.detach())     # exact
+    wy, wx = rng.randn(*vyo.shape).astype(np.float32), rng.randn(*vxo.shape).astype(np.float32)
+    _backward_weighted([vyo, vxo], [torch.tensor(wy), torch.tensor(wx)])
+    _backward_weighted([vyc, vxc], [torch.tensor(wy).cuda(), torch.tensor(wx).cuda()])
+    assert rel_err(pc.grad.cpu(), po.grad) < 1e-6
+    # PhiFlow/tests/test_fields.py:114-119: div(curl) == 0
+    assert float(ops.mask_divergence(vyc.detach(), vxc.detach(), False).abs().max()) < 1e-5
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("shape,box,vscale", [((2, 33, 40), None, 2.5), ((1, 128, 128), None, 1.5), ((2, 24, 18), (0.5, -1.0, 3.0, 4.5), 0.4)])
+def test_advect_centered_forward_and_adjoint(mode, shape, box, vscale):
+    ops = _ops()
+    B, ny, nx = shape
+    rng = np.random.RandomState(ny + mode)
+    rho, vy, vx = _fields(rng, B, ny, nx, vscale)
+    geo = F.Geometry(ny, nx) if box is None else F.Geometry(ny, nx, box[:2], box[2:])
+    (ro, yo, xo), (rc, yc, xc) = _pair([rho, vy, vx])
+    oo = F.advect_centered(ro, yo, xo, 0.8, geo, mode)
+    oc = ops.advect_centered(rc, yc, xc, 0.8, mode, box)
+    assert rel_err(oc.detach().cpu(), oo.detach()) < 1e-5
+    w = rng.randn(B, ny, nx).astype(np.float32)
+    (oo * torch.tensor(w)).sum().backward()
+    (oc * torch.tensor(w).cuda()).sum().backward()
+    assert rel_err(rc.grad.cpu(), ro.grad) < 1e-3
+    assert rel_err(yc.grad.cpu(), yo.grad) < 1e-3 and rel_err(xc.grad.cpu(), xo.grad) < 1e-3
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("shape,box,vscale", [((2, 33, 40), None, 2.5), ((1, 128, 128), None, 1.5), ((2, 24, 18), (0.5, -1.0, 3.0, 4.5), 0.4)])
+def test_advect_staggered_forward_and_adjoint(mode, shape, box, vscale):
+    ops = _ops()
+    B, ny, nx = shape
+    rng = np.random.RandomState(nx + mode)
+    _, vy, vx = _fields(rng, B, ny, nx, vscale)
+    geo = F.Geometry(ny, nx) if box is None else F.Geometry(ny, nx, box[:2], box[2:])
+    (yo, xo), (yc, xc) = _pair([vy, vx])
+    ayo, axo = F.advect_staggered(yo, xo, 0.8, geo, mode)
+    ayc, axc = ops.advect_staggered(yc, xc, 0.8, mode, box)
+    assert rel_err(ayc.detach().cpu(), ayo.detach()) < 1e-5 and rel_err(axc.detach().cpu(), axo.detach()) < 1e-5
+    wy, wx = rng.randn(*vy.shape).astype(np.float32), rng.randn(*vx.shape).astype(np.float32)
+    _backward_weighted([ayo, axo], [torch.tensor(wy), torch.tensor(wx)])
+    _backward_weighted([ayc, axc], [torch.tensor(wy).cuda(), torch.tensor(wx).cuda()])
+    assert rel_err(yc.grad.cpu(), yo.grad) < 1e-3 and rel_err(xc.grad.cpu(), xo.grad) < 1e-3
+
+
+@pytest.mark.parametrize("bd", ["open", "closed"])
+def test_divergence_and_gradient_subtraction_forward_and_adjoint(bd):
+    ops = _ops()
+    rng = np.random.RandomState(8)
+    B, ny, nx = 2, 19, 30
+    _, vy, vx = _fields(rng, B, ny, nx, 1.0)
+    p = rng.randn(B, ny, nx).astype(np.float32)
+    box = (0.0, 0.0, 9.5, 15.0)           # dx = 0.5
+    geo = F.Geometry(ny, nx, box[:2], box[2:])
+    closed = bd == "closed"
+    (yo, xo, po), (yc, xc, pc) = _pair([vy, vx, p])
+    my, mx = F.hard_boundary_mask(yo, xo, bd)
+    do = F.divergence(my, mx)
+    oyo, oxo = F.subtract_pressure_gradient(my, mx, po, geo, bd)
+    dc = ops.mask_divergence(yc, xc, closed)
+    oyc, oxc = ops.subtract_pressure_gradient(yc, xc, pc, closed, box)
+    assert rel_err(dc.detach().cpu(), do.detach()) < 1e-6
+    assert rel_err(oyc.detach().cpu(), oyo.detach()) < 1e-6 and rel_err(oxc.detach().cpu(), oxo.detach()) < 1e-6
+    ws = [rng.randn(*t.shape).astype(np.float32) for t in (do, oyo, oxo)]
+    _backward_weighted([do, oyo, oxo], [torch.tensor(w) for w in ws])
+    _backward_weighted([dc, oyc, oxc], [torch.tensor(w).cuda() for w in ws])
+    for a, b in ((yc, yo), (xc, xo), (pc, po)):
+        assert rel_err(a.grad.cpu(), b.grad) < 1e-5
+
+
+def test_normalize_forward_and_adjoint():
+    ops = _ops()
+    rng = np.random.RandomState(9)
+    t, s = rng.rand(3, 40, 50).astype(np.float32), rng.rand(3, 40, 50).astype(np.float32)
+    t[2] = 0                                  # sum(target) < epsilon branch
+    (to, so), (tc, sc) = _pair([t, s])
+    oo, oc = F.normalize_to(to, so), ops.normalize_to(tc, sc)
+    assert rel_err(oc.detach().cpu(), oo.detach()) < 1e-5
+    w = rng.randn(3, 40, 50).astype(np.float32)
+    (oo * torch.tensor(w)).sum().backward()
+    (oc * torch.tensor(w).cuda()).sum().backward()
+    assert rel_err(tc.grad.cpu(), to.grad) < 1e-3 and rel_err(sc.grad.cpu(), so.grad) < 1e-3
+
+
+def _demean(p):
+    return p - p.mean((1, 2), keepdims=True)
+
+
+@pytest.mark.parametrize("bd", ["open", "closed"])
+def test_cg_matches_reference_golden_and_direct_solve(bd):
+    """poisson_40x32.npz: pressure from the reference's SparseCG(accuracy=1e-6); and the fp64 direct solve."""
+    ops = _ops()
+    g = np.load(os.path.join(GOLDEN, "poisson_40x32.npz"))
+    rhs = torch.tensor(g["rhs_" + bd]).cuda()
+    p, iters, resid = ops.pressure_solve(rhs, bd == "closed", accuracy=1e-6, max_iterations=5000)
+    ref = g["p_" + bd]
+    direct = F.pressure_solve(torch.tensor(g["rhs_" + bd]), bd).numpy()
+    got = p.cpu().numpy()
+    if bd == "closed":
+        ref, direct, got = _demean(ref), _demean(direct), _demean(got)
+    assert rel_err(got, ref) < 1e-5 and rel_err(got, direct) < 1e-5
+    assert 50 < int(iters.max()) < 1000 and float(resid.max()) < 1e-6
+    # PhiFlow/tests/test_poisson_solve.py:26-35: laplace(solve(rhs)) == rhs
+    assert rel_err(F.laplace_apply(p.cpu(), bd), g["rhs_" + bd]) < 1e-5
+
+
+@pytest.mark.parametrize("bd", ["open", "closed"])
+@pytest.mark.parametrize("ny,nx", [(128, 128), (64, 64), (17, 23), (100, 90), (160, 144)])
+def test_cg_solves_the_restated_operator(bd, ny, nx):
+    """All kernel shapes: one-CTA shared-memory kernel at several block sizes, and (160x144 > 16384 cells) the cooperative
+    global-memory kernel.  Property: A p == rhs to the accuracy of the solve; p equals the fp64 direct solve."""
+    ops = _ops()
+    rng = np.random.RandomState(ny * nx)
+    rhs = _smooth(rng, (3, ny, nx), 1.0, passes=2)
+    if bd == "closed":
+        rhs -= rhs.mean((1, 2), keepdims=True)       # compatibility condition of the Neumann problem
+    p, iters, resid = ops.pressure_solve(torch.tensor(rhs).cuda(), bd == "closed", accuracy=2e-6, max_iterations=4000)
+    assert float(resid.max()) < 2e-6 and int(iters.max()) < 4000
+    assert float((F.laplace_apply(p.cpu(), bd) - torch.tensor(rhs)).abs().max()) < 1e-5
+    direct = F.pressure_solve(torch.tensor(rhs), bd).numpy()
+    got = p.cpu().numpy()
+    if bd == "closed":
+        direct, got = _demean(direct), _demean(got)
+    assert rel_err(got, direct) < 2e-4
+
+
+def test_cg_iteration_semantics_guess_and_batch_independence():
+    ops = _ops()
+    rng = np.random.RandomState(1)
+    rhs = _smooth(rng, (4, 32, 32), 1.0, passes=1)
+    rhs_c = torch.tensor(rhs).cuda()
+    # fixed iteration count (accuracy=None: "the algorithm runs until max_iterations", blas.py:13) == oracle CG iterates
+    p5, it5, _ = ops.pressure_solve(rhs_c, False, accuracy=None, max_iterations=5)
+    o5, _ = F.conjugate_gradient(torch.tensor(rhs), "open", accuracy=None, max_iterations=5)
+    assert int(it5.min()) == 5 and rel_err(p5.cpu(), o5) < 1e-5
+    # already-converged input: zero iterations, zero pressure
+    p0, it0, _ = ops.pressure_solve(rhs_c * 1e-9, False, accuracy=1e-5)
+    assert int(it0.max()) == 0 and float(p0.abs().max()) == 0.0
+    # a good initial guess needs fewer iterations and gives the same solution
+    p, it, _ = ops.pressure_solve(rhs_c, False, accuracy=1e-5)
+    pg, itg, _ = ops.pressure_solve(rhs_c, False, accuracy=1e-5, guess=p)
+    assert int(itg.max()) <= 2 and rel_err(pg.cpu(), p.cpu()) < 1e-4
+    # per-element stop: iteration counts differ per element; element 0 is bit-identical whatever else is in the batch
+    # (PhiFlow/tests/test_fluid.py:80-100)
+    rhs2 = rhs.copy()
+    rhs2[1:] = 0
+    pb, itb, _ = ops.pressure_solve(torch.tensor(rhs2).cuda(), False, accuracy=1e-5)
+    assert torch.equal(pb[0], p[0]) and int(itb[1]) == 0
+    # whole-batch stop rule is declared but not available for B > 1
+    from pde_control_b200._lib import PdecError
+    with pytest.raises(PdecError):
+        ops.pressure_solve(rhs_c, False, accuracy=1e-5, stop_mode=ops.CG_STOP_WHOLE_BATCH)
+
+
+def test_pressure_solve_gradient_is_a_second_solve():
+    ops = _ops()
+    rng = np.random.RandomState(2)
+    rhs = _smooth(rng, (2, 24, 24), 1.0, passes=1)
+    w = _smooth(rng, (2, 24, 24), 1.0, passes=1)
+    (ro,), (rc,) = _pair([rhs])
+    (F.pressure_solve(ro, "open") * torch.tensor(w)).sum().backward()
+    p, _, _ = ops.pressure_solve(rc, False, accuracy=1e-6, max_iterations=3000)
+    (p * torch.tensor(w).cuda()).sum().backward()
+    assert rel_err(rc.grad.cpu(), ro.grad) < 1e-3
+
+
+@pytest.mark.parametrize("name", ["fluid_open_32", "fluid_closed_32x24", "fluid_open_128"])
+def test_projected_step_vs_reference_golden(name):
+    """One IncompressibleFlow.step from every golden frame.  The kernels follow the TF edge rule; the golden vectors come
+    from the NumPy backend, so samples with xi == N-1 exactly (boundary faces with velocity exactly 0) are excluded --
+    they are identified with the oracle under both rules and reported."""
+    ops = _ops()
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    B, ny, nx = g["rho0"].shape
+    bd, dt = str(g["boundary"]), float(g["dt"])
+    geo = F.Geometry(ny, nx)
+    for k in range(int(g["steps"])):
+        rho, vy, vx = [g["%s%d" % (n, k)] for n in ("rho", "vy", "vx")]
+        rc, yc, xc, pc, iters = ops.incompressible_step(*[torch.tensor(a).cuda() for a in (rho, vy, vx)], dt, bd == "closed",
+                                                        accuracy=1e-6, max_iterations=3000)
+        # advected (pre-projection) velocity: per-step tolerance 1e-5 away from exact-edge samples
+        ay, ax = ops.advect_staggered(torch.tensor(vy).cuda(), torch.tensor(vx).cuda(), dt, F.modes_of(bd)[1])
+        t = [torch.tensor(a) for a in (vy, vx)]
+        tf_rule = F.advect_staggered(t[0], t[1], dt, geo, F.modes_of(bd)[1])
+        R.NUMPY_EDGE_RULE = True
+        try:
+            np_rule = F.advect_staggered(t[0], t[1], dt, geo, F.modes_of(bd)[1])
+        finally:
+            R.NUMPY_EDGE_RULE = False
+        flips = sum(int((a != b).sum()) for a, b in zip(tf_rule, np_rule))
+        for got, gold, a, b in ((ay, g["avy%d" % (k + 1)], tf_rule[0], np_rule[0]), (ax, g["avx%d" % (k + 1)], tf_rule[1], np_rule[1])):
+            keep = (a == b).numpy()
+            assert rel_err(got.cpu().numpy() * keep, gold * keep) < 1e-5
+        assert rel_err(rc.cpu(), g["rho%d" % (k + 1)]) < 1e-5
+        if flips == 0:      # the projection is global: compare projected velocities only when no edge sample flipped
+            assert rel_err(yc.cpu(), g["vy%d" % (k + 1)]) < 2e-5 and rel_err(xc.cpu(), g["vx%d" % (k + 1)]) < 2e-5
+
+
+@pytest.mark.parametrize("bd", ["open", "closed"])
+def test_trajectory_and_gradient_vs_oracle(bd):
+    """4 projected steps: states within 1e-4 over the trajectory, control-loss gradients within 1e-3.
+    Oracle pressure = fp64 direct solve; CUDA CG runs to 1e-6."""
+    ops = _ops()
+    rng = np.random.RandomState(12)
+    B, ny, nx = 2, 32, 32
+    rho, vy, vx = _fields(rng, B, ny, nx, 1.2)
+    geo = F.Geometry(ny, nx)
+    (ro, yo, xo), (rc, yc, xc) = _pair([rho, vy, vx])
+    so, sc = (ro, yo, xo), (rc, yc, xc)
+    for _ in range(4):
+        so = F.incompressible_step(*so, 0.9, geo, bd)[:3]
+        sc = ops.incompressible_step(*sc, 0.9, bd == "closed", accuracy=1e-6, max_iterations=3000)[:3]
+    for a, b in zip(sc, so):
+        assert rel_err(a.detach().cpu(), b.detach()) < 1e-4
+    target = _fields(rng, B, ny, nx, 1.0)[0]
+    (R.l2_loss(so[0] - torch.tensor(target)) + 0.1 * R.l2_loss(so[1]) + 0.1 * R.l2_loss(so[2])).backward()
+    d = sc[0] - torch.tensor(target).cuda()
+    ((d ** 2).sum() / 2 / B + 0.1 * (sc[1] ** 2).sum() / 2 / B + 0.1 * (sc[2] ** 2).sum() / 2 / B).backward()
+    for a, b in ((rc, ro), (yc, yo), (xc, xo)):
+        assert rel_err(a.grad.cpu(), b.grad) < 1e-3
+
+
+def test_controlled_variant_and_force_loss_vs_golden_and_oracle():
+    """Notebook variant (src/control/pde/incompressible_flow.py:53-59, 31-43): curl -> advect density; force loss =
+    l2(semi_lagrangian(v, v) - v_next)."""
+    ops = _ops()
+    g = np.load(os.path.join(GOLDEN, "fluid_controlled_64.npz"))
+    dt = float(g["dt"])
+    (ro, po), (rc, pc) = _pair([g["rho"], g["phi"]])
+    vyc, vxc = ops.curl_2d(pc, R.CONSTANT)
+    nxt = ops.advect_centered(rc, vyc, vxc, dt, R.CONSTANT)
+    ay, ax = ops.advect_staggered(vyc, vxc, dt, R.REPLICATE)
+    assert rel_err(vyc.detach().cpu(), g["vy"]) == 0.0 and rel_err(vxc.detach().cpu(), g["vx"]) == 0.0
+    assert rel_err(nxt.detach().cpu(), g["rho_next"]) < 1e-5
+    assert rel_err(ay.detach().cpu(), g["avy"]) < 1e-5 and rel_err(ax.detach().cpu(), g["avx"]) < 1e-5
+    # gradient of (density loss + force loss) w.r.t. the potential and the density
+    geo = F.Geometry(64, 64)
+    rng = np.random.RandomState(4)
+    tgt = rng.rand(*g["rho"].shape).astype(np.float32)
+    v2y, v2x = g["avy"] * 0.9, g["avx"] * 1.1
+    n2, vyo, vxo = F.controlled_step(ro, po, dt, geo)
+    lo = R.l2_loss(n2 - torch.tensor(tgt)) + F.force_loss([vyo, torch.tensor(v2y)], [vxo, torch.tensor(v2x)], dt, geo)
+    lo.backward()
+    B = tgt.shape[0]
+    lc = ((nxt - torch.tensor(tgt).cuda()) ** 2).sum() / 2 / B + ((ay - torch.tensor(v2y).cuda()) ** 2).sum() / 2 / B \
+        + ((ax - torch.tensor(v2x).cuda()) ** 2).sum() / 2 / B
+    lc.backward()
+    assert abs(lc.item() - lo.item()) < 1e-4 * abs(lo.item())
+    assert rel_err(pc.grad.cpu(), po.grad) < 1e-3 and rel_err(rc.grad.cpu(), ro.grad) < 1e-3
+
+
+def test_adjoint_is_bit_reproducible_and_batch_independent():
+    ops = _ops()
+    rng = np.random.RandomState(6)
+    rho, vy, vx = _fields(rng, 4, 48, 48, 2.0)
+
+    def run(r, y, x):
+        t = [torch.tensor(a, device="cuda", requires_grad=True) for a in (r, y, x)]
+        out = ops.incompressible_step(*t, 1.0, False, accuracy=1e-5)
+        (out[0].sum() + (out[1] ** 2).sum() + (out[2] ** 2).sum()).backward()
+        return [a.grad.clone() for a in t] + [o.detach() for o in out[:3]]
+
+    a, b = run(rho, vy, vx), run(rho, vy, vx)
+    assert all(torch.equal(p, q) for p, q in zip(a, b))
+    rho2, vy2, vx2 = rho.copy(), vy.copy(), vx.copy()
+    rho2[1:], vy2[1:], vx2[1:] = 0, 0, 0
+    c = run(rho2, vy2, vx2)
+    assert all(torch.equal(p[0], q[0]) for p, q in zip(a, c))      # PhiFlow/tests/test_fluid.py:80-100
+
+
+def test_full_size_config3_properties():
+    """BASELINE config 3 size (128x128, batch 64): size-independent properties.
+    (1) CLOSED projection is divergence-free everywhere, OPEN only in the interior;
+    (2) the projection is linear and its adjoint kernels are its transpose: <P u, w> == <u, P^T w>;
+    (3) projecting twice changes nothing (idempotence)."""
+    ops = _ops()
+    rng = np.random.RandomState(3)
+    B, n = 64, 128
+    vy = torch.tensor(_smooth(rng, (B, n + 1, n), 0.5), device="cuda")
+    vx = torch.tensor(_smooth(rng, (B, n, n + 1), 0.5), device="cuda")
+    for closed in (False, True):
+        u = [vy.clone().requires_grad_(True), vx.clone().requires_grad_(True)]
+        py, px, p, iters, div = ops.divergence_free(u[0], u[1], closed, accuracy=1e-5)
+        d2 = ops.mask_divergence(py.detach(), px.detach(), closed)
+        inner = d2[:, 1:-1, 1:-1] if not closed else d2
+        assert float(inner.abs().max()) < 5e-5 and int(iters.max()) < 2000
+        if not closed:
+            assert float(d2.abs().max()) > 1e-3
+        wy, wx = torch.randn_like(py), torch.randn_like(px)
+        ((py * wy).sum() + (px * wx).sum()).backward()
+        lhs = float((py.detach().double() * wy.double()).sum() + (px.detach().double() * wx.double()).sum())
+        rhs = float((u[0].grad.double() * vy.double()).sum() + (u[1].grad.double() * vx.double()).sum())
+        assert abs(lhs - rhs) < 1e-3 * max(abs(lhs), 1.0)
+        qy, qx, _, _, _ = ops.divergence_free(py.detach(), px.detach(), closed, accuracy=1e-5)
+        if closed:
+            assert rel_err(qy.cpu(), py.detach().cpu()) < 1e-4 and rel_err(qx.cpu(), px.detach().cpu()) < 1e-4
+
+
+def test_edge_cases():
+    ops = _ops()
+    from pde_control_b200._lib import PdecError
+    z = torch.zeros(0, 8, 8, device="cuda")
+    assert ops.advect_centered(z, torch.zeros(0, 9, 8, device="cuda"), torch.zeros(0, 8, 9, device="cuda"), 1.0).shape == (0, 8, 8)
+    with pytest.raises(PdecError):
+        ops.curl_2d(torch.zeros(1, 1, 8, device="cuda"))                       # ny < 2
+    with pytest.raises(RuntimeError):
+        ops.mask_divergence(torch.zeros(1, 9, 8), torch.zeros(1, 8, 9), False)  # CPU tensors: no fallback
+    # huge velocities: every back-trace leaves the domain -> zeros ('constant') and finite gradients
+    rho = torch.rand(1, 16, 16, device="cuda", requires_grad=True)
+    vy = torch.full((1, 17, 16), 1e4, device="cuda", requires_grad=True)
+    vx = torch.full((1, 16, 17), -1e4, device="cuda", requires_grad=True)
+    out = ops.advect_centered(rho, vy, vx, 1.0, R.CONSTANT)
+    out.sum().backward()
+    assert float(out.abs().max()) == 0.0 and bool(torch.isfinite(rho.grad).all()) and float(rho.grad.abs().max()) == 0.0
