@@ -26,6 +26,8 @@ class FluidWorkload:
     ACCURACY, MAX_IT = 1e-5, 2000
 
     def __init__(self, device, rank, closed=False, use_graph=True):
+        import os
+        use_graph = use_graph and not os.environ.get("PDEC_BENCH_NO_GRAPH")
         from . import ops, datagen
         self.ops, self.dev, self.closed = ops, device, closed
         B, n = self.B, self.N
@@ -45,21 +47,23 @@ class FluidWorkload:
         self.d2h = self.h2d + 4
         self.iters = []
         self.graph = None
-        self._trajectory()              # eager warm-up (also sizes the workspaces)
-        torch.cuda.synchronize()
+        # Everything that touches autograd runs on ONE side stream (warm-up and capture): autograd binds a leaf's gradient
+        # sink to the stream of its first use, and a sink bound to the legacy stream cannot be captured.
+        side = torch.cuda.Stream(device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                self._trajectory()      # warm-up (also sizes the workspaces)
+        side.synchronize()
         if use_graph:
-            side = torch.cuda.Stream(device)
-            side.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(side):
-                for _ in range(2):
-                    self._trajectory()
-            torch.cuda.current_stream().wait_stream(side)
-            torch.cuda.synchronize()
             self.graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self.graph):
+            with torch.cuda.graph(self.graph, stream=side):
                 self._trajectory()
-            torch.cuda.synchronize()
-        self.graph_launches = None
+        else:
+            self.side = side
+        torch.cuda.synchronize()
+        self.step()                      # one replay so that the iteration counters hold real values
+        torch.cuda.synchronize()
         its = torch.stack(self.iters).float()
         self.mean_iterations_fwd = float(its.mean())
         # adjoint solves run the same CG on the incoming gradient: measured separately below
@@ -91,7 +95,10 @@ class FluidWorkload:
         if self.graph is not None:
             self.graph.replay()
         else:
-            self._trajectory()
+            self.side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.side):
+                self._trajectory()
+            torch.cuda.current_stream().wait_stream(self.side)
 
     def step_e2e(self):
         with torch.no_grad():
@@ -109,7 +116,7 @@ class FluidWorkload:
                 "cuda_graph": self.graph is not None, "l2": self.l2_policy}
 
     def extra(self):
-        return {"loss": float(self.loss), "cg_iterations_last_step": [int(v) for v in self.iters[-1][:4].tolist()]}
+        return {"loss": float(self.loss.detach()), "cg_iterations_last_step": [int(v) for v in self.iters[-1][:4].tolist()]}
 
     # ---- CPU leg (oracle port) -------------------------------------------------------------------------------
     @staticmethod

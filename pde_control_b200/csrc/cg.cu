@@ -162,6 +162,155 @@ __global__ void __launch_bounds__(THREADS, 1) cg_smem_kernel(const float* __rest
 }
 
 // -------------------------------------------------------------------------------------------------------------
+// cg_tile_kernel: the production one-CTA-per-element kernel for grids up to 128 x 128.
+// Thread (tx, ty) of a 32 x TY block owns the cells (i = 4*ty + ky, j = tx + 32*kx), kx, ky < 4: a warp always touches 32
+// consecutive columns of one row (conflict-free shared memory, affine offsets).  r, Am and the thread's OWN m values live in
+// registers; shared memory holds m with a one-cell halo ring (pitch nx+2) and x.  The halo ring removes every boundary
+// predicate from the 5-point stencil: it stays 0 for the open operator (p = 0 outside) and mirrors the border cell for the
+// closed one (sum of in-domain neighbours - count * centre == sum of 4 - 4 * centre with mirrored ghosts).
+// Per cell and iteration: 4 LDS + 1 LDS/STS pair (x) + 1 STS (m) and ~12 FP32 ops; beta = (r.Am)/(m.Am) is formed once
+// per iteration (the reference divides per element, blas.py:54 -- same value up to rounding; CG iterates are not the
+// parity oracle).
+// -------------------------------------------------------------------------------------------------------------
+template <int TY, bool FULL>
+__global__ void __launch_bounds__(32 * TY, 1) cg_tile_kernel(const float* __restrict__ rhs, const float* __restrict__ guess, float* __restrict__ out,
+                                                             int* __restrict__ iters, float* __restrict__ resid, int ny, int nx, int closed,
+                                                             float accuracy, int max_it) {
+    constexpr int THREADS = 32 * TY;
+    extern __shared__ __align__(16) float smem_dyn[];
+    __shared__ float redA[2][32], redB[2][32];
+    const int pitch = nx + 2;
+    const int padded = (ny + 2) * pitch;
+    float* sm_m = smem_dyn;                 // [(ny+2) x pitch], halo ring
+    float* sm_x = smem_dyn + padded;        // same indexing (halo unused)
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const size_t base = (size_t)blockIdx.x * ny * nx;
+    float r[16], am[16], m[16];
+    unsigned valid = 0u;                    // bit (ky*4+kx): the cell exists
+    for (int q = threadIdx.x; q < padded; q += THREADS) { sm_m[q] = 0.0f; sm_x[q] = 0.0f; }
+    __syncthreads();
+#pragma unroll
+    for (int ky = 0; ky < 4; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 4; ++kx) {
+            const int c = ky * 4 + kx, i = 4 * ty + ky, j = tx + 32 * kx;
+            r[c] = 0.0f; am[c] = 0.0f; m[c] = 0.0f;
+            if (i < ny && j < nx) {
+                valid |= 1u << c;
+                r[c] = rhs[base + (size_t)i * nx + j];
+                if (guess != nullptr) {
+                    const float g0 = guess[base + (size_t)i * nx + j];
+                    const int off = (i + 1) * pitch + j + 1;
+                    sm_x[off] = g0;
+                    sm_m[off] = g0;
+                    if (closed) {
+                        if (i == 0) sm_m[off - pitch] = g0;
+                        if (i == ny - 1) sm_m[off + pitch] = g0;
+                        if (j == 0) sm_m[off - 1] = g0;
+                        if (j == nx - 1) sm_m[off + 1] = g0;
+                    }
+                }
+            }
+        }
+    const int off0 = (4 * ty + 1) * pitch + tx + 1, sy = pitch;
+    if (guess != nullptr) {                 // momentum = k - A x0   (blas.py:24-26)
+        __syncthreads();
+#pragma unroll
+        for (int ky = 0; ky < 4; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx) {
+                const int c = ky * 4 + kx;
+                if (FULL || (valid & (1u << c))) {
+                    const int off = off0 + ky * sy + kx * 32;
+                    r[c] -= (sm_m[off - pitch] + sm_m[off - 1]) + (sm_m[off + 1] + sm_m[off + pitch]) - 4.0f * sm_m[off];
+                }
+            }
+        __syncthreads();
+    }
+    float rmax = 0.0f, dummy = 0.0f;
+    auto publish_m = [&]() {                // own m -> shared memory (+ mirrored ghosts for the closed operator)
+#pragma unroll
+        for (int ky = 0; ky < 4; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx) {
+                const int c = ky * 4 + kx;
+                if (FULL || (valid & (1u << c))) {
+                    const int off = off0 + ky * sy + kx * 32;
+                    sm_m[off] = m[c];
+                    if (closed) {
+                        const int i = 4 * ty + ky, j = tx + 32 * kx;
+                        if (i == 0) sm_m[off - pitch] = m[c];
+                        if (i == ny - 1) sm_m[off + pitch] = m[c];
+                        if (j == 0) sm_m[off - 1] = m[c];
+                        if (j == nx - 1) sm_m[off + 1] = m[c];
+                    }
+                }
+            }
+    };
+    auto matvec = [&]() {                   // vertical neighbours inside the thread's 4-row strip come from registers
+#pragma unroll
+        for (int ky = 0; ky < 4; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx) {
+                const int c = ky * 4 + kx;
+                if (FULL || (valid & (1u << c))) {
+                    const int off = off0 + ky * sy + kx * 32;
+                    const float up = (FULL && ky > 0) ? m[c - 4 >= 0 ? c - 4 : 0] : sm_m[off - pitch];
+                    const float dn = (FULL && ky < 3) ? m[c + 4 <= 15 ? c + 4 : 15] : sm_m[off + pitch];
+                    am[c] = (up + sm_m[off - 1]) + (sm_m[off + 1] + dn) - 4.0f * m[c];
+                }
+            }
+    };
+#pragma unroll
+    for (int c = 0; c < 16; ++c) { m[c] = r[c]; rmax = fmaxf(rmax, fabsf(r[c])); }
+    publish_m();
+    block_reduce2<THREADS>(dummy, rmax, redB, true);     // its __syncthreads also orders publish_m before the matvec
+    matvec();
+    int it = 0;
+    while (it < max_it && (accuracy <= 0.0f || rmax >= accuracy)) {
+        float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 16; ++c) { s1 += m[c] * am[c]; s2 += m[c] * r[c]; }
+        block_reduce2<THREADS>(s1, s2, redA, false);
+        const float tmp = s1, a = div_no_nan(s2, tmp);
+        float s3 = 0.0f, mx = 0.0f;
+#pragma unroll
+        for (int ky = 0; ky < 4; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx) {
+                const int c = ky * 4 + kx;
+                if (FULL || (valid & (1u << c))) {
+                    const int off = off0 + ky * sy + kx * 32;
+                    sm_x[off] += a * m[c];
+                    r[c] -= a * am[c];
+                    s3 += r[c] * am[c];
+                    mx = fmaxf(mx, fabsf(r[c]));
+                }
+            }
+        block_reduce2<THREADS>(s3, mx, redB, true);
+        const float beta = div_no_nan(s3, tmp);
+#pragma unroll
+        for (int c = 0; c < 16; ++c) m[c] = r[c] - beta * m[c];
+        publish_m();                        // all stencil reads of the old m completed before reduction A's barrier
+        __syncthreads();
+        matvec();
+        rmax = mx;
+        ++it;
+    }
+#pragma unroll
+    for (int ky = 0; ky < 4; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 4; ++kx) {
+            const int c = ky * 4 + kx, i = 4 * ty + ky, j = tx + 32 * kx;
+            if (FULL || (valid & (1u << c))) out[base + (size_t)i * nx + j] = sm_x[off0 + ky * sy + kx * 32];
+        }
+    if (threadIdx.x == 0) {
+        if (iters) iters[blockIdx.x] = it;
+        if (resid) resid[blockIdx.x] = rmax;
+    }
+}
+
+// -------------------------------------------------------------------------------------------------------------
 // Large grids: cooperative persistent kernel, vectors in global memory (L2 resident up to ~20 MB per vector).
 // Unit of work = (batch element b, chunk c of consecutive cells); blocks take units grid-stride.
 // Per iteration TWO passes separated by grid-wide barriers:
@@ -362,6 +511,24 @@ extern "C" size_t pdec_cg_poisson_2d_workspace_bytes(int B, int ny, int nx) {
     return 4 * b * N * sizeof(float) + 8 * b * global_chunks((int)N) * sizeof(float) + b * sizeof(int) + 1024;
 }
 
+template <int TY, bool FULL>
+static int launch_tile_(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
+                       int closed, float accuracy, int max_iterations, cudaStream_t st) {
+    const size_t smem = (size_t)2 * (ny + 2) * (nx + 2) * sizeof(float);
+    auto kernel = cg_tile_kernel<TY, FULL>;
+    if (smem > 48 * 1024 && cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return PDEC_ERR_CUDA_LAUNCH;
+    kernel<<<B, 32 * TY, smem, st>>>(rhs, guess, p, iterations, residual, ny, nx, closed, accuracy, max_iterations);
+    return PDEC_OK;
+}
+
+template <int TY>
+static int launch_tile(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
+                       int closed, float accuracy, int max_iterations, cudaStream_t st) {
+    if (ny == 4 * TY && nx == 128) return launch_tile_<TY, true>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+    return launch_tile_<TY, false>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+}
+
 template <int THREADS, int CPT = 16>
 static int launch_smem(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
                        int closed, float accuracy, int max_iterations, cudaStream_t st) {
@@ -388,6 +555,14 @@ extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p
     closed = closed ? 1 : 0;
     const long long N = (long long)ny * nx;
     int rc = PDEC_OK;
+    if (ny <= 128 && nx <= 128 && variant == 0) {
+        if (ny > 64) rc = launch_tile<32>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+        else if (ny > 32) rc = launch_tile<16>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+        else rc = launch_tile<8>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
+        if (rc != PDEC_OK) return rc;
+        PDEC_CHECK_LAUNCH();
+        return PDEC_OK;
+    }
     if (N <= PDEC_CG_SMEM_MAX_CELLS) {
         if (N > 8192 && variant == 1) rc = launch_smem<512, 32>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
         else if (N > 8192) rc = launch_smem<1024>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
