@@ -1,0 +1,158 @@
+"""Fluid state, IncompressibleFlow physics, divergence_free and the pressure-solver objects over the CUDA kernels.
+
+Mirrors  Fluid               PF/physics/fluid.py:21-60
+         IncompressibleFlow  PF/physics/fluid.py:73-114   (default flags; no obstacles; buoyancy_factor 0)
+         divergence_free     PF/physics/fluid.py:214-243
+         SparseCG            PF/physics/pressuresolver/sparse.py:40-102  (parameters only; the solve is pdec_cg_poisson_2d)
+         poisson_solve       PF/physics/pressuresolver/solver_api.py:132-158
+         advect.semi_lagrangian, staggered_curl_2d  PF/physics/field/advect.py:24-40, util.py:60-67
+"""
+import torch
+
+from .. import ops
+from .._lib import MODE_OF_EXTRAPOLATION
+from .burgers import DomainState
+from .domain import Domain, OPEN
+from .field import CenteredGrid, StaggeredGrid, effect_applied
+from .world import Physics, StateDependency
+
+
+class SparseCG(object):
+    """Conjugate-gradient pressure solver parameters (sparse.py:42-71).  'mirror' gradient iterations are treated as
+    'same' (the device decides the iteration count)."""
+
+    def __init__(self, accuracy=1e-5, gradient_accuracy="same", max_iterations=2000, max_gradient_iterations="same", autodiff=False):
+        assert not autodiff, "autodiff through the CG loop is not provided: the gradient is a second solve (sparse.py:93-94)"
+        self.accuracy = accuracy
+        self.gradient_accuracy = accuracy if gradient_accuracy == "same" else gradient_accuracy
+        self.max_iterations = max_iterations
+        self.max_gradient_iterations = max_iterations if max_gradient_iterations in ("same", "mirror") else max_gradient_iterations
+
+    def solve(self, field, domain, guess=None):
+        """field [B, ny, nx, 1] or [B, ny, nx] -> (pressure of the same shape, iterations[B])."""
+        t = field[..., 0] if field.dim() == 4 else field
+        g = None if guess is None else (guess[..., 0] if guess.dim() == 4 else guess)
+        p, iters, _ = ops.pressure_solve(t, _closed(domain), self.accuracy, self.max_iterations, self.gradient_accuracy,
+                                         self.max_gradient_iterations, g)
+        return (p.unsqueeze(-1) if field.dim() == 4 else p), iters
+
+
+def _closed(domain):
+    domain = domain.domain if hasattr(domain, "domain") else domain
+    m = domain.boundaries
+    if m.periodic:
+        raise NotImplementedError("periodic pressure solves are not on the B200 path (SURVEY 8f N4)")
+    return bool(m.solid)
+
+
+def poisson_solve(input_field, poisson_domain, solver=None, guess=None):
+    """Solves laplace(p) = input_field (solver_api.py:132-158) -> (pressure CenteredGrid, iterations)."""
+    assert isinstance(input_field, CenteredGrid)
+    solver = solver or SparseCG()
+    p, it = solver.solve(input_field.data, poisson_domain, None if guess is None else guess.data)
+    return CenteredGrid(p, input_field.box, extrapolation=input_field.extrapolation, name="pressure"), it
+
+
+def semi_lagrangian(field, velocity_field, dt):
+    """advect.semi_lagrangian (advect.py:24-40) for the two cases on the path: a centred scalar field advected by a
+    staggered velocity, and a staggered velocity advected by itself."""
+    if isinstance(field, StaggeredGrid):
+        assert velocity_field is field or velocity_field.compatible(field), "staggered fields are self-advected on the B200 path"
+        vy, vx = field.tensors
+        ay, ax = ops.advect_staggered(vy, vx, dt, MODE_OF_EXTRAPOLATION[field.extrapolation], _box4(field.box))
+        return field.with_tensors([ay, ax])
+    assert isinstance(field, CenteredGrid) and isinstance(velocity_field, StaggeredGrid) and field.rank == 2
+    vy, vx = velocity_field.tensors
+    out = ops.advect_centered(field.tensor, vy, vx, dt, MODE_OF_EXTRAPOLATION[field.extrapolation], _box4(field.box))
+    return field.with_tensor(out)
+
+
+def staggered_curl_2d(grid):
+    """staggered_curl_2d (util.py:60-67): result has the StaggeredGrid default extrapolation 'boundary'."""
+    assert isinstance(grid, CenteredGrid) and grid.rank == 2
+    vy, vx = ops.curl_2d(grid.tensor, MODE_OF_EXTRAPOLATION[grid.extrapolation])
+    return StaggeredGrid([vy.unsqueeze(-1), vx.unsqueeze(-1)], box=grid.box, batch_size=grid._batch_size)
+
+
+def _box4(box):
+    return tuple(float(v) for v in box.lower) + tuple(float(v) for v in box.size)
+
+
+def divergence_free(velocity, domain=None, obstacles=(), pressure_solver=None, return_info=False):
+    """Pressure projection (fluid.py:214-243) without obstacles."""
+    assert isinstance(velocity, StaggeredGrid)
+    if len(obstacles) > 0:
+        raise NotImplementedError("obstacles are not on the B200 path (SURVEY 8f N3)")
+    if domain is None:
+        domain = Domain(velocity.resolution, OPEN, box=velocity.box)
+    solver = pressure_solver or SparseCG()
+    vy, vx = velocity.tensors
+    oy, ox, p, iters, div = ops.divergence_free(vy, vx, _closed(domain), _box4(velocity.box), solver.accuracy, solver.max_iterations,
+                                                solver.gradient_accuracy, solver.max_gradient_iterations)
+    result = velocity.with_tensors([oy, ox])
+    if not return_info:
+        return result
+    pressure = CenteredGrid(p.unsqueeze(-1), velocity.box, extrapolation="boundary", name="pressure") * 1.0
+    pressure = pressure.copied_with(data=pressure.data * float(velocity.dx[0]))       # fluid.py:240
+    divergence = CenteredGrid(div.unsqueeze(-1), velocity.box, name="div")
+    return result, {"pressure": pressure, "iterations": iters, "divergence": divergence}
+
+
+class Fluid(DomainState):
+
+    def __init__(self, domain, density=0.0, velocity=0.0, buoyancy_factor=0.0, tags=("fluid", "velocityfield", "velocity"),
+                 name="fluid", age=0.0, batch_size=None, device="cuda"):
+        DomainState.__init__(self, domain, tags=tags, name=name, age=age, batch_size=batch_size)
+        self.buoyancy_factor = buoyancy_factor
+        self.density = self.centered_grid("density", density, device=device)
+        self.velocity = self._staggered("velocity", velocity, device)
+        self.solve_info = {}
+
+    def _staggered(self, name, value, device):
+        mode = self.domain.boundaries.vector_extrapolation_mode
+        if isinstance(value, StaggeredGrid):
+            return value if value.extrapolation == mode else value.copied_with(extrapolation=mode)
+        if isinstance(value, (int, float)):
+            return StaggeredGrid.sample(value, self.domain, batch_size=self._batch_size, name=name, device=device)
+        t = value if isinstance(value, torch.Tensor) else torch.as_tensor(value, dtype=torch.float32)
+        return StaggeredGrid(t.to(device), box=self.domain.box, name=name, extrapolation=mode, batch_size=self._batch_size)
+
+    def default_physics(self):
+        return INCOMPRESSIBLE_FLOW
+
+
+class IncompressibleFlow(Physics):
+
+    def __init__(self, pressure_solver=None, make_input_divfree=False, make_output_divfree=True, conserve_density=True):
+        Physics.__init__(self, [StateDependency("obstacles", "obstacle"),
+                                StateDependency("density_effects", "density_effect", blocking=True),
+                                StateDependency("velocity_effects", "velocity_effect", blocking=True)])
+        self.pressure_solver = pressure_solver
+        self.make_input_divfree = make_input_divfree
+        self.make_output_divfree = make_output_divfree
+        self.conserve_density = conserve_density
+
+    def step(self, fluid, dt=1.0, obstacles=(), density_effects=(), velocity_effects=()):
+        if fluid.buoyancy_factor != 0:
+            raise NotImplementedError("buoyancy is not on the B200 path (SURVEY 8f N3)")
+        velocity, density = fluid.velocity, fluid.density
+        solve_info = {}
+        if self.make_input_divfree:
+            velocity, solve_info = divergence_free(velocity, fluid.domain, obstacles, self.pressure_solver, return_info=True)
+        new_density = semi_lagrangian(density, velocity, dt)
+        velocity = advected_velocity = semi_lagrangian(velocity, velocity, dt)
+        if self.conserve_density and fluid.domain.boundaries.solid:
+            new_density = new_density.with_tensor(ops.normalize_to(new_density.tensor, density.tensor))
+        density = new_density
+        for effect in density_effects:
+            density = effect_applied(effect, density, dt)
+        for effect in velocity_effects:
+            velocity = effect_applied(effect, velocity, dt)
+        divergent_velocity = velocity
+        if self.make_output_divfree:
+            velocity, solve_info = divergence_free(velocity, fluid.domain, obstacles, self.pressure_solver, return_info=True)
+        solve_info = dict(solve_info, advected_velocity=advected_velocity, divergent_velocity=divergent_velocity)
+        return fluid.copied_with(density=density, velocity=velocity, age=fluid.age + dt, solve_info=solve_info)
+
+
+INCOMPRESSIBLE_FLOW = IncompressibleFlow()

@@ -1,0 +1,64 @@
+"""CPU, world_size 2, gloo: the data-parallel path of ControlTraining (batch sharded by rank, one flat all-reduce of the
+network gradients per step) and the shard arithmetic bench.py uses.  The physics needs no collective."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from pde_control_b200 import control as C
+    rng = np.random.RandomState(0)
+    ends = rng.randn(32, 1, 1).astype(np.float32)
+    frames = np.stack([ends * t / 2 for t in range(3)], 1)
+    torch.manual_seed(100 + rank)                       # different initial weights per rank: prepare() must broadcast rank 0's
+    pde = C.IncrementPDE(learnable=True)
+    app = C.ControlTraining(2, pde, {"scalar": frames}, None, range(32), obs_loss_frames=(1,), trainable_networks=("OP2",),
+                            sequence_class=C.SkipSequence, batch_size=8, device="cpu", learning_rate=0.05)
+    assert app.world_size == world and app._train.size == 16          # shard of the simulations
+    app.prepare()
+    w0 = float(pde.networks["OP2"].weight)
+    for _ in range(5):
+        app.step()
+    np.save(os.path.join(out_dir, "w_%d.npy" % rank), np.array([w0, float(pde.networks["OP2"].weight)]))
+    dist.destroy_process_group()
+
+
+def _single(frames, w0):
+    from pde_control_b200 import control as C
+    pde = C.IncrementPDE(learnable=True)
+    app = C.ControlTraining(2, pde, {"scalar": frames}, None, range(32), obs_loss_frames=(1,), trainable_networks=("OP2",),
+                            sequence_class=C.SkipSequence, batch_size=16, device="cpu", learning_rate=0.05)
+    app.prepare()
+    with torch.no_grad():
+        pde.networks["OP2"].weight.fill_(w0)
+    return app, pde
+
+
+def test_two_rank_data_parallel_training_matches_single_process(tmp_path):
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    a, b = np.load(tmp_path / "w_0.npy"), np.load(tmp_path / "w_1.npy")
+    assert a[0] == b[0]                                   # broadcast initial weights
+    assert a[1] == b[1]                                   # identical after averaged-gradient steps
+    # equals one process training on the union batch (rank 0 sims 0-7 + rank 1 sims 16-23 each step ...):
+    rng = np.random.RandomState(0)
+    ends = rng.randn(32, 1, 1).astype(np.float32)
+    frames = np.stack([ends * t / 2 for t in range(3)], 1)
+    order = np.concatenate([np.arange(0, 16).reshape(2, 8), np.arange(16, 32).reshape(2, 8)], 1)   # per step: 8 of each shard
+    app, pde = _single(frames[np.concatenate([order[0], order[1]])], float(a[0]))
+    # the single process sees [step-0 union batch, step-1 union batch] alternately with batch 16
+    for _ in range(5):
+        app.step()
+    assert abs(float(pde.networks["OP2"].weight) - a[1]) < 1e-5
