@@ -452,10 +452,14 @@ extern "C" int pdec_burgers_trajectory_bwd(const float* u0, const float* frames,
     return PDEC_OK;
 }
 
+// burgers_fast.cu: register-resident kernel for n == 128 (returns 1 when the shape is not eligible)
+int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials, int T, int B, int n, int mode, double dt, double viscosity,
+                                float lower, float size, int substeps, int resubstep, float gl2, float gl1, int* nchunks_out,
+                                cudaStream_t st);
+
 extern "C" size_t pdec_burgers_pair_loss_workspace_bytes(int B, int n, int T) {
     (void)n;
-    (void)T;
-    return (size_t)(B > 0 ? B : 1) * sizeof(float2);
+    return (size_t)(B > 0 ? B : 1) * (size_t)(T > 0 ? T : 1) * sizeof(float2);     // one loss partial per (row, chunk of pairs)
 }
 
 extern "C" int pdec_burgers_pair_loss(const float* s, float* grad_s, float* losses, int T, int B, int n, int mode,
@@ -467,14 +471,25 @@ extern "C" int pdec_burgers_pair_loss(const float* s, float* grad_s, float* loss
     if (rc != PDEC_OK) return rc;
     if (B < 1 || T < 1 || !s || !losses || !workspace) return PDEC_ERR_INVALID_ARGUMENT;
     if (workspace_bytes < pdec_burgers_pair_loss_workspace_bytes(B, n, T)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+    cudaStream_t st = (cudaStream_t)stream;
+    float2* partials = reinterpret_cast<float2*>(workspace);
+    const float invB = 1.0f / (float)B;
+    {
+        int nchunks = 1;
+        rc = pdec_burgers_pair_loss_fast(s, grad_s, partials, T, B, n, mode, dt, viscosity, box_lower, box_size, substeps, resubstep, gl2,
+                                         gl1, &nchunks, st);
+        if (rc < 0) return rc;
+        if (rc == PDEC_OK) {
+            burgers_loss_reduce_kernel<<<1, 1024, 0, st>>>(partials, B * nchunks, invB, losses);
+            PDEC_CHECK_LAUNCH();
+            return PDEC_OK;
+        }
+    }
     const int wpc = pick_wpc(p.nrow, PL_ROWS);
     if (wpc == 0) return PDEC_ERR_UNSUPPORTED_SIZE;
     const size_t smem = ((size_t)p.nrow * (1 + (size_t)wpc * PL_ROWS)) * sizeof(float);
     const int vec4 = (n % 4 == 0) && aligned16(s) && (grad_s == nullptr || aligned16(grad_s));
     const int grid = rows_grid(B, wpc, smem);
-    cudaStream_t st = (cudaStream_t)stream;
-    float2* partials = reinterpret_cast<float2*>(workspace);
-    const float invB = 1.0f / (float)B;
 #define LAUNCH_PL(M)                                                                                           \
     do {                                                                                                       \
         rc = set_smem(burgers_pair_loss_kernel<M>, smem);                                                      \

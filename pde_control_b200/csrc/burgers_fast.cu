@@ -1,0 +1,272 @@
+// burgers_fast.cu -- register-resident fused force-loss kernel for rows of exactly 128 cells (BASELINE configs 2 and 4).
+// SURVEY row B5 / K-B3; compiled with -fmad=false like burgers.cu (same fp32 operation order in the forward step).
+//
+// Work unit = (batch row b, chunk of C consecutive frame pairs); one WARP per unit, lane l owns the four cells 4l..4l+3:
+//   * every frame row moves between HBM and registers as ONE 16-byte load / store per lane (512 B per warp instruction);
+//   * the 3-point stencils take their neighbours from the lane's own registers plus TWO warp shuffles per row;
+//   * shared memory holds only the gather source row and the transpose accumulator, in a skewed layout
+//     phys(j) = j + (j >> 5) so that the stride-4 gathers of a warp instruction hit 32 different banks;
+//   * the advection adjoint w.r.t. the data (transpose of the gather) is accumulated WITHOUT atomics: one warp instruction
+//     handles cells 4l+k for fixed k, whose source indices floor(xi) are strictly increasing in l except at extreme
+//     gradients -- a shuffle/vote check proves the indices distinct, then a plain read-modify-write is exact and ordered;
+//     otherwise the instruction falls back to the ranked (match_any) ordered scatter.  Either way the summation order is a
+//     function of the data only: bit-reproducible.
+// A chunk that does not start at frame 0 recomputes the residual of the pair before it (one extra forward step per chunk)
+// instead of exchanging it with the neighbouring warp; chunking exists so that B x T/C warps fill the 148 SMs.
+#include "pdec_common.cuh"
+
+namespace pdec {
+
+struct FastP {
+    int mode, substeps;
+    float dt, lower, size, nf, hi;   // hi = n - 1
+    float inv_size;                  // exact reciprocal when size is a power of two (EXACT), unused otherwise
+    float a;                         // float32(dt * viscosity / substeps)
+    float dx2, inv_dx2;              // float32(dx^2) and its exact reciprocal (EXACT)
+    float c2;                        // a * substeps / dx2: diffusion adjoint coefficient
+    float dxi_du;                    // -dt * n / size
+    float gl2, gl1;                  // dL/d(l2), dL/d(l1), already divided by B
+};
+
+__device__ __forceinline__ int skew(int j) { return j + (j >> 5); }
+#define FAST_ROW 132                 // 128 + 4 skew slots
+
+template <bool EXACT>
+__device__ __forceinline__ float to_index(const FastP& p, float x0, float u) {
+    const float x = x0 - u * p.dt;                                   // advect.py:35
+    const float local = EXACT ? (x - p.lower) * p.inv_size : (x - p.lower) / p.size;   // _box.py:50-52
+    return local * p.nf - 0.5f;                                      // grid.py:104-105
+}
+
+// neighbours of the lane's 4 cells: left of cell 0 and right of cell 3 come from the adjacent lanes
+template <int MODE>
+__device__ __forceinline__ void edge_neighbours(const float (&v)[4], int lane, float& left, float& right) {
+    left = __shfl_sync(PDEC_FULL_MASK, v[3], (lane + 31) & 31);
+    right = __shfl_sync(PDEC_FULL_MASK, v[0], (lane + 1) & 31);
+    if (MODE == PDEC_MODE_CONSTANT) {
+        if (lane == 0) left = 0.0f;
+        if (lane == 31) right = 0.0f;
+    } else if (MODE == PDEC_MODE_REPLICATE) {
+        if (lane == 0) left = v[0];
+        if (lane == 31) right = v[3];
+    }
+}
+
+struct Gathered {                    // what the forward step leaves behind for its adjoint
+    int pf[4], pc[4];                // skewed shared-memory indices of the floor / ceil sample
+    float w0[4], w1[4];              // weight of the ceil / floor sample
+    float du[4];                     // u[ceil] - u[floor]
+    int base[4];                     // floor(xi) before clamping (monotonicity test)
+    unsigned active;                 // bit k: the sample contributes ('constant': inside the domain)
+};
+
+// one forward step of the row held in u[] (and mirrored in shared memory su[] by the caller) -> v[]
+template <int MODE, bool EXACT>
+__device__ __forceinline__ void fast_forward(const FastP& p, const float (&x0)[4], const float (&u)[4], const float* su, int lane,
+                                             float (&v)[4], Gathered& G) {
+    float adv[4];
+    G.active = 0u;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float xi = to_index<EXACT>(p, x0[k], u[k]);
+        int fi, ci;
+        interp_setup<MODE>(xi, 128, fi, ci, G.w0[k], G.w1[k]);
+        const float basef = floorf(xi);
+        G.base[k] = (int)fminf(fmaxf(basef, -1.0e6f), 1.0e6f);
+        G.pf[k] = skew(fi);
+        G.pc[k] = skew(ci);
+        const float sf = su[G.pf[k]], sc = su[G.pc[k]];
+        adv[k] = sf * G.w1[k] + sc * G.w0[k];                         // tf_backend.py:491-497
+        G.du[k] = sc - sf;
+        if (MODE != PDEC_MODE_CONSTANT || fi != ci) G.active |= 1u << k;
+    }
+    float left, right;
+    edge_neighbours<MODE>(adv, lane, left, right);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float lo = k == 0 ? left : adv[k - 1], up = k == 3 ? right : adv[k + 1];
+        const float raw = up + lo - 2.0f * adv[k];                    // nd.py:281-282
+        const float lap = EXACT ? raw * p.inv_dx2 : raw / p.dx2;      // grid.py:190
+        float r = adv[k];
+        for (int s = 0; s < p.substeps; ++s) r = r + p.a * lap;       // util.py:41-43, TF semantics
+        v[k] = r;
+    }
+}
+
+// adjoint of one step: g[] = dL/d(step output) -> returns dL/d(step input) in gin[]; sacc must be all-zero on entry and is
+// all-zero again on exit
+template <int MODE>
+__device__ __forceinline__ void fast_adjoint(const FastP& p, const Gathered& G, float (&g)[4], float* sacc, int lane, float (&gin)[4]) {
+    float left, right, g1[4];
+    edge_neighbours<MODE>(g, lane, left, right);                      // the stencil matrix is symmetric for all pad modes
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float lo = k == 0 ? left : g[k - 1], up = k == 3 ? right : g[k + 1];
+        g1[k] = g[k] + p.c2 * (up + lo - 2.0f * g[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const bool act = (G.active >> k) & 1u;
+        // distinctness proof for this warp instruction
+        bool ordered;
+        if (MODE == PDEC_MODE_CONSTANT) {
+            const int prev = __shfl_up_sync(PDEC_FULL_MASK, G.base[k], 1);
+            ordered = lane == 0 || G.base[k] > prev;
+        } else {
+            const int pf_prev = __shfl_up_sync(PDEC_FULL_MASK, G.pf[k], 1), pc_prev = __shfl_up_sync(PDEC_FULL_MASK, G.pc[k], 1);
+            ordered = lane == 0 || (G.pf[k] > pf_prev && G.pc[k] > pc_prev);
+        }
+        if (__all_sync(PDEC_FULL_MASK, ordered)) {
+            if (act) sacc[G.pf[k]] += g1[k] * G.w1[k];
+            __syncwarp();
+            if (act) sacc[G.pc[k]] += g1[k] * G.w0[k];
+            __syncwarp();
+        } else {
+            warp_ordered_scatter_add(sacc, G.pf[k], g1[k] * G.w1[k], act);
+            warp_ordered_scatter_add(sacc, G.pc[k], g1[k] * G.w0[k], act);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int q = skew(4 * lane + k);
+        gin[k] = sacc[q] + g1[k] * G.du[k] * p.dxi_du;                // transpose of the gather + derivative through xi(u)
+        sacc[q] = 0.0f;
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ void row_to_smem(float* su, const float (&u)[4], int lane) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) su[skew(4 * lane + k)] = u[k];
+    __syncwarp();
+}
+
+template <int MODE, bool EXACT, bool L1TERM>
+__global__ void __launch_bounds__(256) burgers_pair_loss_fast_kernel(FastP p, const float* __restrict__ s, float* __restrict__ grad_s,
+                                                                      float2* __restrict__ partials, int T, int B, int C, int nchunks) {
+    __shared__ float smem[8][2][FAST_ROW];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float* su = smem[warp][0];
+    float* sacc = smem[warp][1];
+    for (int q = lane; q < FAST_ROW; q += 32) { su[q] = 0.0f; sacc[q] = 0.0f; }
+    __syncwarp();
+    float x0[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) x0[k] = cell_center_local(4 * lane + k, 128) * p.size + p.lower;
+    const size_t fstride = (size_t)B * 128;
+    const long long units = (long long)B * nchunks;
+    for (long long unit = (long long)blockIdx.x * 8 + warp; unit < units; unit += (long long)gridDim.x * 8) {
+        const int chunk = (int)(unit / B), b = (int)(unit - (long long)chunk * B);      // consecutive warps -> consecutive rows
+        const int t0 = chunk * C, t1 = min(T, t0 + C);
+        const float4* row = reinterpret_cast<const float4*>(s + (size_t)b * 128) + lane;
+        float4* grow = grad_s ? reinterpret_cast<float4*>(grad_s + (size_t)b * 128) + lane : nullptr;
+        const size_t f4 = fstride / 4;
+        float u[4], nxt[4], carry[4], v[4], g[4], gin[4];
+        Gathered G;
+        {
+            const float4 q = row[(size_t)t0 * f4];
+            u[0] = q.x; u[1] = q.y; u[2] = q.z; u[3] = q.w;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) carry[k] = 0.0f;
+        if (t0 > 0 && grad_s != nullptr) {          // residual gradient of the pair (t0-1, t0): frame t0 is its target
+            const float4 q = row[(size_t)(t0 - 1) * f4];
+            float w[4] = {q.x, q.y, q.z, q.w};
+            row_to_smem(su, w, lane);
+            fast_forward<MODE, EXACT>(p, x0, w, su, lane, v, G);
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float d = u[k] - v[k];
+                carry[k] = p.gl2 * d;
+                if (L1TERM) carry[k] += p.gl1 * ((d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f));
+            }
+        }
+        float acc2 = 0.0f, acc1 = 0.0f;
+        float4 pre = row[(size_t)(t0 + 1) * f4];
+        for (int t = t0; t < t1; ++t) {
+            nxt[0] = pre.x; nxt[1] = pre.y; nxt[2] = pre.z; nxt[3] = pre.w;
+            if (t + 2 <= T) pre = row[(size_t)(t + 2) * f4];       // prefetch: in flight during this pair's arithmetic
+            row_to_smem(su, u, lane);
+            fast_forward<MODE, EXACT>(p, x0, u, su, lane, v, G);
+            float gd[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float d = nxt[k] - v[k];                      // burgers.py:29
+                acc2 += d * d;
+                acc1 += fabsf(d);
+                gd[k] = p.gl2 * d;
+                if (L1TERM) gd[k] += p.gl1 * ((d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f));
+                g[k] = -gd[k];
+            }
+            if (grad_s != nullptr) {
+                fast_adjoint<MODE>(p, G, g, sacc, lane, gin);
+                grow[(size_t)t * f4] = make_float4(gin[0] + carry[0], gin[1] + carry[1], gin[2] + carry[2], gin[3] + carry[3]);
+            } else {
+                __syncwarp();
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { carry[k] = gd[k]; u[k] = nxt[k]; }
+        }
+        if (grad_s != nullptr && t1 == T) grow[(size_t)T * f4] = make_float4(carry[0], carry[1], carry[2], carry[3]);
+        acc2 = warp_sum(acc2);
+        acc1 = warp_sum(acc1);
+        if (lane == 0) partials[(size_t)b * nchunks + chunk] = make_float2(acc2, acc1);
+    }
+}
+
+}  // namespace pdec
+
+using namespace pdec;
+
+static bool is_pow2f(float x) {
+    int e;
+    return x > 0.0f && frexpf(x, &e) == 0.5f;
+}
+
+// Chunk length: the largest power of two <= T that still yields >= 2 waves of warps (148 SMs x 24 resident warps).
+static int pair_loss_chunk(int B, int T) {
+    int C = 1;
+    while (C * 2 <= T) C *= 2;
+    while (C > 1 && (long long)B * ((T + C - 1) / C) < 2LL * 148 * 24) C /= 2;
+    return C;
+}
+
+// returns PDEC_OK if it handled the call, 1 if the shape is not eligible (caller uses the general kernel)
+int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials, int T, int B, int n, int mode, double dt, double viscosity,
+                                float lower, float size, int substeps, int resubstep, float gl2, float gl1, int* nchunks_out,
+                                cudaStream_t st) {
+    if (n != 128 || (resubstep && substeps > 1)) return 1;
+    if ((reinterpret_cast<uintptr_t>(s) & 15u) || (grad_s && (reinterpret_cast<uintptr_t>(grad_s) & 15u))) return 1;
+    FastP p;
+    p.mode = mode; p.substeps = substeps;
+    p.dt = (float)dt; p.lower = lower; p.size = size; p.nf = 128.0f; p.hi = 127.0f;
+    p.a = (float)(dt * viscosity / (double)substeps);
+    const double dx = (double)size / 128.0;
+    p.dx2 = (float)(dx * dx);
+    p.inv_size = 1.0f / size;
+    p.inv_dx2 = 1.0f / p.dx2;
+    p.c2 = (float)((double)p.a * substeps / (double)p.dx2);
+    p.dxi_du = -(p.nf / size) * p.dt;
+    const float invB = 1.0f / (float)B;
+    p.gl2 = gl2 * invB; p.gl1 = gl1 * invB;
+    const bool exact = is_pow2f(size) && is_pow2f(p.dx2);
+    const int C = pair_loss_chunk(B, T), nchunks = (T + C - 1) / C;
+    *nchunks_out = nchunks;
+    const long long units = (long long)B * nchunks;
+    long long grid = (units + 7) / 8;
+    if (grid > 148LL * 64) grid = 148LL * 64;
+    const bool l1 = gl1 != 0.0f;
+#define LAUNCH(M, E, L) burgers_pair_loss_fast_kernel<M, E, L><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, C, nchunks)
+#define PICK(M)                                                            \
+    do {                                                                   \
+        if (exact) { if (l1) LAUNCH(M, true, true); else LAUNCH(M, true, false); }   \
+        else { if (l1) LAUNCH(M, false, true); else LAUNCH(M, false, false); }       \
+    } while (0)
+    if (mode == PDEC_MODE_CONSTANT) PICK(PDEC_MODE_CONSTANT);
+    else if (mode == PDEC_MODE_REPLICATE) PICK(PDEC_MODE_REPLICATE);
+    else PICK(PDEC_MODE_CIRCULAR);
+#undef PICK
+#undef LAUNCH
+    return cudaPeekAtLastError() == cudaSuccess ? PDEC_OK : PDEC_ERR_CUDA_LAUNCH;
+}
