@@ -1,5 +1,7 @@
 // burgers_fast.cu -- register-resident fused force-loss kernel for rows of exactly 128 cells (BASELINE configs 2 and 4).
-// SURVEY row B5 / K-B3; compiled with -fmad=false like burgers.cu (same fp32 operation order in the forward step).
+// SURVEY row B5 / K-B3.  Compiled WITH fma contraction: the forward step spells its fp32 operation order out with
+// __fmul_rn / __fadd_rn / __fsub_rn (never contracted: same rounding sequence as the reference and as burgers.cu), while the
+// adjoint and the loss sums -- compared at 1e-3 -- may use FMA.
 //
 // Work unit = (batch row b, chunk of C consecutive frame pairs); one WARP per unit, lane l owns the four cells 4l..4l+3:
 //   * every frame row moves between HBM and registers as ONE 16-byte load / store per lane (512 B per warp instruction);
@@ -33,9 +35,10 @@ __device__ __forceinline__ int skew(int j) { return j + (j >> 5); }
 
 template <bool EXACT>
 __device__ __forceinline__ float to_index(const FastP& p, float x0, float u) {
-    const float x = x0 - u * p.dt;                                   // advect.py:35
-    const float local = EXACT ? (x - p.lower) * p.inv_size : (x - p.lower) / p.size;   // _box.py:50-52
-    return local * p.nf - 0.5f;                                      // grid.py:104-105
+    const float x = __fsub_rn(x0, __fmul_rn(u, p.dt));               // advect.py:35
+    const float rel = __fsub_rn(x, p.lower);
+    const float local = EXACT ? __fmul_rn(rel, p.inv_size) : __fdiv_rn(rel, p.size);   // _box.py:50-52
+    return __fsub_rn(__fmul_rn(local, p.nf), 0.5f);                  // grid.py:104-105
 }
 
 // neighbours of the lane's 4 cells: left of cell 0 and right of cell 3 come from the adjacent lanes
@@ -61,7 +64,7 @@ struct Gathered {                    // what the forward step leaves behind for 
 };
 
 // one forward step of the row held in u[] (and mirrored in shared memory su[] by the caller) -> v[]
-template <int MODE, bool EXACT>
+template <int MODE, bool EXACT, int SUBSTEPS>
 __device__ __forceinline__ void fast_forward(const FastP& p, const float (&x0)[4], const float (&u)[4], const float* su, int lane,
                                              float (&v)[4], Gathered& G) {
     float adv[4];
@@ -76,7 +79,7 @@ __device__ __forceinline__ void fast_forward(const FastP& p, const float (&x0)[4
         G.pf[k] = skew(fi);
         G.pc[k] = skew(ci);
         const float sf = su[G.pf[k]], sc = su[G.pc[k]];
-        adv[k] = sf * G.w1[k] + sc * G.w0[k];                         // tf_backend.py:491-497
+        adv[k] = __fadd_rn(__fmul_rn(sf, G.w1[k]), __fmul_rn(sc, G.w0[k]));     // tf_backend.py:491-497
         G.du[k] = sc - sf;
         if (MODE != PDEC_MODE_CONSTANT || fi != ci) G.active |= 1u << k;
     }
@@ -85,10 +88,12 @@ __device__ __forceinline__ void fast_forward(const FastP& p, const float (&x0)[4
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const float lo = k == 0 ? left : adv[k - 1], up = k == 3 ? right : adv[k + 1];
-        const float raw = up + lo - 2.0f * adv[k];                    // nd.py:281-282
-        const float lap = EXACT ? raw * p.inv_dx2 : raw / p.dx2;      // grid.py:190
+        const float raw = __fsub_rn(__fadd_rn(up, lo), __fmul_rn(2.0f, adv[k]));   // nd.py:281-282
+        const float lap = EXACT ? __fmul_rn(raw, p.inv_dx2) : __fdiv_rn(raw, p.dx2);   // grid.py:190
+        const float inc = __fmul_rn(p.a, lap);
         float r = adv[k];
-        for (int s = 0; s < p.substeps; ++s) r = r + p.a * lap;       // util.py:41-43, TF semantics
+        if (SUBSTEPS == 1) r = __fadd_rn(r, inc);
+        else for (int s = 0; s < p.substeps; ++s) r = __fadd_rn(r, inc);    // util.py:41-43, TF semantics
         v[k] = r;
     }
 }
@@ -141,7 +146,7 @@ __device__ __forceinline__ void row_to_smem(float* su, const float (&u)[4], int 
     __syncwarp();
 }
 
-template <int MODE, bool EXACT, bool L1TERM>
+template <int MODE, bool EXACT, bool L1TERM, int SUBSTEPS>
 __global__ void __launch_bounds__(256) burgers_pair_loss_fast_kernel(FastP p, const float* __restrict__ s, float* __restrict__ grad_s,
                                                                       float2* __restrict__ partials, int T, int B, int C, int nchunks) {
     __shared__ float smem[8][2][FAST_ROW];
@@ -152,7 +157,7 @@ __global__ void __launch_bounds__(256) burgers_pair_loss_fast_kernel(FastP p, co
     __syncwarp();
     float x0[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) x0[k] = cell_center_local(4 * lane + k, 128) * p.size + p.lower;
+    for (int k = 0; k < 4; ++k) x0[k] = __fadd_rn(__fmul_rn(cell_center_local(4 * lane + k, 128), p.size), p.lower);
     const size_t fstride = (size_t)B * 128;
     const long long units = (long long)B * nchunks;
     for (long long unit = (long long)blockIdx.x * 8 + warp; unit < units; unit += (long long)gridDim.x * 8) {
@@ -173,7 +178,7 @@ __global__ void __launch_bounds__(256) burgers_pair_loss_fast_kernel(FastP p, co
             const float4 q = row[(size_t)(t0 - 1) * f4];
             float w[4] = {q.x, q.y, q.z, q.w};
             row_to_smem(su, w, lane);
-            fast_forward<MODE, EXACT>(p, x0, w, su, lane, v, G);
+            fast_forward<MODE, EXACT, SUBSTEPS>(p, x0, w, su, lane, v, G);
             __syncwarp();
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -188,7 +193,7 @@ __global__ void __launch_bounds__(256) burgers_pair_loss_fast_kernel(FastP p, co
             nxt[0] = pre.x; nxt[1] = pre.y; nxt[2] = pre.z; nxt[3] = pre.w;
             if (t + 2 <= T) pre = row[(size_t)(t + 2) * f4];       // prefetch: in flight during this pair's arithmetic
             row_to_smem(su, u, lane);
-            fast_forward<MODE, EXACT>(p, x0, u, su, lane, v, G);
+            fast_forward<MODE, EXACT, SUBSTEPS>(p, x0, u, su, lane, v, G);
             float gd[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -257,7 +262,11 @@ int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials,
     long long grid = (units + 7) / 8;
     if (grid > 148LL * 64) grid = 148LL * 64;
     const bool l1 = gl1 != 0.0f;
-#define LAUNCH(M, E, L) burgers_pair_loss_fast_kernel<M, E, L><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, C, nchunks)
+#define LAUNCH(M, E, L)                                                                                                   \
+    do {                                                                                                                  \
+        if (substeps == 1) burgers_pair_loss_fast_kernel<M, E, L, 1><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, C, nchunks); \
+        else burgers_pair_loss_fast_kernel<M, E, L, 0><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, C, nchunks);             \
+    } while (0)
 #define PICK(M)                                                            \
     do {                                                                   \
         if (exact) { if (l1) LAUNCH(M, true, true); else LAUNCH(M, true, false); }   \
