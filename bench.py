@@ -100,6 +100,8 @@ class BurgersWorkload:
     name = "burgers_pair_loss res=128 T=32 B=4096/gpu (BASELINE config 2: force loss fwd+adjoint)"
     algorithmic_bytes_per_cell_update = 8.0     # read each frame once + write its gradient once
     dtype = "f32"
+    dominant_kernel = "burgers_pair_loss_fast_kernel"
+    ncu_traffic_bytes = 96.4e6      # dram read 69.3 MB + write 27.1 MB per launch, profiles/r1c_burgers_pair_loss_fast_summary.md
 
     def __init__(self, device, rank, B=4096, n=128, T=32):
         import torch
@@ -299,7 +301,7 @@ def run_b200(args):
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": getattr(wl, "ncu_traffic_bytes", None), "peak_source": peak_src,
                              "algorithmic_bytes_per_cell_update": wl.algorithmic_bytes_per_cell_update,
-                             "kernel": getattr(wl, "dominant_kernel", "burgers_pair_loss_kernel")}}
+                             "kernel": wl.dominant_kernel}}
         if hasattr(wl, "extra"):
             line["extra"] = wl.extra()
         if world == 1 and not args.no_cpu:
