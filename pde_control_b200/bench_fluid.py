@@ -20,7 +20,7 @@ def _smooth(rng, shape, scale, passes=6):
 class FluidWorkload:
     name = "incompressible_flow 128x128 steps=16 B=64/gpu OPEN (BASELINE config 3: projected step + CG + adjoint)"
     dtype = "f32"
-    dominant_kernel = "cg_tile_kernel"
+    dominant_kernel = "cg_block_kernel"
     ncu_traffic_bytes = 4.23e6      # dram read per launch (rhs); the solution is still in L2 at kernel end, profiles/r1b_fluid_summary.md
     cpu_sample_batch = 2
     STEPS, N, B = 16, 128, 64

@@ -311,6 +311,271 @@ __global__ void __launch_bounds__(32 * TY, 1) cg_tile_kernel(const float* __rest
 }
 
 // -------------------------------------------------------------------------------------------------------------
+// cg_block_kernel: production one-CTA-per-element kernel for grids up to 128 x 128 (second generation).
+// cg_tile_kernel is bound by shared-memory instruction issue (88 LDS/STS per thread and iteration + 40 reduction shuffles on
+// 32 warps).  Here a thread owns a BLOCK of 8 rows x 4 consecutive columns (cells i = 8*warp + ky, j = 4*lane + kx):
+//   * r, Am, m of the 32 cells stay in registers (96 registers; 16 warps x 128 registers fill the register file);
+//   * left/right neighbours come from registers or ONE shuffle per row and side; up/down neighbours from registers except
+//     the block's first/last row, which read the neighbouring warp's edge row from shared memory (2 LDS.128 per thread);
+//     only those two edge rows are ever published (2 STS.128);
+//   * x is the one vector that does not fit the register file: it lives in shared memory as float4 (8 LDS.128 + 8 STS.128);
+//   * out-of-domain neighbours contribute 0 and the diagonal carries the boundary rule (-4 open; -(in-domain neighbours)
+//     closed, sparse.py:151-221), so there are no ghost cells to maintain;
+//   * both block reductions carry two values in ONE butterfly (the half-warps reduce different values: 5 shuffles), and the
+//     second stage reads the 2 x WARPS partials with one LDS per lane.
+// Per iteration: 3 barriers, ~24 shuffles, 20 128-bit shared-memory accesses and ~11 FP32 instructions per cell.
+// -------------------------------------------------------------------------------------------------------------
+template <int WARPS>
+__device__ __forceinline__ void block_reduce_pair(float& a, float& b, float* red, const bool second_is_max) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const bool hi = lane >= 16;
+    const bool mx = hi && second_is_max;
+    float keep = hi ? b : a;
+    float recv = __shfl_xor_sync(0xffffffffu, hi ? a : b, 16);
+    keep = mx ? fmaxf(keep, recv) : keep + recv;
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) {
+        recv = __shfl_xor_sync(0xffffffffu, keep, o);
+        keep = mx ? fmaxf(keep, recv) : keep + recv;
+    }
+    if ((lane & 15) == 0) red[(lane >> 4) * 16 + w] = keep;
+    __syncthreads();
+    float v = (lane & 15) < WARPS ? red[lane] : 0.0f;       // lane = value * 16 + warp
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) {
+        recv = __shfl_xor_sync(0xffffffffu, v, o);
+        v = mx ? fmaxf(v, recv) : v + recv;
+    }
+    recv = __shfl_xor_sync(0xffffffffu, v, 16);
+    a = hi ? recv : v;
+    b = hi ? v : recv;
+}
+
+// Four sums and one maximum in ONE block reduction (one barrier).  Stage 1 is a transposing butterfly: at xor 16 the half-warps
+// trade two of the four sums, at xor 8 one of the remaining two, so lanes 0/8/16/24 end up with the warp totals of s1/s2/s4/s5
+// after 6 shuffles (+5 for the maximum).  Stage 2: lane (h, w') sums the partials of warp w' for (s1|s2, s4|s5, max), a 16-lane
+// butterfly, then the half-warps swap.  Every lane of every warp gets bit-identical totals (fixed order, commutative pairs).
+template <int WARPS>
+__device__ __forceinline__ void block_reduce5(float& s1, float& s2, float& s4, float& s5, float& mx, float* red /* [5][16] */) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const bool h16 = (lane & 16) != 0, h8 = (lane & 8) != 0;
+    float k0 = h16 ? s4 : s1, k1 = h16 ? s5 : s2;
+    k0 += __shfl_xor_sync(0xffffffffu, h16 ? s1 : s4, 16);
+    k1 += __shfl_xor_sync(0xffffffffu, h16 ? s2 : s5, 16);
+    float keep = h8 ? k1 : k0;
+    keep += __shfl_xor_sync(0xffffffffu, h8 ? k0 : k1, 8);
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) keep += __shfl_xor_sync(0xffffffffu, keep, o);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((lane & 7) == 0) red[(lane >> 3) * 16 + w] = keep;
+    if (lane == 1) red[64 + w] = mx;
+    __syncthreads();
+    const int wq = lane & 15, h = lane >> 4;
+    float A = 0.0f, B = 0.0f, C = 0.0f;
+    if (wq < WARPS) { A = red[h * 16 + wq]; B = red[(2 + h) * 16 + wq]; C = red[64 + wq]; }
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) {
+        A += __shfl_xor_sync(0xffffffffu, A, o);
+        B += __shfl_xor_sync(0xffffffffu, B, o);
+        C = fmaxf(C, __shfl_xor_sync(0xffffffffu, C, o));
+    }
+    const float A2 = __shfl_xor_sync(0xffffffffu, A, 16), B2 = __shfl_xor_sync(0xffffffffu, B, 16);
+    s1 = h ? A2 : A; s2 = h ? A : A2;
+    s4 = h ? B2 : B; s5 = h ? B : B2;
+    mx = C;
+}
+
+template <int WARPS, bool FULL, bool FUSED>
+__global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __restrict__ rhs, const float* __restrict__ guess, float* __restrict__ out,
+                                                                 int* __restrict__ iters, float* __restrict__ resid, int ny, int nx, int closed,
+                                                                 float accuracy, int max_it) {
+    constexpr int ROWS = 8 * WARPS;
+    extern __shared__ __align__(16) float smem_dyn[];
+    __shared__ float redA[32], redB[32], red5[2][80];
+    float4* sm_x = reinterpret_cast<float4*>(smem_dyn);          // [ROWS][32] float4 (row pitch 128 floats)
+    float4* sm_e = sm_x + ROWS * 32;                            // [2*WARPS + 2][32]: 0 = zeros, 1+2w / 2+2w = first / last row of warp w
+    const int tx = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int i0 = 8 * w, j0 = 4 * tx;
+    const size_t base = (size_t)blockIdx.x * ny * nx;
+    float r[32], am[32], m[32];
+    unsigned valid = 0u;
+    // diagonal = dcol[kx] + drow[ky]
+    float dcol[4], drow[8];
+    const float cf = closed ? 1.0f : 0.0f;
+#pragma unroll
+    for (int kx = 0; kx < 4; ++kx) dcol[kx] = -4.0f + cf * ((j0 + kx == 0 ? 1.0f : 0.0f) + (j0 + kx == nx - 1 ? 1.0f : 0.0f));
+#pragma unroll
+    for (int ky = 0; ky < 8; ++ky) drow[ky] = cf * ((i0 + ky == 0 ? 1.0f : 0.0f) + (i0 + ky == ny - 1 ? 1.0f : 0.0f));
+    const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    for (int q = threadIdx.x; q < (2 * WARPS + 2) * 32; q += 32 * WARPS) sm_e[q] = zero4;
+#pragma unroll
+    for (int ky = 0; ky < 8; ++ky) {
+        float4 g4 = zero4, r4 = zero4;
+        if (FULL) {
+            r4 = *reinterpret_cast<const float4*>(rhs + base + (size_t)(i0 + ky) * nx + j0);
+            if (guess != nullptr) g4 = *reinterpret_cast<const float4*>(guess + base + (size_t)(i0 + ky) * nx + j0);
+        } else {
+            float rv[4] = {0.0f, 0.0f, 0.0f, 0.0f}, gv[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx)
+                if (i0 + ky < ny && j0 + kx < nx) {
+                    valid |= 1u << (ky * 4 + kx);
+                    rv[kx] = rhs[base + (size_t)(i0 + ky) * nx + j0 + kx];
+                    if (guess != nullptr) gv[kx] = guess[base + (size_t)(i0 + ky) * nx + j0 + kx];
+                }
+            r4 = make_float4(rv[0], rv[1], rv[2], rv[3]);
+            g4 = make_float4(gv[0], gv[1], gv[2], gv[3]);
+        }
+        r[ky * 4 + 0] = r4.x; r[ky * 4 + 1] = r4.y; r[ky * 4 + 2] = r4.z; r[ky * 4 + 3] = r4.w;
+        m[ky * 4 + 0] = g4.x; m[ky * 4 + 1] = g4.y; m[ky * 4 + 2] = g4.z; m[ky * 4 + 3] = g4.w;
+        sm_x[(i0 + ky) * 32 + tx] = g4;
+    }
+    __syncthreads();                         // zero-fill of the edge rows completes before anyone publishes
+    auto publish = [&]() {                   // the block's first and last row, read by the warps above / below
+        sm_e[(1 + 2 * w) * 32 + tx] = make_float4(m[0], m[1], m[2], m[3]);
+        sm_e[(2 + 2 * w) * 32 + tx] = make_float4(m[28], m[29], m[30], m[31]);
+    };
+    auto matvec = [&]() {
+        const float4 u4 = sm_e[(2 * w) * 32 + tx], d4 = sm_e[(2 * w + 3) * 32 + tx];
+        const float upv[4] = {u4.x, u4.y, u4.z, u4.w}, dnv[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+        for (int ky = 0; ky < 8; ++ky) {
+            float left = __shfl_up_sync(0xffffffffu, m[ky * 4 + 3], 1);
+            float right = __shfl_down_sync(0xffffffffu, m[ky * 4 + 0], 1);
+            if (tx == 0) left = 0.0f;
+            if (tx == 31) right = 0.0f;
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx) {
+                const int c = ky * 4 + kx;
+                const float u = ky > 0 ? m[c >= 4 ? c - 4 : 0] : upv[kx];
+                const float d = ky < 7 ? m[c + 4 <= 31 ? c + 4 : 31] : dnv[kx];
+                const float l = kx > 0 ? m[c >= 1 ? c - 1 : 0] : left;
+                const float rr = kx < 3 ? m[c + 1 <= 31 ? c + 1 : 31] : right;
+                float dg;
+                if (FULL && kx > 0 && kx < 3 && ky > 0 && ky < 7) dg = -4.0f;
+                else if (FULL && kx > 0 && kx < 3) dg = -4.0f + drow[ky];
+                else if (FULL && ky > 0 && ky < 7) dg = dcol[kx];
+                else dg = dcol[kx] + drow[ky];
+                const float val = (u + l) + (rr + d) + dg * m[c];
+                am[c] = (FULL || (valid & (1u << c))) ? val : 0.0f;
+            }
+        }
+    };
+    if (guess != nullptr) {                  // momentum = k - A x0   (blas.py:24-26); m holds x0 here
+        publish();
+        __syncthreads();
+        matvec();
+#pragma unroll
+        for (int c = 0; c < 32; ++c) r[c] -= am[c];
+        __syncthreads();                     // x0 edge rows read before the first real publish
+    }
+    float rmax = 0.0f;
+    int it = 0;
+    if (FUSED) {
+        // One reduction per iteration.  With q = A m:  a = (m.r)/(m.q) and, since r' = r - a q,
+        //   beta = (r'.q)/(m.q) = ((r.q) - a (q.q))/(m.q)
+        // so all four dot products are taken BEFORE the update and travel with max|r| (the stop test of blas.py:33-37, applied
+        // to the current residual exactly as the two-reduction loop does).  The coefficients differ from the reference's by
+        // rounding only; CG iterates are not the parity oracle, the solution is.
+#pragma unroll
+        for (int c = 0; c < 32; ++c) m[c] = r[c];
+        publish();
+        __syncthreads();
+        matvec();
+        while (true) {
+            float p1[4] = {0.0f, 0.0f, 0.0f, 0.0f}, p2[4] = {0.0f, 0.0f, 0.0f, 0.0f}, p4[4] = {0.0f, 0.0f, 0.0f, 0.0f},
+                  p5[4] = {0.0f, 0.0f, 0.0f, 0.0f}, pm[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+            for (int c = 0; c < 32; ++c) {
+                p1[c & 3] += m[c] * am[c];
+                p2[c & 3] += m[c] * r[c];
+                p4[c & 3] += r[c] * am[c];
+                p5[c & 3] += am[c] * am[c];
+                pm[c & 3] = fmaxf(pm[c & 3], fabsf(r[c]));
+            }
+            float s1 = (p1[0] + p1[1]) + (p1[2] + p1[3]), s2 = (p2[0] + p2[1]) + (p2[2] + p2[3]);
+            float s4 = (p4[0] + p4[1]) + (p4[2] + p4[3]), s5 = (p5[0] + p5[1]) + (p5[2] + p5[3]);
+            float mx = fmaxf(fmaxf(pm[0], pm[1]), fmaxf(pm[2], pm[3]));
+            block_reduce5<WARPS>(s1, s2, s4, s5, mx, red5[it & 1]);
+            rmax = mx;
+            if (!(it < max_it && (accuracy <= 0.0f || rmax >= accuracy))) break;
+            const float a = div_no_nan(s2, s1);
+            const float beta = div_no_nan(s4 - a * s5, s1);
+#pragma unroll
+            for (int ky = 0; ky < 8; ++ky) {
+                float4 x4 = sm_x[(i0 + ky) * 32 + tx];
+                x4.x += a * m[ky * 4 + 0]; x4.y += a * m[ky * 4 + 1]; x4.z += a * m[ky * 4 + 2]; x4.w += a * m[ky * 4 + 3];
+                sm_x[(i0 + ky) * 32 + tx] = x4;
+#pragma unroll
+                for (int kx = 0; kx < 4; ++kx) {
+                    const int c = ky * 4 + kx;
+                    r[c] -= a * am[c];
+                    m[c] = r[c] - beta * m[c];
+                }
+            }
+            publish();                       // edge-row reads of the old m finished before the reduction's barrier
+            __syncthreads();
+            matvec();
+            ++it;
+        }
+    } else {
+        float dummy = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) { m[c] = r[c]; rmax = fmaxf(rmax, fabsf(r[c])); }
+        publish();
+        block_reduce_pair<WARPS>(dummy, rmax, redB, true);      // its barrier also orders publish before the matvec
+        matvec();
+        while (it < max_it && (accuracy <= 0.0f || rmax >= accuracy)) {
+            float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+            for (int c = 0; c < 32; ++c) { s1 += m[c] * am[c]; s2 += m[c] * r[c]; }
+            block_reduce_pair<WARPS>(s1, s2, redA, false);
+            const float tmp = s1, a = div_no_nan(s2, tmp);
+            float s3 = 0.0f, mx = 0.0f;
+#pragma unroll
+            for (int ky = 0; ky < 8; ++ky) {
+                float4 x4 = sm_x[(i0 + ky) * 32 + tx];
+                x4.x += a * m[ky * 4 + 0]; x4.y += a * m[ky * 4 + 1]; x4.z += a * m[ky * 4 + 2]; x4.w += a * m[ky * 4 + 3];
+                sm_x[(i0 + ky) * 32 + tx] = x4;
+#pragma unroll
+                for (int kx = 0; kx < 4; ++kx) {
+                    const int c = ky * 4 + kx;
+                    r[c] -= a * am[c];
+                    s3 += r[c] * am[c];
+                    mx = fmaxf(mx, fabsf(r[c]));
+                }
+            }
+            block_reduce_pair<WARPS>(s3, mx, redB, true);
+            const float beta = div_no_nan(s3, tmp);
+#pragma unroll
+            for (int c = 0; c < 32; ++c) m[c] = r[c] - beta * m[c];
+            publish();                       // every edge-row read of the old m happened before reduction A's barrier
+            __syncthreads();
+            matvec();
+            rmax = mx;
+            ++it;
+        }
+    }
+#pragma unroll
+    for (int ky = 0; ky < 8; ++ky) {
+        const float4 x4 = sm_x[(i0 + ky) * 32 + tx];
+        if (FULL) {
+            *reinterpret_cast<float4*>(out + base + (size_t)(i0 + ky) * nx + j0) = x4;
+        } else {
+            const float xv[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx)
+                if (valid & (1u << (ky * 4 + kx))) out[base + (size_t)(i0 + ky) * nx + j0 + kx] = xv[kx];
+        }
+    }
+    if (threadIdx.x == 0) {
+        if (iters) iters[blockIdx.x] = it;
+        if (resid) resid[blockIdx.x] = rmax;
+    }
+}
+
+// -------------------------------------------------------------------------------------------------------------
 // Large grids: cooperative persistent kernel, vectors in global memory (L2 resident up to ~20 MB per vector).
 // Unit of work = (batch element b, chunk c of consecutive cells); blocks take units grid-stride.
 // Per iteration TWO passes separated by grid-wide barriers:
@@ -324,7 +589,7 @@ __global__ void __launch_bounds__(32 * TY, 1) cg_tile_kernel(const float* __rest
 struct CgGlobal {
     const float* rhs; const float* guess; float* x; float* r; float* m[2]; float* am; float* part;
     int* iters; float* resid; int* count;
-    int B, ny, nx, closed, chunks, max_it;
+    int B, ny, nx, closed, chunks, max_it, whole_batch;
     float accuracy;
 };
 
@@ -412,7 +677,7 @@ __global__ void __launch_bounds__(256) cg_global_kernel(CgGlobal P) {
         for (int u = blockIdx.x; u < units; u += gridDim.x) {
             const int b = u / P.chunks, c = u - b * P.chunks;
             const float rmax = reduce_chunks_max(part_ptr(P, prev, S_MAX, b), P.chunks, sh);
-            if (P.accuracy > 0.0f && rmax < P.accuracy) continue;
+            if (!P.whole_batch && P.accuracy > 0.0f && rmax < P.accuracy) continue;
             const float t_prev = reduce_chunks_sum(part_ptr(P, prev, S_MAM, b), P.chunks, sh);
             const float s3 = reduce_chunks_sum(part_ptr(P, prev, S_RAM, b), P.chunks, sh);
             const size_t base = (size_t)b * N;
@@ -448,7 +713,7 @@ __global__ void __launch_bounds__(256) cg_global_kernel(CgGlobal P) {
         for (int u = blockIdx.x; u < units; u += gridDim.x) {
             const int b = u / P.chunks, c = u - b * P.chunks;
             const float rmax = reduce_chunks_max(part_ptr(P, prev, S_MAX, b), P.chunks, sh);
-            if (P.accuracy > 0.0f && rmax < P.accuracy) {       // converged earlier: carry its state forward
+            if (!P.whole_batch && P.accuracy > 0.0f && rmax < P.accuracy) {       // converged earlier: carry its state forward
                 if (threadIdx.x == 0) {
                     part_ptr(P, cur, S_MAX, b)[c] = part_ptr(P, prev, S_MAX, b)[c];
                     part_ptr(P, cur, S_MAM, b)[c] = 0.0f;
@@ -506,7 +771,6 @@ static int global_chunks(int N) {
 
 extern "C" size_t pdec_cg_poisson_2d_workspace_bytes(int B, int ny, int nx) {
     const size_t N = (size_t)ny * nx, b = B > 0 ? B : 1;
-    if (N <= PDEC_CG_SMEM_MAX_CELLS) return 256;
     // r, m[2], Am + 2 parities x 4 partial slots + iteration counters
     return 4 * b * N * sizeof(float) + 8 * b * global_chunks((int)N) * sizeof(float) + b * sizeof(int) + 1024;
 }
@@ -529,6 +793,20 @@ static int launch_tile(const float* rhs, const float* guess, float* p, int* iter
     return launch_tile_<TY, false>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
 }
 
+template <int WARPS>
+static int launch_block(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
+                        int closed, float accuracy, int max_iterations, cudaStream_t st, bool fused) {
+    const size_t smem = (size_t)(8 * WARPS * 32 + (2 * WARPS + 2) * 32) * sizeof(float4);
+    const bool full = ny == 8 * WARPS && nx == 128 && (reinterpret_cast<uintptr_t>(rhs) & 15) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0 &&
+                      (guess == nullptr || (reinterpret_cast<uintptr_t>(guess) & 15) == 0);
+    auto kernel = fused ? (full ? cg_block_kernel<WARPS, true, true> : cg_block_kernel<WARPS, false, true>)
+                        : (full ? cg_block_kernel<WARPS, true, false> : cg_block_kernel<WARPS, false, false>);
+    if (smem > 48 * 1024 && cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return PDEC_ERR_CUDA_LAUNCH;
+    kernel<<<B, 32 * WARPS, smem, st>>>(rhs, guess, p, iterations, residual, ny, nx, closed, accuracy, max_iterations);
+    return PDEC_OK;
+}
+
 template <int THREADS, int CPT = 16>
 static int launch_smem(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
                        int closed, float accuracy, int max_iterations, cudaStream_t st) {
@@ -547,15 +825,29 @@ extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p
     const int variant = (stop_mode >> 8) & 0xff;      // experimental kernel-shape selector (benchmarks only)
     stop_mode &= 0xff;
     if (stop_mode != PDEC_CG_STOP_PER_ELEMENT && stop_mode != PDEC_CG_STOP_WHOLE_BATCH) return PDEC_ERR_INVALID_ARGUMENT;
-    if (stop_mode == PDEC_CG_STOP_WHOLE_BATCH && accuracy > 0.0f && B > 1) return PDEC_ERR_UNSUPPORTED_SIZE;
+    // the reference's rule (all elements iterate until the batch-wide max|r| < accuracy, blas.py:33-37) needs a batch-wide
+    // exchange every iteration: it runs on the cooperative kernel, whatever the grid size
+    const bool whole_batch = stop_mode == PDEC_CG_STOP_WHOLE_BATCH && accuracy > 0.0f && B > 1;
     if (B == 0) return PDEC_OK;
     if (!rhs || !p) return PDEC_ERR_INVALID_ARGUMENT;
-    if (workspace_bytes < pdec_cg_poisson_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+    const bool on_chip = !whole_batch && (long long)ny * nx <= PDEC_CG_SMEM_MAX_CELLS;
+    if (!on_chip && workspace_bytes < pdec_cg_poisson_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
     cudaStream_t st = (cudaStream_t)stream;
     closed = closed ? 1 : 0;
     const long long N = (long long)ny * nx;
     int rc = PDEC_OK;
-    if (ny <= 128 && nx <= 128 && variant == 0) {
+    if (on_chip && ny <= 128 && nx <= 128 && (variant == 0 || variant == 4 || variant == 5)) {
+        // one-reduction loop wins while the iteration is latency-bound (<= 8 warps); at 16 warps the iteration is
+        // throughput-bound and the extra dot product costs more than the barrier it saves (profiles/r1e_*)
+        const bool fused = variant == 0 ? ny <= 64 : variant == 5;
+        if (ny > 64) rc = launch_block<16>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st, fused);
+        else if (ny > 32) rc = launch_block<8>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st, fused);
+        else rc = launch_block<4>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st, fused);
+        if (rc != PDEC_OK) return rc;
+        PDEC_CHECK_LAUNCH();
+        return PDEC_OK;
+    }
+    if (on_chip && ny <= 128 && nx <= 128 && variant == 3) {
         if (ny > 64) rc = launch_tile<32>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
         else if (ny > 32) rc = launch_tile<16>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
         else rc = launch_tile<8>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
@@ -563,7 +855,7 @@ extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p
         PDEC_CHECK_LAUNCH();
         return PDEC_OK;
     }
-    if (N <= PDEC_CG_SMEM_MAX_CELLS) {
+    if (on_chip) {
         if (N > 8192 && variant == 1) rc = launch_smem<512, 32>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
         else if (N > 8192) rc = launch_smem<1024>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
         else if (N > 4096) rc = launch_smem<512>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
@@ -584,6 +876,7 @@ extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p
     P.count = reinterpret_cast<int*>(P.part + (size_t)8 * B * P.chunks);
     P.iters = iterations; P.resid = residual;
     P.B = B; P.ny = ny; P.nx = nx; P.closed = closed; P.max_it = max_iterations; P.accuracy = accuracy;
+    P.whole_batch = whole_batch ? 1 : 0;
     int dev = 0, sms = 148, per_sm = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

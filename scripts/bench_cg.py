@@ -16,8 +16,8 @@ for B, n in ((64, 128), (148, 128), (296, 128), (64, 64)):
     out = torch.empty_like(rhs)
     it = torch.zeros(B, dtype=torch.int32, device="cuda")
     res = torch.zeros(B, device="cuda")
-    for variant, name in ((0, "tile"), (2, "smem1024x16"), (1, "smem512x32")):
-        if n != 128 and variant: continue
+    for variant, name in ((0, "block"), (5, "block-fused"), (4, "block-2red"), (3, "tile")):
+        if B > 148 and variant: continue
         for closed in (False, True):
             for acc, mi in ((1e-5, 2000), (0.0, 200)):
                 args = (rhs, out, closed, acc, mi, None, it, res, variant << 8)
