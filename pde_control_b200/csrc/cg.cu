@@ -340,15 +340,37 @@ __device__ __forceinline__ void block_reduce_pair(float& a, float& b, float* red
     }
     if ((lane & 15) == 0) red[(lane >> 4) * 16 + w] = keep;
     __syncthreads();
-    float v = (lane & 15) < WARPS ? red[lane] : 0.0f;       // lane = value * 16 + warp
+    if (WARPS >= 16) {      // throughput-bound iteration: one LDS + five shuffles per lane
+        float v = red[lane];                                  // lane = value * 16 + warp
 #pragma unroll
-    for (int o = 8; o > 0; o >>= 1) {
-        recv = __shfl_xor_sync(0xffffffffu, v, o);
-        v = mx ? fmaxf(v, recv) : v + recv;
+        for (int o = 8; o > 0; o >>= 1) {
+            recv = __shfl_xor_sync(0xffffffffu, v, o);
+            v = mx ? fmaxf(v, recv) : v + recv;
+        }
+        recv = __shfl_xor_sync(0xffffffffu, v, 16);
+        a = hi ? recv : v;
+        b = hi ? v : recv;
+        return;
     }
-    recv = __shfl_xor_sync(0xffffffffu, v, 16);
-    a = hi ? recv : v;
-    b = hi ? v : recv;
+    // latency-bound iteration (<= 8 warps): every lane reads all 2 x WARPS partials (broadcast LDS.128) and adds them in a fixed
+    // tree -- ~45 cycles instead of five dependent shuffles; bit-identical totals in every lane of every warp
+    const float4* r4 = reinterpret_cast<const float4*>(red);
+    float ta[WARPS / 4], tb[WARPS / 4];
+#pragma unroll
+    for (int q = 0; q < WARPS / 4; ++q) {
+        const float4 va = r4[q], vb = r4[4 + q];
+        ta[q] = (va.x + va.y) + (va.z + va.w);
+        tb[q] = second_is_max ? fmaxf(fmaxf(vb.x, vb.y), fmaxf(vb.z, vb.w)) : (vb.x + vb.y) + (vb.z + vb.w);
+    }
+#pragma unroll
+    for (int q = WARPS / 4; q > 1; q >>= 1)
+#pragma unroll
+        for (int k = 0; k < q / 2; ++k) {
+            ta[k] = ta[2 * k] + ta[2 * k + 1];
+            tb[k] = second_is_max ? fmaxf(tb[2 * k], tb[2 * k + 1]) : tb[2 * k] + tb[2 * k + 1];
+        }
+    a = ta[0];
+    b = tb[0];
 }
 
 // Four sums and one maximum in ONE block reduction (one barrier).  Stage 1 is a transposing butterfly: at xor 16 the half-warps
@@ -392,7 +414,7 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
                                                                  float accuracy, int max_it) {
     constexpr int ROWS = 8 * WARPS;
     extern __shared__ __align__(16) float smem_dyn[];
-    __shared__ float redA[32], redB[32], red5[2][80];
+    __shared__ __align__(16) float redA[32], redB[32], red5[2][80];
     float4* sm_x = reinterpret_cast<float4*>(smem_dyn);          // [ROWS][32] float4 (row pitch 128 floats)
     float4* sm_e = sm_x + ROWS * 32;                            // [2*WARPS + 2][32]: 0 = zeros, 1+2w / 2+2w = first / last row of warp w
     const int tx = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -837,9 +859,8 @@ extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p
     const long long N = (long long)ny * nx;
     int rc = PDEC_OK;
     if (on_chip && ny <= 128 && nx <= 128 && (variant == 0 || variant == 4 || variant == 5)) {
-        // one-reduction loop wins while the iteration is latency-bound (<= 8 warps); at 16 warps the iteration is
-        // throughput-bound and the extra dot product costs more than the barrier it saves (profiles/r1e_*)
-        const bool fused = variant == 0 ? ny <= 64 : variant == 5;
+        // the one-reduction loop (variant 5) saves a barrier but costs a fifth dot product: measured slower (profiles/r1e_*)
+        const bool fused = variant == 5;
         if (ny > 64) rc = launch_block<16>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st, fused);
         else if (ny > 32) rc = launch_block<8>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st, fused);
         else rc = launch_block<4>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st, fused);
