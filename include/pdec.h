@@ -170,6 +170,35 @@ int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p, int* iter
                        int closed, float accuracy, int max_iterations, int stop_mode, void* workspace, size_t workspace_bytes,
                        void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Tiled / slab-decomposed CG  (BASELINE config 5: 2048 x 2048, row slabs over 2/4/8 GPUs)
+ * The same solve as pdec_cg_poisson_2d (zero initial guess, per-element stop rule), on a grid of on-chip tiles with ONE
+ * grid-wide barrier per iteration; with nranks > 1 every rank passes its slab of rows [row0, row0 + ny_local) of the
+ * [ny_global, nx] domain and the barrier spans the GPUs over peer memory (halo rows and the dot-product partials are stored
+ * straight into the neighbours' communication buffers; no NCCL call on the data path).  Replaces, for the decomposed case,
+ * the halo exchange + allreduce a distributed PF/math/blas.py:5-64 would need around sparse.py:105-111.
+ * All ranks must call with the same B, nx, ny_global, accuracy, max_iterations, in the same order.
+ * Requirements: ny_local a multiple of 8; B * tiles <= resident CTAs (else PDEC_ERR_UNSUPPORTED_SIZE).
+ * iterations[b] = -1 if the solve was abandoned (a participant timed out).
+ * Communication buffer: pdec_cg_slab_comm_bytes(B, nx) bytes per rank, peer-accessible (pdec_comm_alloc + pdec_comm_open on
+ * the other ranks, or any other peer-mapped allocation), initialised ONCE by pdec_cg_slab_comm_init before the peers use it. */
+typedef struct pdec_slab_comm {
+    void* local;     /* this rank's communication buffer */
+    void* peers[8];  /* every rank's buffer as mapped into THIS process (peers[rank] == local) */
+    int rank, nranks;
+} pdec_slab_comm;
+size_t pdec_cg_slab_comm_bytes(int B, int nx);
+size_t pdec_cg_slab_workspace_bytes(int B, int ny_local, int nx);
+int pdec_cg_slab_comm_init(void* comm, int B, int nx, void* stream);
+int pdec_cg_poisson_2d_slab(const float* rhs, float* p, int* iterations, float* residual, int B, int ny_local, int nx,
+                            int ny_global, int row0, int closed, float accuracy, int max_iterations, const pdec_slab_comm* comm,
+                            void* workspace, size_t workspace_bytes, void* stream);
+/* peer-visible device allocations for the above: cudaMalloc + CUDA IPC handle (64 bytes, exchanged by the host program) */
+int pdec_comm_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+int pdec_comm_open(const unsigned char* handle64, void** ptr);
+int pdec_comm_close(void* ptr);
+int pdec_comm_free(void* ptr);
+
 #ifdef __cplusplus
 }
 #endif

@@ -63,7 +63,22 @@ _SIGNATURES = {
     "pdec_cg_poisson_2d_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int]),
     "pdec_cg_poisson_2d": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _c.c_int, _c.c_int,
                                        _P, _c.c_size_t, _P]),
+    # ---- tiled / slab-decomposed CG ----
+    "pdec_cg_slab_comm_bytes": (_c.c_size_t, [_c.c_int, _c.c_int]),
+    "pdec_cg_slab_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int]),
+    "pdec_cg_slab_comm_init": (_c.c_int, [_P, _c.c_int, _c.c_int, _P]),
+    "pdec_cg_poisson_2d_slab": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_float,
+                                            _c.c_int, _P, _P, _c.c_size_t, _P]),
+    "pdec_comm_alloc": (_c.c_int, [_c.c_size_t, _c.POINTER(_P), _c.POINTER(_c.c_ubyte)]),
+    "pdec_comm_open": (_c.c_int, [_c.POINTER(_c.c_ubyte), _c.POINTER(_P)]),
+    "pdec_comm_close": (_c.c_int, [_P]),
+    "pdec_comm_free": (_c.c_int, [_P]),
 }
+
+
+class SlabCommStruct(_c.Structure):
+    """pdec_slab_comm of include/pdec.h"""
+    _fields_ = [("local", _P), ("peers", _P * 8), ("rank", _c.c_int), ("nranks", _c.c_int)]
 
 
 def exported_symbols():

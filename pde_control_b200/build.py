@@ -21,6 +21,7 @@ SOURCES = {
     "burgers_fast.cu": [],          # forward op order spelled out with __f*_rn intrinsics; adjoint may contract
     "fluid.cu": ["-fmad=false"],
     "cg.cu": [],
+    "cg_tiled.cu": [],
     "host_pipeline.cu": [],
 }
 
@@ -33,7 +34,7 @@ def _stale():
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = [s for s, _ in _sources()] + [os.path.join(CSRC, "pdec_common.cuh"),
+    deps = [s for s, _ in _sources()] + [os.path.join(CSRC, "pdec_common.cuh"), os.path.join(CSRC, "cg_reduce.cuh"),
                                          os.path.join(HERE, "..", "include", "pdec.h"), __file__]
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 

@@ -15,13 +15,13 @@
 //    iteration (matvec fused with the dots of pass 1; axpys fused with the dot of pass 2; the m-update is folded into the
 //    next matvec), grid-wide barriers between passes, deterministic two-stage reductions.
 #include "pdec_common.cuh"
+#include "cg_reduce.cuh"
 #include <cooperative_groups.h>
 
 namespace cg = cooperative_groups;
 
 namespace pdec {
 
-__device__ __forceinline__ float div_no_nan(float a, float b) { return b == 0.0f ? 0.0f : a / b; }
 
 // neighbour-availability nibble: bit0 up (i-1), bit1 down (i+1), bit2 left (j-1), bit3 right (j+1)
 __device__ __forceinline__ unsigned cell_nibble(int i, int j, int ny, int nx) {
@@ -371,41 +371,6 @@ __device__ __forceinline__ void block_reduce_pair(float& a, float& b, float* red
         }
     a = ta[0];
     b = tb[0];
-}
-
-// Four sums and one maximum in ONE block reduction (one barrier).  Stage 1 is a transposing butterfly: at xor 16 the half-warps
-// trade two of the four sums, at xor 8 one of the remaining two, so lanes 0/8/16/24 end up with the warp totals of s1/s2/s4/s5
-// after 6 shuffles (+5 for the maximum).  Stage 2: lane (h, w') sums the partials of warp w' for (s1|s2, s4|s5, max), a 16-lane
-// butterfly, then the half-warps swap.  Every lane of every warp gets bit-identical totals (fixed order, commutative pairs).
-template <int WARPS>
-__device__ __forceinline__ void block_reduce5(float& s1, float& s2, float& s4, float& s5, float& mx, float* red /* [5][16] */) {
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const bool h16 = (lane & 16) != 0, h8 = (lane & 8) != 0;
-    float k0 = h16 ? s4 : s1, k1 = h16 ? s5 : s2;
-    k0 += __shfl_xor_sync(0xffffffffu, h16 ? s1 : s4, 16);
-    k1 += __shfl_xor_sync(0xffffffffu, h16 ? s2 : s5, 16);
-    float keep = h8 ? k1 : k0;
-    keep += __shfl_xor_sync(0xffffffffu, h8 ? k0 : k1, 8);
-#pragma unroll
-    for (int o = 4; o > 0; o >>= 1) keep += __shfl_xor_sync(0xffffffffu, keep, o);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if ((lane & 7) == 0) red[(lane >> 3) * 16 + w] = keep;
-    if (lane == 1) red[64 + w] = mx;
-    __syncthreads();
-    const int wq = lane & 15, h = lane >> 4;
-    float A = 0.0f, B = 0.0f, C = 0.0f;
-    if (wq < WARPS) { A = red[h * 16 + wq]; B = red[(2 + h) * 16 + wq]; C = red[64 + wq]; }
-#pragma unroll
-    for (int o = 8; o > 0; o >>= 1) {
-        A += __shfl_xor_sync(0xffffffffu, A, o);
-        B += __shfl_xor_sync(0xffffffffu, B, o);
-        C = fmaxf(C, __shfl_xor_sync(0xffffffffu, C, o));
-    }
-    const float A2 = __shfl_xor_sync(0xffffffffu, A, 16), B2 = __shfl_xor_sync(0xffffffffu, B, 16);
-    s1 = h ? A2 : A; s2 = h ? A : A2;
-    s4 = h ? B2 : B; s5 = h ? B : B2;
-    mx = C;
 }
 
 template <int WARPS, bool FULL, bool FUSED>
@@ -793,8 +758,10 @@ static int global_chunks(int N) {
 
 extern "C" size_t pdec_cg_poisson_2d_workspace_bytes(int B, int ny, int nx) {
     const size_t N = (size_t)ny * nx, b = B > 0 ? B : 1;
-    // r, m[2], Am + 2 parities x 4 partial slots + iteration counters
-    return 4 * b * N * sizeof(float) + 8 * b * global_chunks((int)N) * sizeof(float) + b * sizeof(int) + 1024;
+    // r, m[2], Am + 2 parities x 4 partial slots + iteration counters; or the tiled kernel's scratch
+    const size_t streaming = 4 * b * N * sizeof(float) + 8 * b * global_chunks((int)N) * sizeof(float) + b * sizeof(int) + 1024;
+    const size_t tiled = pdec_cg_slab_workspace_bytes(B, ny, nx);
+    return streaming > tiled ? streaming : tiled;
 }
 
 template <int TY, bool FULL>
@@ -889,6 +856,13 @@ extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p
         return PDEC_OK;
     }
     if (N > 0x7fffffffLL || !workspace) return PDEC_ERR_UNSUPPORTED_SIZE;
+    // medium grids: a grid of on-chip tiles with one grid-wide barrier per iteration (cg_tiled.cu); it declines what it cannot
+    // keep resident (or an initial guess / the whole-batch rule), which then streams through L2 with the cooperative kernel below
+    if (!whole_batch && guess == nullptr && variant == 0) {
+        rc = pdec_cg_poisson_2d_slab(rhs, p, iterations, residual, B, ny, nx, ny, 0, closed, accuracy, max_iterations, nullptr, workspace,
+                                     workspace_bytes, stream);
+        if (rc != PDEC_ERR_UNSUPPORTED_SIZE) return rc;
+    }
     CgGlobal P;
     const size_t n = (size_t)B * N;
     float* w = reinterpret_cast<float*>(workspace);

@@ -298,6 +298,68 @@ def cg_poisson_raw(rhs, out, closed, accuracy, max_iterations, guess=None, itera
               _lib.stream_ptr())
 
 
+class SlabComm(object):
+    """Peer-visible communication buffers of the slab-decomposed CG (include/pdec.h, pdec_slab_comm): one buffer per rank,
+    allocated by the library (cudaMalloc), exchanged as CUDA IPC handles over `torch.distributed` and mapped into every
+    process.  One process per GPU; `group` defaults to the world group.  With world size 1 no buffer is needed (pass
+    comm=None to cg_poisson_slab_raw)."""
+
+    def __init__(self, B, nx, group=None):
+        import ctypes
+        import torch.distributed as dist
+        L = _lib.lib()
+        self.rank, self.nranks = dist.get_rank(group), dist.get_world_size(group)
+        assert 1 < self.nranks <= 8
+        self.B, self.nx = B, nx
+        nbytes = L.pdec_cg_slab_comm_bytes(B, nx)
+        local = ctypes.c_void_p()
+        handle = (ctypes.c_ubyte * 64)()
+        _lib.check(L.pdec_comm_alloc(nbytes, ctypes.byref(local), handle), "pdec_comm_alloc")
+        _lib.check(L.pdec_cg_slab_comm_init(local, B, nx, _lib.stream_ptr()), "pdec_cg_slab_comm_init")
+        torch.cuda.synchronize()
+        handles = [None] * self.nranks
+        dist.all_gather_object(handles, bytes(handle), group=group)      # also orders every rank's init before any peer use
+        self.struct = _lib.SlabCommStruct()
+        self.struct.local = local
+        self.struct.rank, self.struct.nranks = self.rank, self.nranks
+        self._opened = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self.struct.peers[r] = local
+                continue
+            mapped = ctypes.c_void_p()
+            buf = (ctypes.c_ubyte * 64).from_buffer_copy(h)
+            _lib.check(L.pdec_comm_open(buf, ctypes.byref(mapped)), "pdec_comm_open")
+            self.struct.peers[r] = mapped
+            self._opened.append(mapped)
+        self._local = local
+        dist.barrier(group=group)
+
+    def close(self):
+        L = _lib.lib()
+        torch.cuda.synchronize()
+        for m in self._opened:
+            L.pdec_comm_close(m)
+        self._opened = []
+        if self._local is not None:
+            L.pdec_comm_free(self._local)
+            self._local = None
+
+
+def cg_poisson_slab_raw(rhs, out, closed, accuracy, max_iterations, ny_global=None, row0=0, comm=None, iterations=None, residual=None):
+    """Tiled on-chip CG of this rank's row slab rhs[B, ny_local, nx] of a [ny_global, nx] domain (whole domain if comm is None)."""
+    import ctypes
+    B, ny, nx = rhs.shape
+    L = _lib.lib()
+    nbytes = L.pdec_cg_slab_workspace_bytes(B, ny, nx)
+    ws = _lib.workspace(rhs.device, nbytes)
+    with torch.cuda.device(rhs.device):
+        _call("pdec_cg_poisson_2d_slab", _lib.ptr(rhs), _lib.ptr(out), _lib.ptr(iterations), _lib.ptr(residual), B, ny, nx,
+              int(ny if ny_global is None else ny_global), int(row0), int(closed), float(accuracy if accuracy is not None else 0.0),
+              int(max_iterations), None if comm is None else ctypes.cast(ctypes.pointer(comm.struct), ctypes.c_void_p),
+              _lib.ptr(ws), nbytes, _lib.stream_ptr())
+
+
 class _PressureSolve(torch.autograd.Function):
     """poisson_solve with SparseCG (solver_api.py:132-158, sparse.py:73-111, math/blas.py:5-64).  Backward = the same
     CG applied to the incoming gradient (sparse.py:93-94: A is symmetric)."""

@@ -161,10 +161,11 @@ def test_cg_matches_reference_golden_and_direct_solve(bd):
 
 
 @pytest.mark.parametrize("bd", ["open", "closed"])
-@pytest.mark.parametrize("ny,nx", [(128, 128), (64, 64), (17, 23), (100, 90), (160, 144)])
+@pytest.mark.parametrize("ny,nx", [(128, 128), (64, 64), (17, 23), (100, 90), (160, 144), (256, 256), (264, 200), (150, 140)])
 def test_cg_solves_the_restated_operator(bd, ny, nx):
-    """All kernel shapes: one-CTA shared-memory kernel at several block sizes, and (160x144 > 16384 cells) the cooperative
-    global-memory kernel.  Property: A p == rhs to the accuracy of the solve; p equals the fp64 direct solve."""
+    """All kernel shapes: the one-CTA on-chip kernel at several block sizes; the grid of on-chip tiles with one grid-wide barrier
+    per iteration (> 16384 cells, rows a multiple of 8: 160x144, 256x256, 264x200 with a ragged last tile column); and the
+    cooperative streaming kernel (150x140).  Property: A p == rhs to the accuracy of the solve; p equals the fp64 direct solve."""
     ops = _ops()
     rng = np.random.RandomState(ny * nx)
     rhs = _smooth(rng, (3, ny, nx), 1.0, passes=2)
