@@ -12,10 +12,14 @@
 //     and forms its neighbours' new search direction on the halo itself: m' = (r - a q) - beta m.  The barrier therefore
 //     carries the reduction AND the halo exchange;
 //   * on several GPUs (row slabs) the same barrier spans the GPUs over NVLink peer memory: edge tiles store their rows straight
-//     into the neighbour GPU's inbox, the last CTA to arrive on each GPU pushes that GPU's five partial sums into every peer's
-//     mailbox and raises a flag; no NCCL call, no host round trip, nothing but the barrier between two iterations.
-// Sums are formed in a fixed order (tile order, then rank order), so every CTA on every GPU computes bit-identical a and beta.
-// Spin loops are bounded (clock64 budget); on a time-out every participant leaves and the iteration count reads -1.
+//     into the neighbour GPU's inbox, every tile stores its five partial sums into EVERY rank's copy of the partials table and
+//     then adds 1 to every rank's arrival counter (a fire-and-forget reduction over NVLink); a tile proceeds when its local
+//     counter shows that all tiles of all ranks have arrived.  No NCCL call, no host round trip, no designated reducer.
+// The barrier is a monotonic counting barrier: sequence numbers continue across launches (a device-resident epoch), and a tile
+// that leaves early (convergence) adds the arrivals it did not use, so the counter of every rank ends each solve at
+// (epoch + max_iterations + 2) x tiles, whatever the iteration count was.
+// Sums are formed in a fixed order (rank, then tile) by every CTA itself, so every CTA on every GPU computes bit-identical
+// a and beta.  Spin loops are bounded (clock64 budget); on a time-out every participant leaves and the iteration count reads -1.
 #include "pdec_common.cuh"
 #include "cg_reduce.cuh"
 #include <string.h>
@@ -27,13 +31,15 @@ typedef unsigned long long u64;
 enum { SIDE_TOP = 0, SIDE_BOTTOM = 1, SIDE_LEFT = 2, SIDE_RIGHT = 3 };
 enum { FROM_ABOVE = 0, FROM_BELOW = 1 };
 #define PDEC_SLAB_MAX_RANKS 8
-// layout of the peer-visible communication buffer (bytes): [flags u64[8] | done u64[8] | abort u32 .. pad to 256]
-//   [epoch u64 (local use) .. pad to 512] [mail float 2 x 8 x B x 8] [inbox float 2 x B x 2 x tiles_x x 3 x 128]
-#define COMM_FLAGS 0
-#define COMM_DONE 64
+// layout of the peer-visible communication buffer (bytes): [arrival counter u64 @0] [this rank's own arrivals u64 @64, local
+// use] [abort u32 @128] [epoch u64 @256, local use] pad to 512 | partials float [2 parities][8 ranks][PDEC_SLAB_MAX_CTAS][8] | inbox float [2][B][2][tiles_x][3][128]
+#define COMM_COUNTER 0
+#define COMM_LOCAL_ARRIVALS 64
 #define COMM_ABORT 128
 #define COMM_EPOCH 256
-#define COMM_MAIL 512
+#define COMM_PARTIALS 512
+#define PDEC_SLAB_MAX_CTAS 1024
+#define COMM_INBOX (COMM_PARTIALS + 2 * PDEC_SLAB_MAX_RANKS * PDEC_SLAB_MAX_CTAS * 8 * 4)
 
 struct CgTiled {
     const float* rhs; float* out; int* iters; float* resid;
@@ -42,9 +48,7 @@ struct CgTiled {
     int tiles_y, tiles_x, tile_rows;
     int rank, nranks;
     // local workspace
-    unsigned* cnt; unsigned* release; unsigned* abort_local;
-    float* totals;      // [2][B][8]
-    float* partials;    // [2][B*tiles][8]
+    unsigned* abort_local;
     float* edges;       // [2][B*tiles][4][3][128]
     // communication buffers (this rank's and the peers' mappings of theirs)
     char* comm; char* peer[PDEC_SLAB_MAX_RANKS];
@@ -56,11 +60,11 @@ __device__ __forceinline__ u64 ld_volatile_u64(const u64* p) { return *reinterpr
 __device__ __forceinline__ void st_volatile_u32(unsigned* p, unsigned v) { *reinterpret_cast<volatile unsigned*>(p) = v; }
 __device__ __forceinline__ void st_volatile_u64(u64* p, u64 v) { *reinterpret_cast<volatile u64*>(p) = v; }
 
-__device__ __forceinline__ float* comm_mail(char* comm, int B, int par, int src_rank, int b) {
-    return reinterpret_cast<float*>(comm + COMM_MAIL) + (((size_t)par * PDEC_SLAB_MAX_RANKS + src_rank) * B + b) * 8;
+__device__ __forceinline__ float* comm_partial(char* comm, int ctas, int par, int src_rank, int cta) {
+    return reinterpret_cast<float*>(comm + COMM_PARTIALS) + (((size_t)par * PDEC_SLAB_MAX_RANKS + src_rank) * ctas + cta) * 8;
 }
 __device__ __forceinline__ float* comm_inbox(char* comm, int B, int tiles_x, int par, int b, int dir, int tx, int vec) {
-    float* base = reinterpret_cast<float*>(comm + COMM_MAIL) + (size_t)2 * PDEC_SLAB_MAX_RANKS * B * 8;
+    float* base = reinterpret_cast<float*>(comm + COMM_INBOX);
     return base + (((((size_t)par * B + b) * 2 + dir) * tiles_x + tx) * 3 + vec) * 128;
 }
 __device__ __forceinline__ float* edge_ptr(const CgTiled& P, int par, int tile_global, int side, int vec) {
@@ -76,94 +80,48 @@ __device__ __forceinline__ bool aborted(const CgTiled& P) {
     return ld_volatile_u32(P.abort_local) != 0u || ld_volatile_u32(reinterpret_cast<const unsigned*>(P.comm + COMM_ABORT)) != 0u;
 }
 
-// Grid-wide (and, with nranks > 1, GPU-wide) barrier number k of this launch.  Before the call every CTA has written its
-// partials(par, tile) and its edges; on return totals(par, b)[0..4] hold the five global reductions of every batch element.
-// Returns false when the solve was abandoned (time-out somewhere).
-template <int THREADS>
-__device__ bool tiled_barrier(const CgTiled& P, unsigned k, u64 seq, unsigned* s_flag) {
-    const int tid = threadIdx.x, par = k & 1;
-    const int tiles = P.tiles_y * P.tiles_x;
+// Arrival at barrier `seq` (global sequence number): everything this CTA stored before (edges, inbox rows, partials) is made
+// visible, then the arrival is counted.  One GPU: +1 on the counter.  Several GPUs: +1 on this rank's own arrival count; the CTA
+// that completes it adds the whole rank's arrivals to EVERY rank's counter (one NVLink reduction per peer and iteration instead
+// of one per tile).  Wait: until the local counter shows all CTAs of all ranks.  Returns false when the solve was abandoned.
+__device__ __forceinline__ void count_arrivals(const CgTiled& P, u64 n, u64 rank_total_after) {
+    if (P.nranks > 1) {
+        __threadfence_system();
+        const u64 old = atomicAdd(reinterpret_cast<u64*>(P.comm + COMM_LOCAL_ARRIVALS), n);
+        if (old + n == rank_total_after) {                  // last tile of this rank for this barrier
+            __threadfence_system();
+            const u64 all = n * gridDim.x;
+            for (int p = 0; p < P.nranks; ++p) atomicAdd_system(reinterpret_cast<u64*>(P.peer[p] + COMM_COUNTER), all);
+        }
+    } else {
+        __threadfence();
+        atomicAdd(reinterpret_cast<u64*>(P.comm + COMM_COUNTER), n);
+    }
+}
+
+__device__ bool tiled_barrier(const CgTiled& P, u64 seq, unsigned* s_flag) {
+    const int tid = threadIdx.x;
     __syncthreads();
     if (tid == 0) {
-        if (P.nranks > 1) __threadfence_system(); else __threadfence();
-        const unsigned old = atomicAdd(P.cnt, 1u);
-        s_flag[0] = (old == (k + 1u) * gridDim.x - 1u) ? 1u : 0u;
-        s_flag[1] = 0u;
-    }
-    __syncthreads();
-    if (s_flag[0]) {                                     // last CTA of this GPU to arrive
-        __threadfence();
-        const int lane = tid & 31, w = tid >> 5;
-        for (int pair = w; pair < P.B * 5; pair += THREADS / 32) {
-            const int b = pair / 5, v = pair - 5 * b;
-            const float* src = P.partials + ((size_t)par * P.B * tiles + (size_t)b * tiles) * 8 + v;
-            float acc = 0.0f;
-            for (int t = lane; t < tiles; t += 32) {
-                const float val = __ldcg(src + (size_t)t * 8);
-                acc = (v == 4) ? fmaxf(acc, val) : acc + val;
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const float other = __shfl_xor_sync(0xffffffffu, acc, o);
-                acc = (v == 4) ? fmaxf(acc, other) : acc + other;
-            }
-            if (lane == 0) {
-                if (P.nranks == 1) P.totals[((size_t)par * P.B + b) * 8 + v] = acc;
-                else
-                    for (int p = 0; p < P.nranks; ++p) comm_mail(P.peer[p], P.B, par, P.rank, b)[v] = acc;
-            }
-        }
-        if (P.nranks > 1) {
-            __syncthreads();
-            if (tid == 0) {
-                __threadfence_system();
-                for (int p = 0; p < P.nranks; ++p)
-                    if (p != P.rank) st_volatile_u64(reinterpret_cast<u64*>(P.peer[p] + COMM_FLAGS) + P.rank, seq);
-                const long long t0 = clock64();
-                bool ok = true;
-                for (int r = 0; r < P.nranks && ok; ++r) {
-                    if (r == P.rank) continue;
-                    while (ld_volatile_u64(reinterpret_cast<const u64*>(P.comm + COMM_FLAGS) + r) < seq) {
-                        if (aborted(P) || clock64() - t0 > P.spin_budget) { ok = false; break; }
-                    }
-                }
-                if (!ok) { raise_abort(P); s_flag[1] = 1u; }
-                __threadfence_system();
-            }
-            __syncthreads();
-            for (int pair = tid; pair < P.B * 5; pair += THREADS) {
-                const int b = pair / 5, v = pair - 5 * b;
-                float acc = 0.0f;
-                for (int r = 0; r < P.nranks; ++r) {
-                    const float val = __ldcg(comm_mail(P.comm, P.B, par, r, b) + v);
-                    acc = (v == 4) ? fmaxf(acc, val) : acc + val;
-                }
-                P.totals[((size_t)par * P.B + b) * 8 + v] = acc;
-            }
-        }
-        __syncthreads();
-        if (tid == 0) {
-            __threadfence();
-            st_volatile_u32(P.release, k + 1u);
-        }
-    } else if (tid == 0) {
+        count_arrivals(P, 1ull, (seq + 1) * gridDim.x);
+        const u64 target = (seq + 1) * (u64)P.nranks * gridDim.x;
         const long long t0 = clock64();
-        while (ld_volatile_u32(P.release) < k + 1u) {
-            if (aborted(P) || clock64() - t0 > P.spin_budget) { raise_abort(P); s_flag[1] = 1u; break; }
+        unsigned bad = 0u;
+        while (ld_volatile_u64(reinterpret_cast<const u64*>(P.comm + COMM_COUNTER)) < target) {
+            if (aborted(P) || clock64() - t0 > P.spin_budget) { raise_abort(P); bad = 1u; break; }
         }
-        __threadfence();
+        if (P.nranks > 1) __threadfence_system(); else __threadfence();
+        s_flag[0] = bad | (aborted(P) ? 1u : 0u);
     }
     __syncthreads();
-    if (tid == 0 && aborted(P)) s_flag[1] = 1u;
-    __syncthreads();
-    return s_flag[1] == 0u;
+    return s_flag[0] == 0u;
 }
 
 template <int WARPS>
 __global__ void __launch_bounds__(32 * WARPS, 1) cg_tiled_kernel(CgTiled P) {
-    constexpr int THREADS = 32 * WARPS, ROWS = 8 * WARPS;
+    constexpr int THREADS = 32 * WARPS, ROWS = 8 * WARPS, NH = 512 / THREADS;
     extern __shared__ __align__(16) float smem_dyn[];
-    __shared__ __align__(16) float red5[2][80];
+    __shared__ __align__(16) float red5[2][80], red5t[2][80];
     __shared__ unsigned s_flag[2];
     __shared__ int s_done;
     float4* sm_x = reinterpret_cast<float4*>(smem_dyn);          // [ROWS][32]
@@ -217,15 +175,16 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_tiled_kernel(CgTiled P) {
     const int tg = b * tiles + t;
     u64* epoch_ptr = reinterpret_cast<u64*>(P.comm + COMM_EPOCH);
     const u64 seq_base = ld_volatile_u64(epoch_ptr);
-    // a peer may still be reading what the PREVIOUS solve put into its mailbox / inbox: wait for its "done" stamp
-    if (P.nranks > 1 && tid == 0) {
+    const int ctas = gridDim.x;                                  // tiles of this rank (all ranks run the same grid)
+    // entry: nobody publishes before every rank has finished the previous solve on this communication buffer (its tiles have
+    // added their unused arrivals, so the counter stands at epoch x tiles-of-all-ranks)
+    if (tid == 0) {
+        const u64 target = seq_base * (u64)P.nranks * gridDim.x;
         const long long t0 = clock64();
-        for (int rk = 0; rk < P.nranks; ++rk) {
-            if (rk == P.rank) continue;
-            while (ld_volatile_u64(reinterpret_cast<const u64*>(P.comm + COMM_DONE) + rk) + 1 < seq_base) {
-                if (aborted(P) || clock64() - t0 > P.spin_budget) { raise_abort(P); break; }
-            }
+        while (ld_volatile_u64(reinterpret_cast<const u64*>(P.comm + COMM_COUNTER)) < target) {
+            if (aborted(P) || clock64() - t0 > P.spin_budget) { raise_abort(P); break; }
         }
+        if (P.nranks > 1) __threadfence_system(); else __threadfence();
     }
     __syncthreads();
     auto publish_local = [&]() {
@@ -309,25 +268,55 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_tiled_kernel(CgTiled P) {
             publish_edges(am, 1);
             publish_edges(m, 2);
         }
-        if (tid == 0) {
-            float* pp = P.partials + ((size_t)par * P.B * tiles + tg) * 8;
-            pp[0] = s1; pp[1] = s2; pp[2] = s4; pp[3] = s5; pp[4] = mx;
+        if (tid < P.nranks) {                                   // this tile's partials into every rank's copy of the table
+            float* pp = comm_partial(P.peer[tid], ctas, par, P.rank, tg);
+            *reinterpret_cast<float4*>(pp) = make_float4(s1, s2, s4, s5);
+            pp[4] = mx;
         }
         // ---- 3. the one barrier of the iteration ----
-        ok = tiled_barrier<THREADS>(P, k, seq_base + k, s_flag);
+        ok = tiled_barrier(P, seq_base + k, s_flag);
         if (!ok) break;
+        // the neighbours' published edges (needed in step 6): issue the loads now, they overlap the reduction of the partials
+        float hr[NH], ha[NH], hm[NH];
+#pragma unroll
+        for (int j = 0; j < NH; ++j) {
+            const int q = tid + j * THREADS, side = q >> 7, idx = q & 127;
+            const float* er = nullptr;
+            if (side == SIDE_TOP && has_up)
+                er = up_remote ? comm_inbox(P.comm, P.B, P.tiles_x, par, b, FROM_ABOVE, txt, 0) : edge_ptr(P, par, tg - P.tiles_x, SIDE_BOTTOM, 0);
+            else if (side == SIDE_BOTTOM && has_dn)
+                er = dn_remote ? comm_inbox(P.comm, P.B, P.tiles_x, par, b, FROM_BELOW, txt, 0) : edge_ptr(P, par, tg + P.tiles_x, SIDE_TOP, 0);
+            else if (side == SIDE_LEFT && has_l && idx < P.tile_rows)
+                er = edge_ptr(P, par, tg - 1, SIDE_RIGHT, 0);
+            else if (side == SIDE_RIGHT && has_r && idx < P.tile_rows)
+                er = edge_ptr(P, par, tg + 1, SIDE_LEFT, 0);
+            hr[j] = er ? __ldcg(er + idx) : 0.0f;
+            ha[j] = er ? __ldcg(er + 128 + idx) : 0.0f;
+            hm[j] = er ? __ldcg(er + 256 + idx) : 0.0f;
+        }
         // ---- 4. stop tests (per batch element; everybody leaves when every element is done) ----
         const int it = k == 0 ? 0 : (int)k - 1;                // real updates applied so far
         const bool budget = it < P.max_it;
         if (tid == 0) s_done = 1;
         __syncthreads();
-        for (int q = tid; q < P.B; q += THREADS) {
-            const float rq = __ldcg(P.totals + ((size_t)par * P.B + q) * 8 + 4);
-            if (budget && (P.accuracy <= 0.0f || rq >= P.accuracy)) s_done = 0;      // benign race: all writers store 0
+        // some element still above the accuracy  <=>  some tile partial of max|r| still above it
+        if (budget && P.accuracy > 0.0f) {
+            for (int rk = 0; rk < P.nranks; ++rk)
+                for (int q = tid; q < ctas; q += THREADS)
+                    if (__ldcg(comm_partial(P.comm, ctas, par, rk, q) + 4) >= P.accuracy) s_done = 0;   // benign race: all store 0
+        } else if (budget && tid == 0) {
+            s_done = 0;
         }
-        const float* tot = P.totals + ((size_t)par * P.B + b) * 8;
-        const float S1 = __ldcg(tot), S2 = __ldcg(tot + 1), S4 = __ldcg(tot + 2), S5 = __ldcg(tot + 3), MX = __ldcg(tot + 4);
-        __syncthreads();
+        // the five sums of THIS element, every CTA by itself, in a fixed order (rank, tile): entry e = rank * tiles + tile
+        float S1 = 0.0f, S2 = 0.0f, S4 = 0.0f, S5 = 0.0f, MX = 0.0f;
+        for (int e = tid; e < P.nranks * tiles; e += THREADS) {
+            const int rk = e / tiles, tt = e - rk * tiles;
+            const float* pp = comm_partial(P.comm, ctas, par, rk, b * tiles + tt);
+            const float4 v = __ldcg(reinterpret_cast<const float4*>(pp));
+            S1 += v.x; S2 += v.y; S4 += v.z; S5 += v.w;
+            MX = fmaxf(MX, __ldcg(pp + 4));
+        }
+        block_reduce5<WARPS>(S1, S2, S4, S5, MX, red5t[par]);    // its barrier also publishes s_done
         const bool all_done = s_done != 0;
         if (!done_me && !(budget && (P.accuracy <= 0.0f || MX >= P.accuracy))) { done_me = true; my_iters = it; my_res = MX; }
         if (all_done) break;
@@ -348,30 +337,10 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_tiled_kernel(CgTiled P) {
             }
         }
         // ---- 6. the neighbours' new search direction on the halo, from their published (r, A m, m) ----
-        for (int q = tid; q < 512; q += THREADS) {
-            const int side = q >> 7, idx = q & 127;
-            const float *er = nullptr, *ea = nullptr, *em = nullptr;
-            bool have = false;
-            if (side == SIDE_TOP && has_up) {
-                have = true;
-                if (up_remote) { er = comm_inbox(P.comm, P.B, P.tiles_x, par, b, FROM_ABOVE, txt, 0); ea = er + 128; em = ea + 128; }
-                else { er = edge_ptr(P, par, tg - P.tiles_x, SIDE_BOTTOM, 0); ea = er + 128; em = ea + 128; }
-            } else if (side == SIDE_BOTTOM && has_dn) {
-                have = true;
-                if (dn_remote) { er = comm_inbox(P.comm, P.B, P.tiles_x, par, b, FROM_BELOW, txt, 0); ea = er + 128; em = ea + 128; }
-                else { er = edge_ptr(P, par, tg + P.tiles_x, SIDE_TOP, 0); ea = er + 128; em = ea + 128; }
-            } else if (side == SIDE_LEFT && has_l) {
-                have = idx < P.tile_rows;
-                er = edge_ptr(P, par, tg - 1, SIDE_RIGHT, 0); ea = er + 128; em = ea + 128;
-            } else if (side == SIDE_RIGHT && has_r) {
-                have = idx < P.tile_rows;
-                er = edge_ptr(P, par, tg + 1, SIDE_LEFT, 0); ea = er + 128; em = ea + 128;
-            }
-            float hv = 0.0f;
-            if (have) {
-                const float rn = __ldcg(er + idx) - a * __ldcg(ea + idx);
-                hv = rn - beta * __ldcg(em + idx);
-            }
+#pragma unroll
+        for (int j = 0; j < NH; ++j) {
+            const int q = tid + j * THREADS, side = q >> 7, idx = q & 127;
+            const float hv = (hr[j] - a * ha[j]) - beta * hm[j];
             if (side == SIDE_TOP) reinterpret_cast<float*>(sm_e)[idx] = hv;
             else if (side == SIDE_BOTTOM) reinterpret_cast<float*>(sm_e + (2 * wu + 1) * 32)[idx] = hv;
             else if (side == SIDE_LEFT) { if (idx < ROWS) sm_lr[idx] = hv; }
@@ -400,15 +369,13 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_tiled_kernel(CgTiled P) {
         if (P.iters) P.iters[b] = ok ? my_iters : -1;
         if (P.resid) P.resid[b] = my_res;
     }
-    if (blockIdx.x == 0 && tid == 0) {
-        // the next solve starts max_it + 2 sequence numbers later on every rank; tell the peers this rank has finished reading
-        const u64 next = seq_base + (u64)P.max_it + 2;
-        st_volatile_u64(epoch_ptr, next);
-        if (P.nranks > 1) {
-            __threadfence_system();
-            for (int p = 0; p < P.nranks; ++p)
-                if (p != P.rank) st_volatile_u64(reinterpret_cast<u64*>(P.peer[p] + COMM_DONE) + P.rank, next - 1);
-        }
+    // every solve consumes max_it + 2 sequence numbers on every rank: hand in the arrivals this tile did not use (after its
+    // last read of peer-written data), so the next solve's entry test sees when everybody has left this one
+    __syncthreads();
+    if (tid == 0 && ok) {
+        const u64 unused = (u64)P.max_it + 2 - ((u64)k + 1);          // the same on every tile: all leave at the same barrier
+        if (unused > 0) count_arrivals(P, unused, (seq_base + (u64)P.max_it + 2) * gridDim.x);
+        if (blockIdx.x == 0) st_volatile_u64(epoch_ptr, seq_base + (u64)P.max_it + 2);
     }
 }
 
@@ -440,7 +407,16 @@ bool choose_tiling(int B, int ny_loc, int nx, Tiling* out) {
     int dev = 0, sms = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return false;
     const int tiles_x = (nx + 127) / 128;
-    const int cap[3] = {resident_ctas<4>(sms), resident_ctas<8>(sms), resident_ctas<16>(sms)};
+    // resident-CTA capacities are a property of (kernel, device): queried once per device (benign race: same values)
+    static int cached[64][3];
+    static bool have[64];
+    int cap[3];
+    if (dev >= 0 && dev < 64 && have[dev]) {
+        cap[0] = cached[dev][0]; cap[1] = cached[dev][1]; cap[2] = cached[dev][2];
+    } else {
+        cap[0] = resident_ctas<4>(sms); cap[1] = resident_ctas<8>(sms); cap[2] = resident_ctas<16>(sms);
+        if (dev >= 0 && dev < 64) { cached[dev][0] = cap[0]; cached[dev][1] = cap[1]; cached[dev][2] = cap[2]; have[dev] = true; }
+    }
     double best = 1e30;
     bool found = false;
     for (int tiles_y = 1; tiles_y <= ny_loc / 8; ++tiles_y) {
@@ -464,24 +440,21 @@ size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 // bytes of the peer-visible communication buffer of one rank
 extern "C" size_t pdec_cg_slab_comm_bytes(int B, int nx) {
     const size_t b = B > 0 ? B : 1, tiles_x = nx > 0 ? (nx + 127) / 128 : 1;
-    return COMM_MAIL + ((size_t)2 * PDEC_SLAB_MAX_RANKS * b * 8 + (size_t)2 * b * 2 * tiles_x * 3 * 128) * sizeof(float);
+    return COMM_INBOX + (size_t)2 * b * 2 * tiles_x * 3 * 128 * sizeof(float);
 }
 
 // local (not peer-visible) scratch: sync words, a single-GPU stand-in for the comm header, totals, partials, edges
 extern "C" size_t pdec_cg_slab_workspace_bytes(int B, int ny_local, int nx) {
     const size_t b = B > 0 ? B : 1;
     size_t bt = b * (size_t)((ny_local + 7) / 8) * ((nx + 127) / 128);            // upper bound: 8-row tiles ...
-    if (bt > 1024) bt = 1024;                                                       // ... all resident at once
-    return 256 + COMM_MAIL + align256(2 * b * 8 * sizeof(float)) + align256(2 * bt * 8 * sizeof(float)) +
-           align256(2 * bt * 4 * 3 * 128 * sizeof(float));
+    if (bt > PDEC_SLAB_MAX_CTAS) bt = PDEC_SLAB_MAX_CTAS;                                                     // ... all resident at once
+    return 256 + COMM_INBOX + align256(2 * bt * 4 * 3 * 128 * sizeof(float));
 }
 
 extern "C" int pdec_cg_slab_comm_init(void* comm, int B, int nx, void* stream) {
     if (!comm) return PDEC_ERR_INVALID_ARGUMENT;
     cudaStream_t st = (cudaStream_t)stream;
     if (cudaMemsetAsync(comm, 0, pdec_cg_slab_comm_bytes(B, nx), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
-    const unsigned long long one = 1ull;          // first sequence number (flags start at 0)
-    if (cudaMemcpyAsync((char*)comm + COMM_EPOCH, &one, sizeof(one), cudaMemcpyHostToDevice, st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
     return PDEC_OK;
 }
 
@@ -498,7 +471,7 @@ extern "C" int pdec_cg_poisson_2d_slab(const float* rhs, float* p, int* iteratio
     if (nranks > 1 && (!comm->local || comm->peers[rank] != comm->local)) return PDEC_ERR_INVALID_ARGUMENT;
     if (workspace_bytes < pdec_cg_slab_workspace_bytes(B, ny_local, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
     Tiling tl;
-    if (!choose_tiling(B, ny_local, nx, &tl) || (size_t)B * tl.tiles_y * tl.tiles_x > 1024) return PDEC_ERR_UNSUPPORTED_SIZE;
+    if (!choose_tiling(B, ny_local, nx, &tl) || (size_t)B * tl.tiles_y * tl.tiles_x > PDEC_SLAB_MAX_CTAS) return PDEC_ERR_UNSUPPORTED_SIZE;
     cudaStream_t st = (cudaStream_t)stream;
     CgTiled P;
     P.rhs = rhs; P.out = p; P.iters = iterations; P.resid = residual;
@@ -507,17 +480,14 @@ extern "C" int pdec_cg_poisson_2d_slab(const float* rhs, float* p, int* iteratio
     P.tiles_y = tl.tiles_y; P.tiles_x = tl.tiles_x; P.tile_rows = tl.tile_rows;
     P.rank = rank; P.nranks = nranks;
     char* w = reinterpret_cast<char*>(workspace);
-    P.cnt = reinterpret_cast<unsigned*>(w); P.release = P.cnt + 1; P.abort_local = P.cnt + 2;
+    P.abort_local = reinterpret_cast<unsigned*>(w);
     char* fake_comm = w + 256;
     const size_t tiles = (size_t)tl.tiles_y * tl.tiles_x;
-    char* q = w + 256 + COMM_MAIL;
-    P.totals = reinterpret_cast<float*>(q); q += align256((size_t)2 * B * 8 * sizeof(float));
-    P.partials = reinterpret_cast<float*>(q); q += align256((size_t)2 * B * tiles * 8 * sizeof(float));
-    P.edges = reinterpret_cast<float*>(q);
+    P.edges = reinterpret_cast<float*>(w + 256 + COMM_INBOX);
     for (int i = 0; i < PDEC_SLAB_MAX_RANKS; ++i) P.peer[i] = nullptr;
     if (nranks == 1) {
-        // single GPU: the sync words AND the stand-in comm header are reset by this launch (nobody else writes them)
-        if (cudaMemsetAsync(w, 0, 256 + COMM_MAIL, st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+        // single GPU: counter, epoch and abort words live in the scratch and are reset by this launch (nobody else writes them)
+        if (cudaMemsetAsync(w, 0, 256 + COMM_PARTIALS, st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
         P.comm = fake_comm; P.peer[0] = fake_comm;
     } else {
         if (cudaMemsetAsync(w, 0, 256, st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
