@@ -394,6 +394,60 @@ def pressure_solve(div, closed, accuracy=1e-5, max_iterations=2000, gradient_acc
     return _PressureSolve.apply(div, bool(closed), accuracy, int(max_iterations), ga, int(gi), guess, int(stop_mode))
 
 
+class SlabSolver(object):
+    """Row-slab decomposition of the pressure solve over the ranks of a process group (BASELINE config 5): every rank holds the
+    whole (replicated) fields -- the stencil operators around the solve are < 1 % of a 2048^2 step -- and solves its slab of rows
+    with the tiled on-chip CG whose per-iteration exchange runs over NVLink peer memory (pdec_cg_poisson_2d_slab); the slabs
+    of the pressure are then all-gathered (NCCL).  The adjoint is the same solve applied to the incoming gradient."""
+
+    def __init__(self, B, ny, nx, group=None):
+        import torch.distributed as dist
+        self.group = group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        assert ny % self.world == 0 and (ny // self.world) % 8 == 0, "slabs must be equal and a multiple of 8 rows"
+        self.B, self.ny, self.nx, self.rows = B, ny, nx, ny // self.world
+        self.comm = SlabComm(B, nx, group) if self.world > 1 else None
+
+    def solve(self, rhs, closed, accuracy, max_iterations):
+        """rhs [B, ny, nx] (replicated) -> (p [B, ny, nx] replicated, iterations, residual)"""
+        import torch.distributed as dist
+        B, ny, nx = rhs.shape
+        assert (B, ny, nx) == (self.B, self.ny, self.nx)
+        lo = self.rank * self.rows
+        mine = rhs[:, lo:lo + self.rows].contiguous()
+        out = torch.empty_like(mine)
+        iters = torch.zeros(B, device=rhs.device, dtype=torch.int32)
+        resid = torch.zeros(B, device=rhs.device, dtype=torch.float32)
+        if self.world == 1:
+            cg_poisson_raw(mine, out, closed, accuracy, max_iterations, None, iters, resid)
+            return out, iters, resid
+        cg_poisson_slab_raw(mine, out, closed, accuracy, max_iterations, ny_global=ny, row0=lo, comm=self.comm, iterations=iters, residual=resid)
+        parts = [torch.empty_like(out) for _ in range(self.world)]
+        dist.all_gather(parts, out, group=self.group)
+        return torch.cat(parts, 1), iters, resid
+
+    def close(self):
+        if self.comm is not None:
+            self.comm.close()
+            self.comm = None
+
+
+class _PressureSolveSlab(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, div, solver, closed, accuracy, max_iterations):
+        _req_cuda(div)
+        p, iters, resid = solver.solve(_c(div), closed, accuracy, max_iterations)
+        ctx.cfg = (solver, closed, accuracy, max_iterations)
+        ctx.mark_non_differentiable(iters, resid)
+        return p, iters, resid
+
+    @staticmethod
+    def backward(ctx, g_p, _gi, _gr):
+        solver, closed, accuracy, max_it = ctx.cfg
+        g_div, _, _ = solver.solve(_c(g_p), closed, accuracy, max_it)
+        return g_div, None, None, None, None
+
+
 class _SubtractPressureGradient(torch.autograd.Function):
     """divergence_free tail (PF/physics/fluid.py:237-242)."""
 
@@ -463,16 +517,20 @@ def normalize_to(target, source, epsilon=1e-5):
 
 
 def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
-                    max_gradient_iterations=None, guess=None):
-    """divergence_free (PF/physics/fluid.py:214-243) without obstacles -> (vy', vx', pressure, iterations, divergence)."""
+                    max_gradient_iterations=None, guess=None, slab=None):
+    """divergence_free (PF/physics/fluid.py:214-243) without obstacles -> (vy', vx', pressure, iterations, divergence).
+    slab: a SlabSolver -> the pressure solve is decomposed over its process group."""
     div = mask_divergence(vy, vx, closed)
-    p, iters, _ = pressure_solve(div, closed, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations, guess)
+    if slab is not None:
+        p, iters, _ = _PressureSolveSlab.apply(div, slab, bool(closed), accuracy, int(max_iterations))
+    else:
+        p, iters, _ = pressure_solve(div, closed, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations, guess)
     oy, ox = subtract_pressure_gradient(vy, vx, p, closed, box)
     return oy, ox, p, iters, div
 
 
 def incompressible_step(rho, vy, vx, dt, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
-                        max_gradient_iterations=None, conserve_density=True):
+                        max_gradient_iterations=None, conserve_density=True, slab=None):
     """IncompressibleFlow.step (PF/physics/fluid.py:90-114), default flags, no obstacles / effects / buoyancy.
     Field modes follow Material.extrapolation_mode / vector_extrapolation_mode: open -> constant, closed -> replicate."""
     mode = MODE_REPLICATE if closed else MODE_CONSTANT
@@ -480,5 +538,6 @@ def incompressible_step(rho, vy, vx, dt, closed, box=None, accuracy=1e-5, max_it
     ay, ax = advect_staggered(vy, vx, dt, mode, box)
     if closed and conserve_density:
         rho2 = normalize_to(rho2, rho)
-    oy, ox, p, iters, _ = divergence_free(ay, ax, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations)
+    oy, ox, p, iters, _ = divergence_free(ay, ax, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations,
+                                         slab=slab)
     return rho2, oy, ox, p, iters
