@@ -62,3 +62,45 @@ def test_two_rank_data_parallel_training_matches_single_process(tmp_path):
     for _ in range(5):
         app.step()
     assert abs(float(pde.networks["OP2"].weight) - a[1]) < 1e-5
+
+
+def _slab_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle import slab_cg as S
+    rng = np.random.RandomState(5)
+    for name, (B, ny, nx, closed) in {"open": (2, 24, 20, False), "closed": (1, 16, 12, True)}.items():
+        rhs = rng.randn(B, ny, nx)
+        rhs[0] *= 1e-3                                   # elements converge at different iterations (per-element stop rule)
+        if closed:
+            rhs -= rhs.mean((1, 2), keepdims=True)
+        rows = ny // world
+        x, iters, exchanges = S.slab_cg(torch.tensor(rhs[:, rank * rows:(rank + 1) * rows]), rank * rows, ny, closed, 1e-9, 500)
+        np.save(os.path.join(out_dir, "%s_%d.npy" % (name, rank)), x.numpy())
+        if rank == 0:
+            np.save(os.path.join(out_dir, "%s_meta.npy" % name), np.array(iters + [exchanges]))
+    dist.destroy_process_group()
+
+
+def test_two_rank_slab_cg_single_exchange_formulation_matches_plain_cg(tmp_path):
+    """The algorithm of csrc/cg_tiled.cu (slabs, ONE exchange per iteration, beta from pre-update dot products, neighbour-formed
+    halo directions) restated on CPU over gloo == the plain restatement of blas.py:5-64 on the whole domain (fp64)."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from oracle import restate_fluid as F
+    port = _free_port()
+    mp.spawn(_slab_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    rng = np.random.RandomState(5)
+    for name, (B, ny, nx, closed) in {"open": (2, 24, 20, False), "closed": (1, 16, 12, True)}.items():
+        rhs = rng.randn(B, ny, nx)
+        rhs[0] *= 1e-3
+        if closed:
+            rhs -= rhs.mean((1, 2), keepdims=True)
+        got = np.concatenate([np.load(tmp_path / ("%s_%d.npy" % (name, r))) for r in range(2)], 1)
+        meta = np.load(tmp_path / ("%s_meta.npy" % name))
+        iters, exchanges = meta[:-1], meta[-1]
+        for b in range(B):                               # the reference stops on the whole batch: compare element by element
+            ref, k = F.conjugate_gradient(torch.tensor(rhs[b:b + 1]), "closed" if closed else "open", accuracy=1e-9, max_iterations=500)
+            assert abs(int(iters[b]) - k) <= 1
+            assert np.abs(got[b] - ref[0].numpy()).max() < 1e-7 * max(1.0, np.abs(ref.numpy()).max())
+        assert exchanges == max(iters) + 2               # one exchange per iteration (+ the set-up pass and the final test)
