@@ -454,12 +454,17 @@ extern "C" int pdec_burgers_trajectory_bwd(const float* u0, const float* frames,
 
 // burgers_fast.cu: register-resident kernel for n == 128 (returns 1 when the shape is not eligible)
 int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials, int T, int B, int n, int mode, double dt, double viscosity,
-                                float lower, float size, int substeps, int resubstep, float gl2, float gl1, int* nchunks_out,
-                                cudaStream_t st);
+                                float lower, float size, int substeps, int resubstep, float gl2, float gl1, unsigned* done_counter,
+                                float* losses, cudaStream_t st);
+
+static size_t pair_loss_partials_bytes(int B, int T) {       // one loss partial per (row, chunk of pairs), rounded to 256 bytes
+    const size_t raw = (size_t)(B > 0 ? B : 1) * (size_t)(T > 0 ? T : 1) * sizeof(float2);
+    return (raw + 255) & ~(size_t)255;
+}
 
 extern "C" size_t pdec_burgers_pair_loss_workspace_bytes(int B, int n, int T) {
     (void)n;
-    return (size_t)(B > 0 ? B : 1) * (size_t)(T > 0 ? T : 1) * sizeof(float2);     // one loss partial per (row, chunk of pairs)
+    return pair_loss_partials_bytes(B, T) + 256;                                   // + the "CTAs done" counter of the fused reduction
 }
 
 extern "C" int pdec_burgers_pair_loss(const float* s, float* grad_s, float* losses, int T, int B, int n, int mode,
@@ -475,15 +480,11 @@ extern "C" int pdec_burgers_pair_loss(const float* s, float* grad_s, float* loss
     float2* partials = reinterpret_cast<float2*>(workspace);
     const float invB = 1.0f / (float)B;
     {
-        int nchunks = 1;
+        // n == 128: register-resident kernel, loss reduction fused into the same launch (counter word behind the partials)
+        unsigned* done_counter = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(workspace) + pair_loss_partials_bytes(B, T));
         rc = pdec_burgers_pair_loss_fast(s, grad_s, partials, T, B, n, mode, dt, viscosity, box_lower, box_size, substeps, resubstep, gl2,
-                                         gl1, &nchunks, st);
-        if (rc < 0) return rc;
-        if (rc == PDEC_OK) {
-            burgers_loss_reduce_kernel<<<1, 1024, 0, st>>>(partials, B * nchunks, invB, losses);
-            PDEC_CHECK_LAUNCH();
-            return PDEC_OK;
-        }
+                                         gl1, done_counter, losses, st);
+        if (rc <= 0) return rc;
     }
     const int wpc = pick_wpc(p.nrow, PL_ROWS);
     if (wpc == 0) return PDEC_ERR_UNSUPPORTED_SIZE;

@@ -72,16 +72,39 @@ __device__ __forceinline__ void fast_forward(const FastP& p, const float (&x0)[4
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const float xi = to_index<EXACT>(p, x0[k], u[k]);
-        int fi, ci;
-        interp_setup<MODE>(xi, 128, fi, ci, G.w0[k], G.w1[k]);
-        const float basef = floorf(xi);
-        G.base[k] = (int)fminf(fmaxf(basef, -1.0e6f), 1.0e6f);
-        G.pf[k] = skew(fi);
-        G.pc[k] = skew(ci);
-        const float sf = su[G.pf[k]], sc = su[G.pc[k]];
-        adv[k] = __fadd_rn(__fmul_rn(sf, G.w1[k]), __fmul_rn(sc, G.w0[k]));     // tf_backend.py:491-497
-        G.du[k] = sc - sf;
-        if (MODE != PDEC_MODE_CONSTANT || fi != ci) G.active |= 1u << k;
+        if (MODE == PDEC_MODE_CONSTANT) {
+            // TF 'constant' rule (tf_backend.py:466-497): weights from CLAMPED indices.  For 0 <= floor(xi) <= N-2 the clamps do
+            // nothing (w0 = xi - floor, w1 = (floor + 1) - xi); everywhere else both clamped indices coincide and the two
+            // products are exact negatives of each other: the sample is exactly +0 and so are its gradients.  One unsigned
+            // compare decides; no float clamps.
+            const float basef = floorf(xi);
+            const int bi = (int)fminf(fmaxf(basef, -2.0f), 130.0f);      // saturate far-away back-traces before the cast
+            const bool inside = (unsigned)bi < 127u;
+            // monotonicity key for the adjoint's distinctness proof: strictly increasing over the lanes whenever the back-trace is
+            // monotone (left-outside lanes, then inside lanes, then right-outside lanes)
+            G.base[k] = inside ? bi : (bi < 0 ? lane - 200 : lane + 200);
+            G.w0[k] = xi - basef;
+            G.w1[k] = (basef + 1.0f) - xi;
+            const int fi = inside ? bi : 0;
+            G.pf[k] = skew(fi);
+            G.pc[k] = skew(fi + 1);
+            const float sf = su[G.pf[k]], sc = su[G.pc[k]];
+            const float val = __fadd_rn(__fmul_rn(sf, G.w1[k]), __fmul_rn(sc, G.w0[k]));     // tf_backend.py:491-497
+            adv[k] = inside ? val : 0.0f;
+            G.du[k] = inside ? sc - sf : 0.0f;
+            if (inside) G.active |= 1u << k;
+        } else {
+            int fi, ci;
+            interp_setup<MODE>(xi, 128, fi, ci, G.w0[k], G.w1[k]);
+            const float basef = floorf(xi);
+            G.base[k] = (int)fminf(fmaxf(basef, -1.0e6f), 1.0e6f);
+            G.pf[k] = skew(fi);
+            G.pc[k] = skew(ci);
+            const float sf = su[G.pf[k]], sc = su[G.pc[k]];
+            adv[k] = __fadd_rn(__fmul_rn(sf, G.w1[k]), __fmul_rn(sc, G.w0[k]));     // tf_backend.py:491-497
+            G.du[k] = sc - sf;
+            G.active |= 1u << k;
+        }
     }
     float left, right;
     edge_neighbours<MODE>(adv, lane, left, right);
@@ -109,24 +132,32 @@ __device__ __forceinline__ void fast_adjoint(const FastP& p, const Gathered& G, 
         const float lo = k == 0 ? left : g[k - 1], up = k == 3 ? right : g[k + 1];
         g1[k] = g[k] + p.c2 * (up + lo - 2.0f * g[k]);
     }
+    // distinctness proof, one vote for the four warp instructions: instruction k touches the cells 4l+k, whose keys are strictly
+    // increasing in l unless the back-trace folds over (extreme gradients)
+    bool ordered = true;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const bool act = (G.active >> k) & 1u;
-        // distinctness proof for this warp instruction
-        bool ordered;
         if (MODE == PDEC_MODE_CONSTANT) {
             const int prev = __shfl_up_sync(PDEC_FULL_MASK, G.base[k], 1);
-            ordered = lane == 0 || G.base[k] > prev;
+            ordered = ordered && (lane == 0 || G.base[k] > prev);
         } else {
             const int pf_prev = __shfl_up_sync(PDEC_FULL_MASK, G.pf[k], 1), pc_prev = __shfl_up_sync(PDEC_FULL_MASK, G.pc[k], 1);
-            ordered = lane == 0 || (G.pf[k] > pf_prev && G.pc[k] > pc_prev);
+            ordered = ordered && (lane == 0 || (G.pf[k] > pf_prev && G.pc[k] > pc_prev));
         }
-        if (__all_sync(PDEC_FULL_MASK, ordered)) {
+    }
+    if (__all_sync(PDEC_FULL_MASK, ordered)) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const bool act = (G.active >> k) & 1u;
             if (act) sacc[G.pf[k]] += g1[k] * G.w1[k];
             __syncwarp();
             if (act) sacc[G.pc[k]] += g1[k] * G.w0[k];
             __syncwarp();
-        } else {
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const bool act = (G.active >> k) & 1u;
             warp_ordered_scatter_add(sacc, G.pf[k], g1[k] * G.w1[k], act);
             warp_ordered_scatter_add(sacc, G.pc[k], g1[k] * G.w0[k], act);
         }
@@ -147,9 +178,12 @@ __device__ __forceinline__ void row_to_smem(float* su, const float (&u)[4], int 
 }
 
 template <int MODE, bool EXACT, bool L1TERM, int SUBSTEPS>
-__global__ void __launch_bounds__(256) burgers_pair_loss_fast_kernel(FastP p, const float* __restrict__ s, float* __restrict__ grad_s,
-                                                                      float2* __restrict__ partials, int T, int B, int C, int nchunks) {
+__global__ void __launch_bounds__(256, 4) burgers_pair_loss_fast_kernel(FastP p, const float* __restrict__ s, float* __restrict__ grad_s,
+                                                                      float2* partials, int T, int B, int C, int nchunks,
+                                                                      unsigned* done_counter, float* __restrict__ losses, float inv_B) {
     __shared__ float smem[8][2][FAST_ROW];
+    __shared__ float red2[8], red1[8];
+    __shared__ unsigned s_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* su = smem[warp][0];
     float* sacc = smem[warp][1];
@@ -188,10 +222,10 @@ __global__ void __launch_bounds__(256) burgers_pair_loss_fast_kernel(FastP p, co
             }
         }
         float acc2 = 0.0f, acc1 = 0.0f;
-        float4 pre = row[(size_t)(t0 + 1) * f4];
+        float4 pre = __ldcs(row + (size_t)(t0 + 1) * f4);                // streamed: every frame is read once per chunk
         for (int t = t0; t < t1; ++t) {
             nxt[0] = pre.x; nxt[1] = pre.y; nxt[2] = pre.z; nxt[3] = pre.w;
-            if (t + 2 <= T) pre = row[(size_t)(t + 2) * f4];       // prefetch: in flight during this pair's arithmetic
+            if (t + 2 <= T) pre = __ldcs(row + (size_t)(t + 2) * f4);       // prefetch: in flight during this pair's arithmetic
             row_to_smem(su, u, lane);
             fast_forward<MODE, EXACT, SUBSTEPS>(p, x0, u, su, lane, v, G);
             float gd[4];
@@ -206,17 +240,47 @@ __global__ void __launch_bounds__(256) burgers_pair_loss_fast_kernel(FastP p, co
             }
             if (grad_s != nullptr) {
                 fast_adjoint<MODE>(p, G, g, sacc, lane, gin);
-                grow[(size_t)t * f4] = make_float4(gin[0] + carry[0], gin[1] + carry[1], gin[2] + carry[2], gin[3] + carry[3]);
+                __stcs(grow + (size_t)t * f4, make_float4(gin[0] + carry[0], gin[1] + carry[1], gin[2] + carry[2], gin[3] + carry[3]));   // written once, never re-read here: evict-first
             } else {
                 __syncwarp();
             }
 #pragma unroll
             for (int k = 0; k < 4; ++k) { carry[k] = gd[k]; u[k] = nxt[k]; }
         }
-        if (grad_s != nullptr && t1 == T) grow[(size_t)T * f4] = make_float4(carry[0], carry[1], carry[2], carry[3]);
+        if (grad_s != nullptr && t1 == T) __stcs(grow + (size_t)T * f4, make_float4(carry[0], carry[1], carry[2], carry[3]));
         acc2 = warp_sum(acc2);
         acc1 = warp_sum(acc1);
         if (lane == 0) partials[(size_t)b * nchunks + chunk] = make_float2(acc2, acc1);
+    }
+    // second stage fused into the same launch: the CTA that finishes last adds all partials in a FIXED order (thread i takes
+    // i, i + 256, ...; then a fixed tree) -- which CTA that is does not matter, the bits are the same.
+    // losses[0] = sum(d^2)/2/B (l2_loss, PF/math/nd.py:115-121), losses[1] = sum|d|/B (l1_loss, nd.py:96-108)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(done_counter, 1u) == gridDim.x - 1u ? 1u : 0u;
+    }
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        float a2 = 0.0f, a1 = 0.0f;
+        const int count = B * nchunks;
+        for (int i = threadIdx.x; i < count; i += 256) {
+            const float2 v = __ldcg(partials + i);
+            a2 += v.x;
+            a1 += v.y;
+        }
+        a2 = warp_sum(a2);
+        a1 = warp_sum(a1);
+        if (lane == 0) { red2[warp] = a2; red1[warp] = a1; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float t2 = 0.0f, t1 = 0.0f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) { t2 += red2[w]; t1 += red1[w]; }
+            losses[0] = t2 * 0.5f * inv_B;
+            losses[1] = t1 * inv_B;
+        }
     }
 }
 
@@ -229,7 +293,9 @@ static bool is_pow2f(float x) {
     return x > 0.0f && frexpf(x, &e) == 0.5f;
 }
 
-// Chunk length: the largest power of two <= T that still yields >= 2 waves of warps (148 SMs x 24 resident warps).
+// Chunk length: the largest power of two <= T that still yields >= 7104 warps (two rounds of 148 SMs x 24 warps).  Measured at
+// B = 4096, T = 32 (64 registers, 4 CTAs per SM): C = 32 -> 86 us (512 CTAs quantise badly over 148 SMs), C = 16 -> 74 us,
+// C = 8 -> 77 us (a chunk that does not start at frame 0 pays one extra forward step).
 static int pair_loss_chunk(int B, int T) {
     int C = 1;
     while (C * 2 <= T) C *= 2;
@@ -239,8 +305,8 @@ static int pair_loss_chunk(int B, int T) {
 
 // returns PDEC_OK if it handled the call, 1 if the shape is not eligible (caller uses the general kernel)
 int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials, int T, int B, int n, int mode, double dt, double viscosity,
-                                float lower, float size, int substeps, int resubstep, float gl2, float gl1, int* nchunks_out,
-                                cudaStream_t st) {
+                                float lower, float size, int substeps, int resubstep, float gl2, float gl1, unsigned* done_counter,
+                                float* losses, cudaStream_t st) {
     if (n != 128 || (resubstep && substeps > 1)) return 1;
     if ((reinterpret_cast<uintptr_t>(s) & 15u) || (grad_s && (reinterpret_cast<uintptr_t>(grad_s) & 15u))) return 1;
     FastP p;
@@ -257,15 +323,15 @@ int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials,
     p.gl2 = gl2 * invB; p.gl1 = gl1 * invB;
     const bool exact = is_pow2f(size) && is_pow2f(p.dx2);
     const int C = pair_loss_chunk(B, T), nchunks = (T + C - 1) / C;
-    *nchunks_out = nchunks;
+    if (cudaMemsetAsync(done_counter, 0, sizeof(unsigned), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
     const long long units = (long long)B * nchunks;
     long long grid = (units + 7) / 8;
     if (grid > 148LL * 64) grid = 148LL * 64;
     const bool l1 = gl1 != 0.0f;
 #define LAUNCH(M, E, L)                                                                                                   \
     do {                                                                                                                  \
-        if (substeps == 1) burgers_pair_loss_fast_kernel<M, E, L, 1><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, C, nchunks); \
-        else burgers_pair_loss_fast_kernel<M, E, L, 0><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, C, nchunks);             \
+        if (substeps == 1) burgers_pair_loss_fast_kernel<M, E, L, 1><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, C, nchunks, done_counter, losses, invB); \
+        else burgers_pair_loss_fast_kernel<M, E, L, 0><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, C, nchunks, done_counter, losses, invB);             \
     } while (0)
 #define PICK(M)                                                            \
     do {                                                                   \
