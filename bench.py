@@ -101,7 +101,7 @@ class BurgersWorkload:
     algorithmic_bytes_per_cell_update = 8.0     # read each frame once + write its gradient once
     dtype = "f32"
     dominant_kernel = "burgers_pair_loss_fast_kernel"
-    ncu_traffic_bytes = 96.4e6      # dram read 69.3 MB + write 27.1 MB per launch, profiles/r1c_burgers_pair_loss_fast_summary.md
+    ncu_traffic_bytes = 124.7e6     # steady state: dram read 60.1 MB + write 64.5 MB per launch, profiles/r1h_burgers_summary.md
 
     def __init__(self, device, rank, B=4096, n=128, T=32):
         import torch
