@@ -33,11 +33,13 @@ struct FastP {
 __device__ __forceinline__ int skew(int j) { return j + (j >> 5); }
 #define FAST_ROW 132                 // 128 + 4 skew slots
 
-template <bool EXACT>
+// EXACT: 0 = general box (IEEE divisions), 1 = size and dx^2 are powers of two (exact reciprocals), 2 = additionally the unit box
+// [0, 1]: x - 0 and x * 1 are exact identities and are dropped
+template <int EXACT>
 __device__ __forceinline__ float to_index(const FastP& p, float x0, float u) {
     const float x = __fsub_rn(x0, __fmul_rn(u, p.dt));               // advect.py:35
-    const float rel = __fsub_rn(x, p.lower);
-    const float local = EXACT ? __fmul_rn(rel, p.inv_size) : __fdiv_rn(rel, p.size);   // _box.py:50-52
+    const float rel = EXACT == 2 ? x : __fsub_rn(x, p.lower);
+    const float local = EXACT == 2 ? rel : (EXACT ? __fmul_rn(rel, p.inv_size) : __fdiv_rn(rel, p.size));   // _box.py:50-52
     return __fsub_rn(__fmul_rn(local, p.nf), 0.5f);                  // grid.py:104-105
 }
 
@@ -64,7 +66,7 @@ struct Gathered {                    // what the forward step leaves behind for 
 };
 
 // one forward step of the row held in u[] (and mirrored in shared memory su[] by the caller) -> v[]
-template <int MODE, bool EXACT, int SUBSTEPS>
+template <int MODE, int EXACT, int SUBSTEPS>
 __device__ __forceinline__ void fast_forward(const FastP& p, const float (&x0)[4], const float (&u)[4], const float* su, int lane,
                                              float (&v)[4], Gathered& G) {
     float adv[4];
@@ -78,21 +80,19 @@ __device__ __forceinline__ void fast_forward(const FastP& p, const float (&x0)[4
             // products are exact negatives of each other: the sample is exactly +0 and so are its gradients.  One unsigned
             // compare decides; no float clamps.
             const float basef = floorf(xi);
-            const int bi = (int)fminf(fmaxf(basef, -2.0f), 130.0f);      // saturate far-away back-traces before the cast
+            const int bi = __float2int_rd(xi);                           // cvt.rmi.s32.f32 saturates: far-away back-traces stay outside
             const bool inside = (unsigned)bi < 127u;
             // monotonicity key for the adjoint's distinctness proof: strictly increasing over the lanes whenever the back-trace is
-            // monotone (left-outside lanes, then inside lanes, then right-outside lanes)
+            // monotone (left-outside lanes, then inside lanes, then right-outside lanes); inside <=> 0 <= key <= 126
             G.base[k] = inside ? bi : (bi < 0 ? lane - 200 : lane + 200);
             G.w0[k] = xi - basef;
             G.w1[k] = (basef + 1.0f) - xi;
-            const int fi = inside ? bi : 0;
-            G.pf[k] = skew(fi);
-            G.pc[k] = skew(fi + 1);
-            const float sf = su[G.pf[k]], sc = su[G.pc[k]];
-            const float val = __fadd_rn(__fmul_rn(sf, G.w1[k]), __fmul_rn(sc, G.w0[k]));     // tf_backend.py:491-497
-            adv[k] = inside ? val : 0.0f;
-            G.du[k] = inside ? sc - sf : 0.0f;
-            if (inside) G.active |= 1u << k;
+            G.pf[k] = skew(bi);
+            G.pc[k] = skew(bi + 1);
+            float sf = 0.0f, sc = 0.0f;                                  // outside: 0 * w1 + 0 * w0 = +0, du = 0
+            if (inside) { sf = su[G.pf[k]]; sc = su[G.pc[k]]; }
+            adv[k] = __fadd_rn(__fmul_rn(sf, G.w1[k]), __fmul_rn(sc, G.w0[k]));     // tf_backend.py:491-497
+            G.du[k] = sc - sf;
         } else {
             int fi, ci;
             interp_setup<MODE>(xi, 128, fi, ci, G.w0[k], G.w1[k]);
@@ -106,6 +106,7 @@ __device__ __forceinline__ void fast_forward(const FastP& p, const float (&x0)[4
             G.active |= 1u << k;
         }
     }
+    if (MODE == PDEC_MODE_CONSTANT) G.active = 0u;      // unused: activity is read off the key
     float left, right;
     edge_neighbours<MODE>(adv, lane, left, right);
 #pragma unroll
@@ -148,7 +149,7 @@ __device__ __forceinline__ void fast_adjoint(const FastP& p, const Gathered& G, 
     if (__all_sync(PDEC_FULL_MASK, ordered)) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const bool act = (G.active >> k) & 1u;
+            const bool act = MODE == PDEC_MODE_CONSTANT ? (unsigned)G.base[k] < 127u : ((G.active >> k) & 1u) != 0u;
             if (act) sacc[G.pf[k]] += g1[k] * G.w1[k];
             __syncwarp();
             if (act) sacc[G.pc[k]] += g1[k] * G.w0[k];
@@ -157,7 +158,7 @@ __device__ __forceinline__ void fast_adjoint(const FastP& p, const Gathered& G, 
     } else {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const bool act = (G.active >> k) & 1u;
+            const bool act = MODE == PDEC_MODE_CONSTANT ? (unsigned)G.base[k] < 127u : ((G.active >> k) & 1u) != 0u;
             warp_ordered_scatter_add(sacc, G.pf[k], g1[k] * G.w1[k], act);
             warp_ordered_scatter_add(sacc, G.pc[k], g1[k] * G.w0[k], act);
         }
@@ -177,8 +178,8 @@ __device__ __forceinline__ void row_to_smem(float* su, const float (&u)[4], int 
     __syncwarp();
 }
 
-template <int MODE, bool EXACT, bool L1TERM, int SUBSTEPS>
-__global__ void __launch_bounds__(256, 4) burgers_pair_loss_fast_kernel(FastP p, const float* __restrict__ s, float* __restrict__ grad_s,
+template <int MODE, int EXACT, bool L1TERM, int SUBSTEPS>
+__global__ void __launch_bounds__(256, 3) burgers_pair_loss_fast_kernel(FastP p, const float* __restrict__ s, float* __restrict__ grad_s,
                                                                       float2* partials, int T, int B, int C, int nchunks,
                                                                       unsigned* done_counter, float* __restrict__ losses, float inv_B) {
     __shared__ float smem[8][2][FAST_ROW];
@@ -223,9 +224,11 @@ __global__ void __launch_bounds__(256, 4) burgers_pair_loss_fast_kernel(FastP p,
         }
         float acc2 = 0.0f, acc1 = 0.0f;
         float4 pre = __ldcs(row + (size_t)(t0 + 1) * f4);                // streamed: every frame is read once per chunk
-        for (int t = t0; t < t1; ++t) {
+        const float4* pre_ptr = row + (size_t)(t0 + 2) * f4;             // running pointers: no 64-bit multiplies in the loop
+        float4* g_ptr = grow + (size_t)t0 * f4;
+        for (int t = t0; t < t1; ++t, pre_ptr += f4, g_ptr += f4) {
             nxt[0] = pre.x; nxt[1] = pre.y; nxt[2] = pre.z; nxt[3] = pre.w;
-            if (t + 2 <= T) pre = __ldcs(row + (size_t)(t + 2) * f4);       // prefetch: in flight during this pair's arithmetic
+            if (t + 2 <= T) pre = __ldcs(pre_ptr);                       // prefetch: in flight during this pair's arithmetic
             row_to_smem(su, u, lane);
             fast_forward<MODE, EXACT, SUBSTEPS>(p, x0, u, su, lane, v, G);
             float gd[4];
@@ -240,7 +243,7 @@ __global__ void __launch_bounds__(256, 4) burgers_pair_loss_fast_kernel(FastP p,
             }
             if (grad_s != nullptr) {
                 fast_adjoint<MODE>(p, G, g, sacc, lane, gin);
-                __stcs(grow + (size_t)t * f4, make_float4(gin[0] + carry[0], gin[1] + carry[1], gin[2] + carry[2], gin[3] + carry[3]));   // written once, never re-read here: evict-first
+                __stcs(g_ptr, make_float4(gin[0] + carry[0], gin[1] + carry[1], gin[2] + carry[2], gin[3] + carry[3]));   // written once, never re-read here: evict-first
             } else {
                 __syncwarp();
             }
@@ -321,7 +324,7 @@ int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials,
     p.dxi_du = -(p.nf / size) * p.dt;
     const float invB = 1.0f / (float)B;
     p.gl2 = gl2 * invB; p.gl1 = gl1 * invB;
-    const bool exact = is_pow2f(size) && is_pow2f(p.dx2);
+    const int exact = (is_pow2f(size) && is_pow2f(p.dx2)) ? ((lower == 0.0f && size == 1.0f) ? 2 : 1) : 0;
     const int C = pair_loss_chunk(B, T), nchunks = (T + C - 1) / C;
     if (cudaMemsetAsync(done_counter, 0, sizeof(unsigned), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
     const long long units = (long long)B * nchunks;
@@ -335,8 +338,9 @@ int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials,
     } while (0)
 #define PICK(M)                                                            \
     do {                                                                   \
-        if (exact) { if (l1) LAUNCH(M, true, true); else LAUNCH(M, true, false); }   \
-        else { if (l1) LAUNCH(M, false, true); else LAUNCH(M, false, false); }       \
+        if (exact == 2) { if (l1) LAUNCH(M, 2, true); else LAUNCH(M, 2, false); }        \
+        else if (exact == 1) { if (l1) LAUNCH(M, 1, true); else LAUNCH(M, 1, false); }   \
+        else { if (l1) LAUNCH(M, 0, true); else LAUNCH(M, 0, false); }                   \
     } while (0)
     if (mode == PDEC_MODE_CONSTANT) PICK(PDEC_MODE_CONSTANT);
     else if (mode == PDEC_MODE_REPLICATE) PICK(PDEC_MODE_REPLICATE);
