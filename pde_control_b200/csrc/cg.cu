@@ -325,8 +325,10 @@ __global__ void __launch_bounds__(32 * TY, 1) cg_tile_kernel(const float* __rest
 //     second stage reads the 2 x WARPS partials with one LDS per lane.
 // Per iteration: 3 barriers, ~24 shuffles, 20 128-bit shared-memory accesses and ~11 FP32 instructions per cell.
 // -------------------------------------------------------------------------------------------------------------
+// The reduction comes in two halves so that independent work can sit between them (in the shadow of the shuffle latency and the
+// barrier): _begin = warp butterfly + one partial per warp and value into shared memory; _end = barrier + second stage.
 template <int WARPS>
-__device__ __forceinline__ void block_reduce_pair(float& a, float& b, float* red, const bool second_is_max) {
+__device__ __forceinline__ void block_reduce_pair_begin(float a, float b, float* red, const bool second_is_max) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const bool hi = lane >= 16;
     const bool mx = hi && second_is_max;
@@ -339,6 +341,13 @@ __device__ __forceinline__ void block_reduce_pair(float& a, float& b, float* red
         keep = mx ? fmaxf(keep, recv) : keep + recv;
     }
     if ((lane & 15) == 0) red[(lane >> 4) * 16 + w] = keep;
+}
+template <int WARPS>
+__device__ __forceinline__ void block_reduce_pair_end(float& a, float& b, float* red, const bool second_is_max) {
+    const int lane = threadIdx.x & 31;
+    const bool hi = lane >= 16;
+    const bool mx = hi && second_is_max;
+    float recv;
     __syncthreads();
     if (WARPS >= 16) {      // throughput-bound iteration: one LDS + five shuffles per lane
         float v = red[lane];                                  // lane = value * 16 + warp
@@ -371,6 +380,11 @@ __device__ __forceinline__ void block_reduce_pair(float& a, float& b, float* red
         }
     a = ta[0];
     b = tb[0];
+}
+template <int WARPS>
+__device__ __forceinline__ void block_reduce_pair(float& a, float& b, float* red, const bool second_is_max) {
+    block_reduce_pair_begin<WARPS>(a, b, red, second_is_max);
+    block_reduce_pair_end<WARPS>(a, b, red, second_is_max);
 }
 
 template <int WARPS, bool FULL, bool FUSED>
@@ -487,8 +501,8 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
             block_reduce5<WARPS>(s1, s2, s4, s5, mx, red5[it & 1]);
             rmax = mx;
             if (!(it < max_it && (accuracy <= 0.0f || rmax >= accuracy))) break;
-            const float a = div_no_nan(s2, s1);
-            const float beta = div_no_nan(s4 - a * s5, s1);
+            const float a = div_no_nan_fast(s2, s1);
+            const float beta = div_no_nan_fast(s4 - a * s5, s1);
 #pragma unroll
             for (int ky = 0; ky < 8; ++ky) {
                 float4 x4 = sm_x[(i0 + ky) * 32 + tx];
@@ -518,7 +532,7 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
 #pragma unroll
             for (int c = 0; c < 32; ++c) { s1 += m[c] * am[c]; s2 += m[c] * r[c]; }
             block_reduce_pair<WARPS>(s1, s2, redA, false);
-            const float tmp = s1, a = div_no_nan(s2, tmp);
+            const float tmp = s1, a = div_no_nan_fast(s2, tmp);
             float s3 = 0.0f, mx = 0.0f;
 #pragma unroll
             for (int ky = 0; ky < 8; ++ky) {
@@ -534,7 +548,7 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
                 }
             }
             block_reduce_pair<WARPS>(s3, mx, redB, true);
-            const float beta = div_no_nan(s3, tmp);
+            const float beta = div_no_nan_fast(s3, tmp);
 #pragma unroll
             for (int c = 0; c < 32; ++c) m[c] = r[c] - beta * m[c];
             publish();                       // every edge-row read of the old m happened before reduction A's barrier

@@ -6,6 +6,10 @@ namespace pdec {
 
 // math.divide_no_nan (PF/math/blas.py:44,54)
 __device__ __forceinline__ float div_no_nan(float a, float b) { return b == 0.0f ? 0.0f : a / b; }
+// the same with the hardware reciprocal (<= 2 ulp): for the CG coefficients of the on-chip kernels, where every thread of the CTA
+// waits on this one division twice per iteration and the IEEE sequence is ~150 cycles of dependent instructions.  x and r are
+// updated with the SAME rounded coefficient, so the recurrence stays consistent; iterates are not the parity oracle.
+__device__ __forceinline__ float div_no_nan_fast(float a, float b) { return b == 0.0f ? 0.0f : __fdividef(a, b); }
 
 // Four sums and one maximum in ONE block reduction (one barrier).  Stage 1 is a transposing butterfly: at xor 16 the half-warps
 // trade two of the four sums, at xor 8 one of the remaining two, so lanes 0/8/16/24 end up with the warp totals of s1/s2/s4/s5
