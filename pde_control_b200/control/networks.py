@@ -6,12 +6,25 @@ Architectures restated from the reference (weights are NOT compatible with the T
   UNet      2-D u_net                  PF/tf/standard_networks.py:9-69 with conv_layer / residual_block
             PF/tf/grid_layers.py:6-51 and math.upsample2x PF/math/nd.py:353-368
 TF 'SYMMETRIC' padding of width 1 == torch 'replicate'; upsample2x (0.25/0.75 weights on a replicate-padded tensor) ==
-F.interpolate(scale_factor=2, mode='(bi)linear', align_corners=False).
+F.interpolate(scale_factor=2, mode='(bi)linear', align_corners=False); the 1-D case is written out (upsample2x_1d).
 Tensors enter and leave in the reference's channels-last layout.
 """
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
+
+
+def upsample2x_1d(y):
+    """math.upsample2x on [B, C, N] (PF/math/nd.py:353-368): 0.25/0.75 weights on a replicate-padded tensor.
+
+    Same values as F.interpolate(scale_factor=2, mode='linear', align_corners=False), written with slices because
+    aten's upsample_linear1d kernels serialise over batch x channels (12 ms per call at [4096, 16, 80] on a B200,
+    80 % of an OPResNet forward+backward; profiles/r1j_opnet_profile.md).
+    """
+    p = F.pad(y, (1, 1), mode="replicate")
+    even = 0.25 * p[..., :-2] + 0.75 * y
+    odd = 0.75 * y + 0.25 * p[..., 2:]
+    return torch.stack([even, odd], -1).flatten(-2)
 
 
 class _ResBlock(nn.Module):
@@ -61,7 +74,7 @@ class OPResNet(nn.Module):
             res.insert(0, y)
         y = self.center(y)
         for i, skip in enumerate(res[1:]):
-            y = F.interpolate(y, scale_factor=2, mode="linear", align_corners=False)
+            y = upsample2x_1d(y)
             y = torch.cat([y, skip[:, :, :y.shape[2]]], 1)
             y = self.up[i](F.pad(y, (0, 1), mode="replicate"))
             if i < len(res) - 2:

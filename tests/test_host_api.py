@@ -195,3 +195,23 @@ def test_control_training_learns_and_checkpoints(tmp_path):
     app.load_checkpoints({"OP2": os.path.join(d, "OP2.pt")})
     assert float(pde.networks["OP2"].weight) == w
     assert "Loss" in app.infer_scalars([0, 1])
+
+
+def test_upsample2x_1d_matches_aten_linear_and_the_reference_weights():
+    """networks.upsample2x_1d == F.interpolate(linear, align_corners=False) == upsample2x of PF/math/nd.py:353-368."""
+    from pde_control_b200.control.networks import upsample2x_1d, OPResNet
+    torch.manual_seed(0)
+    y = torch.randn(3, 5, 11)
+    ref = torch.nn.functional.interpolate(y, scale_factor=2, mode="linear", align_corners=False)
+    out = upsample2x_1d(y)
+    assert out.shape == ref.shape
+    np.testing.assert_allclose(out.numpy(), ref.numpy(), rtol=1e-6, atol=1e-6)
+    # reference recipe written out in numpy: replicate pad, (0.25 lower + 0.75 centre, 0.75 centre + 0.25 upper) interleaved
+    a = y.numpy(); p = np.pad(a, ((0, 0), (0, 0), (1, 1)), mode="edge")
+    exp = np.stack([0.25 * p[..., :-2] + 0.75 * a, 0.75 * a + 0.25 * p[..., 2:]], -1).reshape(3, 5, 22)
+    np.testing.assert_allclose(out.numpy(), exp, rtol=1e-6, atol=1e-6)
+    net = OPResNet()
+    o = net(torch.randn(2, 128, 1), torch.randn(2, 128, 1))
+    assert o.shape == (2, 128, 1)
+    o.sum().backward()
+    assert all(q.grad is not None for q in net.parameters())
