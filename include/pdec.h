@@ -95,6 +95,23 @@ int pdec_burgers_pair_loss(const float* s, float* grad_s, float* losses, int T, 
                            double viscosity, float box_lower, float box_size, int substeps, int resubstep,
                            float gl2, float gl1, void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same force loss fed from HOST arrays: what the reference does every optimisation step through
+ * session.run(fetches, feed_dict) (src/control/control_training.py:113-142, PF/tf/session.py:30-70 copies every fed array to
+ * the device and every fetched one back).  s_host [T+1,B,n], grad_host [T+1,B,n] or NULL and losses_host[2] are HOST pointers
+ * (page-locked for the copies to be asynchronous).  The batch is cut into chunks of `chunk_rows` rows; H2D of chunk c+1, the
+ * fused kernel of chunk c and D2H of chunk c-1 overlap on three streams owned by the pipeline object, which also owns the
+ * device staging (allocated by _create, never by the call).  The call is ordered on `stream` like a kernel launch: it starts
+ * after the work already enqueued there and `stream` waits for the last copy; the host buffers are valid after
+ * synchronising `stream`.  Results equal pdec_burgers_pair_loss on the whole batch (the gradient bit for bit when
+ * B / chunk_rows is a power of two; the loss scalars are summed chunk by chunk in ascending order).
+ * max_chunks bounds B <= chunk_rows * max_chunks. */
+typedef struct pdec_host_pipeline pdec_host_pipeline;
+int pdec_host_pipeline_create(pdec_host_pipeline** pipeline, int chunk_rows, int n, int T, int max_chunks);
+int pdec_host_pipeline_destroy(pdec_host_pipeline* pipeline);
+int pdec_burgers_pair_loss_host(pdec_host_pipeline* pipeline, const float* s_host, float* grad_host, float* losses_host, int T,
+                                int B, int n, int mode, double dt, double viscosity, float box_lower, float box_size,
+                                int substeps, int resubstep, float gl2, float gl1, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * 2-D incompressible flow  
  * Layouts: rho[B,ny,nx], vy[B,ny+1,nx], vx[B,ny,nx+1] (PF/physics/field/staggered_grid.py:33-39), axis 0 = y.

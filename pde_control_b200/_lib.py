@@ -6,7 +6,7 @@ import ctypes
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libpdec.so")
+LIB_PATH = os.environ.get("PDEC_LIB_PATH") or os.path.join(HERE, "libpdec.so")     # override: A/B builds (scripts/diag)
 
 MODE_CONSTANT, MODE_REPLICATE, MODE_CIRCULAR = 0, 1, 2
 EFFECT_NONE, EFFECT_GROW, EFFECT_ADD = 0, 1, 2
@@ -39,6 +39,10 @@ _SIGNATURES = {
     "pdec_burgers_pair_loss": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _c.c_double,
                                            _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_float, _c.c_float, _P,
                                            _c.c_size_t, _P]),
+    "pdec_host_pipeline_create": (_c.c_int, [_c.POINTER(_P), _c.c_int, _c.c_int, _c.c_int, _c.c_int]),
+    "pdec_host_pipeline_destroy": (_c.c_int, [_P]),
+    "pdec_burgers_pair_loss_host": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _c.c_double,
+                                                _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_float, _c.c_float, _P]),
     # ---- 2-D incompressible flow ----
     "pdec_curl_2d_fwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),
     "pdec_curl_2d_bwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),

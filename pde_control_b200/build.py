@@ -19,6 +19,7 @@ SOURCES = {
     "abi.cu": [],
     "burgers.cu": ["-fmad=false"],
     "burgers_fast.cu": [],          # forward op order spelled out with __f*_rn intrinsics; adjoint may contract
+    "burgers_fast2.cu": [],         # same, packed fp32 (f32x2) forward
     "fluid.cu": ["-fmad=false"],
     "cg.cu": [],
     "cg_tiled.cu": [],
@@ -45,8 +46,14 @@ def build(force=False, verbose=False):
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
     objs = []
+    headers = [os.path.join(CSRC, "pdec_common.cuh"), os.path.join(CSRC, "cg_reduce.cuh"),
+               os.path.join(HERE, "..", "include", "pdec.h"), __file__]
     for src, flags in _sources():
         obj = os.path.join(objdir, os.path.basename(src) + ".o")
+        objs.append(obj)
+        if not force and not verbose and os.path.exists(obj) and all(
+                os.path.getmtime(d) <= os.path.getmtime(obj) for d in [src] + headers if os.path.exists(d)):
+            continue        # object newer than its source and the shared headers
         cmd = [NVCC] + [f for f in COMMON if f != "--use_fast_math=false"] + flags + ["-c", src, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
@@ -55,7 +62,6 @@ def build(force=False, verbose=False):
             raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))
         if verbose:
             print(r.stderr)
-        objs.append(obj)
     cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-lcudart"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:

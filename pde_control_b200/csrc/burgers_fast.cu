@@ -15,6 +15,7 @@
 //     function of the data only: bit-reproducible.
 // A chunk that does not start at frame 0 recomputes the residual of the pair before it (one extra forward step per chunk)
 // instead of exchanging it with the neighbouring warp; chunking exists so that B x T/C warps fill the 148 SMs.
+#include <cstdlib>
 #include "pdec_common.cuh"
 
 namespace pdec {
@@ -306,6 +307,10 @@ static int pair_loss_chunk(int B, int T) {
     return C;
 }
 
+// burgers_fast2.cu: packed-fp32 / float2-tap kernel for 'constant' rows on the unit box with one diffusion substep
+int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int C, int nchunks, double dt, double viscosity,
+                                float gl2, float gl1, unsigned* done_counter, float* losses, cudaStream_t st);
+
 // returns PDEC_OK if it handled the call, 1 if the shape is not eligible (caller uses the general kernel)
 int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials, int T, int B, int n, int mode, double dt, double viscosity,
                                 float lower, float size, int substeps, int resubstep, float gl2, float gl1, unsigned* done_counter,
@@ -327,6 +332,11 @@ int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials,
     const int exact = (is_pow2f(size) && is_pow2f(p.dx2)) ? ((lower == 0.0f && size == 1.0f) ? 2 : 1) : 0;
     const int C = pair_loss_chunk(B, T), nchunks = (T + C - 1) / C;
     if (cudaMemsetAsync(done_counter, 0, sizeof(unsigned), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+    if (mode == PDEC_MODE_CONSTANT && exact == 2 && substeps == 1 && getenv("PDEC_BURGERS_FAST_V1") == nullptr) {
+        // headline case (BASELINE configs 2 and 4)
+        const int rc = pdec_burgers_pair_loss_unit(s, grad_s, partials, T, B, C, nchunks, dt, viscosity, gl2, gl1, done_counter, losses, st);
+        if (rc <= 0) return rc;
+    }
     const long long units = (long long)B * nchunks;
     long long grid = (units + 7) / 8;
     if (grid > 148LL * 64) grid = 148LL * 64;

@@ -130,6 +130,61 @@ def burgers_pair_loss_raw(s, grad_out, losses_out, workspace, dt, viscosity, low
     _lib.check(rc, "pdec_burgers_pair_loss")
 
 
+class HostPipeline(object):
+    """Force loss fed from page-locked HOST arrays (the reference feeds and fetches host arrays every optimisation step:
+    src/control/control_training.py:113-142 through PF/tf/session.py).  Owns three streams and the device staging of
+    pdec_host_pipeline (include/pdec.h); `chunk_rows` rows of the batch travel per leg, so H2D, the fused kernel and D2H of
+    neighbouring chunks overlap."""
+
+    def __init__(self, n, T, chunk_rows=256, max_batch=1 << 20, device=None):
+        import ctypes
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.n, self.T, self.chunk_rows = int(n), int(T), int(chunk_rows)
+        self.max_chunks = (int(max_batch) + self.chunk_rows - 1) // self.chunk_rows
+        h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            rc = _lib.lib().pdec_host_pipeline_create(ctypes.byref(h), self.chunk_rows, self.n, self.T, self.max_chunks)
+        _lib.check(rc, "pdec_host_pipeline_create")
+        self._h = h
+
+    def pair_loss(self, s_host, grad_host, losses_host, dt, viscosity, lower=0.0, size=1.0, mode=MODE_CONSTANT, substeps=1,
+                  resubstep=False, gl2=1.0, gl1=0.0):
+        """s_host [T+1,B,n], grad_host (same shape, or None: losses only), losses_host [2]: contiguous fp32 CPU tensors,
+        pinned.  Asynchronous on the current stream of the pipeline's device; synchronise it before reading the outputs."""
+        for t in (s_host, grad_host, losses_host):
+            if t is None:
+                continue
+            if t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
+                raise ValueError("host pipeline takes contiguous fp32 CPU tensors")
+            if not t.is_pinned():
+                raise ValueError("host pipeline needs page-locked (pinned) host tensors")
+        T1, B, n = s_host.shape
+        if grad_host is not None and tuple(grad_host.shape) != (T1, B, n):
+            raise ValueError("grad_host must have the shape of s_host")
+        if losses_host.numel() != 2:
+            raise ValueError("losses_host must hold 2 floats")
+        import ctypes
+        with torch.cuda.device(self.device):
+            rc = _lib.lib().pdec_burgers_pair_loss_host(
+                self._h, ctypes.c_void_p(s_host.data_ptr()), None if grad_host is None else ctypes.c_void_p(grad_host.data_ptr()),
+                ctypes.c_void_p(losses_host.data_ptr()), T1 - 1, B, n, int(mode), float(dt), float(viscosity), float(lower),
+                float(size), int(substeps), int(resubstep), float(gl2), float(gl1), _lib.stream_ptr())
+        _lib.check(rc, "pdec_burgers_pair_loss_host")
+
+    def close(self):
+        if self._h is not None:
+            with torch.cuda.device(self.device):
+                torch.cuda.synchronize()
+                _lib.lib().pdec_host_pipeline_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 # ------------------------------------------------------------------------------------------------
 # 2-D incompressible flow.  Layouts: rho[B,ny,nx], vy[B,ny+1,nx], vx[B,ny,nx+1]; axis 0 = y.
 # box = (lower_y, lower_x, size_y, size_x) of the domain; None -> AABox(0, resolution) (dx = 1).

@@ -172,6 +172,43 @@ def test_full_size_config2_properties():
     assert abs(l2.item() - tot) < 1e-4 * tot
 
 
+@pytest.mark.parametrize("B,chunk_rows,n,T", [(512, 128, 128, 8), (300, 128, 128, 5), (40, 16, 50, 3), (64, 256, 128, 4)])
+def test_host_pipeline_equals_resident_call(B, chunk_rows, n, T):
+    """pdec_burgers_pair_loss_host (chunked H2D / kernel / D2H over three streams) == the resident single launch:
+    gradient bit for bit when the chunk scale is a power of two, else to rounding of the 1/B scale; losses to 1e-6;
+    ragged last chunk, a batch smaller than one chunk, the general-n kernel and two calls in a row (slot re-use)."""
+    ops = _ops()
+    rng = np.random.RandomState(B + T)
+    s = np.stack([R.gaussian_clash(B, n, rng) for _ in range(T + 1)]).astype(np.float32)
+    s += 0.02 * rng.randn(*s.shape).astype(np.float32)
+    sc = torch.tensor(s, device="cuda", requires_grad=True)
+    l2, l1 = ops.burgers_pair_loss(sc, 0.03, 0.003)
+    l2.backward()
+    pipe = ops.HostPipeline(n, T, chunk_rows=chunk_rows, max_batch=1024)
+    hs = torch.tensor(s).pin_memory()
+    hg = torch.full(s.shape, float("nan")).pin_memory()
+    hl = torch.zeros(2).pin_memory()
+    for _ in range(2):
+        hg.fill_(float("nan"))
+        pipe.pair_loss(hs, hg, hl, 0.03, 0.003)
+        torch.cuda.current_stream().synchronize()
+        pow2 = B % chunk_rows == 0 and ((B // chunk_rows) & (B // chunk_rows - 1)) == 0 or B <= chunk_rows
+        if pow2:
+            assert torch.equal(hg, sc.grad.cpu())
+        else:
+            assert rel_err(hg, sc.grad.cpu()) < 1e-6
+        assert abs(hl[0].item() - l2.item()) <= 1e-6 * abs(l2.item())
+        assert abs(hl[1].item() - l1.item()) <= 1e-6 * abs(l1.item())
+    # losses only
+    hl.zero_()
+    pipe.pair_loss(hs, None, hl, 0.03, 0.003)
+    torch.cuda.current_stream().synchronize()
+    assert abs(hl[0].item() - l2.item()) <= 1e-6 * abs(l2.item())
+    with pytest.raises(ValueError):
+        pipe.pair_loss(torch.tensor(s), hg, hl, 0.03, 0.003)        # not pinned
+    pipe.close()
+
+
 def test_edge_cases_empty_batch_and_bad_arguments():
     ops = _ops()
     from pde_control_b200._lib import PdecError
