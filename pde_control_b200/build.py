@@ -19,7 +19,7 @@ SOURCES = {
     "abi.cu": [],
     "burgers.cu": ["-fmad=false"],
     "burgers_fast.cu": [],          # forward op order spelled out with __f*_rn intrinsics; adjoint may contract
-    "burgers_fast2.cu": [],         # same, packed fp32 (f32x2) forward
+    "burgers_fast2.cu": ["-fmad=false"],    # nvcc contracts __fmul2_rn + __fadd2_rn into FFMA2 (unlike the scalar _rn intrinsics): off; the adjoint calls fmaf / __ffma2_rn explicitly
     "fluid.cu": ["-fmad=false"],
     "cg.cu": [],
     "cg_tiled.cu": [],

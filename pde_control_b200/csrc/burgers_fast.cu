@@ -308,8 +308,8 @@ static int pair_loss_chunk(int B, int T) {
 }
 
 // burgers_fast2.cu: packed-fp32 / float2-tap kernel for 'constant' rows on the unit box with one diffusion substep
-int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int C, int nchunks, double dt, double viscosity,
-                                float gl2, float gl1, unsigned* done_counter, float* losses, cudaStream_t st);
+int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, double dt, double viscosity, float gl2, float gl1,
+                                unsigned* done_counter, float* losses, cudaStream_t st);
 
 // returns PDEC_OK if it handled the call, 1 if the shape is not eligible (caller uses the general kernel)
 int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials, int T, int B, int n, int mode, double dt, double viscosity,
@@ -334,7 +334,7 @@ int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials,
     if (cudaMemsetAsync(done_counter, 0, sizeof(unsigned), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
     if (mode == PDEC_MODE_CONSTANT && exact == 2 && substeps == 1 && getenv("PDEC_BURGERS_FAST_V1") == nullptr) {
         // headline case (BASELINE configs 2 and 4)
-        const int rc = pdec_burgers_pair_loss_unit(s, grad_s, partials, T, B, C, nchunks, dt, viscosity, gl2, gl1, done_counter, losses, st);
+        const int rc = pdec_burgers_pair_loss_unit(s, grad_s, partials, T, B, dt, viscosity, gl2, gl1, done_counter, losses, st);
         if (rc <= 0) return rc;
     }
     const long long units = (long long)B * nchunks;

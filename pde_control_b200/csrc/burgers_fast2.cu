@@ -1,20 +1,22 @@
 // burgers_fast2.cu -- second-generation fused force-loss kernel for the headline case of BASELINE config 2: rows of 128 cells on
-// the unit box, 'constant' extrapolation, one diffusion substep (SURVEY rows B1-B6 in one launch).  Same work split as
-// burgers_fast.cu (one warp per (row, chunk of frame pairs), lane l owns cells 4l..4l+3, one 16-byte load / store per frame) but
-// built around what the B200 issue model charges for (scripts/diag/f32x2_throughput.cu: the integer/ALU pipe runs at half rate,
-// a packed fp32 instruction does two lane-operations in one issue slot):
-//   * the fp32 chains run on PAIRS of cells with add/mul/fma.rn.f32x2 -- explicit round-to-nearest, so the forward step still
-//     rounds exactly like the reference's unfused TF ops (same operation order as burgers_fast.cu / burgers.cu);
-//   * shared memory holds the gather source as float2 (u[j], u[j+1]) per cell, so ONE 8-byte load brings both taps of the linear
-//     interpolation and one address computation serves both; the transpose accumulator is float2 as well ((floor, ceil) parts of
-//     the same back-traced sample), so the scatter is one read-modify-write per sample instead of two;
-//   * out-of-domain samples ('constant' rule: exactly +0 and zero gradient, tf_backend.py:466-497) read a dedicated zero slot
-//     and scatter into a dummy slot instead of being predicated; their index needs no clamping (one unsigned compare);
-//   * index arithmetic is folded: xi = (i + 0.5) - u * (128 dt) - 0.5 is bit-identical to the reference's
-//     ((x0 - u dt) - lower) / size * N - 0.5 on the unit box (x0 = (2i+1)/256 exactly; scaling by 128 commutes with rounding);
-//     a * (raw / dx^2) = (a / dx^2) * raw because 1/dx^2 = 2^14.
-// Slots are skewed by one float2 per 16 (pskew) so that the 16 lanes of a shared-memory wavefront, which touch every 4th cell,
-// fall into 16 different bank pairs.
+// the unit box, 'constant' extrapolation, one diffusion substep (SURVEY rows B1-B6 in one launch).  One warp per row segment,
+// lane l owns cells 4l..4l+3 (one 16-byte load / store per frame), as in burgers_fast.cu, but shaped by three measurements
+// (profiles/r1k_burgers_summary.md):
+//   (1) the integer/ALU pipe runs at half rate and a packed fp32 instruction does two lane-operations in one issue slot
+//       (scripts/diag/f32x2_throughput.cu): the fp32 chains run on PAIRS of cells with add/mul/fma.rn.f32x2 -- explicit
+//       round-to-nearest, so the forward step still rounds exactly like the reference's unfused TF ops;
+//   (2) with the instruction count halved the kernel is bound by shared-memory wavefronts, a third of them bank conflicts of the
+//       data-dependent gathers/scatters: the row lives in shared memory TRANSPOSED, word(j) = (j & 3) * 32 + (j >> 2), i.e. bank =
+//       j >> 2.  Four ADJACENT cells share a bank, so two lanes of one instruction (whose back-traced indices increase with the
+//       lane) can only collide where the flow compresses 4 cells into fewer than 4 (shocks) -- never in smooth or expanding
+//       regions -- and a lane's own four cells sit in its own bank (own-row stores / loads are conflict-free);
+//   (3) 1024 CTAs over 148 x 3 resident slots left the SMs idle 22 % of the time (tail): the (row, pair) space is cut into
+//       equal contiguous ranges, one per resident warp, crossing row boundaries; a range that starts inside a row recomputes
+//       the residual of the pair before it (one extra forward step per ~37 pairs).
+// Index arithmetic is folded without changing a bit: xi = ((i + 0.5) - u * (128 dt)) - 0.5 equals the reference's
+// ((x0 - u dt) - lower) / size * N - 0.5 on the unit box (x0 = (2i+1)/256 exactly; scaling by 128 commutes with rounding) and
+// a * (raw / dx^2) = (a / dx^2) * raw because 1/dx^2 = 2^14.  Out-of-domain samples ('constant' rule: exactly +0 and zero
+// gradient, tf_backend.py:466-497) are redirected to zero / dummy words instead of being predicated.
 // The adjoint scatter is deterministic without atomics as in burgers_fast.cu: if floor(xi) is strictly increasing over the lanes
 // of one warp instruction the targets are distinct (plain read-modify-write); otherwise lanes take turns in ascending order.
 #include "pdec_common.cuh"
@@ -27,19 +29,12 @@ struct Unit2P {
     float gl2, gl1;  // dL/d(l2), dL/d(l1), already divided by B
 };
 
-#define F2_ROW 144                    // 128 + 7 skew slots, rounded up; slot 143 = zero (source row) / dummy (accumulator row)
-#define F2_DUMMY 143
-constexpr int kUnroll =
-#ifdef F2_UNROLL
-    F2_UNROLL;
-#else
-    2;
-#endif
+// shared-memory row: words 0..127 = cells (transposed), words 128 and 160 = the taps of an out-of-domain sample (zero in the
+// source row, scratch in the accumulator row); byte offset of cell j = j + (j & 3) * 127
+#define F2_ROW 164
+#define F2_OUT 512                    // "floor index" given to out-of-domain samples: taps at bytes 512 and 640
 #ifndef F2_MINB
-#define F2_MINB 4
-#endif
-#ifndef F2_UNROLL
-#define F2_UNROLL 2
+#define F2_MINB 3
 #endif
 
 __device__ __forceinline__ float2 f2(float x, float y) { return make_float2(x, y); }
@@ -47,19 +42,18 @@ __device__ __forceinline__ float2 sub2(float2 a, float2 b) { return __ffma2_rn(b
 
 struct Step2 {                        // what the forward step leaves for its adjoint
     int bi[4];                        // floor(xi)
-    int slot[4];                      // skewed slot of the sample (dummy when outside)
+    unsigned offF[4], offC[4];        // byte offsets of the floor / ceil tap inside a row
     float2 w0[2], w1[2];              // weight of the ceil / floor tap, cells (0,1) and (2,3)
     float du[4];                      // u[ceil] - u[floor]
 };
 
-// forward step of the row (u01, u23) -> (v01, v23); su2 = this warp's source row, mine = su2 + pskew(4 lane)
-__device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float2 X23, float2 u01, float2 u23, float2* su2, float2* mine,
-                                              int lane, float2& v01, float2& v23, Step2& S) {
-    const float unext = __shfl_down_sync(PDEC_FULL_MASK, u01.x, 1);    // u[4l+4]; lane 31: unused tap of cell 127
-    mine[0] = u01;
-    mine[1] = f2(u01.y, u23.x);
-    mine[2] = u23;
-    mine[3] = f2(u23.y, unext);
+__device__ __forceinline__ float lds_off(const float* row, unsigned off) { return *reinterpret_cast<const float*>(reinterpret_cast<const char*>(row) + off); }
+__device__ __forceinline__ float* ptr_off(float* row, unsigned off) { return reinterpret_cast<float*>(reinterpret_cast<char*>(row) + off); }
+
+// forward step of the row (u01, u23) -> (v01, v23); su = this warp's source row, mine = su + lane (own cells at mine[32 k])
+__device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float2 X23, float2 u01, float2 u23, float* su, float* mine, int lane,
+                                              float2& v01, float2& v23, Step2& S) {
+    mine[0] = u01.x; mine[32] = u01.y; mine[64] = u23.x; mine[96] = u23.y;
     __syncwarp();
     const float2 dt2 = f2(p.dt128, p.dt128), half2v = f2(-0.5f, -0.5f), one2 = f2(1.0f, 1.0f);
     // advect.py:35, _box.py:50-52, grid.py:104-105 folded (see the header): xi = ((i + 0.5) - u * 128dt) - 0.5
@@ -84,11 +78,12 @@ __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float
     float adv[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const int b = S.bi[k];
-        S.slot[k] = (unsigned)b < 127u ? b + (b >> 4) : F2_DUMMY;
-        const float2 tap = su2[S.slot[k]];                             // (u[floor], u[floor + 1]) or (0, 0)
-        adv[k] = __fadd_rn(__fmul_rn(tap.x, w1[k]), __fmul_rn(tap.y, w0[k]));   // tf_backend.py:491-497
-        S.du[k] = tap.y - tap.x;
+        const unsigned b = (unsigned)S.bi[k] < 127u ? (unsigned)S.bi[k] : (unsigned)F2_OUT;
+        S.offF[k] = b + (b & 3u) * 127u;
+        S.offC[k] = b + ((b + 1u) & 3u) * 127u + 1u;
+        const float tf = lds_off(su, S.offF[k]), tc = lds_off(su, S.offC[k]);     // (u[floor], u[floor + 1]) or (0, 0)
+        adv[k] = __fadd_rn(__fmul_rn(tf, w1[k]), __fmul_rn(tc, w0[k]));           // tf_backend.py:491-497
+        S.du[k] = tc - tf;
     }
     float left = __shfl_up_sync(PDEC_FULL_MASK, adv[3], 1), right = __shfl_down_sync(PDEC_FULL_MASK, adv[0], 1);
     if (lane == 0) left = 0.0f;                                        // zero padding of the 'constant' field (nd.py:271-283)
@@ -99,14 +94,17 @@ __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float
     // util.py:41-43 folded into one multiply (power-of-two dx^2); then u + increment
     const float2 raw01 = __ffma2_rn(a01, m2, __fadd2_rn(mid, f2(left, adv[0])));
     const float2 raw23 = __ffma2_rn(a23, m2, __fadd2_rn(f2(adv[3], right), mid));
-    v01 = __fadd2_rn(a01, __fmul2_rn(raw01, c2v));
-    v23 = __fadd2_rn(a23, __fmul2_rn(raw23, c2v));
+    // ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under --fmad=false (it never touches the scalar .rn forms; measured:
+    // scripts/diag/dump_forward.py): the final sum u + increment is done with scalar adds
+    const float2 inc01 = __fmul2_rn(raw01, c2v), inc23 = __fmul2_rn(raw23, c2v);
+    v01 = f2(__fadd_rn(adv[0], inc01.x), __fadd_rn(adv[1], inc01.y));
+    v23 = f2(__fadd_rn(adv[2], inc23.x), __fadd_rn(adv[3], inc23.y));
 }
 
 // adjoint of one step.  h = -(dL/d step output) on entry (the caller keeps the sign of the residual gradient); returns dL/d(step
-// input) in (gin01, gin23).  The accumulator row is all-zero on entry (own slots) and again on exit.
-__device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, float2 h01, float2 h23, float2* sacc2, float2* mine_acc,
-                                              int lane, float2& gin01, float2& gin23) {
+// input) in (gin01, gin23).  The accumulator row's cell words are all-zero on entry and again on exit.
+__device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, float2 h01, float2 h23, float* sacc, float* mine_acc, int lane,
+                                              float2& gin01, float2& gin23) {
     float hl = __shfl_up_sync(PDEC_FULL_MASK, h23.y, 1), hr = __shfl_down_sync(PDEC_FULL_MASK, h01.x, 1);
     if (lane == 0) hl = 0.0f;
     if (lane == 31) hr = 0.0f;
@@ -123,80 +121,102 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
         const int prev = __shfl_up_sync(PDEC_FULL_MASK, S.bi[k], 1);
         ordered = ordered && (lane == 0 || S.bi[k] > prev);
     }
+#ifdef F2_SKIP_SCATTER
+    if (false) {
+#else
     if (__all_sync(PDEC_FULL_MASK, ordered)) {
-        // strictly increasing floor(xi) over the lanes: the in-domain targets of one warp instruction are distinct
+#endif
+        // strictly increasing floor(xi) over the lanes: the in-domain targets of one warp instruction are distinct (floor targets
+        // among themselves, ceil targets among themselves); out-of-domain lanes all hit the scratch words
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            float2 a = sacc2[S.slot[k]];
-            a.x = fmaf(-q[k], w1[k], a.x);
-            a.y = fmaf(-q[k], w0[k], a.y);
-            sacc2[S.slot[k]] = a;
+            float* af = ptr_off(sacc, S.offF[k]);
+            *af = fmaf(-q[k], w1[k], *af);
+            __syncwarp();
+            float* ac = ptr_off(sacc, S.offC[k]);
+            *ac = fmaf(-q[k], w0[k], *ac);
             __syncwarp();
         }
-    } else {
-        // folded back-trace (a shock steeper than one cell per cell): lanes take turns, ascending -- same sums, fixed order
+    } else
+#ifdef F2_SKIP_SCATTER
+    if (false)
+#endif
+    {
+        // folded back-trace (a shock steeper than one cell per cell): lanes that share a floor index are ranked by lane id
+        // (match_any) and take turns by rank -- same sums in a fixed order, as many rounds as the largest group
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-#pragma unroll 1
-            for (int turn = 0; turn < 32; ++turn) {
-                if (lane == turn && S.slot[k] != F2_DUMMY) {
-                    float2 a = sacc2[S.slot[k]];
-                    a.x = fmaf(-q[k], w1[k], a.x);
-                    a.y = fmaf(-q[k], w0[k], a.y);
-                    sacc2[S.slot[k]] = a;
+            const bool inside = (unsigned)S.bi[k] < 127u;
+            const unsigned peers = __match_any_sync(PDEC_FULL_MASK, inside ? S.bi[k] : -1 - lane);
+            const int rank = __popc(peers & ((1u << lane) - 1u));
+            for (int r = 0; __any_sync(PDEC_FULL_MASK, inside && rank >= r); ++r) {
+                if (inside && rank == r) {
+                    float* af = ptr_off(sacc, S.offF[k]);
+                    *af = fmaf(-q[k], w1[k], *af);
+                }
+                __syncwarp();
+                if (inside && rank == r) {
+                    float* ac = ptr_off(sacc, S.offC[k]);
+                    *ac = fmaf(-q[k], w0[k], *ac);
                 }
                 __syncwarp();
             }
         }
     }
-    // cell j receives the floor part of slot j and the ceil part of slot j - 1, plus the derivative through xi(u)
-    const float2 o0 = mine_acc[0], o1 = mine_acc[1], o2 = mine_acc[2], o3 = mine_acc[3];
-    float cprev = __shfl_up_sync(PDEC_FULL_MASK, o3.y, 1);
-    if (lane == 0) cprev = 0.0f;
-    const float2 z = f2(0.0f, 0.0f);
-    mine_acc[0] = z; mine_acc[1] = z; mine_acc[2] = z; mine_acc[3] = z;
+    // transpose of the gather (own four cells) plus the derivative through xi(u)
+    const float o0 = mine_acc[0], o1 = mine_acc[32], o2 = mine_acc[64], o3 = mine_acc[96];
+    mine_acc[0] = 0.0f; mine_acc[32] = 0.0f; mine_acc[64] = 0.0f; mine_acc[96] = 0.0f;
     const float2 dt2 = f2(p.dt128, p.dt128);
     const float2 e01 = __fmul2_rn(f2(S.du[0], S.du[1]), dt2), e23 = __fmul2_rn(f2(S.du[2], S.du[3]), dt2);   // -du * dxi/du
-    gin01 = __ffma2_rn(q01, e01, __fadd2_rn(f2(o0.x, o1.x), f2(cprev, o0.y)));
-    gin23 = __ffma2_rn(q23, e23, __fadd2_rn(f2(o2.x, o3.x), f2(o1.y, o2.y)));
+    gin01 = __ffma2_rn(q01, e01, f2(o0, o1));
+    gin23 = __ffma2_rn(q23, e23, f2(o2, o3));
     __syncwarp();
 }
 
 __device__ __forceinline__ float sgn(float d) { return (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f); }
 
+// Work = the B x T (row, pair) space in row-major order, cut into gridDim.x * 8 equal contiguous ranges (one per warp).  A warp
+// walks the FRAMES of its range -- (b, f), f = 0..T, then row b + 1 -- with the next frame always in flight; consecutive frames
+// of one row form a pair, the step from frame T of a row to frame 0 of the next one only closes the row.
 template <bool L1TERM>
 __global__ void __launch_bounds__(256, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
-                                                                      float2* partials, int T, int B, int C, int nchunks,
-                                                                      unsigned* done_counter, float* __restrict__ losses, float inv_B) {
-    __shared__ float2 smem[8][2][F2_ROW];
+                                                                            float2* partials, int T, int B, long long per_warp,
+                                                                            unsigned* done_counter, float* __restrict__ losses, float inv_B) {
+    __shared__ float smem[8][2][F2_ROW];
     __shared__ float red2[8], red1[8];
     __shared__ unsigned s_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float2* su2 = smem[warp][0];
-    float2* sacc2 = smem[warp][1];
-    for (int q = lane; q < F2_ROW; q += 32) { su2[q] = f2(0.0f, 0.0f); sacc2[q] = f2(0.0f, 0.0f); }
+    float* su = smem[warp][0];
+    float* sacc = smem[warp][1];
+    for (int q = lane; q < F2_ROW; q += 32) { su[q] = 0.0f; sacc[q] = 0.0f; }
     __syncwarp();
-    const int own = 4 * lane + (lane >> 2);                           // pskew(4 lane); cells 4l..4l+3 never straddle a skew step
-    float2* mine = su2 + own;
-    float2* mine_acc = sacc2 + own;
+    float* mine = su + lane;
+    float* mine_acc = sacc + lane;
     const float2 X01 = f2((float)(4 * lane) + 0.5f, (float)(4 * lane) + 1.5f), X23 = f2((float)(4 * lane) + 2.5f, (float)(4 * lane) + 3.5f);
     const size_t f4 = (size_t)B * 32;                                 // float4 stride between frames
-    const long long units = (long long)B * nchunks;
+    const float4* s4 = reinterpret_cast<const float4*>(s) + lane;
+    float4* g4 = grad_s ? reinterpret_cast<float4*>(grad_s) + lane : nullptr;
     const float2 gl2v = f2(p.gl2, p.gl2);
-    for (long long unit = (long long)blockIdx.x * 8 + warp; unit < units; unit += (long long)gridDim.x * 8) {
-        const int chunk = (int)(unit / B), b = (int)(unit - (long long)chunk * B);      // consecutive warps -> consecutive rows
-        const int t0 = chunk * C, t1 = min(T, t0 + C);
-        const float4* row = reinterpret_cast<const float4*>(s + (size_t)b * 128) + lane;
-        float4* grow = grad_s ? reinterpret_cast<float4*>(grad_s + (size_t)b * 128) + lane : nullptr;
+    const long long total = (long long)B * T;
+    const long long P0 = ((long long)blockIdx.x * 8 + warp) * per_warp;
+    const long long P1 = min(total, P0 + per_warp);
+    float2 acc2 = f2(0.0f, 0.0f);
+    float acc1 = 0.0f;
+    if (P0 < P1) {
+        int b = (int)(P0 / T), f = (int)(P0 - (long long)b * T);       // frame held in u
+        const int b_last = (int)((P1 - 1) / T), t_last = (int)((P1 - 1) - (long long)b_last * T);
+        // frames to walk: from (b, f) to (b_last, t_last + 1)
+        const long long nframes = ((long long)b_last * (T + 1) + t_last + 1) - ((long long)b * (T + 1) + f) + 1;
+        size_t off = (size_t)f * f4 + (size_t)b * 32;                  // float4 offset of frame (b, f)
         float2 u01, u23, carry01 = f2(0.0f, 0.0f), carry23 = f2(0.0f, 0.0f), v01, v23;
         Step2 S;
         {
-            const float4 q = row[(size_t)t0 * f4];
+            const float4 q = s4[off];
             u01 = f2(q.x, q.y); u23 = f2(q.z, q.w);
         }
-        if (t0 > 0 && grad_s != nullptr) {          // residual gradient of the pair (t0-1, t0): frame t0 is its target
-            const float4 q = row[(size_t)(t0 - 1) * f4];
-            step2_forward(p, X01, X23, f2(q.x, q.y), f2(q.z, q.w), su2, mine, lane, v01, v23, S);
+        if (f > 0 && g4 != nullptr) {               // residual gradient of the pair (f-1, f): frame f is its target
+            const float4 q = s4[off - f4];
+            step2_forward(p, X01, X23, f2(q.x, q.y), f2(q.z, q.w), su, mine, lane, v01, v23, S);
             __syncwarp();
             const float2 d01 = sub2(u01, v01), d23 = sub2(u23, v23);
             carry01 = __fmul2_rn(d01, gl2v);
@@ -206,41 +226,60 @@ __global__ void __launch_bounds__(256, F2_MINB) burgers_pair_loss_unit_kernel(Un
                 carry23.x += p.gl1 * sgn(d23.x); carry23.y += p.gl1 * sgn(d23.y);
             }
         }
-        float2 acc2 = f2(0.0f, 0.0f);
-        float acc1 = 0.0f;
-        float4 pre = __ldcs(row + (size_t)(t0 + 1) * f4);                // streamed: every frame is read once per chunk
-        const float4* pre_ptr = row + (size_t)(t0 + 2) * f4;             // running pointers: no 64-bit multiplies in the loop
-        float4* g_ptr = grow + (size_t)t0 * f4;
-#pragma unroll kUnroll
-        for (int t = t0; t < t1; ++t, pre_ptr += f4, g_ptr += f4) {
+        // position of the frame after u, and of the one after that (prefetch)
+        int fn = f + 1, bn = b;                                        // f <= T - 1 here, so the next frame is in the same row
+        size_t offn = off + f4;
+        float4 pre = __ldcs(s4 + offn);                                // streamed: every frame is read once per range
+        for (long long i = 1; i < nframes; ++i) {
             const float2 n01 = f2(pre.x, pre.y), n23 = f2(pre.z, pre.w);
-            if (t + 2 <= T) pre = __ldcs(pre_ptr);                       // prefetch: in flight during this pair's arithmetic
-            step2_forward(p, X01, X23, u01, u23, su2, mine, lane, v01, v23, S);
-            const float2 d01 = sub2(n01, v01), d23 = sub2(n23, v23);     // burgers.py:29
-            acc2 = __ffma2_rn(d01, d01, acc2);
-            acc2 = __ffma2_rn(d23, d23, acc2);
-            acc1 += (fabsf(d01.x) + fabsf(d01.y)) + (fabsf(d23.x) + fabsf(d23.y));
-            float2 gd01 = __fmul2_rn(d01, gl2v), gd23 = __fmul2_rn(d23, gl2v);
-            if (L1TERM) {
-                gd01.x += p.gl1 * sgn(d01.x); gd01.y += p.gl1 * sgn(d01.y);
-                gd23.x += p.gl1 * sgn(d23.x); gd23.y += p.gl1 * sgn(d23.y);
-            }
-            if (grad_s != nullptr) {
-                float2 gin01, gin23;
-                step2_adjoint(p, S, gd01, gd23, sacc2, mine_acc, lane, gin01, gin23);     // dL/dv = -gd
-                gin01 = __fadd2_rn(gin01, carry01);
-                gin23 = __fadd2_rn(gin23, carry23);
-                __stcs(g_ptr, make_float4(gin01.x, gin01.y, gin23.x, gin23.y));          // written once, never re-read here
+            const int fcur = fn, bcur = bn;
+            const size_t offcur = offn;
+            if (fn == T) { fn = 0; bn += 1; offn = (size_t)bn * 32; } else { fn += 1; offn += f4; }
+            if (i + 1 < nframes) pre = __ldcs(s4 + offn);              // in flight during this step's arithmetic
+            if (fcur != 0) {
+                // (u, n) = frames (f, f + 1) of row b: one pair
+#ifdef F2_MEMONLY
+                v01 = u01; v23 = u23;
+#else
+                step2_forward(p, X01, X23, u01, u23, su, mine, lane, v01, v23, S);
+#endif
+                const float2 d01 = sub2(n01, v01), d23 = sub2(n23, v23);     // burgers.py:29
+                acc2 = __ffma2_rn(d01, d01, acc2);
+                acc2 = __ffma2_rn(d23, d23, acc2);
+                acc1 += (fabsf(d01.x) + fabsf(d01.y)) + (fabsf(d23.x) + fabsf(d23.y));
+                float2 gd01 = __fmul2_rn(d01, gl2v), gd23 = __fmul2_rn(d23, gl2v);
+                if (L1TERM) {
+                    gd01.x += p.gl1 * sgn(d01.x); gd01.y += p.gl1 * sgn(d01.y);
+                    gd23.x += p.gl1 * sgn(d23.x); gd23.y += p.gl1 * sgn(d23.y);
+                }
+                if (g4 != nullptr) {
+                    float2 gin01, gin23;
+#if defined(F2_MEMONLY) || defined(F2_SKIP_ADJ)
+                    gin01 = gd01; gin23 = gd23;
+#else
+                    step2_adjoint(p, S, gd01, gd23, sacc, mine_acc, lane, gin01, gin23);      // dL/dv = -gd
+#endif
+                    gin01 = __fadd2_rn(gin01, carry01);
+                    gin23 = __fadd2_rn(gin23, carry23);
+                    __stcs(g4 + off, make_float4(gin01.x, gin01.y, gin23.x, gin23.y));        // written once, never re-read here
+                } else {
+                    __syncwarp();
+                }
+                carry01 = gd01; carry23 = gd23;
             } else {
-                __syncwarp();
+                // u = frame T of row b, n = frame 0 of row b + 1: close the row
+                if (g4 != nullptr) __stcs(g4 + off, make_float4(carry01.x, carry01.y, carry23.x, carry23.y));
+                carry01 = f2(0.0f, 0.0f); carry23 = f2(0.0f, 0.0f);
             }
-            carry01 = gd01; carry23 = gd23;
             u01 = n01; u23 = n23;
+            f = fcur; b = bcur; off = offcur;
         }
-        if (grad_s != nullptr && t1 == T) __stcs(grow + (size_t)T * f4, make_float4(carry01.x, carry01.y, carry23.x, carry23.y));
+        if (f == T && g4 != nullptr) __stcs(g4 + off, make_float4(carry01.x, carry01.y, carry23.x, carry23.y));   // range ends with its row
+    }
+    {
         const float a2 = warp_sum(acc2.x + acc2.y);
         acc1 = warp_sum(acc1);
-        if (lane == 0) partials[(size_t)b * nchunks + chunk] = make_float2(a2, acc1);
+        if (lane == 0) partials[(size_t)blockIdx.x * 8 + warp] = make_float2(a2, acc1);
     }
     // second stage fused into the same launch: the CTA that finishes last adds all partials in a FIXED order
     // losses[0] = sum(d^2)/2/B (l2_loss, PF/math/nd.py:115-121), losses[1] = sum|d|/B (l1_loss, nd.py:96-108)
@@ -253,7 +292,7 @@ __global__ void __launch_bounds__(256, F2_MINB) burgers_pair_loss_unit_kernel(Un
     if (s_last) {
         __threadfence();
         float a2 = 0.0f, a1 = 0.0f;
-        const int count = B * nchunks;
+        const int count = (int)gridDim.x * 8;
         for (int i = threadIdx.x; i < count; i += 256) {
             const float2 v = __ldcg(partials + i);
             a2 += v.x;
@@ -277,20 +316,23 @@ __global__ void __launch_bounds__(256, F2_MINB) burgers_pair_loss_unit_kernel(Un
 
 using namespace pdec;
 
-// returns PDEC_OK if it handled the call, 1 if the case is not this kernel's (caller falls back to burgers_fast.cu)
-int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int C, int nchunks, double dt, double viscosity,
-                                float gl2, float gl1, unsigned* done_counter, float* losses, cudaStream_t st) {
+// returns PDEC_OK if it handled the call, 1 if the case is not this kernel's (caller falls back to burgers_fast.cu).
+// partials must hold max(32, B * T) float2 (pdec_burgers_pair_loss_workspace_bytes)
+int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, double dt, double viscosity, float gl2, float gl1,
+                                unsigned* done_counter, float* losses, cudaStream_t st) {
     Unit2P p;
     const float dtf = (float)dt;
     p.dt128 = dtf * 128.0f;                                   // exact (power-of-two scale)
     p.c = (float)(dt * viscosity) * 16384.0f;                 // a / dx^2, dx^2 = 2^-14: exact scale of float32(dt * nu)
-    if (!(p.dt128 < 3.0e38f) || !(p.c < 3.0e38f)) return 1;
+    if (!(fabsf(p.dt128) < 3.0e38f) || !(fabsf(p.c) < 3.0e38f)) return 1;
     const float invB = 1.0f / (float)B;
     p.gl2 = gl2 * invB; p.gl1 = gl1 * invB;
-    const long long units = (long long)B * nchunks;
-    long long grid = (units + 7) / 8;
-    if (grid > 148LL * 64) grid = 148LL * 64;
-    if (gl1 != 0.0f) burgers_pair_loss_unit_kernel<true><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, C, nchunks, done_counter, losses, invB);
-    else burgers_pair_loss_unit_kernel<false><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, C, nchunks, done_counter, losses, invB);
+    const long long total = (long long)B * T;
+    // one range per resident warp (148 SMs x F2_MINB CTAs x 8 warps), at least 4 pairs per range
+    long long grid = 148LL * F2_MINB;
+    if (grid * 8 * 4 > total) grid = total / 32 > 0 ? total / 32 : 1;
+    const long long per_warp = (total + grid * 8 - 1) / (grid * 8);
+    if (gl1 != 0.0f) burgers_pair_loss_unit_kernel<true><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, per_warp, done_counter, losses, invB);
+    else burgers_pair_loss_unit_kernel<false><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, per_warp, done_counter, losses, invB);
     return cudaPeekAtLastError() == cudaSuccess ? PDEC_OK : PDEC_ERR_CUDA_LAUNCH;
 }

@@ -102,7 +102,7 @@ def test_trajectory_gradient_with_intermediate_frame_losses():
 
 
 @pytest.mark.parametrize("mode", [R.CONSTANT, R.REPLICATE, R.CIRCULAR])
-@pytest.mark.parametrize("B,n,T", [(8, 128, 32), (3, 50, 4), (1, 128, 1)])
+@pytest.mark.parametrize("B,n,T", [(8, 128, 32), (3, 50, 4), (1, 128, 1), (37, 128, 5), (700, 128, 3)])
 def test_pair_loss_and_gradient_vs_oracle(mode, B, n, T):
     ops = _ops()
     rng = np.random.RandomState(B * n + T)
