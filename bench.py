@@ -100,8 +100,8 @@ class BurgersWorkload:
     name = "burgers_pair_loss res=128 T=32 B=4096/gpu (BASELINE config 2: force loss fwd+adjoint)"
     algorithmic_bytes_per_cell_update = 8.0     # read each frame once + write its gradient once
     dtype = "f32"
-    dominant_kernel = "burgers_pair_loss_fast_kernel"
-    ncu_traffic_bytes = 124.7e6     # steady state: dram read 60.1 MB + write 64.5 MB per launch, profiles/r1h_burgers_summary.md
+    dominant_kernel = "burgers_pair_loss_unit_kernel"
+    ncu_traffic_bytes = 129.0e6     # steady state: dram read 66.1 MB + write 62.9 MB per launch, profiles/r1k_burgers_summary.md
 
     def __init__(self, device, rank, B=4096, n=128, T=32):
         import torch
@@ -128,7 +128,7 @@ class BurgersWorkload:
         self.host_losses = torch.empty(2, dtype=torch.float32).pin_memory()
         self.h2d = self.host_s.numel() * 4
         self.d2h = self.host_grad.numel() * 4 + 8
-        self.pipe = ops.HostPipeline(n, T, chunk_rows=256, max_batch=B)     # the public host-buffer call (e2e)
+        self.pipe = ops.HostPipeline(n, T, chunk_rows=512, max_batch=B)     # the public host-buffer call (e2e)
         self.launches_per_step = 1      # fused pair-loss kernel (its last CTA does the fixed-order loss reduction)
         self.l2_policy = "inputs rotate over %d resident sets (%.0f MB > 2x 126 MB L2)" % (self.nsets, self.nsets * set_bytes / 1e6)
         self.i = 0
@@ -154,7 +154,7 @@ class BurgersWorkload:
 
     def step_e2e(self):
         """Host buffers in, host buffers out, through the public host-buffer op (ops.HostPipeline.pair_loss ->
-        pdec_burgers_pair_loss_host): per 256-row chunk H2D of the frames, the fused kernel, D2H of the gradient, the three
+        pdec_burgers_pair_loss_host): per 512-row chunk H2D of the frames, the fused kernel, D2H of the gradient, the three
         legs overlapped on three streams; plus the two loss scalars.  The step ends when the host holds the results."""
         self.i += 1
         self.pipe.pair_loss(self.host_s, self.host_grad, self.host_losses, DT, VISC)

@@ -95,6 +95,17 @@ int pdec_burgers_pair_loss(const float* s, float* grad_s, float* losses, int T, 
                            double viscosity, float box_lower, float box_size, int substeps, int resubstep,
                            float gl2, float gl1, void* workspace, size_t workspace_bytes, void* stream);
 
+/* A WINDOW of frame pairs [t0, t1) of the same loss (0 <= t0 < t1 <= T): losses[2] <- the window's share of (L2, L1) (the shares
+ * of disjoint windows add up to the whole), grad_s frames t0 .. t1-1 (and frame T when t1 == T) <- their COMPLETE gradient
+ * (frame t0 includes the residual term of the pair before the window, recomputed from frame t0-1, which must be present).
+ * Only frames t0-1 .. t1 of s are read: the host pipeline below runs window k while frames of window k+1 are still in flight.
+ * Supported for the fused unit-box kernel only (n = 128, PDEC_MODE_CONSTANT, box [0, 1], one substep):
+ * pdec_burgers_pair_loss_window_supported() != 0, else PDEC_ERR_UNSUPPORTED_SIZE.  Workspace as for pdec_burgers_pair_loss. */
+int pdec_burgers_pair_loss_window_supported(int n, int mode, float box_lower, float box_size, int substeps);
+int pdec_burgers_pair_loss_window(const float* s, float* grad_s, float* losses, int T, int B, int n, int t0, int t1, int mode, double dt,
+                                  double viscosity, float box_lower, float box_size, int substeps, int resubstep, float gl2, float gl1,
+                                  void* workspace, size_t workspace_bytes, void* stream);
+
 /* The same force loss fed from HOST arrays: what the reference does every optimisation step through
  * session.run(fetches, feed_dict) (src/control/control_training.py:113-142, PF/tf/session.py:30-70 copies every fed array to
  * the device and every fetched one back).  s_host [T+1,B,n], grad_host [T+1,B,n] or NULL and losses_host[2] are HOST pointers
@@ -104,9 +115,12 @@ int pdec_burgers_pair_loss(const float* s, float* grad_s, float* losses, int T, 
  * after the work already enqueued there and `stream` waits for the last copy; the host buffers are valid after
  * synchronising `stream`.  Results equal pdec_burgers_pair_loss on the whole batch (the gradient bit for bit when
  * B / chunk_rows is a power of two; the loss scalars are summed chunk by chunk in ascending order).
- * max_chunks bounds B <= chunk_rows * max_chunks. */
+ * max_chunks bounds B <= chunk_rows * max_chunks.
+ * frames_per_slice > 0 additionally allocates whole-batch staging ((T+1) * chunk_rows * max_chunks * n floats, twice) and, when
+ * pdec_burgers_pair_loss_window_supported(), cuts the work along TIME instead (slices of that many frame pairs of all rows):
+ * every copy is then one contiguous block.  Same results contract. */
 typedef struct pdec_host_pipeline pdec_host_pipeline;
-int pdec_host_pipeline_create(pdec_host_pipeline** pipeline, int chunk_rows, int n, int T, int max_chunks);
+int pdec_host_pipeline_create(pdec_host_pipeline** pipeline, int chunk_rows, int n, int T, int max_chunks, int frames_per_slice);
 int pdec_host_pipeline_destroy(pdec_host_pipeline* pipeline);
 int pdec_burgers_pair_loss_host(pdec_host_pipeline* pipeline, const float* s_host, float* grad_host, float* losses_host, int T,
                                 int B, int n, int mode, double dt, double viscosity, float box_lower, float box_size,

@@ -34,7 +34,10 @@ struct Unit2P {
 #define F2_ROW 164
 #define F2_OUT 512                    // "floor index" given to out-of-domain samples: taps at bytes 512 and 640
 #ifndef F2_MINB
-#define F2_MINB 3
+#define F2_MINB 2                     // resident CTAs per SM (A/B on one box, us per step: 8x3 54.5, 7x4 53.5, 12x2 52.8, 4x6 55.3, 8x4 60.9 and 6x5 63.6 spill)
+#endif
+#ifndef F2_WARPS
+#define F2_WARPS 12                   // warps per CTA
 #endif
 
 __device__ __forceinline__ float2 f2(float x, float y) { return make_float2(x, y); }
@@ -175,15 +178,18 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
 
 __device__ __forceinline__ float sgn(float d) { return (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f); }
 
-// Work = the B x T (row, pair) space in row-major order, cut into gridDim.x * 8 equal contiguous ranges (one per warp).  A warp
-// walks the FRAMES of its range -- (b, f), f = 0..T, then row b + 1 -- with the next frame always in flight; consecutive frames
-// of one row form a pair, the step from frame T of a row to frame 0 of the next one only closes the row.
+// Work = the (row, pair) space B x [t0, t1) in row-major order (t0 = 0, t1 = T: the whole sequence; a narrower window serves the
+// frame-sliced host pipeline), cut into gridDim.x * F2_WARPS equal contiguous ranges, one per warp.  A warp walks the FRAMES of
+// its range -- (b, f), f = first..t1, then row b + 1 -- with the next frame always in flight.  Consecutive frames of a row form
+// a pair; a pair below the range's / window's first one is walked "carry-only" (forward step only: its residual gradient w.r.t.
+// its target frame is the carry the first real pair needs); the step from the last frame of a row to the first frame of the
+// next one only closes the row.
 template <bool L1TERM>
-__global__ void __launch_bounds__(256, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
-                                                                            float2* partials, int T, int B, long long per_warp,
+__global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
+                                                                            float2* partials, int T, int B, int t0, int t1, long long per_warp,
                                                                             unsigned* done_counter, float* __restrict__ losses, float inv_B) {
-    __shared__ float smem[8][2][F2_ROW];
-    __shared__ float red2[8], red1[8];
+    __shared__ float smem[F2_WARPS][2][F2_ROW];
+    __shared__ float red2[F2_WARPS], red1[F2_WARPS];
     __shared__ unsigned s_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* su = smem[warp][0];
@@ -197,16 +203,18 @@ __global__ void __launch_bounds__(256, F2_MINB) burgers_pair_loss_unit_kernel(Un
     const float4* s4 = reinterpret_cast<const float4*>(s) + lane;
     float4* g4 = grad_s ? reinterpret_cast<float4*>(grad_s) + lane : nullptr;
     const float2 gl2v = f2(p.gl2, p.gl2);
-    const long long total = (long long)B * T;
-    const long long P0 = ((long long)blockIdx.x * 8 + warp) * per_warp;
+    const int Cw = t1 - t0;                                            // pairs per row in the window
+    const long long total = (long long)B * Cw;
+    const long long P0 = ((long long)blockIdx.x * F2_WARPS + warp) * per_warp;
     const long long P1 = min(total, P0 + per_warp);
     float2 acc2 = f2(0.0f, 0.0f);
     float acc1 = 0.0f;
     if (P0 < P1) {
-        int b = (int)(P0 / T), f = (int)(P0 - (long long)b * T);       // frame held in u
-        const int b_last = (int)((P1 - 1) / T), t_last = (int)((P1 - 1) - (long long)b_last * T);
-        // frames to walk: from (b, f) to (b_last, t_last + 1)
-        const long long nframes = ((long long)b_last * (T + 1) + t_last + 1) - ((long long)b * (T + 1) + f) + 1;
+        long long remaining = P1 - P0;                                 // real pairs still to do
+        int b = (int)(P0 / Cw);
+        int lo = t0 + (int)(P0 - (long long)b * Cw);                   // first real pair of the current row
+        const int row_first = g4 != nullptr && t0 > 0 ? t0 - 1 : t0;   // first frame walked in every later row
+        int f = g4 != nullptr && lo > 0 ? lo - 1 : lo;                 // frame held in u (one early: carry-only pair)
         size_t off = (size_t)f * f4 + (size_t)b * 32;                  // float4 offset of frame (b, f)
         float2 u01, u23, carry01 = f2(0.0f, 0.0f), carry23 = f2(0.0f, 0.0f), v01, v23;
         Step2 S;
@@ -214,72 +222,65 @@ __global__ void __launch_bounds__(256, F2_MINB) burgers_pair_loss_unit_kernel(Un
             const float4 q = s4[off];
             u01 = f2(q.x, q.y); u23 = f2(q.z, q.w);
         }
-        if (f > 0 && g4 != nullptr) {               // residual gradient of the pair (f-1, f): frame f is its target
-            const float4 q = s4[off - f4];
-            step2_forward(p, X01, X23, f2(q.x, q.y), f2(q.z, q.w), su, mine, lane, v01, v23, S);
-            __syncwarp();
-            const float2 d01 = sub2(u01, v01), d23 = sub2(u23, v23);
-            carry01 = __fmul2_rn(d01, gl2v);
-            carry23 = __fmul2_rn(d23, gl2v);
-            if (L1TERM) {
-                carry01.x += p.gl1 * sgn(d01.x); carry01.y += p.gl1 * sgn(d01.y);
-                carry23.x += p.gl1 * sgn(d23.x); carry23.y += p.gl1 * sgn(d23.y);
-            }
-        }
-        // position of the frame after u, and of the one after that (prefetch)
-        int fn = f + 1, bn = b;                                        // f <= T - 1 here, so the next frame is in the same row
+        // position of the frame after u (f <= t1 - 1 here, so it is in the same row), then the one after that is prefetched
+        int fn = f + 1, bn = b;
         size_t offn = off + f4;
         float4 pre = __ldcs(s4 + offn);                                // streamed: every frame is read once per range
-        for (long long i = 1; i < nframes; ++i) {
+        while (true) {
             const float2 n01 = f2(pre.x, pre.y), n23 = f2(pre.z, pre.w);
-            const int fcur = fn, bcur = bn;
+            const int fcur = fn, bcur = bn;                            // position of n
             const size_t offcur = offn;
-            if (fn == T) { fn = 0; bn += 1; offn = (size_t)bn * 32; } else { fn += 1; offn += f4; }
-            if (i + 1 < nframes) pre = __ldcs(s4 + offn);              // in flight during this step's arithmetic
-            if (fcur != 0) {
-                // (u, n) = frames (f, f + 1) of row b: one pair
-#ifdef F2_MEMONLY
-                v01 = u01; v23 = u23;
-#else
+            const bool closing = bcur != b;                            // u = last frame of row b, n = first frame of row b + 1
+            const bool real = !closing && fcur - 1 >= lo;              // (u, n) = pair fcur - 1 of row b, inside the range
+            if (fn == t1) { fn = row_first; bn += 1; offn = (size_t)row_first * f4 + (size_t)bn * 32; } else { fn += 1; offn += f4; }
+            if (remaining - (real ? 1 : 0) > 0) pre = __ldcs(s4 + offn);      // in flight during this step's arithmetic
+            if (!closing) {
                 step2_forward(p, X01, X23, u01, u23, su, mine, lane, v01, v23, S);
-#endif
                 const float2 d01 = sub2(n01, v01), d23 = sub2(n23, v23);     // burgers.py:29
-                acc2 = __ffma2_rn(d01, d01, acc2);
-                acc2 = __ffma2_rn(d23, d23, acc2);
-                acc1 += (fabsf(d01.x) + fabsf(d01.y)) + (fabsf(d23.x) + fabsf(d23.y));
                 float2 gd01 = __fmul2_rn(d01, gl2v), gd23 = __fmul2_rn(d23, gl2v);
                 if (L1TERM) {
                     gd01.x += p.gl1 * sgn(d01.x); gd01.y += p.gl1 * sgn(d01.y);
                     gd23.x += p.gl1 * sgn(d23.x); gd23.y += p.gl1 * sgn(d23.y);
                 }
-                if (g4 != nullptr) {
-                    float2 gin01, gin23;
-#if defined(F2_MEMONLY) || defined(F2_SKIP_ADJ)
-                    gin01 = gd01; gin23 = gd23;
+                if (real) {
+                    acc2 = __ffma2_rn(d01, d01, acc2);
+                    acc2 = __ffma2_rn(d23, d23, acc2);
+                    acc1 += (fabsf(d01.x) + fabsf(d01.y)) + (fabsf(d23.x) + fabsf(d23.y));
+                    if (g4 != nullptr) {
+                        float2 gin01, gin23;
+#if defined(F2_SKIP_ADJ)
+                        gin01 = gd01; gin23 = gd23;
 #else
-                    step2_adjoint(p, S, gd01, gd23, sacc, mine_acc, lane, gin01, gin23);      // dL/dv = -gd
+                        step2_adjoint(p, S, gd01, gd23, sacc, mine_acc, lane, gin01, gin23);      // dL/dv = -gd
 #endif
-                    gin01 = __fadd2_rn(gin01, carry01);
-                    gin23 = __fadd2_rn(gin23, carry23);
-                    __stcs(g4 + off, make_float4(gin01.x, gin01.y, gin23.x, gin23.y));        // written once, never re-read here
+                        gin01 = __fadd2_rn(gin01, carry01);
+                        gin23 = __fadd2_rn(gin23, carry23);
+                        __stcs(g4 + off, make_float4(gin01.x, gin01.y, gin23.x, gin23.y));        // written once, never re-read here
+                    } else {
+                        __syncwarp();
+                    }
+                    remaining -= 1;
                 } else {
-                    __syncwarp();
+                    __syncwarp();                                      // carry-only pair: nothing stored, nothing summed
                 }
                 carry01 = gd01; carry23 = gd23;
             } else {
-                // u = frame T of row b, n = frame 0 of row b + 1: close the row
-                if (g4 != nullptr) __stcs(g4 + off, make_float4(carry01.x, carry01.y, carry23.x, carry23.y));
+                // close row b: frame T receives the residual gradient of the last pair (a window that ends earlier leaves its
+                // last frame to the next window); the next row starts with a zero carry and its first real pair at t0
+                if (g4 != nullptr && f == T) __stcs(g4 + off, make_float4(carry01.x, carry01.y, carry23.x, carry23.y));
                 carry01 = f2(0.0f, 0.0f); carry23 = f2(0.0f, 0.0f);
+                lo = t0;
             }
             u01 = n01; u23 = n23;
             f = fcur; b = bcur; off = offcur;
+            if (remaining == 0) break;
         }
         if (f == T && g4 != nullptr) __stcs(g4 + off, make_float4(carry01.x, carry01.y, carry23.x, carry23.y));   // range ends with its row
     }
     {
         const float a2 = warp_sum(acc2.x + acc2.y);
         acc1 = warp_sum(acc1);
-        if (lane == 0) partials[(size_t)blockIdx.x * 8 + warp] = make_float2(a2, acc1);
+        if (lane == 0) partials[(size_t)blockIdx.x * F2_WARPS + warp] = make_float2(a2, acc1);
     }
     // second stage fused into the same launch: the CTA that finishes last adds all partials in a FIXED order
     // losses[0] = sum(d^2)/2/B (l2_loss, PF/math/nd.py:115-121), losses[1] = sum|d|/B (l1_loss, nd.py:96-108)
@@ -292,8 +293,8 @@ __global__ void __launch_bounds__(256, F2_MINB) burgers_pair_loss_unit_kernel(Un
     if (s_last) {
         __threadfence();
         float a2 = 0.0f, a1 = 0.0f;
-        const int count = (int)gridDim.x * 8;
-        for (int i = threadIdx.x; i < count; i += 256) {
+        const int count = (int)gridDim.x * F2_WARPS;
+        for (int i = threadIdx.x; i < count; i += 32 * F2_WARPS) {
             const float2 v = __ldcg(partials + i);
             a2 += v.x;
             a1 += v.y;
@@ -305,7 +306,7 @@ __global__ void __launch_bounds__(256, F2_MINB) burgers_pair_loss_unit_kernel(Un
         if (threadIdx.x == 0) {
             float t2 = 0.0f, t1 = 0.0f;
 #pragma unroll
-            for (int w = 0; w < 8; ++w) { t2 += red2[w]; t1 += red1[w]; }
+            for (int w = 0; w < F2_WARPS; ++w) { t2 += red2[w]; t1 += red1[w]; }
             losses[0] = t2 * 0.5f * inv_B;
             losses[1] = t1 * inv_B;
         }
@@ -317,9 +318,11 @@ __global__ void __launch_bounds__(256, F2_MINB) burgers_pair_loss_unit_kernel(Un
 using namespace pdec;
 
 // returns PDEC_OK if it handled the call, 1 if the case is not this kernel's (caller falls back to burgers_fast.cu).
-// partials must hold max(32, B * T) float2 (pdec_burgers_pair_loss_workspace_bytes)
-int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, double dt, double viscosity, float gl2, float gl1,
-                                unsigned* done_counter, float* losses, cudaStream_t st) {
+// partials must hold max(32, B * T) float2 (pdec_burgers_pair_loss_workspace_bytes).  [t0, t1) = window of pairs (0, T = all):
+// losses <- the window's share of (L2, L1); grad_s frames t0..t1-1 (and T when t1 == T) <- their complete gradient
+int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int t0, int t1, double dt, double viscosity, float gl2,
+                                float gl1, unsigned* done_counter, float* losses, cudaStream_t st) {
+    if (t0 < 0 || t1 > T || t0 >= t1) return PDEC_ERR_INVALID_ARGUMENT;
     Unit2P p;
     const float dtf = (float)dt;
     p.dt128 = dtf * 128.0f;                                   // exact (power-of-two scale)
@@ -327,12 +330,12 @@ int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials,
     if (!(fabsf(p.dt128) < 3.0e38f) || !(fabsf(p.c) < 3.0e38f)) return 1;
     const float invB = 1.0f / (float)B;
     p.gl2 = gl2 * invB; p.gl1 = gl1 * invB;
-    const long long total = (long long)B * T;
-    // one range per resident warp (148 SMs x F2_MINB CTAs x 8 warps), at least 4 pairs per range
+    const long long total = (long long)B * (t1 - t0);
+    // one range per resident warp (148 SMs x F2_MINB CTAs x F2_WARPS warps), at least 4 pairs per range
     long long grid = 148LL * F2_MINB;
-    if (grid * 8 * 4 > total) grid = total / 32 > 0 ? total / 32 : 1;
-    const long long per_warp = (total + grid * 8 - 1) / (grid * 8);
-    if (gl1 != 0.0f) burgers_pair_loss_unit_kernel<true><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, per_warp, done_counter, losses, invB);
-    else burgers_pair_loss_unit_kernel<false><<<(unsigned)grid, 256, 0, st>>>(p, s, grad_s, partials, T, B, per_warp, done_counter, losses, invB);
+    if (grid * F2_WARPS * 4 > total) grid = total / (4 * F2_WARPS) > 0 ? total / (4 * F2_WARPS) : 1;
+    const long long per_warp = (total + grid * F2_WARPS - 1) / (grid * F2_WARPS);
+    if (gl1 != 0.0f) burgers_pair_loss_unit_kernel<true><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, done_counter, losses, invB);
+    else burgers_pair_loss_unit_kernel<false><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, done_counter, losses, invB);
     return cudaPeekAtLastError() == cudaSuccess ? PDEC_OK : PDEC_ERR_CUDA_LAUNCH;
 }

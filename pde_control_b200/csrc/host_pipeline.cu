@@ -4,9 +4,16 @@
 // so PCIe is busy in both directions at once and the kernel hides behind the copies.  The frame-major host layout
 // [T+1, B, n] makes a chunk of rows a pitched 2-D region; cudaMemcpy2DAsync moves it with the copy engines, no packing pass.
 //
+// When the fused unit-box kernel applies (pdec_burgers_pair_loss_window_supported) and the pipeline was created with
+// frames_per_slice > 0, the batch is cut along TIME instead: slice k = pairs [k m, (k+1) m) of ALL rows.  Its frames are one
+// contiguous block on the host and on the device, so both PCIe legs are plain large 1-D copies (measured: pitched D2H pieces
+// reach ~35 GB/s, contiguous ones 49 GB/s with both directions busy, scripts/diag/pcie_probe.py); the kernel of slice k needs
+// only frames <= (k+1) m and completes the gradient of frames [k m, (k+1) m).
+//
 // A pipeline object owns its streams, events and device staging (allocated once at create time); the call itself allocates
 // nothing, never synchronises the device and is ordered on the caller's stream like every other entry of the library: work
 // enqueued on `stream` before the call happens-before the first copy, and `stream` waits for the last copy.
+#include <cstdlib>
 #include <new>
 #include "pdec_common.cuh"
 
@@ -30,8 +37,15 @@ struct pdec_host_pipeline {
     cudaEvent_t begin = nullptr, end = nullptr;
     void* ws = nullptr;
     size_t ws_bytes = 0;
-    float* chunk_losses = nullptr;   // [max_chunks][2] device
+    float* chunk_losses = nullptr;   // [max(max_chunks, T)][2] device
     float* losses = nullptr;         // [2] device
+    // frame-sliced mode
+    int slice = 0;                   // pairs per slice (0: mode not available)
+    long long max_batch = 0;
+    float* full_s = nullptr;         // [T+1, max_batch, n]
+    float* full_g = nullptr;
+    cudaEvent_t* ev_h2d = nullptr;   // [T]
+    cudaEvent_t* ev_kernel = nullptr;
 };
 
 namespace pdec {
@@ -46,7 +60,7 @@ __global__ void combine_chunk_losses_kernel(const float* __restrict__ chunk_loss
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         float l2 = 0.0f, l1 = 0.0f;
         for (int c = 0; c < nchunks; ++c) {
-            const float sc = chunk_scale(c, nchunks, rows, B);
+            const float sc = rows > 0 ? chunk_scale(c, nchunks, rows, B) : 1.0f;      // rows == 0: time slices, already per B
             l2 += chunk_losses[2 * c] * sc;
             l1 += chunk_losses[2 * c + 1] * sc;
         }
@@ -71,6 +85,14 @@ extern "C" int pdec_host_pipeline_destroy(pdec_host_pipeline* h) {
         if (h->slot[i].kernel) cudaEventDestroy(h->slot[i].kernel);
         if (h->slot[i].d2h) cudaEventDestroy(h->slot[i].d2h);
     }
+    if (h->full_s) cudaFree(h->full_s);
+    if (h->full_g) cudaFree(h->full_g);
+    for (int i = 0; i < h->T; ++i) {
+        if (h->ev_h2d && h->ev_h2d[i]) cudaEventDestroy(h->ev_h2d[i]);
+        if (h->ev_kernel && h->ev_kernel[i]) cudaEventDestroy(h->ev_kernel[i]);
+    }
+    delete[] h->ev_h2d;
+    delete[] h->ev_kernel;
     if (h->ws) cudaFree(h->ws);
     if (h->chunk_losses) cudaFree(h->chunk_losses);
     if (h->losses) cudaFree(h->losses);
@@ -83,8 +105,8 @@ extern "C" int pdec_host_pipeline_destroy(pdec_host_pipeline* h) {
     return PDEC_OK;
 }
 
-extern "C" int pdec_host_pipeline_create(pdec_host_pipeline** out, int chunk_rows, int n, int T, int max_chunks) {
-    if (!out || chunk_rows < 1 || n < 1 || T < 1 || max_chunks < 1) return PDEC_ERR_INVALID_ARGUMENT;
+extern "C" int pdec_host_pipeline_create(pdec_host_pipeline** out, int chunk_rows, int n, int T, int max_chunks, int frames_per_slice) {
+    if (!out || chunk_rows < 1 || n < 1 || T < 1 || max_chunks < 1 || frames_per_slice < 0) return PDEC_ERR_INVALID_ARGUMENT;
     pdec_host_pipeline* h = new (std::nothrow) pdec_host_pipeline();
     if (!h) return PDEC_ERR_INVALID_ARGUMENT;
     h->rows = chunk_rows; h->n = n; h->T = T; h->max_chunks = max_chunks;
@@ -97,9 +119,24 @@ extern "C" int pdec_host_pipeline_create(pdec_host_pipeline** out, int chunk_row
             HP_TRY(cudaEventCreateWithFlags(&h->slot[i].kernel, cudaEventDisableTiming));
             HP_TRY(cudaEventCreateWithFlags(&h->slot[i].d2h, cudaEventDisableTiming));
         }
-        h->ws_bytes = pdec_burgers_pair_loss_workspace_bytes(chunk_rows, n, T);
+        h->max_batch = (long long)chunk_rows * max_chunks;
+        if (frames_per_slice > 0) {
+            if (h->max_batch > (1LL << 24)) { pdec_host_pipeline_destroy(h); return PDEC_ERR_INVALID_ARGUMENT; }
+            h->slice = frames_per_slice;
+            const size_t full = (size_t)(T + 1) * (size_t)h->max_batch * n * sizeof(float);
+            HP_TRY(cudaMalloc(&h->full_s, full));
+            HP_TRY(cudaMalloc(&h->full_g, full));
+            h->ev_h2d = new (std::nothrow) cudaEvent_t[T]();
+            h->ev_kernel = new (std::nothrow) cudaEvent_t[T]();
+            if (!h->ev_h2d || !h->ev_kernel) goto fail;
+            for (int i = 0; i < T; ++i) {
+                HP_TRY(cudaEventCreateWithFlags(&h->ev_h2d[i], cudaEventDisableTiming));
+                HP_TRY(cudaEventCreateWithFlags(&h->ev_kernel[i], cudaEventDisableTiming));
+            }
+        }
+        h->ws_bytes = pdec_burgers_pair_loss_workspace_bytes(frames_per_slice > 0 ? (int)h->max_batch : chunk_rows, n, T);
         HP_TRY(cudaMalloc(&h->ws, h->ws_bytes));
-        HP_TRY(cudaMalloc(&h->chunk_losses, sizeof(float) * 2 * max_chunks));
+        HP_TRY(cudaMalloc(&h->chunk_losses, sizeof(float) * 2 * (max_chunks > T ? max_chunks : T)));
         HP_TRY(cudaMalloc(&h->losses, sizeof(float) * 2));
         HP_TRY(cudaStreamCreateWithFlags(&h->in, cudaStreamNonBlocking));
         HP_TRY(cudaStreamCreateWithFlags(&h->compute, cudaStreamNonBlocking));
@@ -129,6 +166,36 @@ extern "C" int pdec_burgers_pair_loss_host(pdec_host_pipeline* h, const float* s
     HP_TRY(cudaStreamWaitEvent(h->in, h->begin, 0));
     HP_TRY(cudaStreamWaitEvent(h->compute, h->begin, 0));
     HP_TRY(cudaStreamWaitEvent(h->out, h->begin, 0));
+    if (h->slice > 0 && B <= h->max_batch && pdec_burgers_pair_loss_window_supported(n, mode, box_lower, box_size, substeps)) {
+        // frame-sliced mode: contiguous frame blocks in both directions
+        const size_t frame = (size_t)B * n;                         // floats per frame
+        const int nsl = (T + h->slice - 1) / h->slice;
+        for (int c = 0; c < nsl; ++c) {
+            const int t0 = c * h->slice, t1 = (t0 + h->slice < T) ? t0 + h->slice : T;
+            const int first = c == 0 ? 0 : t0 + 1;                  // frame t0 came with the previous slice
+            HP_TRY(cudaMemcpyAsync(h->full_s + first * frame, s_host + first * frame, (size_t)(t1 - first + 1) * frame * sizeof(float),
+                                   cudaMemcpyHostToDevice, h->in));
+            HP_TRY(cudaEventRecord(h->ev_h2d[c], h->in));
+            HP_TRY(cudaStreamWaitEvent(h->compute, h->ev_h2d[c], 0));
+            rc = pdec_burgers_pair_loss_window(h->full_s, grad_host ? h->full_g : nullptr, h->chunk_losses + 2 * c, T, B, n, t0, t1, mode, dt,
+                                               viscosity, box_lower, box_size, substeps, resubstep, gl2, gl1, h->ws, h->ws_bytes, h->compute);
+            if (rc != PDEC_OK) return rc;
+            HP_TRY(cudaEventRecord(h->ev_kernel[c], h->compute));
+            if (grad_host) {
+                const int last = t1 == T ? T : t1 - 1;              // frames whose gradient is complete after this slice
+                HP_TRY(cudaStreamWaitEvent(h->out, h->ev_kernel[c], 0));
+                HP_TRY(cudaMemcpyAsync(grad_host + t0 * frame, h->full_g + t0 * frame, (size_t)(last - t0 + 1) * frame * sizeof(float),
+                                       cudaMemcpyDeviceToHost, h->out));
+            }
+        }
+        HP_TRY(cudaStreamWaitEvent(h->out, h->ev_kernel[nsl - 1], 0));
+        pdec::combine_chunk_losses_kernel<<<1, 32, 0, h->out>>>(h->chunk_losses, nsl, 0, B, h->losses);
+        HP_TRY(cudaPeekAtLastError());
+        HP_TRY(cudaMemcpyAsync(losses_host, h->losses, 2 * sizeof(float), cudaMemcpyDeviceToHost, h->out));
+        HP_TRY(cudaEventRecord(h->end, h->out));
+        HP_TRY(cudaStreamWaitEvent(user, h->end, 0));
+        return PDEC_OK;
+    }
     for (int c = 0; c < nchunks; ++c) {
         Slot& sl = h->slot[c % SLOTS];
         const int b0 = c * rows, bc = (c + 1 < nchunks) ? rows : B - b0;

@@ -134,16 +134,20 @@ class HostPipeline(object):
     """Force loss fed from page-locked HOST arrays (the reference feeds and fetches host arrays every optimisation step:
     src/control/control_training.py:113-142 through PF/tf/session.py).  Owns three streams and the device staging of
     pdec_host_pipeline (include/pdec.h); `chunk_rows` rows of the batch travel per leg, so H2D, the fused kernel and D2H of
-    neighbouring chunks overlap."""
+    neighbouring chunks overlap.  frames_per_slice > 0: when the fused unit-box kernel applies the work is cut along time instead
+    (slices of that many frame pairs of all rows; contiguous copies both ways), at the price of whole-batch device staging for
+    max_batch rows.  Measured on B200 (scripts/diag/pcie_probe.py, pcie_timeline.py): both cuts reach the same 1.84-1.86 ms for
+    2 x 69 MB, within 8 % of what chunked full-duplex PCIe delivers (about 44 GB/s per direction), so rows are the default."""
 
-    def __init__(self, n, T, chunk_rows=256, max_batch=1 << 20, device=None):
+    def __init__(self, n, T, chunk_rows=512, max_batch=4096, frames_per_slice=0, device=None):
         import ctypes
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.n, self.T, self.chunk_rows = int(n), int(T), int(chunk_rows)
         self.max_chunks = (int(max_batch) + self.chunk_rows - 1) // self.chunk_rows
         h = ctypes.c_void_p()
         with torch.cuda.device(self.device):
-            rc = _lib.lib().pdec_host_pipeline_create(ctypes.byref(h), self.chunk_rows, self.n, self.T, self.max_chunks)
+            rc = _lib.lib().pdec_host_pipeline_create(ctypes.byref(h), self.chunk_rows, self.n, self.T, self.max_chunks,
+                                                      int(frames_per_slice))
         _lib.check(rc, "pdec_host_pipeline_create")
         self._h = h
 

@@ -172,11 +172,14 @@ def test_full_size_config2_properties():
     assert abs(l2.item() - tot) < 1e-4 * tot
 
 
+@pytest.mark.parametrize("frames_per_slice", [0, 1, 3])
 @pytest.mark.parametrize("B,chunk_rows,n,T", [(512, 128, 128, 8), (300, 128, 128, 5), (40, 16, 50, 3), (64, 256, 128, 4)])
-def test_host_pipeline_equals_resident_call(B, chunk_rows, n, T):
+def test_host_pipeline_equals_resident_call(B, chunk_rows, n, T, frames_per_slice):
     """pdec_burgers_pair_loss_host (chunked H2D / kernel / D2H over three streams) == the resident single launch:
     gradient bit for bit when the chunk scale is a power of two, else to rounding of the 1/B scale; losses to 1e-6;
-    ragged last chunk, a batch smaller than one chunk, the general-n kernel and two calls in a row (slot re-use)."""
+    ragged last chunk, a batch smaller than one chunk, the general-n kernel and two calls in a row (slot re-use).
+    frames_per_slice > 0: the frame-sliced mode (windows of pairs through pdec_burgers_pair_loss_window; n = 128 only, other
+    sizes fall back to row chunks): gradient bit for bit."""
     ops = _ops()
     rng = np.random.RandomState(B + T)
     s = np.stack([R.gaussian_clash(B, n, rng) for _ in range(T + 1)]).astype(np.float32)
@@ -184,7 +187,7 @@ def test_host_pipeline_equals_resident_call(B, chunk_rows, n, T):
     sc = torch.tensor(s, device="cuda", requires_grad=True)
     l2, l1 = ops.burgers_pair_loss(sc, 0.03, 0.003)
     l2.backward()
-    pipe = ops.HostPipeline(n, T, chunk_rows=chunk_rows, max_batch=1024)
+    pipe = ops.HostPipeline(n, T, chunk_rows=chunk_rows, max_batch=1024, frames_per_slice=frames_per_slice)
     hs = torch.tensor(s).pin_memory()
     hg = torch.full(s.shape, float("nan")).pin_memory()
     hl = torch.zeros(2).pin_memory()
@@ -192,7 +195,7 @@ def test_host_pipeline_equals_resident_call(B, chunk_rows, n, T):
         hg.fill_(float("nan"))
         pipe.pair_loss(hs, hg, hl, 0.03, 0.003)
         torch.cuda.current_stream().synchronize()
-        pow2 = B % chunk_rows == 0 and ((B // chunk_rows) & (B // chunk_rows - 1)) == 0 or B <= chunk_rows
+        pow2 = B % chunk_rows == 0 and ((B // chunk_rows) & (B // chunk_rows - 1)) == 0 or B <= chunk_rows or (frames_per_slice > 0 and n == 128)
         if pow2:
             assert torch.equal(hg, sc.grad.cpu())
         else:
