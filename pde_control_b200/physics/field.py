@@ -110,8 +110,25 @@ class CenteredGrid(Field):
         return isinstance(other, (CenteredGrid, Domain)) and self.box == other.box and np.array_equal(self.resolution, other.resolution)
 
     def at(self, other):
+        """Resampling to another field's sample points (grid.py:109-124).  Supported: a compatible centred grid (identity)
+        and a staggered grid of the same domain: component d (or the single component) is sampled at the centres of the
+        faces normal to axis d, which on the reference's fast path (padded by one cell with the field's extrapolation, then
+        interpolate_linear at offset 0.5, grid.py:112-120 via field.py:219-226 broadcast_at) is the mean of the two adjacent cells."""
         if self.compatible(other):
             return self
+        if isinstance(other, StaggeredGrid) and other.box == self.box and np.array_equal(other.resolution, self.resolution):
+            if self.component_count not in (1, other.component_count):
+                raise ValueError("Can only resample to staggered fields with same number of components")
+            comps = []
+            for d in range(other.component_count):
+                c = self.data[..., d:d + 1] if self.component_count > 1 else self.data
+                widths = [[0, 0]] * self.rank
+                widths[d] = [1, 1]
+                padded = self.copied_with(data=c).padded(widths).data
+                lo = padded.narrow(1 + d, 0, padded.shape[1 + d] - 1)
+                hi = padded.narrow(1 + d, 1, padded.shape[1 + d] - 1)
+                comps.append(lo * 0.5 + hi * 0.5)                      # interpolate_linear: x0 * (1 - w) + x1 * w, w = 0.5 (nd.py:378-392)
+            return other.with_data(comps)
         raise NotImplementedError("general resampling between grids is not on the B200 path")
 
     def padded(self, widths):

@@ -1,12 +1,13 @@
 """Fluid state, IncompressibleFlow physics, divergence_free and the pressure-solver objects over the CUDA kernels.
 
 Mirrors  Fluid               PF/physics/fluid.py:21-60
-         IncompressibleFlow  PF/physics/fluid.py:73-114   (default flags; no obstacles; buoyancy_factor 0)
+         IncompressibleFlow  PF/physics/fluid.py:73-114   (no obstacles; buoyancy through Gravity, PF/physics/field/effect.py:77-112)
          divergence_free     PF/physics/fluid.py:214-243
          SparseCG            PF/physics/pressuresolver/sparse.py:40-102  (parameters only; the solve is pdec_cg_poisson_2d)
          poisson_solve       PF/physics/pressuresolver/solver_api.py:132-158
          advect.semi_lagrangian, staggered_curl_2d  PF/physics/field/advect.py:24-40, util.py:60-67
 """
+import numpy as np
 import torch
 
 from .. import ops
@@ -121,10 +122,34 @@ class Fluid(DomainState):
         return INCOMPRESSIBLE_FLOW
 
 
+class Gravity(object):
+    """Gravity state (effect.py:77-104): a scalar acts along -up (axis 0, physics_config.py:25-29), a vector as given."""
+    tags = ("gravity",)
+
+    def __init__(self, gravity=-9.81, name="gravity"):
+        assert gravity is not None
+        self.gravity = gravity
+        self.name = name
+
+
+def gravity_tensor(gravity, rank):
+    """effect.py:106-112: [rank] vector; scalar g -> g * up_vector = (g, 0, ...)."""
+    if isinstance(gravity, Gravity):
+        gravity = gravity.gravity
+    if isinstance(gravity, (tuple, list)) and len(gravity) > 0 and isinstance(gravity[0], Gravity):
+        gravity = sum(np.asarray(gravity_tensor(g, rank)) for g in gravity)      # several gravity states add up (effect.py:88-96)
+    g = np.asarray(gravity, np.float32)
+    if g.ndim == 0:
+        g = g * np.asarray([1.0] + [0.0] * (rank - 1), np.float32)
+    assert g.shape[-1] == rank
+    return g.reshape(-1)[-rank:]
+
+
 class IncompressibleFlow(Physics):
 
     def __init__(self, pressure_solver=None, make_input_divfree=False, make_output_divfree=True, conserve_density=True):
         Physics.__init__(self, [StateDependency("obstacles", "obstacle"),
+                                StateDependency("gravity", "gravity", single_state=True),
                                 StateDependency("density_effects", "density_effect", blocking=True),
                                 StateDependency("velocity_effects", "velocity_effect", blocking=True)])
         self.pressure_solver = pressure_solver
@@ -132,9 +157,9 @@ class IncompressibleFlow(Physics):
         self.make_output_divfree = make_output_divfree
         self.conserve_density = conserve_density
 
-    def step(self, fluid, dt=1.0, obstacles=(), density_effects=(), velocity_effects=()):
-        if fluid.buoyancy_factor != 0:
-            raise NotImplementedError("buoyancy is not on the B200 path (SURVEY 8f N3)")
+    def step(self, fluid, dt=1.0, obstacles=(), gravity=None, density_effects=(), velocity_effects=()):
+        gravity = gravity_tensor(Gravity() if gravity is None or (isinstance(gravity, (tuple, list)) and len(gravity) == 0) else gravity,
+                                 fluid.rank)
         velocity, density = fluid.velocity, fluid.density
         solve_info = {}
         if self.make_input_divfree:
@@ -148,6 +173,11 @@ class IncompressibleFlow(Physics):
             density = effect_applied(effect, density, dt)
         for effect in velocity_effects:
             velocity = effect_applied(effect, velocity, dt)
+        if fluid.buoyancy_factor != 0:
+            # velocity += (density * -gravity * buoyancy_factor * dt).at(velocity)   (fluid.py:107)
+            factors = [float(-g) * float(fluid.buoyancy_factor) * float(dt) for g in gravity]
+            lift = CenteredGrid(torch.cat([density.data * f for f in factors], -1), density.box, extrapolation=density.extrapolation)
+            velocity = velocity + lift.at(velocity)
         divergent_velocity = velocity
         if self.make_output_divfree:
             velocity, solve_info = divergence_free(velocity, fluid.domain, obstacles, self.pressure_solver, return_info=True)
