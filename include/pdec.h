@@ -201,6 +201,15 @@ int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p, int* iter
                        int closed, float accuracy, int max_iterations, int stop_mode, void* workspace, size_t workspace_bytes,
                        void* stream);
 
+/* The same solve on a domain with OBSTACLES (PoissonDomain active / accessible masks, solver_api.py:51-121; matrix
+ * sparse.py:157-221): `code` [ny*nx] bytes (device, shared by the batch) gives every cell its stencil: bits 0..3 = coupled to the
+ * neighbour above (i-1) / below (i+1) / left (j-1) / right (j+1), i.e. active_self * active_neighbour; bits 4..7 = minus the
+ * diagonal = number of accessible neighbours clamped to >= 1 (domain boundaries count as accessible when open).  Streaming
+ * cooperative kernel; workspace as pdec_cg_poisson_2d.  The adjoint is the same call (the masked matrix is symmetric). */
+int pdec_cg_poisson_2d_masked(const float* rhs, const float* guess, float* p, int* iterations, float* residual,
+                              const unsigned char* code, int B, int ny, int nx, float accuracy, int max_iterations, int stop_mode,
+                              void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Tiled / slab-decomposed CG  (BASELINE config 5: 2048 x 2048, row slabs over 2/4/8 GPUs)
  * The same solve as pdec_cg_poisson_2d (zero initial guess, per-element stop rule), on a grid of on-chip tiles with ONE

@@ -25,18 +25,28 @@ def staggered_tensor(vy, vx):
     return t
 
 
-def fluid_step_case(pf, ny, nx, B, boundary, seed, steps, dt, solver="direct"):
+def fluid_step_case(pf, ny, nx, B, boundary, seed, steps, dt, solver="direct", buoyancy=0.0, density_effect=False, obstacles=()):
     rng = np.random.RandomState(seed)
     rho = np.abs(_smooth(rng, (B, ny, nx), 1.0))
     vy, vx = random_staggered(rng, B, ny, nx, 1.5)
     material = pf.OPEN if boundary == "open" else pf.CLOSED
     dom = pf.Domain([ny, nx], boundaries=material)
-    fluid = pf.Fluid(dom, density=rho[..., None].copy(), velocity=staggered_tensor(vy, vx), batch_size=B)
+    fluid = pf.Fluid(dom, density=rho[..., None].copy(), velocity=staggered_tensor(vy, vx), batch_size=B, buoyancy_factor=buoyancy)
+    effects = []
+    if density_effect:          # a GROW effect on the density (what Inflow is, effect.py:62) given as a plain grid
+        src = np.zeros((1, ny, nx, 1), np.float32)
+        src[:, ny // 4:ny // 2, nx // 3:2 * nx // 3] = 0.25
+        effects = [pf.FieldEffect(pf.CenteredGrid(src, box=dom.box), ["density"], pf.GROW)]
     psolver = pf.SparseSciPy() if solver == "direct" else pf.SparseCG(accuracy=1e-7, max_iterations=5000)
     phys = pf.IncompressibleFlow(pressure_solver=psolver)
-    out = dict(rho0=rho, vy0=vy, vx0=vx, dt=dt, boundary=boundary, steps=steps)
+    out = dict(rho0=rho, vy0=vy, vx0=vx, dt=dt, boundary=boundary, steps=steps, buoyancy=buoyancy)
+    obs = [pf.Obstacle(pf.box[y0:y1, x0:x1]) for (y0, y1, x0, x1) in obstacles]
+    if obstacles:
+        out["obstacles"] = np.asarray(obstacles, np.float32)
+    if density_effect:
+        out["density_source"] = src[0, ..., 0]
     for s in range(steps):
-        fluid = phys.step(fluid, dt)
+        fluid = phys.step(fluid, dt, obstacles=obs, density_effects=effects)
         out["rho%d" % (s + 1)] = np.asarray(fluid.density.data[..., 0], np.float32)
         out["vy%d" % (s + 1)] = np.asarray(fluid.velocity.data[0].data[..., 0], np.float32)
         out["vx%d" % (s + 1)] = np.asarray(fluid.velocity.data[1].data[..., 0], np.float32)
@@ -85,5 +95,14 @@ def main(pf, out_dir):
     np.savez_compressed(os.path.join(out_dir, "fluid_open_32.npz"), **fluid_step_case(pf, 32, 32, 2, "open", 3, 3, 1.0))
     np.savez_compressed(os.path.join(out_dir, "fluid_closed_32x24.npz"), **fluid_step_case(pf, 32, 24, 2, "closed", 5, 3, 0.7))
     np.savez_compressed(os.path.join(out_dir, "fluid_open_128.npz"), **fluid_step_case(pf, 128, 128, 1, "open", 7, 1, 1.0))
+    np.savez_compressed(os.path.join(out_dir, "fluid_buoyancy_open_32.npz"),
+                        **fluid_step_case(pf, 32, 32, 2, "open", 11, 3, 0.5, buoyancy=0.2, density_effect=True))
+    np.savez_compressed(os.path.join(out_dir, "fluid_buoyancy_closed_24x32.npz"),
+                        **fluid_step_case(pf, 24, 32, 2, "closed", 13, 3, 0.5, buoyancy=0.2, density_effect=True))
+    # obstacles: one inside the domain, one touching the lower x boundary (accessible-mask extrapolation), SURVEY 8f N3
+    np.savez_compressed(os.path.join(out_dir, "fluid_obstacle_open_32.npz"),
+                        **fluid_step_case(pf, 32, 32, 2, "open", 17, 2, 0.5, obstacles=[(8, 14, 10, 20), (20, 26, 0, 5)]))
+    np.savez_compressed(os.path.join(out_dir, "fluid_obstacle_closed_24x32.npz"),
+                        **fluid_step_case(pf, 24, 32, 2, "closed", 19, 2, 0.5, obstacles=[(6, 12, 10, 20), (16, 24, 27, 32)]))
     np.savez_compressed(os.path.join(out_dir, "fluid_controlled_64.npz"), **controlled_case(pf, 64, 64, 2, 9, 1.0))
     np.savez_compressed(os.path.join(out_dir, "poisson_40x32.npz"), **poisson_cases(pf))

@@ -336,3 +336,92 @@ def force_loss(vys, vxs, dt, geo, mode=REPLICATE):
         ay, ax = advect_staggered(vys[t], vxs[t], dt, geo, mode)
         loss = loss + l2_loss(ay - vys[t + 1]) + l2_loss(ax - vxs[t + 1])
     return loss / n
+
+
+# ---- obstacles and buoyancy (restated for the CPU checker; test infrastructure only) -------------------------
+
+def obstacle_active(ny, nx, boxes, lower=(0.0, 0.0), size=None):
+    """active = 1 - union of the obstacle boxes sampled at the cell centres (fluid.py:228-233; _box.py:58-61 bounds included)."""
+    size = size or (float(ny), float(nx))
+    cy = (np.arange(ny) + 0.5) / ny * size[0] + lower[0]
+    cx = (np.arange(nx) + 0.5) / nx * size[1] + lower[1]
+    solid = np.zeros((ny, nx), bool)
+    for (y0, y1, x0, x1) in boxes:
+        solid |= ((cy >= y0) & (cy <= y1))[:, None] & ((cx >= x0) & (cx <= x1))[None, :]
+    return (~solid).astype(np.float64)
+
+
+def masked_operator(active, boundary):
+    """Dense matrix of sparse.py:157-221 for a [ny, nx] active mask: off-diagonal active_self * active_nb (0 outside the domain),
+    diagonal -(sum of accessible neighbours; outside: 1 on open, 0 on closed domains: solver_api.py:98-109) clamped to <= -1;
+    and the face masks of _frictionless_velocity_mask (:111-121: accessible grid extended by its own extrapolation)."""
+    ny, nx = active.shape
+    out = 0.0 if boundary == CLOSED else 1.0
+    eact = np.pad(active, 1, constant_values=0.0)
+    eacc = np.pad(active, 1, constant_values=out)
+    N = ny * nx
+    A = np.zeros((N, N))
+    for i in range(ny):
+        for j in range(nx):
+            k = i * nx + j
+            d = 0.0
+            for di, dj in ((-1, 0), (1, 0), (0, -1), (0, 1)):
+                d -= eacc[i + 1 + di, j + 1 + dj]
+                if 0 <= i + di < ny and 0 <= j + dj < nx:
+                    A[k, (i + di) * nx + (j + dj)] = eact[i + 1 + di, j + 1 + dj] * active[i, j]
+            A[k, k] = min(d, -1.0)
+    mode = "constant" if boundary == CLOSED else "edge"
+    py = np.pad(active, ((1, 1), (0, 0)), mode=mode)
+    px = np.pad(active, ((0, 0), (1, 1)), mode=mode)
+    return A, np.minimum(py[:-1], py[1:]), np.minimum(px[:, :-1], px[:, 1:])
+
+
+def divergence_free_obstacles(vy, vx, geo, boundary, active):
+    """divergence_free (fluid.py:214-243) with obstacles; direct dense solve in float64 (least squares: the closed matrix is singular)."""
+    A, fy, fx = masked_operator(active, boundary)
+    dtp = vy.dtype
+    fy_t, fx_t = torch.tensor(fy, dtype=dtp), torch.tensor(fx, dtype=dtp)
+    my, mx = vy * fy_t, vx * fx_t
+    div = divergence(my, mx)
+    B, ny, nx = div.shape
+    if boundary == OPEN:        # non-singular: differentiable dense solve (gradient oracle for the masked projection)
+        p = torch.linalg.solve(torch.tensor(A), div.double().reshape(B, -1, 1)).reshape(B, ny, nx).to(dtp)
+    else:
+        sol = np.linalg.lstsq(A, div.detach().double().numpy().reshape(B, -1).T, rcond=None)[0].T.reshape(B, ny, nx)
+        p = torch.tensor(sol, dtype=dtp)
+    p_s = p * torch.tensor(float(geo.dx[0]), dtype=dtp)
+    py = pad_axis(p_s, 1, 1, 1, REPLICATE)
+    px = pad_axis(p_s, 2, 1, 1, REPLICATE)
+    gy = (py[:, 1:, :] - py[:, :-1, :]) / torch.tensor(float(geo.dx[0]), dtype=dtp)
+    gx = (px[:, :, 1:] - px[:, :, :-1]) / torch.tensor(float(geo.dx[1]), dtype=dtp)
+    return my - gy * fy_t, mx - gx * fx_t, p, div
+
+
+def centered_to_faces(rho, mode):
+    """CenteredGrid.at(StaggeredGrid) on the fast path (grid.py:112-120): pad one cell with the field's extrapolation, average
+    adjacent cells -> ([B, ny+1, nx], [B, ny, nx+1])."""
+    py = pad_axis(rho, 1, 1, 1, mode)
+    px = pad_axis(rho, 2, 1, 1, mode)
+    return py[:, :-1, :] * 0.5 + py[:, 1:, :] * 0.5, px[:, :, :-1] * 0.5 + px[:, :, 1:] * 0.5
+
+
+def incompressible_step_general(rho, vy, vx, dt, geo, boundary, buoyancy=0.0, gravity=-9.81, density_source=None, active=None,
+                                solver=pressure_solve):
+    """IncompressibleFlow.step (fluid.py:90-114) with a GROW density effect, buoyancy (gravity along -axis 0) and obstacles."""
+    rmode, vmode = modes_of(boundary)
+    rho2 = advect_centered(rho, vy, vx, dt, geo, rmode)
+    ay, ax = advect_staggered(vy, vx, dt, geo, vmode)
+    if boundary == CLOSED:
+        rho2 = normalize_to(rho2, rho)
+    if density_source is not None:
+        rho2 = rho2 + density_source * dt                       # effect_applied GROW (effect.py:48-51)
+    if buoyancy != 0.0:
+        # fluid.py:107, up = axis 0.  The two-component lift grid is unstacked before resampling and CenteredGrid.unstack
+        # (grid.py:126-129) drops the extrapolation: the components are padded with the default 'boundary' (replicate)
+        ly, _lx = centered_to_faces(rho2 * (-gravity * buoyancy * dt), REPLICATE)
+        ay = ay + ly
+    if active is not None:
+        vy2, vx2, p, div = divergence_free_obstacles(ay, ax, geo, boundary, active)
+    else:
+        vy2, vx2, p, div = divergence_free(ay, ax, geo, boundary, solver)
+    return rho2, vy2, vx2, p

@@ -71,6 +71,8 @@ _SIGNATURES = {
     "pdec_cg_poisson_2d_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int]),
     "pdec_cg_poisson_2d": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _c.c_int, _c.c_int,
                                        _P, _c.c_size_t, _P]),
+    "pdec_cg_poisson_2d_masked": (_c.c_int, [_P, _P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _c.c_int, _c.c_int,
+                                              _P, _c.c_size_t, _P]),
     # ---- tiled / slab-decomposed CG ----
     "pdec_cg_slab_comm_bytes": (_c.c_size_t, [_c.c_int, _c.c_int]),
     "pdec_cg_slab_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int]),

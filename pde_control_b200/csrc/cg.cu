@@ -589,6 +589,7 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
 // -------------------------------------------------------------------------------------------------------------
 struct CgGlobal {
     const float* rhs; const float* guess; float* x; float* r; float* m[2]; float* am; float* part;
+    const unsigned char* code;      // optional [ny * nx] per-cell stencil code (obstacles): low nibble = coupled neighbours, high = -diagonal
     int* iters; float* resid; int* count;
     int B, ny, nx, closed, chunks, max_it, whole_batch;
     float accuracy;
@@ -646,8 +647,9 @@ __global__ void __launch_bounds__(256) cg_global_kernel(CgGlobal P) {
             if (P.guess) {
                 xx = P.guess[base + idx];
                 const int i = idx / nx, j = idx - i * nx;
-                const unsigned nib = cell_nibble(i, j, ny, nx);
-                rr -= stencil_apply(P.guess + base, idx, nx, nib, cell_diag(nib, P.closed));
+                const unsigned cd = P.code ? P.code[idx] : 0u;
+                const unsigned nib = P.code ? (cd & 15u) : cell_nibble(i, j, ny, nx);
+                rr -= stencil_apply(P.guess + base, idx, nx, nib, P.code ? -(float)(cd >> 4) : cell_diag(nib, P.closed));
             }
             P.x[base + idx] = xx;
             P.r[base + idx] = rr;
@@ -689,12 +691,13 @@ __global__ void __launch_bounds__(256) cg_global_kernel(CgGlobal P) {
             float s1 = 0.0f, s2 = 0.0f;
             for (int idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
                 const int i = idx / nx, j = idx - i * nx;
-                const unsigned nib = cell_nibble(i, j, ny, nx);
+                const unsigned cd = P.code ? P.code[idx] : 0u;
+                const unsigned nib = P.code ? (cd & 15u) : cell_nibble(i, j, ny, nx);
                 const float mm = mval(idx);
                 float a_m = 0.0f;
                 if (nib & 1u) a_m += mval(idx - nx);
                 if (nib & 4u) a_m += mval(idx - 1);
-                a_m += cell_diag(nib, P.closed) * mm;
+                a_m += (P.code ? -(float)(cd >> 4) : cell_diag(nib, P.closed)) * mm;
                 if (nib & 8u) a_m += mval(idx + 1);
                 if (nib & 2u) a_m += mval(idx + nx);
                 m_new[base + idx] = mm;
@@ -821,6 +824,9 @@ static int launch_smem(const float* rhs, const float* guess, float* p, int* iter
     return PDEC_OK;
 }
 
+static int launch_global(const float* rhs, const float* guess, float* p, int* iterations, float* residual, const unsigned char* code, int B, int ny,
+                         int nx, int closed, float accuracy, int max_iterations, bool whole_batch, void* workspace, cudaStream_t st);
+
 extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
                                   int closed, float accuracy, int max_iterations, int stop_mode, void* workspace, size_t workspace_bytes,
                                   void* stream) {
@@ -877,9 +883,16 @@ extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p
                                      workspace_bytes, stream);
         if (rc != PDEC_ERR_UNSUPPORTED_SIZE) return rc;
     }
+    return launch_global(rhs, guess, p, iterations, residual, nullptr, B, ny, nx, closed, accuracy, max_iterations, whole_batch, workspace, st);
+}
+
+static int launch_global(const float* rhs, const float* guess, float* p, int* iterations, float* residual, const unsigned char* code, int B, int ny,
+                         int nx, int closed, float accuracy, int max_iterations, bool whole_batch, void* workspace, cudaStream_t st) {
+    const long long N = (long long)ny * nx;
     CgGlobal P;
     const size_t n = (size_t)B * N;
     float* w = reinterpret_cast<float*>(workspace);
+    P.code = code;
     P.rhs = rhs; P.guess = guess; P.x = p; P.r = w; P.m[0] = w + n; P.m[1] = w + 2 * n; P.am = w + 3 * n; P.part = w + 4 * n;
     P.chunks = global_chunks((int)N);
     P.count = reinterpret_cast<int*>(P.part + (size_t)8 * B * P.chunks);
@@ -899,4 +912,17 @@ extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p
         return PDEC_ERR_CUDA_LAUNCH;
     }
     return PDEC_OK;
+}
+
+// Masked operator (obstacles): the stencil of every cell comes from `code` [ny * nx] (shared by the batch): bits 0..3 = coupled
+// neighbour above / below / left / right (active_self * active_neighbour, sparse.py:186-205), bits 4..7 = minus the diagonal
+// (number of accessible neighbours, at least 1, sparse.py:207-213).  Always the streaming kernel.
+extern "C" int pdec_cg_poisson_2d_masked(const float* rhs, const float* guess, float* p, int* iterations, float* residual,
+                                         const unsigned char* code, int B, int ny, int nx, float accuracy, int max_iterations, int stop_mode,
+                                         void* workspace, size_t workspace_bytes, void* stream) {
+    if (!rhs || !p || !code || !workspace || B < 1 || ny < 1 || nx < 1 || max_iterations < 0) return PDEC_ERR_INVALID_ARGUMENT;
+    if ((long long)ny * nx > 0x7fffffffLL) return PDEC_ERR_UNSUPPORTED_SIZE;
+    if (workspace_bytes < pdec_cg_poisson_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+    return launch_global(rhs, guess, p, iterations, residual, code, B, ny, nx, 0, accuracy, max_iterations,
+                         stop_mode == PDEC_CG_STOP_WHOLE_BATCH && B > 1, workspace, (cudaStream_t)stream);
 }

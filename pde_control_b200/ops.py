@@ -588,6 +588,90 @@ def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000
     return oy, ox, p, iters, div
 
 
+class ObstacleMasks(object):
+    """Per-scene masks of a domain with obstacles (PoissonDomain, solver_api.py:51-121), built once from the cell mask
+    `active` [ny, nx] (1 = fluid, 0 = obstacle; the reference samples the obstacle geometries at the cell centres,
+    fluid.py:228-233):
+      fy [ny+1, nx], fx [ny, nx+1]  face masks = min of the two adjacent `accessible` cells, the accessible grid extended with its
+                                    own extrapolation (replicate on open, 0 on closed domains: _frictionless_velocity_mask :111-121)
+      code [ny, nx] uint8           stencil of pdec_cg_poisson_2d_masked: off-diagonals active_self * active_neighbour (0 outside),
+                                    diagonal -(accessible neighbours), outside = 1 on open / 0 on closed domains, clamped to <= -1
+                                    (sparse.py:186-213 with active_tensor / accessible_tensor, solver_api.py:88-109)."""
+
+    def __init__(self, active, closed):
+        a = active.to(torch.float32)
+        assert a.dim() == 2 and a.is_cuda
+        self.closed = bool(closed)
+        self.active = a
+        pad = torch.nn.functional.pad
+        ext_act = pad(a, (1, 1, 1, 1), value=0.0)
+        ext_acc = pad(a, (1, 1, 1, 1), value=0.0 if closed else 1.0)
+        up, down = ext_act[:-2, 1:-1] * a, ext_act[2:, 1:-1] * a
+        left, right = ext_act[1:-1, :-2] * a, ext_act[1:-1, 2:] * a
+        diag = (ext_acc[:-2, 1:-1] + ext_acc[2:, 1:-1] + ext_acc[1:-1, :-2] + ext_acc[1:-1, 2:]).clamp_min(1.0)
+        self.code = (up + 2 * down + 4 * left + 8 * right + 16 * diag).to(torch.uint8).contiguous()
+        if closed:
+            py, px = pad(a, (0, 0, 1, 1), value=0.0), pad(a, (1, 1, 0, 0), value=0.0)
+        else:
+            py = pad(a[None, None], (0, 0, 1, 1), mode="replicate")[0, 0]
+            px = pad(a[None, None], (1, 1, 0, 0), mode="replicate")[0, 0]
+        self.fy = torch.minimum(py[:-1], py[1:]).contiguous()
+        self.fx = torch.minimum(px[:, :-1], px[:, 1:]).contiguous()
+
+
+def cg_poisson_masked_raw(rhs, out, code, accuracy, max_iterations, guess=None, iterations=None, residual=None, stop_mode=0):
+    B, ny, nx = rhs.shape
+    assert code.dtype == torch.uint8 and tuple(code.shape) == (ny, nx) and code.is_contiguous()
+    L = _lib.lib()
+    nbytes = L.pdec_cg_poisson_2d_workspace_bytes(B, ny, nx)
+    ws = _lib.workspace(rhs.device, nbytes)
+    with torch.cuda.device(rhs.device):
+        _call("pdec_cg_poisson_2d_masked", _lib.ptr(rhs), _lib.ptr(guess), _lib.ptr(out), _lib.ptr(iterations), _lib.ptr(residual),
+              _lib.ptr(code), B, ny, nx, float(accuracy if accuracy is not None else 0.0), int(max_iterations), int(stop_mode),
+              _lib.ptr(ws), nbytes, _lib.stream_ptr())
+
+
+class _PressureSolveMasked(torch.autograd.Function):
+    """SparseCG on a domain with obstacles; backward = the same masked solve of the incoming gradient (sparse.py:93-94)."""
+
+    @staticmethod
+    def forward(ctx, div, code, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations):
+        _req_cuda(div)
+        assert code.is_cuda and code.dtype == torch.uint8
+        div = _c(div)
+        B = div.shape[0]
+        p = torch.empty_like(div)
+        iters = torch.zeros(B, device=div.device, dtype=torch.int32)
+        resid = torch.zeros(B, device=div.device, dtype=torch.float32)
+        cg_poisson_masked_raw(div, p, code, accuracy, max_iterations, None, iters, resid)
+        ctx.code = code
+        ctx.cfg = (gradient_accuracy, max_gradient_iterations)
+        ctx.mark_non_differentiable(iters, resid)
+        return p, iters, resid
+
+    @staticmethod
+    def backward(ctx, g_p, _gi, _gr):
+        accuracy, max_it = ctx.cfg
+        g_p = _c(g_p)
+        g_div = torch.empty_like(g_p)
+        cg_poisson_masked_raw(g_p, g_div, ctx.code, accuracy, max_it)
+        return g_div, None, None, None, None, None
+
+
+def divergence_free_masked(vy, vx, masks, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
+                           max_gradient_iterations=None):
+    """divergence_free (PF/physics/fluid.py:214-243) WITH obstacles -> (vy', vx', pressure, iterations, divergence).
+    The face masks are applied with plain multiplies (autograd), the divergence / gradient kernels run unmasked on the masked
+    velocity, the solve is the masked streaming CG."""
+    ga = accuracy if gradient_accuracy is None else gradient_accuracy
+    gi = max_iterations if max_gradient_iterations is None else max_gradient_iterations
+    my, mx = vy * masks.fy, vx * masks.fx                      # with_hard_boundary_conditions(velocity)
+    div = mask_divergence(my, mx, False)
+    p, iters, _ = _PressureSolveMasked.apply(div, masks.code, accuracy, int(max_iterations), ga, int(gi))
+    oy, ox = subtract_pressure_gradient(my, mx, p, False, box)  # my - grad(p dx)/dx, boundary-face gradient 0
+    return oy * masks.fy, ox * masks.fx, p, iters, div         # = my - mask * grad p for binary masks
+
+
 def incompressible_step(rho, vy, vx, dt, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
                         max_gradient_iterations=None, conserve_density=True, slab=None):
     """IncompressibleFlow.step (PF/physics/fluid.py:90-114), default flags, no obstacles / effects / buoyancy.

@@ -124,7 +124,10 @@ class CenteredGrid(Field):
                 c = self.data[..., d:d + 1] if self.component_count > 1 else self.data
                 widths = [[0, 0]] * self.rank
                 widths[d] = [1, 1]
-                padded = self.copied_with(data=c).padded(widths).data
+                # a multi-component grid is unstacked first and CenteredGrid.unstack (grid.py:126-129) does not pass the
+                # extrapolation on: its components are padded with the default 'boundary' whatever the field's own mode
+                source = self.copied_with(data=c, extrapolation="boundary") if self.component_count > 1 else self.copied_with(data=c)
+                padded = source.padded(widths).data
                 lo = padded.narrow(1 + d, 0, padded.shape[1 + d] - 1)
                 hi = padded.narrow(1 + d, 1, padded.shape[1 + d] - 1)
                 comps.append(lo * 0.5 + hi * 0.5)                      # interpolate_linear: x0 * (1 - w) + x1 * w, w = 0.5 (nd.py:378-392)

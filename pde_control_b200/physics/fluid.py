@@ -15,7 +15,7 @@ from .._lib import MODE_OF_EXTRAPOLATION
 from .burgers import DomainState
 from .domain import Domain, OPEN
 from .field import CenteredGrid, StaggeredGrid, effect_applied
-from .world import Physics, StateDependency
+from .world import Physics, State, StateDependency, Gravity
 
 
 class SparseCG(object):
@@ -79,17 +79,57 @@ def _box4(box):
     return tuple(float(v) for v in box.lower) + tuple(float(v) for v in box.size)
 
 
+class Obstacle(State):
+    """Solid body inside the domain (PF/physics/obstacle.py:10-27): `geometry` is an AABox (or a list of them) in physical units;
+    cells whose centre lies inside (bounds included, geom/_box.py:58-61) are inactive and inaccessible."""
+
+    def __init__(self, geometry, material=None, velocity=0, tags=("obstacle",), name=None, **kwargs):
+        State.__init__(self, name=name, tags=tags, **kwargs)
+        self.geometry = geometry
+        self.material = material
+        self.velocity = velocity
+
+
+_MASK_CACHE = {}
+
+
+def obstacle_masks(obstacles, velocity, domain):
+    """active = 1 - union of the obstacle geometries sampled at the cell centres (fluid.py:228-233) -> ops.ObstacleMasks (cached
+    per geometry set, resolution, box and boundary type: obstacles are static on this path)."""
+    boxes = []
+    for o in obstacles:
+        geo = o.geometry if hasattr(o, "geometry") else o
+        boxes += list(geo) if isinstance(geo, (list, tuple)) else [geo]
+    key = (tuple((tuple(map(float, b.lower)), tuple(map(float, b.upper))) for b in boxes), tuple(int(r) for r in velocity.resolution),
+           _box4(velocity.box), _closed(domain), str(velocity.data[0].data.device))
+    if key not in _MASK_CACHE:
+        ny, nx = (int(r) for r in velocity.resolution)
+        lo, size = velocity.box.lower, velocity.box.size
+        cy = (np.arange(ny) + 0.5) / ny * float(size[0]) + float(lo[0])
+        cx = (np.arange(nx) + 0.5) / nx * float(size[1]) + float(lo[1])
+        solid = np.zeros((ny, nx), bool)
+        for b in boxes:
+            solid |= ((cy >= b.lower[0]) & (cy <= b.upper[0]))[:, None] & ((cx >= b.lower[1]) & (cx <= b.upper[1]))[None, :]
+        active = torch.tensor((~solid).astype(np.float32), device=velocity.data[0].data.device)
+        _MASK_CACHE[key] = ops.ObstacleMasks(active, _closed(domain))
+    return _MASK_CACHE[key]
+
+
 def divergence_free(velocity, domain=None, obstacles=(), pressure_solver=None, return_info=False):
-    """Pressure projection (fluid.py:214-243) without obstacles."""
+    """Pressure projection (fluid.py:214-243); with obstacles the masked operators of ops.divergence_free_masked."""
     assert isinstance(velocity, StaggeredGrid)
-    if len(obstacles) > 0:
-        raise NotImplementedError("obstacles are not on the B200 path (SURVEY 8f N3)")
     if domain is None:
         domain = Domain(velocity.resolution, OPEN, box=velocity.box)
     solver = pressure_solver or SparseCG()
     vy, vx = velocity.tensors
-    oy, ox, p, iters, div = ops.divergence_free(vy, vx, _closed(domain), _box4(velocity.box), solver.accuracy, solver.max_iterations,
-                                                solver.gradient_accuracy, solver.max_gradient_iterations)
+    if len(obstacles) > 0:
+        assert velocity.rank == 2
+        masks = obstacle_masks(obstacles, velocity, domain)
+        oy, ox, p, iters, div = ops.divergence_free_masked(vy, vx, masks, _box4(velocity.box), solver.accuracy, solver.max_iterations,
+                                                           solver.gradient_accuracy, solver.max_gradient_iterations)
+    else:
+        oy, ox, p, iters, div = ops.divergence_free(vy, vx, _closed(domain), _box4(velocity.box), solver.accuracy, solver.max_iterations,
+                                                    solver.gradient_accuracy, solver.max_gradient_iterations)
     result = velocity.with_tensors([oy, ox])
     if not return_info:
         return result
@@ -120,16 +160,6 @@ class Fluid(DomainState):
 
     def default_physics(self):
         return INCOMPRESSIBLE_FLOW
-
-
-class Gravity(object):
-    """Gravity state (effect.py:77-104): a scalar acts along -up (axis 0, physics_config.py:25-29), a vector as given."""
-    tags = ("gravity",)
-
-    def __init__(self, gravity=-9.81, name="gravity"):
-        assert gravity is not None
-        self.gravity = gravity
-        self.name = name
 
 
 def gravity_tensor(gravity, rank):

@@ -42,6 +42,16 @@ class State(object):
         return '%s[name="%s"]' % (self.__class__.__name__, self.name)
 
 
+class Gravity(State):
+    """Gravity state (PF/physics/field/effect.py:77-104): a scalar acts along -up (axis 0, physics_config.py:25-29), a vector
+    as given.  A World adds one by default (world.py:128-130)."""
+
+    def __init__(self, gravity=-9.81, name="gravity", **kwargs):
+        assert gravity is not None
+        State.__init__(self, name=name, tags=("gravity",), **kwargs)
+        self.gravity = gravity
+
+
 class StateDependency(object):
     """Request for other states, resolved by CollectivePhysics (PF/physics/physics.py:71-100)."""
 
@@ -282,6 +292,8 @@ class World(object):
         self.physics = CollectivePhysics()
         self.observers = set()
         self.batch_size = batch_size
+        if add_default_objects:
+            self.add(Gravity())                                # world.py:128-130
 
     @property
     def state(self):
@@ -346,6 +358,8 @@ class World(object):
         self._state = StateCollection()
         self.physics = CollectivePhysics()
         self.batch_size = batch_size
+        if add_default_objects:
+            self.add(Gravity())
 
     def clear(self):
         self.reset(self.batch_size)

@@ -161,3 +161,23 @@ def test_restatement_vs_live_reference_random_box():
             assert rel_err(x2, out.velocity.data[1].data[..., 0]) < 2e-5
     finally:
         R.NUMPY_EDGE_RULE = False
+
+
+@pytest.mark.parametrize("name", ["fluid_buoyancy_open_32", "fluid_buoyancy_closed_24x32", "fluid_obstacle_open_32",
+                                  "fluid_obstacle_closed_24x32"])
+def test_buoyancy_effects_and_obstacles_match_reference_golden(name, numpy_edge_rule):
+    """SURVEY 8f N3 restatement (buoyancy through the face-sampled density, GROW density effect, obstacle masks in the
+    divergence / matrix / gradient) vs the live reference's NumPy path."""
+    g = _load(name)
+    B, ny, nx = g["rho0"].shape
+    geo = F.Geometry(ny, nx)
+    bd, dt = str(g["boundary"]), float(g["dt"])
+    src = torch.tensor(g["density_source"])[None] if "density_source" in g.files else None
+    active = F.obstacle_active(ny, nx, g["obstacles"].tolist()) if "obstacles" in g.files else None
+    rho, vy, vx = [torch.tensor(g[k]) for k in ("rho0", "vy0", "vx0")]
+    for k in range(1, int(g["steps"]) + 1):
+        rho, vy, vx, p = F.incompressible_step_general(rho, vy, vx, dt, geo, bd, buoyancy=float(g["buoyancy"]), density_source=src,
+                                                       active=active)
+        tol = 1e-5 if k == 1 else 1e-4
+        assert rel_err(rho, g["rho%d" % k]) < tol
+        assert rel_err(vy, g["vy%d" % k]) < 2 * tol and rel_err(vx, g["vx%d" % k]) < 2 * tol
