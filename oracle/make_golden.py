@@ -58,12 +58,33 @@ def burgers_single_steps(pf):
                         substeps=1, resubstep=0, lower=0.0, size=1.0)
 
 
+def burgers_periodic(pf):
+    """PERIODIC domain -> diffuse takes the FFT branch (PF/physics/field/util.py:30-37); advection wraps around
+    ('circular' resample); with a GROW force.  4 steps, batch 3, N = 128, box [0, 1]."""
+    rng = np.random.RandomState(21)
+    B, N = 3, 128
+    x = (np.arange(N) + 0.5) / N
+    u0 = np.stack([a * np.sin(2 * np.pi * (k * x + ph)) for a, k, ph in zip(rng.uniform(0.5, 2.5, B), (1, 2, 3), rng.rand(B))]).astype(np.float32)
+    force = (0.5 * np.cos(2 * np.pi * x))[None].repeat(B, 0).astype(np.float32)
+    dom = pf.Domain([N], boundaries=pf.PERIODIC, box=pf.box[0:1])
+    world = pf.World(batch_size=B)
+    st = world.add(pf.BurgersVelocity(dom, velocity=u0[..., None].copy(), viscosity=0.01, batch_size=B), physics=pf.Burgers())
+    world.add(pf.FieldEffect(pf.CenteredGrid(force[..., None].copy(), box=dom.box, extrapolation="periodic"), ['velocity']))
+    frames = [u0]
+    for _ in range(4):
+        world.step(dt=0.03)
+        frames.append(np.asarray(st.velocity.data[..., 0], np.float32).copy())
+    np.savez_compressed(os.path.join(OUT, "burgers_periodic.npz"), frames=np.stack(frames), force=force, dt=0.03, viscosity=0.01,
+                        extrapolation=str(st.velocity.extrapolation))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     warnings.simplefilter("ignore")
     pf = ref_shim.flow()
     burgers_config1(pf)
     burgers_single_steps(pf)
+    burgers_periodic(pf)
     try:
         from . import make_golden_fluid
         make_golden_fluid.main(pf, OUT)

@@ -88,6 +88,8 @@ def poisson_cases(pf):
         p, _ = pf.poisson_solve(field, dom, solver=pf.SparseCG(accuracy=1e-6, max_iterations=5000))
         out["rhs_" + name] = rhs
         out["p_" + name] = np.asarray(p.data[..., 0], np.float32)
+        # FourierSolver (fourier.py:17-18 -> math.fourier_poisson, nd.py:305-314): the first link of the TF-default solver chain
+        out["fft_" + name] = np.asarray(pf.math.fourier_poisson(rhs[..., None].copy())[..., 0], np.float32)
     return out
 
 

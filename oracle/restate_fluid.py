@@ -425,3 +425,14 @@ def incompressible_step_general(rho, vy, vx, dt, geo, boundary, buoyancy=0.0, gr
     else:
         vy2, vx2, p, div = divergence_free(ay, ax, geo, boundary, solver)
     return rho2, vy2, vx2, p
+
+
+def fourier_poisson(rhs):
+    """FourierSolver (fourier.py:17-18) = math.fourier_poisson (nd.py:305-314): spectrum / (-(2 pi)^2 |k|^2), k = fftfreq in cycles
+    per cell, the k = 0 mode set to 0.  rhs [B, ny, nx]."""
+    ny, nx = rhs.shape[1:]
+    ky = torch.fft.fftfreq(ny, dtype=torch.float64)[:, None]
+    kx = torch.fft.fftfreq(nx, dtype=torch.float64)[None, :]
+    lap = -(2 * np.pi) ** 2 * (ky ** 2 + kx ** 2).to(torch.float32).to(torch.float64)       # fftfreq(..., dtype=np.float32)
+    inv = torch.where(lap == 0, torch.zeros_like(lap), 1.0 / torch.where(lap == 0, torch.ones_like(lap), lap))
+    return torch.fft.ifft2(torch.fft.fft2(rhs.to(torch.complex128)) * inv).real.to(rhs.dtype)

@@ -7,7 +7,7 @@ from .field import (Field, CenteredGrid, StaggeredGrid, FieldEffect, GROW, ADD, 
                     staggered_component_box)
 from .burgers import DomainState, BurgersVelocity, Burgers
 from .fluid import (Fluid, IncompressibleFlow, INCOMPRESSIBLE_FLOW, SparseCG, poisson_solve, divergence_free, semi_lagrangian,
-                    staggered_curl_2d, gravity_tensor, Obstacle)
+                    staggered_curl_2d, gravity_tensor, Obstacle, FourierSolver)
 
 
 class _Advect(object):

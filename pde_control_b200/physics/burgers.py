@@ -58,6 +58,15 @@ class BurgersVelocity(DomainState):
         return Burgers()
 
 
+def fourier_diffuse(u, amount, dx):
+    """diffuse, periodic branch (PF/physics/field/util.py:30-37) for u [B, n]: differentiable (torch.fft)."""
+    import math
+    import torch
+    k = torch.fft.fftfreq(u.shape[1], device=u.device, dtype=torch.float32) / dx
+    kernel = torch.exp(-(2.0 * math.pi) ** 2 * k * k * amount)
+    return torch.fft.ifft(torch.fft.fft(u.to(torch.complex64), dim=1) * kernel, dim=1).real.contiguous()
+
+
 class Burgers(Physics):
 
     def __init__(self, default_viscosity=0.1, viscosity=None, diffusion_substeps=1, tf_substeps=True):
@@ -80,6 +89,16 @@ class Burgers(Physics):
         further effects are added afterwards (effect.py:48-53)."""
         assert isinstance(v, CenteredGrid) and v.rank == 1, "the B200 Burgers path is 1-D"
         effects = tuple(effects)
+        if v.extrapolation == "periodic":
+            # the reference's diffuse switches to its FFT branch on periodic fields (PF/physics/field/util.py:30-37): circular
+            # advection by the kernel (viscosity 0 adds exactly 0), then the spectrum times exp(-(2 pi k / dx)^2 nu dt) with cuFFT
+            # through torch.fft (the reference calls the backend's fft the same way), then the effects
+            out = ops.burgers_step(v.tensor, dt, 0.0, lower=float(v.box.lower[0]), size=float(v.box.size[0]),
+                                   mode=MODE_OF_EXTRAPOLATION[v.extrapolation])
+            v = v.with_tensor(fourier_diffuse(out, float(dt) * float(viscosity), float(v.dx[0])))
+            for effect in effects:
+                v = effect_applied(effect, v, dt)
+            return v.copied_with(age=v.age + dt)
         force, effect_mode, rest = None, None, effects
         if effects and isinstance(effects[0], FieldEffect) and effects[0].mode in (GROW, ADD):
             force = effects[0].field.at(v).tensor

@@ -18,7 +18,12 @@ from .field import CenteredGrid, StaggeredGrid, effect_applied
 from .world import Physics, State, StateDependency, Gravity
 
 
-class SparseCG(object):
+class _Chainable(object):
+    def __and__(self, other):
+        return _SolverChain((self, other))
+
+
+class SparseCG(_Chainable):
     """Conjugate-gradient pressure solver parameters (sparse.py:42-71).  'mirror' gradient iterations are treated as
     'same' (the device decides the iteration count)."""
 
@@ -36,6 +41,41 @@ class SparseCG(object):
         p, iters, _ = ops.pressure_solve(t, _closed(domain), self.accuracy, self.max_iterations, self.gradient_accuracy,
                                          self.max_gradient_iterations, g)
         return (p.unsqueeze(-1) if field.dim() == 4 else p), iters
+
+
+class _SolverChain(object):
+    """solver1 & solver2 (solver_api.py:161-174): each solver's result is the next one's initial guess.  The reference's default
+    on the TensorFlow backend is FourierSolver() & SparseCG() (solver_api.py:149-155)."""
+
+    def __init__(self, solvers):
+        self.solvers = tuple(solvers)
+
+    def __and__(self, other):
+        return _SolverChain(self.solvers + (other,))
+
+    def solve(self, field, domain, guess=None):
+        iterations = None
+        for solver in self.solvers:
+            guess, iterations = solver.solve(field, domain, guess)
+        return guess, iterations
+
+
+class FourierSolver(object):
+    """Inverse Laplace in Fourier space (pressuresolver/fourier.py:5-18 -> math.fourier_poisson, nd.py:305-314): exact for periodic
+    domains, an initial guess for the others.  cuFFT through torch.fft, as the reference goes through its backend's fft."""
+
+    def __and__(self, other):
+        return _SolverChain((self, other))
+
+    def solve(self, field, domain, guess=None):
+        t = field[..., 0] if field.dim() == 4 else field
+        ny, nx = t.shape[1:]
+        ky = torch.fft.fftfreq(ny, device=t.device, dtype=torch.float32)[:, None]
+        kx = torch.fft.fftfreq(nx, device=t.device, dtype=torch.float32)[None, :]
+        lap = -(2.0 * np.pi) ** 2 * (ky * ky + kx * kx)
+        inv = torch.where(lap == 0, torch.zeros_like(lap), 1.0 / torch.where(lap == 0, torch.ones_like(lap), lap))
+        p = torch.fft.ifft2(torch.fft.fft2(t.to(torch.complex64)) * inv).real.contiguous()
+        return (p.unsqueeze(-1) if field.dim() == 4 else p), None
 
 
 def _closed(domain):

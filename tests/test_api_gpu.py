@@ -143,6 +143,40 @@ def test_masked_projection_gradient_vs_oracle():
     assert float((cy.detach() * (1 - masks.fy)).abs().max()) == 0.0 and float((cx.detach() * (1 - masks.fx)).abs().max()) == 0.0
 
 
+def test_periodic_burgers_takes_the_fft_diffusion_branch():
+    """PERIODIC Burgers through World (circular advection kernel + FFT diffusion + GROW effect) vs the live reference."""
+    from pde_control_b200.physics import World, Domain, BurgersVelocity, Burgers, PERIODIC, box, FieldEffect, CenteredGrid
+    g = np.load(os.path.join(GOLDEN, "burgers_periodic.npz"))
+    B, N = g["frames"].shape[1:]
+    dom = Domain([N], boundaries=PERIODIC, box=box[0:1])
+    world = World(batch_size=B)
+    u = world.add(BurgersVelocity(dom, velocity=g["frames"][0][..., None], viscosity=float(g["viscosity"]), batch_size=B), physics=Burgers())
+    world.add(FieldEffect(CenteredGrid(torch.tensor(g["force"][..., None]).cuda(), box=dom.box, extrapolation="periodic"), ["velocity"]))
+    assert u.velocity.extrapolation == "periodic"
+    for k in range(1, 5):
+        world.step(dt=float(g["dt"]))
+        assert rel_err(u.velocity.data[..., 0].cpu(), g["frames"][k]) < (1e-5 if k == 1 else 1e-4)
+
+
+@pytest.mark.parametrize("bd", ["open", "closed"])
+def test_fourier_solver_and_solver_chain(bd):
+    """FourierSolver == the reference's math.fourier_poisson; FourierSolver() & SparseCG() (the reference's TF default chain,
+    solver_api.py:149-155) converges to the same pressure as SparseCG alone."""
+    from pde_control_b200.physics import Domain, SparseCG, FourierSolver, CenteredGrid, poisson_solve, OPEN, CLOSED
+    g = np.load(os.path.join(GOLDEN, "poisson_40x32.npz"))
+    rhs = torch.tensor(g["rhs_" + bd]).cuda()
+    dom = Domain([40, 32], boundaries=OPEN if bd == "open" else CLOSED)
+    p0, it0 = FourierSolver().solve(rhs, dom)
+    assert it0 is None and rel_err(p0.cpu(), g["fft_" + bd]) < 1e-5
+    field = CenteredGrid(rhs[..., None], box=dom.box)
+    pa, ita = poisson_solve(field, dom, solver=SparseCG(accuracy=1e-6, max_iterations=5000))
+    pb, itb = poisson_solve(field, dom, solver=FourierSolver() & SparseCG(accuracy=1e-6, max_iterations=5000))
+    a, b = pa.data[..., 0].cpu(), pb.data[..., 0].cpu()
+    if bd == "closed":
+        a, b = a - a.mean((1, 2), keepdim=True), b - b.mean((1, 2), keepdim=True)
+    assert rel_err(b, a) < 1e-4 and int(itb.max()) > 0
+
+
 def test_control_training_burgers_runs_the_fused_force_loss():
     from pde_control_b200 import ops, datagen
     from pde_control_b200.physics import Domain, box

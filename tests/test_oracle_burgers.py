@@ -89,3 +89,14 @@ def test_restatement_vs_live_reference_random_modes():
         ref = pf.Burgers().step_velocity(grid, 0.01, 0.05, (), 1).data[..., 0]
         got = R.burgers_step(torch.tensor(u), 0.05, 0.01, lower=0.0, size=2.0, mode=mode).numpy()
         assert rel_err(got, ref) < 1e-5, extr
+
+
+def test_periodic_fft_diffusion_matches_reference_golden():
+    """PERIODIC Burgers (circular advection + FFT diffusion + GROW force), 4 steps vs the live reference."""
+    g = np.load(os.path.join(GOLDEN, "burgers_periodic.npz"))
+    assert str(g["extrapolation"]) == "periodic"
+    u = torch.tensor(g["frames"][0])
+    f = torch.tensor(g["force"])
+    for k in range(1, 5):
+        u = R.burgers_step_periodic(u, float(g["dt"]), float(g["viscosity"]), force=f)
+        assert rel_err(u, g["frames"][k]) < (1e-5 if k == 1 else 1e-4)

@@ -181,3 +181,10 @@ def test_buoyancy_effects_and_obstacles_match_reference_golden(name, numpy_edge_
         tol = 1e-5 if k == 1 else 1e-4
         assert rel_err(rho, g["rho%d" % k]) < tol
         assert rel_err(vy, g["vy%d" % k]) < 2 * tol and rel_err(vx, g["vx%d" % k]) < 2 * tol
+
+
+@pytest.mark.parametrize("bd", ["open", "closed"])
+def test_fourier_poisson_matches_reference(bd):
+    """FourierSolver's guess (math.fourier_poisson) vs the live reference."""
+    g = _load("poisson_40x32")
+    assert rel_err(F.fourier_poisson(torch.tensor(g["rhs_" + bd])), g["fft_" + bd]) < 1e-5
