@@ -133,12 +133,22 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
         // among themselves, ceil targets among themselves); out-of-domain lanes all hit the scratch words
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
+#ifdef F2_SPLIT
+            // floor and ceil parts in two rows, both at the floor offset: two independent read-modify-writes per sample
+            float* af = ptr_off(sacc, S.offF[k]);
+            float* ac = ptr_off(sacc + F2_ROW, S.offF[k]);
+            const float a = *af, c = *ac;
+            *af = fmaf(-q[k], w1[k], a);
+            *ac = fmaf(-q[k], w0[k], c);
+            __syncwarp();
+#else
             float* af = ptr_off(sacc, S.offF[k]);
             *af = fmaf(-q[k], w1[k], *af);
             __syncwarp();
             float* ac = ptr_off(sacc, S.offC[k]);
             *ac = fmaf(-q[k], w0[k], *ac);
             __syncwarp();
+#endif
         }
     } else
 #ifdef F2_SKIP_SCATTER
@@ -159,7 +169,11 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
                 }
                 __syncwarp();
                 if (inside && rank == r) {
+#ifdef F2_SPLIT
+                    float* ac = ptr_off(sacc + F2_ROW, S.offF[k]);
+#else
                     float* ac = ptr_off(sacc, S.offC[k]);
+#endif
                     *ac = fmaf(-q[k], w0[k], *ac);
                 }
                 __syncwarp();
@@ -167,8 +181,19 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
         }
     }
     // transpose of the gather (own four cells) plus the derivative through xi(u)
+#ifdef F2_SPLIT
+    // cell j = floor part of slot j + ceil part of slot j - 1 (for the lane's first cell that is the previous lane's last slot)
+    float* mine_c = mine_acc + F2_ROW;
+    const float cprev = lane > 0 ? mine_c[95] : 0.0f;
+    const float c0 = mine_c[0], c1 = mine_c[32], c2 = mine_c[64];
+    const float o0 = mine_acc[0] + cprev, o1 = mine_acc[32] + c0, o2 = mine_acc[64] + c1, o3 = mine_acc[96] + c2;
+    __syncwarp();                                                      // the neighbour's slot is read before its owner clears it
+    mine_acc[0] = 0.0f; mine_acc[32] = 0.0f; mine_acc[64] = 0.0f; mine_acc[96] = 0.0f;
+    mine_c[0] = 0.0f; mine_c[32] = 0.0f; mine_c[64] = 0.0f; mine_c[96] = 0.0f;
+#else
     const float o0 = mine_acc[0], o1 = mine_acc[32], o2 = mine_acc[64], o3 = mine_acc[96];
     mine_acc[0] = 0.0f; mine_acc[32] = 0.0f; mine_acc[64] = 0.0f; mine_acc[96] = 0.0f;
+#endif
     const float2 dt2 = f2(p.dt128, p.dt128);
     const float2 e01 = __fmul2_rn(f2(S.du[0], S.du[1]), dt2), e23 = __fmul2_rn(f2(S.du[2], S.du[3]), dt2);   // -du * dxi/du
     gin01 = __ffma2_rn(q01, e01, f2(o0, o1));
@@ -188,13 +213,20 @@ template <bool L1TERM>
 __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
                                                                             float2* partials, int T, int B, int t0, int t1, long long per_warp,
                                                                             unsigned* done_counter, float* __restrict__ losses, float inv_B) {
+#ifdef F2_SPLIT
+    __shared__ float smem[F2_WARPS][3][F2_ROW];
+#else
     __shared__ float smem[F2_WARPS][2][F2_ROW];
+#endif
     __shared__ float red2[F2_WARPS], red1[F2_WARPS];
     __shared__ unsigned s_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* su = smem[warp][0];
     float* sacc = smem[warp][1];
     for (int q = lane; q < F2_ROW; q += 32) { su[q] = 0.0f; sacc[q] = 0.0f; }
+#ifdef F2_SPLIT
+    for (int q = lane; q < F2_ROW; q += 32) sacc[F2_ROW + q] = 0.0f;
+#endif
     __syncwarp();
     float* mine = su + lane;
     float* mine_acc = sacc + lane;
@@ -226,6 +258,14 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
         int fn = f + 1, bn = b;
         size_t offn = off + f4;
         float4 pre = __ldcs(s4 + offn);                                // streamed: every frame is read once per range
+#ifdef F2_PF2
+        // second load cursor, one frame further: two frames in flight per warp.  It walks the same frame sequence and may run past
+        // the end of the range (never past the array): those frames are loaded and dropped
+        int fl = fn, bl = bn;
+        size_t offl = offn;
+        if (fl == t1) { fl = row_first; bl += 1; offl = (size_t)row_first * f4 + (size_t)bl * 32; } else { fl += 1; offl += f4; }
+        float4 pre2 = bl < B ? __ldcs(s4 + offl) : pre;
+#endif
         while (true) {
             const float2 n01 = f2(pre.x, pre.y), n23 = f2(pre.z, pre.w);
             const int fcur = fn, bcur = bn;                            // position of n
@@ -233,7 +273,13 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
             const bool closing = bcur != b;                            // u = last frame of row b, n = first frame of row b + 1
             const bool real = !closing && fcur - 1 >= lo;              // (u, n) = pair fcur - 1 of row b, inside the range
             if (fn == t1) { fn = row_first; bn += 1; offn = (size_t)row_first * f4 + (size_t)bn * 32; } else { fn += 1; offn += f4; }
+#ifdef F2_PF2
+            pre = pre2;
+            if (fl == t1) { fl = row_first; bl += 1; offl = (size_t)row_first * f4 + (size_t)bl * 32; } else { fl += 1; offl += f4; }
+            if (bl < B && remaining - (real ? 1 : 0) > 0) pre2 = __ldcs(s4 + offl);
+#else
             if (remaining - (real ? 1 : 0) > 0) pre = __ldcs(s4 + offn);      // in flight during this step's arithmetic
+#endif
             if (!closing) {
                 step2_forward(p, X01, X23, u01, u23, su, mine, lane, v01, v23, S);
                 const float2 d01 = sub2(n01, v01), d23 = sub2(n23, v23);     // burgers.py:29
