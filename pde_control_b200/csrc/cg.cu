@@ -577,6 +577,12 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
 }
 
 // -------------------------------------------------------------------------------------------------------------
+// Measured and dropped (round 1, profiles/r1n_cg_packed.md): a packed-fp32 twin of cg_block_kernel (vectors as float2 pairs of rows
+// q and q + 4, add/fma.rn.f32x2, lane halo through shared memory or shuffles) has 17-20 % fewer instructions per iteration (388-399
+// against 482) and is SLOWER: 1.99-2.62 us per iteration at 128x128 against 1.78.  The kernel is bound by the barrier / reduction
+// latency chain at 4 warps per scheduler and by the fp32 pipe's lane throughput (which packing does not change), not by issue slots.
+// -------------------------------------------------------------------------------------------------------------
+// -------------------------------------------------------------------------------------------------------------
 // Large grids: cooperative persistent kernel, vectors in global memory (L2 resident up to ~20 MB per vector).
 // Unit of work = (batch element b, chunk c of consecutive cells); blocks take units grid-stride.
 // Per iteration TWO passes separated by grid-wide barriers:
