@@ -57,6 +57,67 @@ def fluid_step_case(pf, ny, nx, B, boundary, seed, steps, dt, solver="direct", b
     return out
 
 
+def _ref_geometry(pf, spec):
+    """Geometry spec tuple of oracle/restate_fluid.lies_inside -> the reference's geometry object."""
+    if spec[0] == "box":
+        return pf.AABox(np.asarray(spec[1], np.float32), np.asarray(spec[2], np.float32))
+    if spec[0] == "sphere":
+        return pf.Sphere(tuple(spec[1]), spec[2])
+    return pf.union([_ref_geometry(pf, s) for s in spec[1:]])
+
+
+def _ref_effect(pf, e, target):
+    """Effect dict of oracle/restate_fluid.apply_effect -> the reference's FieldEffect (through its own shorthands where one exists)."""
+    if e["mode"] == "fix":
+        if target == "velocity":
+            return pf.ConstantVelocity(_ref_geometry(pf, e["bounds"]), e["value"])
+        return pf.FieldEffect(pf.ConstantField(e["value"]), [target], pf.FIX, bounds=_ref_geometry(pf, e["bounds"]))
+    assert e["mode"] == "grow"
+    if target == "velocity":
+        return pf.Accelerator(_ref_geometry(pf, e["geometry"]), e["value"])
+    return pf.Inflow(_ref_geometry(pf, e["geometry"]), rate=e["value"])
+
+
+EFFECT_SCENES = {
+    # Inflow through a sphere, a fan with a per-component acceleration, a FIX velocity region, a sphere obstacle, buoyancy
+    "fluid_effects_open_32": dict(ny=32, nx=32, B=2, boundary="open", seed=23, steps=3, dt=0.5, buoyancy=0.1,
+                                  density_effects=[dict(mode="grow", geometry=("sphere", (8, 16), 4), value=0.3)],
+                                  velocity_effects=[dict(mode="grow", geometry=("box", (16, 8), (24, 20)), value=[0.2, -0.1]),
+                                                    dict(mode="fix", bounds=("box", (26, 20), (30, 28)), value=[0.3, 0.0], geometry=None)],
+                                  obstacle=("sphere", (16, 26), 3)),
+    # closed box: FIX density region, scalar fan, obstacle = union of a sphere and a box in the corner
+    "fluid_effects_closed_24x32": dict(ny=24, nx=32, B=2, boundary="closed", seed=29, steps=2, dt=0.5, buoyancy=0.0,
+                                       density_effects=[dict(mode="fix", bounds=("sphere", (6, 10), 3), value=0.7, geometry=None),
+                                                        dict(mode="grow", geometry=("box", (14, 4), (18, 9)), value=0.25)],
+                                       velocity_effects=[dict(mode="grow", geometry=("box", (2, 16), (8, 28)), value=0.2)],
+                                       obstacle=("union", ("sphere", (14, 20), 3.5), ("box", (20, 0), (24, 4)))),
+}
+
+
+def effects_case(pf, name):
+    s = EFFECT_SCENES[name]
+    ny, nx, B, dt = s["ny"], s["nx"], s["B"], s["dt"]
+    rng = np.random.RandomState(s["seed"])
+    rho = np.abs(_smooth(rng, (B, ny, nx), 1.0))
+    vy, vx = random_staggered(rng, B, ny, nx, 1.5)
+    dom = pf.Domain([ny, nx], boundaries=pf.OPEN if s["boundary"] == "open" else pf.CLOSED)
+    fluid = pf.Fluid(dom, density=rho[..., None].copy(), velocity=staggered_tensor(vy, vx), batch_size=B, buoyancy_factor=s["buoyancy"])
+    phys = pf.IncompressibleFlow(pressure_solver=pf.SparseSciPy())
+    de = [_ref_effect(pf, e, "density") for e in s["density_effects"]]
+    ve = [_ref_effect(pf, e, "velocity") for e in s["velocity_effects"]]
+    obs = [pf.Obstacle(_ref_geometry(pf, s["obstacle"]))]
+    out = dict(rho0=rho, vy0=vy, vx0=vx)
+    for k in range(s["steps"]):
+        fluid = phys.step(fluid, dt, obstacles=obs, density_effects=de, velocity_effects=ve)
+        out["rho%d" % (k + 1)] = np.asarray(fluid.density.data[..., 0], np.float32)
+        out["vy%d" % (k + 1)] = np.asarray(fluid.velocity.data[0].data[..., 0], np.float32)
+        out["vx%d" % (k + 1)] = np.asarray(fluid.velocity.data[1].data[..., 0], np.float32)
+        out["p%d" % (k + 1)] = np.asarray(fluid.solve_info["pressure"].data[..., 0], np.float32)
+        out["dvy%d" % (k + 1)] = np.asarray(fluid.solve_info["divergent_velocity"].data[0].data[..., 0], np.float32)
+        out["dvx%d" % (k + 1)] = np.asarray(fluid.solve_info["divergent_velocity"].data[1].data[..., 0], np.float32)
+    return out
+
+
 def controlled_case(pf, ny, nx, B, seed, dt):
     """Notebook variant: curl of a potential ('constant' extrapolation, like the U-Net output) advects the
     density; staggered self-advection of that velocity (force loss)."""
@@ -106,5 +167,7 @@ def main(pf, out_dir):
                         **fluid_step_case(pf, 32, 32, 2, "open", 17, 2, 0.5, obstacles=[(8, 14, 10, 20), (20, 26, 0, 5)]))
     np.savez_compressed(os.path.join(out_dir, "fluid_obstacle_closed_24x32.npz"),
                         **fluid_step_case(pf, 24, 32, 2, "closed", 19, 2, 0.5, obstacles=[(6, 12, 10, 20), (16, 24, 27, 32)]))
+    for name in EFFECT_SCENES:          # Inflow / Accelerator / FIX effects, sphere and union obstacles
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), **effects_case(pf, name))
     np.savez_compressed(os.path.join(out_dir, "fluid_controlled_64.npz"), **controlled_case(pf, 64, 64, 2, 9, 1.0))
     np.savez_compressed(os.path.join(out_dir, "poisson_40x32.npz"), **poisson_cases(pf))

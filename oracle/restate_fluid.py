@@ -436,3 +436,79 @@ def fourier_poisson(rhs):
     lap = -(2 * np.pi) ** 2 * (ky ** 2 + kx ** 2).to(torch.float32).to(torch.float64)       # fftfreq(..., dtype=np.float32)
     inv = torch.where(lap == 0, torch.zeros_like(lap), 1.0 / torch.where(lap == 0, torch.ones_like(lap), lap))
     return torch.fft.ifft2(torch.fft.fft2(rhs.to(torch.complex128)) * inv).real.to(rhs.dtype)
+
+
+# ---- geometry masks and effects (Inflow, Accelerator / Fan, FIX effects, sphere / union obstacles) ----
+def lies_inside(points, geometry):
+    """Geometry.lies_inside for a spec tuple: ("box", (y0, x0), (y1, x1)) bounds included in float32 (_box.py:58-61);
+    ("sphere", (cy, cx), r) |x - c|^2 <= r^2 in float64 (_sphere.py:24-28); ("union", spec, ...) (_union.py:24-25).
+    points [ny, nx, 2] float32 -> bool [ny, nx]."""
+    kind = geometry[0]
+    if kind == "box":
+        lo, hi = np.asarray(geometry[1], np.float32), np.asarray(geometry[2], np.float32)
+        return np.all((points >= lo) & (points <= hi), axis=-1)
+    if kind == "sphere":
+        return np.sum((points - np.asarray(geometry[1])) ** 2, axis=-1) <= geometry[2] ** 2
+    if kind == "union":
+        out = lies_inside(points, geometry[1])
+        for g in geometry[2:]:
+            out = out | lies_inside(points, g)
+        return out
+    raise ValueError(kind)
+
+
+def sample_points(res, lower, size):
+    """float32 [res0, res1, 2] sample points of a centred grid (grid.py:176-181)."""
+    ys, xs = _points(res, lower, size, torch.float32)
+    return np.stack(np.meshgrid(ys.numpy(), xs.numpy(), indexing="ij"), -1)
+
+
+def geometry_mask(geometry, geo, axis=None):
+    """GeometryMask.at(grid) (mask.py:45-55): 1 inside, 0 outside, at the cell centres (axis None) or at the faces of staggered
+    component `axis`."""
+    res, lower, size = (geo.res, geo.lower, geo.size) if axis is None else geo.component(axis)
+    return lies_inside(sample_points(res, lower, size), geometry).astype(np.float64)
+
+
+def apply_effect(arrays, effect, dt, geo, staggered):
+    """effect_applied (effect.py:48-59).  effect = dict(mode 'grow' | 'add' | 'fix', geometry spec or None (constant field),
+    value: number or one per component, bounds: spec for 'fix').  arrays: [rho] or [vy, vx]."""
+    out = []
+    for d, a in enumerate(arrays):
+        axis = d if staggered else None
+        value = effect["value"]
+        value = float(value[d]) if np.ndim(value) > 0 else float(value)
+        field = value if effect.get("geometry") is None else torch.tensor(geometry_mask(effect["geometry"], geo, axis), dtype=a.dtype) * value
+        if effect["mode"] == "grow":
+            out.append(a + field * dt)
+        elif effect["mode"] == "add":
+            out.append(a + field)
+        else:
+            inside = torch.tensor(geometry_mask(effect["bounds"], geo, axis) > 0)
+            out.append(torch.where(inside, torch.as_tensor(field, dtype=a.dtype).expand_as(a) if not torch.is_tensor(field)
+                                   else field.expand_as(a), a))
+    return out
+
+
+def incompressible_step_effects(rho, vy, vx, dt, geo, boundary, buoyancy=0.0, gravity=-9.81, density_effects=(), velocity_effects=(),
+                                obstacle=None):
+    """IncompressibleFlow.step (fluid.py:90-114): advect, normalise (closed), density effects, velocity effects, buoyancy, projection
+    with the obstacle geometry's active mask."""
+    rmode, vmode = modes_of(boundary)
+    rho2 = advect_centered(rho, vy, vx, dt, geo, rmode)
+    ay, ax = advect_staggered(vy, vx, dt, geo, vmode)
+    if boundary == CLOSED:
+        rho2 = normalize_to(rho2, rho)
+    for e in density_effects:
+        rho2, = apply_effect([rho2], e, dt, geo, False)
+    for e in velocity_effects:
+        ay, ax = apply_effect([ay, ax], e, dt, geo, True)
+    if buoyancy != 0.0:
+        ly, _lx = centered_to_faces(rho2 * (-gravity * buoyancy * dt), REPLICATE)
+        ay = ay + ly
+    if obstacle is not None:
+        active = 1.0 - geometry_mask(obstacle, geo)
+        vy2, vx2, p, div = divergence_free_obstacles(ay, ax, geo, boundary, active)
+    else:
+        vy2, vx2, p, div = divergence_free(ay, ax, geo, boundary)
+    return rho2, vy2, vx2, p

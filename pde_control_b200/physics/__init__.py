@@ -8,6 +8,8 @@ from .field import (Field, CenteredGrid, StaggeredGrid, FieldEffect, GROW, ADD, 
 from .burgers import DomainState, BurgersVelocity, Burgers
 from .fluid import (Fluid, IncompressibleFlow, INCOMPRESSIBLE_FLOW, SparseCG, poisson_solve, divergence_free, semi_lagrangian,
                     staggered_curl_2d, gravity_tensor, Obstacle, FourierSolver)
+from .geom import (Geometry, Sphere, Union, union, GeometryMask, mask, ConstantField, AnalyticField, Inflow, Accelerator, Fan,
+                   ConstantVelocity, HeatSource, ColdSource)
 
 
 class _Advect(object):

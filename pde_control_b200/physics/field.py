@@ -275,20 +275,29 @@ def unstack_staggered_tensor(tensor):
 class FieldEffect(State):
     """A field that acts on the states carrying one of `targets` as a tag (effect.py:16-45)."""
 
-    def __init__(self, field, targets, mode=GROW, tags=("effect",), name=None, age=0.0, batch_size=None):
+    def __init__(self, field, targets, mode=GROW, bounds=None, tags=("effect",), name=None, age=0.0, batch_size=None):
         targets = (targets,) if isinstance(targets, str) else tuple(targets)
         tags = tuple(tags) + tuple("%s_effect" % t for t in targets)
         State.__init__(self, name=name, tags=tags, age=age, batch_size=batch_size)
         assert mode in (GROW, ADD, FIX)
-        self.field, self.targets, self.mode = field, targets, mode
+        self.field, self.targets, self.mode, self.bounds = field, targets, mode, bounds
+
+    def __repr__(self):
+        return "%s(%s to %s)" % (self.mode, self.field, self.targets)
 
 
 def effect_applied(effect, field, dt):
-    """effect_applied (effect.py:48-59), GROW: field + effect*dt, ADD: field + effect.  FIX needs geometry masks
-    (out of scope)."""
+    """effect_applied (effect.py:48-59).  GROW: field + effect * dt, ADD: field + effect, FIX: effect inside `bounds`, field outside."""
     resampled = effect.field.at(field)
     if effect.mode == GROW:
         return field + resampled * dt
     if effect.mode == ADD:
         return field + resampled
-    raise NotImplementedError("FieldEffect mode '%s' is not on the B200 path" % effect.mode)
+    if effect.mode == FIX:
+        assert effect.bounds is not None
+        from .geom import GeometryMask
+        inside = GeometryMask([effect.bounds]).at(field)
+        if isinstance(field, StaggeredGrid):
+            return field.with_data([torch.where(m.data > 0, e.data, f.data) for m, e, f in zip(inside.data, resampled.data, field.data)])
+        return field.copied_with(data=torch.where(inside.data > 0, resampled.data, field.data))
+    raise ValueError("Invalid mode: %s" % effect.mode)

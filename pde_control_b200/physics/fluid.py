@@ -135,23 +135,20 @@ _MASK_CACHE = {}
 
 def obstacle_masks(obstacles, velocity, domain):
     """active = 1 - union of the obstacle geometries sampled at the cell centres (fluid.py:228-233) -> ops.ObstacleMasks (cached
-    per geometry set, resolution, box and boundary type: obstacles are static on this path)."""
-    boxes = []
+    per geometry set, resolution, box and boundary type: obstacles are static on this path).  Geometries: AABox, Sphere, unions."""
+    from .geom import geometry_mask_tensor, union
+    geos = []
     for o in obstacles:
         geo = o.geometry if hasattr(o, "geometry") else o
-        boxes += list(geo) if isinstance(geo, (list, tuple)) else [geo]
-    key = (tuple((tuple(map(float, b.lower)), tuple(map(float, b.upper))) for b in boxes), tuple(int(r) for r in velocity.resolution),
-           _box4(velocity.box), _closed(domain), str(velocity.data[0].data.device))
+        geos += list(geo) if isinstance(geo, (list, tuple)) else [geo]
+    geometry = union(geos)
+    device = velocity.data[0].data.device
+    key = (geometry.key(), tuple(int(r) for r in velocity.resolution), _box4(velocity.box), _closed(domain), str(device))
     if key not in _MASK_CACHE:
         ny, nx = (int(r) for r in velocity.resolution)
-        lo, size = velocity.box.lower, velocity.box.size
-        cy = (np.arange(ny) + 0.5) / ny * float(size[0]) + float(lo[0])
-        cx = (np.arange(nx) + 0.5) / nx * float(size[1]) + float(lo[1])
-        solid = np.zeros((ny, nx), bool)
-        for b in boxes:
-            solid |= ((cy >= b.lower[0]) & (cy <= b.upper[0]))[:, None] & ((cx >= b.lower[1]) & (cx <= b.upper[1]))[None, :]
-        active = torch.tensor((~solid).astype(np.float32), device=velocity.data[0].data.device)
-        _MASK_CACHE[key] = ops.ObstacleMasks(active, _closed(domain))
+        centers = CenteredGrid(torch.zeros(1, ny, nx, 1, device=device), box=velocity.box)         # velocity.center_points
+        active = 1.0 - geometry_mask_tensor(geometry, centers)[0, ..., 0]
+        _MASK_CACHE[key] = ops.ObstacleMasks(active.contiguous(), _closed(domain))
     return _MASK_CACHE[key]
 
 

@@ -115,6 +115,57 @@ def test_world_step_with_obstacles_matches_reference_golden(name):
     assert int(fluid.solve_info["iterations"].max()) > 5
 
 
+def _product_geometry(spec):
+    from pde_control_b200.physics import AABox, Sphere, union
+    if spec[0] == "box":
+        return AABox(spec[1], spec[2])
+    if spec[0] == "sphere":
+        return Sphere(spec[1], spec[2])
+    return union([_product_geometry(s) for s in spec[1:]])
+
+
+@pytest.mark.parametrize("name", ["fluid_effects_open_32", "fluid_effects_closed_24x32"])
+def test_world_step_with_geometry_effects_matches_reference_golden(name):
+    """Inflow, Accelerator (Fan), ConstantVelocity / FIX effects and sphere / union obstacles added to a World the way
+    a PhiFlow scene does it; step 1 vs the live reference, later steps vs the oracle under the TF edge rule."""
+    from pde_control_b200.physics import (World, Domain, Fluid, IncompressibleFlow, SparseCG, OPEN, CLOSED, Obstacle, Inflow, Accelerator,
+                                          ConstantVelocity, ConstantField, FieldEffect, FIX)
+    from oracle.make_golden_fluid import staggered_tensor, EFFECT_SCENES
+    from oracle import restate_fluid as F
+    g, s = np.load(os.path.join(GOLDEN, name + ".npz")), EFFECT_SCENES[name]
+    B, ny, nx, dt = s["B"], s["ny"], s["nx"], s["dt"]
+    dom = Domain([ny, nx], boundaries=OPEN if s["boundary"] == "open" else CLOSED)
+    world = World(batch_size=B)
+    fluid = world.add(Fluid(dom, density=g["rho0"][..., None], velocity=staggered_tensor(g["vy0"], g["vx0"]), batch_size=B,
+                            buoyancy_factor=s["buoyancy"]),
+                      physics=IncompressibleFlow(pressure_solver=SparseCG(accuracy=1e-6, max_iterations=3000)))
+    for e in s["density_effects"]:
+        if e["mode"] == "fix":
+            world.add(FieldEffect(ConstantField(e["value"]), ["density"], FIX, bounds=_product_geometry(e["bounds"])))
+        else:
+            world.add(Inflow(_product_geometry(e["geometry"]), rate=e["value"]))
+    for e in s["velocity_effects"]:
+        if e["mode"] == "fix":
+            world.add(ConstantVelocity(_product_geometry(e["bounds"]), e["value"]))
+        else:
+            world.add(Accelerator(_product_geometry(e["geometry"]), e["value"]))
+    world.add(Obstacle(_product_geometry(s["obstacle"])))
+    geo = F.Geometry(ny, nx)
+    o = [torch.tensor(g[k]) for k in ("rho0", "vy0", "vx0")]
+    for k in range(1, s["steps"] + 1):
+        world.step(dt=dt)
+        o = list(F.incompressible_step_effects(o[0], o[1], o[2], dt, geo, s["boundary"], buoyancy=s["buoyancy"],
+                                               density_effects=s["density_effects"], velocity_effects=s["velocity_effects"],
+                                               obstacle=s["obstacle"]))[:3]
+        got = (fluid.density.data[..., 0].cpu(), fluid.velocity.data[0].data[..., 0].cpu(), fluid.velocity.data[1].data[..., 0].cpu())
+        if k == 1:
+            assert rel_err(got[0], g["rho1"]) < 2e-5 and rel_err(got[1], g["vy1"]) < 4e-5 and rel_err(got[2], g["vx1"]) < 4e-5
+            dv = fluid.solve_info["divergent_velocity"]
+            assert rel_err(dv.data[0].data[..., 0].cpu(), g["dvy1"]) < 1e-5 and rel_err(dv.data[1].data[..., 0].cpu(), g["dvx1"]) < 1e-5
+        tol = 4e-5 if k == 1 else 1e-4
+        assert all(rel_err(a, b) < tol for a, b in zip(got, o)), [rel_err(a, b) for a, b in zip(got, o)]
+
+
 def test_masked_projection_gradient_vs_oracle():
     """Adjoint of the projection with obstacles (mask multiplies + the masked CG solving the incoming gradient) vs the oracle's
     differentiable dense solve (OPEN: non-singular matrix); 1e-3 on gradients."""

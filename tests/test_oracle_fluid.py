@@ -183,6 +183,23 @@ def test_buoyancy_effects_and_obstacles_match_reference_golden(name, numpy_edge_
         assert rel_err(vy, g["vy%d" % k]) < 2 * tol and rel_err(vx, g["vx%d" % k]) < 2 * tol
 
 
+@pytest.mark.parametrize("name", ["fluid_effects_open_32", "fluid_effects_closed_24x32"])
+def test_geometry_effects_match_reference_golden(name, numpy_edge_rule):
+    """SURVEY 8f N3 restatement of Inflow / Accelerator / FIX effects and of sphere / union obstacles (geometry masks at cell
+    centres and face centres) vs the live reference's NumPy path."""
+    from oracle.make_golden_fluid import EFFECT_SCENES
+    g, s = _load(name), EFFECT_SCENES[name]
+    geo = F.Geometry(s["ny"], s["nx"])
+    rho, vy, vx = [torch.tensor(g[k]) for k in ("rho0", "vy0", "vx0")]
+    for k in range(1, s["steps"] + 1):
+        rho, vy, vx, p = F.incompressible_step_effects(rho, vy, vx, s["dt"], geo, s["boundary"], buoyancy=s["buoyancy"],
+                                                       density_effects=s["density_effects"], velocity_effects=s["velocity_effects"],
+                                                       obstacle=s["obstacle"])
+        tol = 1e-5 if k == 1 else 1e-4
+        assert rel_err(rho, g["rho%d" % k]) < tol
+        assert rel_err(vy, g["vy%d" % k]) < 2 * tol and rel_err(vx, g["vx%d" % k]) < 2 * tol
+
+
 @pytest.mark.parametrize("bd", ["open", "closed"])
 def test_fourier_poisson_matches_reference(bd):
     """FourierSolver's guess (math.fourier_poisson) vs the live reference."""
