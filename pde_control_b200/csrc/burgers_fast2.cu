@@ -39,6 +39,12 @@ struct Unit2P {
 #ifndef F2_WARPS
 #define F2_WARPS 12                   // warps per CTA
 #endif
+#ifndef F2_PIECES
+#define F2_PIECES 1                   // most ranges per warp (power of two)
+#endif
+#ifndef F2_PIECE_MIN
+#define F2_PIECE_MIN 4                // shortest range, in pairs
+#endif
 
 __device__ __forceinline__ float2 f2(float x, float y) { return make_float2(x, y); }
 __device__ __forceinline__ float2 sub2(float2 a, float2 b) { return __ffma2_rn(b, f2(-1.0f, -1.0f), a); }   // rn(a - b), one rounding
@@ -211,7 +217,7 @@ __device__ __forceinline__ float sgn(float d) { return (d > 0.0f) ? 1.0f : ((d <
 // next one only closes the row.
 template <bool L1TERM>
 __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
-                                                                            float2* partials, int T, int B, int t0, int t1, long long per_warp,
+                                                                            float2* partials, int T, int B, int t0, int t1, long long per_warp, int pieces,
                                                                             unsigned* done_counter, float* __restrict__ losses, float inv_B) {
 #ifdef F2_SPLIT
     __shared__ float smem[F2_WARPS][3][F2_ROW];
@@ -237,11 +243,15 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
     const float2 gl2v = f2(p.gl2, p.gl2);
     const int Cw = t1 - t0;                                            // pairs per row in the window
     const long long total = (long long)B * Cw;
-    const long long P0 = ((long long)blockIdx.x * F2_WARPS + warp) * per_warp;
-    const long long P1 = min(total, P0 + per_warp);
+    // a warp's share = `pieces` ranges of per_warp pairs, piece k of warp w at ((k * warps) + w) * per_warp: rows that take the slow
+    // scatter path for all their pairs (shocks) are spread over several warps instead of landing on one
+    const long long n_warps = (long long)gridDim.x * F2_WARPS;
     float2 acc2 = f2(0.0f, 0.0f);
     float acc1 = 0.0f;
-    if (P0 < P1) {
+    for (int piece = 0; piece < pieces; ++piece) {
+        const long long P0 = ((long long)piece * n_warps + (long long)blockIdx.x * F2_WARPS + warp) * per_warp;
+        const long long P1 = min(total, P0 + per_warp);
+        if (P0 >= P1) break;
         long long remaining = P1 - P0;                                 // real pairs still to do
         int b = (int)(P0 / Cw);
         int lo = t0 + (int)(P0 - (long long)b * Cw);                   // first real pair of the current row
@@ -380,8 +390,12 @@ int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials,
     // one range per resident warp (148 SMs x F2_MINB CTAs x F2_WARPS warps), at least 4 pairs per range
     long long grid = 148LL * F2_MINB;
     if (grid * F2_WARPS * 4 > total) grid = total / (4 * F2_WARPS) > 0 ? total / (4 * F2_WARPS) : 1;
-    const long long per_warp = (total + grid * F2_WARPS - 1) / (grid * F2_WARPS);
-    if (gl1 != 0.0f) burgers_pair_loss_unit_kernel<true><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, done_counter, losses, invB);
-    else burgers_pair_loss_unit_kernel<false><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, done_counter, losses, invB);
+    long long per_warp = (total + grid * F2_WARPS - 1) / (grid * F2_WARPS);
+    // several shorter ranges per warp when there is enough work (each range start costs one carry-only forward step)
+    int pieces = 1;
+    while (pieces < F2_PIECES && per_warp / (pieces * 2) >= F2_PIECE_MIN) pieces *= 2;
+    per_warp = (total + grid * F2_WARPS * pieces - 1) / (grid * F2_WARPS * pieces);
+    if (gl1 != 0.0f) burgers_pair_loss_unit_kernel<true><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, done_counter, losses, invB);
+    else burgers_pair_loss_unit_kernel<false><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, done_counter, losses, invB);
     return cudaPeekAtLastError() == cudaSuccess ? PDEC_OK : PDEC_ERR_CUDA_LAUNCH;
 }
