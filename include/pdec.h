@@ -204,8 +204,10 @@ int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p, int* iter
 /* The same solve on a domain with OBSTACLES (PoissonDomain active / accessible masks, solver_api.py:51-121; matrix
  * sparse.py:157-221): `code` [ny*nx] bytes (device, shared by the batch) gives every cell its stencil: bits 0..3 = coupled to the
  * neighbour above (i-1) / below (i+1) / left (j-1) / right (j+1), i.e. active_self * active_neighbour; bits 4..7 = minus the
- * diagonal = number of accessible neighbours clamped to >= 1 (domain boundaries count as accessible when open).  Streaming
- * cooperative kernel; workspace as pdec_cg_poisson_2d.  The adjoint is the same call (the masked matrix is symmetric). */
+ * diagonal = number of accessible neighbours clamped to >= 1 (domain boundaries count as accessible when open).  Grids up to
+ * 128 x 128 with guess == NULL and the per-element stop rule run on chip (one CTA per batch element; rows without a coupled
+ * neighbour are solved directly: p = rhs / diagonal); everything else runs on the streaming cooperative kernel (stop_mode | 0x100
+ * forces it).  Workspace as pdec_cg_poisson_2d.  The adjoint is the same call (the masked matrix is symmetric). */
 int pdec_cg_poisson_2d_masked(const float* rhs, const float* guess, float* p, int* iterations, float* residual,
                               const unsigned char* code, int B, int ny, int nx, float accuracy, int max_iterations, int stop_mode,
                               void* workspace, size_t workspace_bytes, void* stream);

@@ -577,6 +577,146 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
 }
 
 // -------------------------------------------------------------------------------------------------------------
+// cg_block_masked_kernel: the on-chip block kernel for a domain with obstacles (any ny <= 8 * WARPS, nx <= 128, zero guess).
+// The masked matrix (sparse.py:157-221) couples cell c to neighbour k with active_c * active_k, so with
+//   a_c  = 1 if c has at least one coupled neighbour, else 0        (low nibble of the stencil code != 0)
+//   dg_c = -(accessible neighbours of c), at most -1               (high nibble)
+// rows with a_c = 0 (obstacle cells, fluid cells walled in on all sides, cells outside the grid) are 1x1 blocks: x_c = rhs_c / dg_c
+// is their exact solution and they take no part in the iteration (r_c = m_c = 0 throughout).  For the others
+//   (A m)_c = a_c * (m_up + m_left + m_right + m_down) + dg_c * m_c
+// because every neighbour that is not coupled has m = 0.  a and dg live in shared memory (one LDS.128 per four cells each).
+// The reference iterates on the decoupled rows too; they are zero in the fluid step (the masked divergence and the incoming pressure
+// gradient vanish inside obstacles), where the iterates are therefore the same.
+// -------------------------------------------------------------------------------------------------------------
+template <int WARPS>
+__global__ void __launch_bounds__(32 * WARPS, 1) cg_block_masked_kernel(const float* __restrict__ rhs, float* __restrict__ out, int* __restrict__ iters,
+                                                                        float* __restrict__ resid, const unsigned char* __restrict__ code,
+                                                                        int ny, int nx, float accuracy, int max_it) {
+    constexpr int ROWS = 8 * WARPS;
+    extern __shared__ __align__(16) float smem_dyn[];
+    __shared__ __align__(16) float redA[32], redB[32];
+    float4* sm_x = reinterpret_cast<float4*>(smem_dyn);          // [ROWS][32] float4 (row pitch 128 floats)
+    float4* sm_e = sm_x + ROWS * 32;                            // [2*WARPS + 2][32]: 0 = zeros, 1+2w / 2+2w = first / last row of warp w
+    float4* sm_a = sm_e + (2 * WARPS + 2) * 32;                 // [ROWS][32]: a
+    float4* sm_d = sm_a + ROWS * 32;                            // [ROWS][32]: dg
+    const int tx = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int i0 = 8 * w, j0 = 4 * tx;
+    const size_t base = (size_t)blockIdx.x * ny * nx;
+    float r[32], am[32], m[32];
+    const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    for (int q = threadIdx.x; q < (2 * WARPS + 2) * 32; q += 32 * WARPS) sm_e[q] = zero4;
+#pragma unroll
+    for (int ky = 0; ky < 8; ++ky) {
+        float av[4], dv[4], xv[4];
+#pragma unroll
+        for (int kx = 0; kx < 4; ++kx) {
+            const int c = ky * 4 + kx;
+            float rv = 0.0f;
+            unsigned cd = 0u;
+            if (i0 + ky < ny && j0 + kx < nx) {
+                rv = rhs[base + (size_t)(i0 + ky) * nx + j0 + kx];
+                cd = code[(size_t)(i0 + ky) * nx + j0 + kx];
+            }
+            const bool coupled = (cd & 15u) != 0u;
+            av[kx] = coupled ? 1.0f : 0.0f;
+            dv[kx] = coupled ? -(float)(cd >> 4) : 0.0f;
+            xv[kx] = (!coupled && cd != 0u) ? rv / -(float)(cd >> 4) : 0.0f;       // decoupled row: solved here
+            r[c] = coupled ? rv : 0.0f;
+        }
+        sm_a[(i0 + ky) * 32 + tx] = make_float4(av[0], av[1], av[2], av[3]);
+        sm_d[(i0 + ky) * 32 + tx] = make_float4(dv[0], dv[1], dv[2], dv[3]);
+        sm_x[(i0 + ky) * 32 + tx] = make_float4(xv[0], xv[1], xv[2], xv[3]);
+    }
+    __syncthreads();                         // zero-fill of the edge rows completes before anyone publishes
+    auto publish = [&]() {
+        sm_e[(1 + 2 * w) * 32 + tx] = make_float4(m[0], m[1], m[2], m[3]);
+        sm_e[(2 + 2 * w) * 32 + tx] = make_float4(m[28], m[29], m[30], m[31]);
+    };
+    auto matvec = [&]() {
+        const float4 u4 = sm_e[(2 * w) * 32 + tx], d4 = sm_e[(2 * w + 3) * 32 + tx];
+        const float upv[4] = {u4.x, u4.y, u4.z, u4.w}, dnv[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+        for (int ky = 0; ky < 8; ++ky) {
+            float left = __shfl_up_sync(0xffffffffu, m[ky * 4 + 3], 1);
+            float right = __shfl_down_sync(0xffffffffu, m[ky * 4 + 0], 1);
+            if (tx == 0) left = 0.0f;
+            if (tx == 31) right = 0.0f;
+            const float4 a4 = sm_a[(i0 + ky) * 32 + tx], g4 = sm_d[(i0 + ky) * 32 + tx];
+            const float av[4] = {a4.x, a4.y, a4.z, a4.w}, gv[4] = {g4.x, g4.y, g4.z, g4.w};
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx) {
+                const int c = ky * 4 + kx;
+                const float u = ky > 0 ? m[c >= 4 ? c - 4 : 0] : upv[kx];
+                const float d = ky < 7 ? m[c + 4 <= 31 ? c + 4 : 31] : dnv[kx];
+                const float l = kx > 0 ? m[c >= 1 ? c - 1 : 0] : left;
+                const float rr = kx < 3 ? m[c + 1 <= 31 ? c + 1 : 31] : right;
+                am[c] = av[kx] * ((u + l) + (rr + d)) + gv[kx] * m[c];
+            }
+        }
+    };
+    float rmax = 0.0f, dummy = 0.0f;
+    int it = 0;
+#pragma unroll
+    for (int c = 0; c < 32; ++c) { m[c] = r[c]; rmax = fmaxf(rmax, fabsf(r[c])); }
+    publish();
+    block_reduce_pair<WARPS>(dummy, rmax, redB, true);      // its barrier also orders publish before the matvec
+    matvec();
+    while (it < max_it && (accuracy <= 0.0f || rmax >= accuracy)) {
+        float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) { s1 += m[c] * am[c]; s2 += m[c] * r[c]; }
+        block_reduce_pair<WARPS>(s1, s2, redA, false);
+        const float tmp = s1, a = div_no_nan_fast(s2, tmp);
+        float s3 = 0.0f, mx = 0.0f;
+#pragma unroll
+        for (int ky = 0; ky < 8; ++ky) {
+            float4 x4 = sm_x[(i0 + ky) * 32 + tx];
+            x4.x += a * m[ky * 4 + 0]; x4.y += a * m[ky * 4 + 1]; x4.z += a * m[ky * 4 + 2]; x4.w += a * m[ky * 4 + 3];
+            sm_x[(i0 + ky) * 32 + tx] = x4;
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx) {
+                const int c = ky * 4 + kx;
+                r[c] -= a * am[c];
+                s3 += r[c] * am[c];
+                mx = fmaxf(mx, fabsf(r[c]));
+            }
+        }
+        block_reduce_pair<WARPS>(s3, mx, redB, true);
+        const float beta = div_no_nan_fast(s3, tmp);
+#pragma unroll
+        for (int c = 0; c < 32; ++c) m[c] = r[c] - beta * m[c];
+        publish();                           // every edge-row read of the old m happened before reduction A's barrier
+        __syncthreads();
+        matvec();
+        rmax = mx;
+        ++it;
+    }
+#pragma unroll
+    for (int ky = 0; ky < 8; ++ky) {
+        const float4 x4 = sm_x[(i0 + ky) * 32 + tx];
+        const float xv[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+        for (int kx = 0; kx < 4; ++kx)
+            if (i0 + ky < ny && j0 + kx < nx) out[base + (size_t)(i0 + ky) * nx + j0 + kx] = xv[kx];
+    }
+    if (threadIdx.x == 0) {
+        if (iters) iters[blockIdx.x] = it;
+        if (resid) resid[blockIdx.x] = rmax;
+    }
+}
+
+template <int WARPS>
+static int launch_block_masked(const float* rhs, float* p, int* iterations, float* residual, const unsigned char* code, int B, int ny, int nx,
+                               float accuracy, int max_iterations, cudaStream_t st) {
+    const size_t smem = (size_t)(3 * 8 * WARPS * 32 + (2 * WARPS + 2) * 32) * sizeof(float4);
+    auto kernel = cg_block_masked_kernel<WARPS>;
+    if (smem > 48 * 1024 && cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return PDEC_ERR_CUDA_LAUNCH;
+    kernel<<<B, 32 * WARPS, smem, st>>>(rhs, p, iterations, residual, code, ny, nx, accuracy, max_iterations);
+    return PDEC_OK;
+}
+
+// -------------------------------------------------------------------------------------------------------------
 // Measured and dropped (round 1, profiles/r1n_cg_packed.md): a packed-fp32 twin of cg_block_kernel (vectors as float2 pairs of rows
 // q and q + 4, add/fma.rn.f32x2, lane halo through shared memory or shuffles) has 17-20 % fewer instructions per iteration (388-399
 // against 482) and is SLOWER: 1.99-2.62 us per iteration at 128x128 against 1.78.  The kernel is bound by the barrier / reduction
@@ -922,12 +1062,26 @@ static int launch_global(const float* rhs, const float* guess, float* p, int* it
 
 // Masked operator (obstacles): the stencil of every cell comes from `code` [ny * nx] (shared by the batch): bits 0..3 = coupled
 // neighbour above / below / left / right (active_self * active_neighbour, sparse.py:186-205), bits 4..7 = minus the diagonal
-// (number of accessible neighbours, at least 1, sparse.py:207-213).  Always the streaming kernel.
+// (number of accessible neighbours, at least 1, sparse.py:207-213).  Grids up to 128 x 128 with a zero guess and the per-element
+// stop rule run on chip (cg_block_masked_kernel), everything else on the streaming kernel (stop_mode bit 8 forces it: benchmarks).
 extern "C" int pdec_cg_poisson_2d_masked(const float* rhs, const float* guess, float* p, int* iterations, float* residual,
                                          const unsigned char* code, int B, int ny, int nx, float accuracy, int max_iterations, int stop_mode,
                                          void* workspace, size_t workspace_bytes, void* stream) {
     if (!rhs || !p || !code || !workspace || B < 1 || ny < 1 || nx < 1 || max_iterations < 0) return PDEC_ERR_INVALID_ARGUMENT;
     if ((long long)ny * nx > 0x7fffffffLL) return PDEC_ERR_UNSUPPORTED_SIZE;
+    const bool force_streaming = (stop_mode >> 8) & 1;
+    stop_mode &= 0xff;
+    const bool whole_batch = stop_mode == PDEC_CG_STOP_WHOLE_BATCH && accuracy > 0.0f && B > 1;
+    if (!force_streaming && !whole_batch && guess == nullptr && ny <= 128 && nx <= 128) {
+        cudaStream_t st = (cudaStream_t)stream;
+        int rc;
+        if (ny > 64) rc = launch_block_masked<16>(rhs, p, iterations, residual, code, B, ny, nx, accuracy, max_iterations, st);
+        else if (ny > 32) rc = launch_block_masked<8>(rhs, p, iterations, residual, code, B, ny, nx, accuracy, max_iterations, st);
+        else rc = launch_block_masked<4>(rhs, p, iterations, residual, code, B, ny, nx, accuracy, max_iterations, st);
+        if (rc != PDEC_OK) return rc;
+        PDEC_CHECK_LAUNCH();
+        return PDEC_OK;
+    }
     if (workspace_bytes < pdec_cg_poisson_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
     return launch_global(rhs, guess, p, iterations, residual, code, B, ny, nx, 0, accuracy, max_iterations,
                          stop_mode == PDEC_CG_STOP_WHOLE_BATCH && B > 1, workspace, (cudaStream_t)stream);

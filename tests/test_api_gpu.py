@@ -273,3 +273,41 @@ def test_control_training_fluid_cfe_and_op():
     assert all(g is not None and bool(torch.isfinite(g).all()) for g in grads) and any(float(g.abs().max()) > 0 for g in grads)
     states = app.infer_all_frames(range(2))
     assert hasattr(states[1].density, "velocity") and states[1].density.velocity.data[0].data.shape == (2, res + 1, res, 1)
+
+
+@pytest.mark.parametrize("ny,nx,closed", [(128, 128, False), (128, 128, True), (64, 100, False), (24, 32, True), (97, 128, False)])
+def test_masked_cg_on_chip_matches_streaming_kernel_and_dense_solve(ny, nx, closed):
+    """pdec_cg_poisson_2d_masked: the on-chip kernel (grids up to 128 x 128) against the streaming kernel (stop_mode bit 8) on the same
+    right-hand side -- zero inside the obstacles, as in the fluid step -- and, with a right-hand side that is NOT zero there (decoupled
+    rows solved directly), against the dense solve of the oracle's masked matrix (sparse.py:157-221)."""
+    from pde_control_b200 import ops
+    from oracle import restate_fluid as F
+    rng = np.random.RandomState(ny * 7 + nx)
+    B = 3
+    boxes = [(ny // 4, ny // 2, nx // 3, 2 * nx // 3), (3 * ny // 4, ny, 0, nx // 8), (ny // 8, ny // 8 + 1, nx - 6, nx - 5)]
+    active = F.obstacle_active(ny, nx, boxes)
+    active[0, 0], active[0, 1], active[1, 0] = 1.0, 0.0, 0.0                       # a fluid cell walled in by two obstacle cells
+    masks = ops.ObstacleMasks(torch.tensor(active, dtype=torch.float32, device="cuda"), closed)
+    rhs = rng.randn(B, ny, nx).astype(np.float32)
+    rhs_fluid = rhs * active.astype(np.float32)
+    if closed:          # singular on a closed domain: make the right-hand side consistent per connected fluid region (one region here)
+        rhs_fluid[:, 0, 0] = 0.0
+        rhs_fluid -= (rhs_fluid.sum((1, 2), keepdims=True) / (active.sum() - 1)) * active.astype(np.float32)
+        rhs_fluid[:, 0, 0] = 0.0
+    res = {}
+    for name, flag in (("chip", 0), ("stream", 1 << 8)):
+        r = torch.tensor(rhs_fluid, device="cuda")
+        out, it, rs = torch.empty_like(r), torch.zeros(B, dtype=torch.int32, device="cuda"), torch.zeros(B, device="cuda")
+        ops.cg_poisson_masked_raw(r, out, masks.code, 1e-6, 4000, None, it, rs, flag)
+        res[name] = (out.cpu(), it.cpu(), rs.cpu())
+    scale = float(res["stream"][0].abs().max())
+    assert float((res["chip"][0] - res["stream"][0]).abs().max()) < 2e-4 * scale
+    assert int((res["chip"][1] - res["stream"][1]).abs().max()) <= max(4, int(res["stream"][1].max()) // 20)
+    assert float(res["chip"][2].max()) < 1e-6 or int(res["chip"][1].max()) == 4000
+    if not closed:
+        A, _fy, _fx = F.masked_operator(active, "open")
+        r = torch.tensor(rhs, device="cuda")
+        out = torch.empty_like(r)
+        ops.cg_poisson_masked_raw(r, out, masks.code, 1e-6, 4000)
+        want = np.linalg.solve(A, rhs.reshape(B, -1).astype(np.float64).T).T.reshape(B, ny, nx)
+        assert rel_err(out.cpu(), want) < 2e-4
