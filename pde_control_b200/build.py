@@ -23,6 +23,7 @@ SOURCES = {
     "fluid.cu": ["-fmad=false"],
     "cg.cu": [],
     "cg_tiled.cu": [],
+    "cg_pair.cu": [],
     "host_pipeline.cu": [],
 }
 

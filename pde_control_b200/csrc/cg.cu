@@ -576,6 +576,10 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
     }
 }
 
+// cg_pair.cu: one batch element on a cluster of two CTAs (128 x 128, zero guess)
+int cg_pair_launch(const float* rhs, float* p, int* iterations, float* residual, int B, int closed, float accuracy, int max_iterations,
+                   bool p2p, cudaStream_t st);
+
 // -------------------------------------------------------------------------------------------------------------
 // cg_block_masked_kernel: the on-chip block kernel for a domain with obstacles (any ny <= 8 * WARPS, nx <= 128, zero guess).
 // The masked matrix (sparse.py:157-221) couples cell c to neighbour k with active_c * active_k, so with
@@ -991,7 +995,15 @@ extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p
     closed = closed ? 1 : 0;
     const long long N = (long long)ny * nx;
     int rc = PDEC_OK;
-    if (on_chip && ny <= 128 && nx <= 128 && (variant == 0 || variant == 4 || variant == 5)) {
+    if (on_chip && ny == 128 && nx == 128 && guess == nullptr && (variant == 6 || variant == 7)) {
+        // two SMs per element (cg_pair.cu; 6 = hardware cluster barriers, 7 = mbarrier hand-shake).  Measured SLOWER than one CTA per
+        // element (1.90 / 2.47 us per iteration against 1.78, profiles/r1p_cg_pair.md): selector only, never the default
+        rc = cg_pair_launch(rhs, p, iterations, residual, B, closed, accuracy, max_iterations, variant == 7, st);
+        if (rc != PDEC_OK) return rc;
+        PDEC_CHECK_LAUNCH();
+        return PDEC_OK;
+    }
+    if (on_chip && ny <= 128 && nx <= 128 && (variant == 0 || variant == 4 || variant == 5 || variant >= 6)) {
         // the one-reduction loop (variant 5) saves a barrier but costs a fifth dot product: measured slower (profiles/r1e_*)
         const bool fused = variant == 5;
         if (ny > 64) rc = launch_block<16>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st, fused);
