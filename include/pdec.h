@@ -105,6 +105,14 @@ int pdec_burgers_pair_loss_window_supported(int n, int mode, float box_lower, fl
 int pdec_burgers_pair_loss_window(const float* s, float* grad_s, float* losses, int T, int B, int n, int t0, int t1, int mode, double dt,
                                   double viscosity, float box_lower, float box_size, int substeps, int resubstep, float gl2, float gl1,
                                   void* workspace, size_t workspace_bytes, void* stream);
+/* The same with a frame stride for the gradient: frame f of row b is written at grad_s + f * grad_frame_stride + b * n (floats;
+ * a multiple of 4, at least B * n; 0 = dense).  grad_s may then be the rows [b0, b0 + B) of a larger batch's array, and it may be
+ * page-locked HOST memory that the device can address (cudaHostAlloc / torch pin_memory under unified addressing): the kernel's
+ * stores then travel over PCIe themselves, 512 contiguous bytes per warp, and no device-to-host copy follows. */
+int pdec_burgers_pair_loss_window_strided(const float* s, float* grad_s, float* losses, int T, int B, int n, int t0, int t1, int mode,
+                                          double dt, double viscosity, float box_lower, float box_size, int substeps, int resubstep,
+                                          float gl2, float gl1, long long grad_frame_stride, void* workspace, size_t workspace_bytes,
+                                          void* stream);
 
 /* The same force loss fed from HOST arrays: what the reference does every optimisation step through
  * session.run(fetches, feed_dict) (src/control/control_training.py:113-142, PF/tf/session.py:30-70 copies every fed array to
@@ -118,7 +126,11 @@ int pdec_burgers_pair_loss_window(const float* s, float* grad_s, float* losses, 
  * max_chunks bounds B <= chunk_rows * max_chunks.
  * frames_per_slice > 0 additionally allocates whole-batch staging ((T+1) * chunk_rows * max_chunks * n floats, twice) and, when
  * pdec_burgers_pair_loss_window_supported(), cuts the work along TIME instead (slices of that many frame pairs of all rows):
- * every copy is then one contiguous block.  Same results contract. */
+ * every copy is then one contiguous block.  Same results contract.
+ * Direct gradient (the default where it applies: fused unit-box kernel, grad_host addressable by the device, frames_per_slice == 0,
+ * PDEC_PIPE_STAGED_D2H unset): the kernel of every row chunk stores its gradient straight into grad_host
+ * (pdec_burgers_pair_loss_window_strided) instead of into device staging followed by a copy: no D2H leg, nothing to drain
+ * (profiles/r1q_host_pipeline.md). */
 typedef struct pdec_host_pipeline pdec_host_pipeline;
 int pdec_host_pipeline_create(pdec_host_pipeline** pipeline, int chunk_rows, int n, int T, int max_chunks, int frames_per_slice);
 int pdec_host_pipeline_destroy(pdec_host_pipeline* pipeline);

@@ -43,6 +43,9 @@ _SIGNATURES = {
     "pdec_burgers_pair_loss_window": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double,
                                                   _c.c_double, _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_float, _c.c_float, _P,
                                                   _c.c_size_t, _P]),
+    "pdec_burgers_pair_loss_window_strided": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double,
+                                                          _c.c_double, _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_float, _c.c_float,
+                                                          _c.c_longlong, _P, _c.c_size_t, _P]),
     "pdec_host_pipeline_create": (_c.c_int, [_c.POINTER(_P), _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int]),
     "pdec_host_pipeline_destroy": (_c.c_int, [_P]),
     "pdec_burgers_pair_loss_host": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _c.c_double,

@@ -218,7 +218,7 @@ __device__ __forceinline__ float sgn(float d) { return (d > 0.0f) ? 1.0f : ((d <
 template <bool L1TERM>
 __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
                                                                             float2* partials, int T, int B, int t0, int t1, long long per_warp, int pieces,
-                                                                            unsigned* done_counter, float* __restrict__ losses, float inv_B) {
+                                                                            long long gf4, unsigned* done_counter, float* __restrict__ losses, float inv_B) {
 #ifdef F2_SPLIT
     __shared__ float smem[F2_WARPS][3][F2_ROW];
 #else
@@ -239,6 +239,8 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
     const float2 X01 = f2((float)(4 * lane) + 0.5f, (float)(4 * lane) + 1.5f), X23 = f2((float)(4 * lane) + 2.5f, (float)(4 * lane) + 3.5f);
     const size_t f4 = (size_t)B * 32;                                 // float4 stride between frames
     const float4* s4 = reinterpret_cast<const float4*>(s) + lane;
+    // frame (b, f) of the gradient lives at g4 + f * gf4 + b * 32: its frame stride may differ from s's (a row chunk written straight
+    // into the caller's full-batch array, which may be page-locked host memory)
     float4* g4 = grad_s ? reinterpret_cast<float4*>(grad_s) + lane : nullptr;
     const float2 gl2v = f2(p.gl2, p.gl2);
     const int Cw = t1 - t0;                                            // pairs per row in the window
@@ -311,7 +313,7 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
 #endif
                         gin01 = __fadd2_rn(gin01, carry01);
                         gin23 = __fadd2_rn(gin23, carry23);
-                        __stcs(g4 + off, make_float4(gin01.x, gin01.y, gin23.x, gin23.y));        // written once, never re-read here
+                        __stcs(g4 + ((size_t)f * gf4 + (size_t)b * 32), make_float4(gin01.x, gin01.y, gin23.x, gin23.y));   // written once, never re-read here
                     } else {
                         __syncwarp();
                     }
@@ -323,7 +325,7 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
             } else {
                 // close row b: frame T receives the residual gradient of the last pair (a window that ends earlier leaves its
                 // last frame to the next window); the next row starts with a zero carry and its first real pair at t0
-                if (g4 != nullptr && f == T) __stcs(g4 + off, make_float4(carry01.x, carry01.y, carry23.x, carry23.y));
+                if (g4 != nullptr && f == T) __stcs(g4 + ((size_t)f * gf4 + (size_t)b * 32), make_float4(carry01.x, carry01.y, carry23.x, carry23.y));
                 carry01 = f2(0.0f, 0.0f); carry23 = f2(0.0f, 0.0f);
                 lo = t0;
             }
@@ -331,7 +333,7 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
             f = fcur; b = bcur; off = offcur;
             if (remaining == 0) break;
         }
-        if (f == T && g4 != nullptr) __stcs(g4 + off, make_float4(carry01.x, carry01.y, carry23.x, carry23.y));   // range ends with its row
+        if (f == T && g4 != nullptr) __stcs(g4 + ((size_t)f * gf4 + (size_t)b * 32), make_float4(carry01.x, carry01.y, carry23.x, carry23.y));   // range ends with its row
     }
     {
         const float a2 = warp_sum(acc2.x + acc2.y);
@@ -376,9 +378,12 @@ using namespace pdec;
 // returns PDEC_OK if it handled the call, 1 if the case is not this kernel's (caller falls back to burgers_fast.cu).
 // partials must hold max(32, B * T) float2 (pdec_burgers_pair_loss_workspace_bytes).  [t0, t1) = window of pairs (0, T = all):
 // losses <- the window's share of (L2, L1); grad_s frames t0..t1-1 (and T when t1 == T) <- their complete gradient
+// grad_frame_stride: floats between consecutive frames of grad_s (0: dense, B * 128)
 int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int t0, int t1, double dt, double viscosity, float gl2,
-                                float gl1, unsigned* done_counter, float* losses, cudaStream_t st) {
+                                float gl1, long long grad_frame_stride, unsigned* done_counter, float* losses, cudaStream_t st) {
     if (t0 < 0 || t1 > T || t0 >= t1) return PDEC_ERR_INVALID_ARGUMENT;
+    if (grad_frame_stride != 0 && (grad_frame_stride < (long long)B * 128 || (grad_frame_stride & 3))) return PDEC_ERR_INVALID_ARGUMENT;
+    const long long gf4 = grad_frame_stride ? grad_frame_stride / 4 : (long long)B * 32;
     Unit2P p;
     const float dtf = (float)dt;
     p.dt128 = dtf * 128.0f;                                   // exact (power-of-two scale)
@@ -395,7 +400,7 @@ int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials,
     int pieces = 1;
     while (pieces < F2_PIECES && per_warp / (pieces * 2) >= F2_PIECE_MIN) pieces *= 2;
     per_warp = (total + grid * F2_WARPS * pieces - 1) / (grid * F2_WARPS * pieces);
-    if (gl1 != 0.0f) burgers_pair_loss_unit_kernel<true><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, done_counter, losses, invB);
-    else burgers_pair_loss_unit_kernel<false><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, done_counter, losses, invB);
+    if (gl1 != 0.0f) burgers_pair_loss_unit_kernel<true><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB);
+    else burgers_pair_loss_unit_kernel<false><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB);
     return cudaPeekAtLastError() == cudaSuccess ? PDEC_OK : PDEC_ERR_CUDA_LAUNCH;
 }

@@ -162,6 +162,7 @@ extern "C" int pdec_burgers_pair_loss_host(pdec_host_pipeline* h, const float* s
     cudaStream_t user = (cudaStream_t)stream;
     const size_t host_pitch = (size_t)B * n * sizeof(float);
     int rc = PDEC_OK;
+    float* grad_direct = nullptr;
     HP_TRY(cudaEventRecord(h->begin, user));
     HP_TRY(cudaStreamWaitEvent(h->in, h->begin, 0));
     HP_TRY(cudaStreamWaitEvent(h->compute, h->begin, 0));
@@ -196,6 +197,14 @@ extern "C" int pdec_burgers_pair_loss_host(pdec_host_pipeline* h, const float* s
         HP_TRY(cudaStreamWaitEvent(user, h->end, 0));
         return PDEC_OK;
     }
+    // direct gradient: can the device address grad_host?  Then the fused kernel stores there itself (no staging, no D2H leg)
+    if (grad_host && getenv("PDEC_PIPE_STAGED_D2H") == nullptr && pdec_burgers_pair_loss_window_supported(n, mode, box_lower, box_size, substeps)) {
+        cudaPointerAttributes attr;
+        if (cudaPointerGetAttributes(&attr, grad_host) == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer != nullptr)
+            grad_direct = static_cast<float*>(attr.devicePointer);
+        else
+            cudaGetLastError();
+    }
     for (int c = 0; c < nchunks; ++c) {
         Slot& sl = h->slot[c % SLOTS];
         const int b0 = c * rows, bc = (c + 1 < nchunks) ? rows : B - b0;
@@ -206,8 +215,16 @@ extern "C" int pdec_burgers_pair_loss_host(pdec_host_pipeline* h, const float* s
         HP_TRY(cudaEventRecord(sl.h2d, h->in));
         // leg 2: fused force loss + gradient of the chunk (the slot's previous gradient must have left)
         HP_TRY(cudaStreamWaitEvent(h->compute, sl.h2d, 0));
-        if (c >= SLOTS && grad_host) HP_TRY(cudaStreamWaitEvent(h->compute, sl.d2h, 0));
         const float scale = pdec::chunk_scale(c, nchunks, rows, B);      // the kernel normalises by its own row count; rescale to 1/B
+        if (grad_direct) {
+            rc = pdec_burgers_pair_loss_window_strided(sl.s, grad_direct + (size_t)b0 * n, h->chunk_losses + 2 * c, T, bc, n, 0, T, mode, dt,
+                                                       viscosity, box_lower, box_size, substeps, resubstep, gl2 * scale, gl1 * scale,
+                                                       (long long)B * n, h->ws, h->ws_bytes, h->compute);
+            if (rc != PDEC_OK) return rc;
+            HP_TRY(cudaEventRecord(sl.kernel, h->compute));
+            continue;
+        }
+        if (c >= SLOTS && grad_host) HP_TRY(cudaStreamWaitEvent(h->compute, sl.d2h, 0));
         rc = pdec_burgers_pair_loss(sl.s, grad_host ? sl.g : nullptr, h->chunk_losses + 2 * c, T, bc, n, mode, dt, viscosity, box_lower,
                                     box_size, substeps, resubstep, gl2 * scale, gl1 * scale, h->ws, h->ws_bytes, h->compute);
         if (rc != PDEC_OK) return rc;

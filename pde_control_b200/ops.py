@@ -137,7 +137,9 @@ class HostPipeline(object):
     neighbouring chunks overlap.  frames_per_slice > 0: when the fused unit-box kernel applies the work is cut along time instead
     (slices of that many frame pairs of all rows; contiguous copies both ways), at the price of whole-batch device staging for
     max_batch rows.  Measured on B200 (scripts/diag/pcie_probe.py, pcie_timeline.py): both cuts reach the same 1.84-1.86 ms for
-    2 x 69 MB, within 8 % of what chunked full-duplex PCIe delivers (about 44 GB/s per direction), so rows are the default."""
+    2 x 69 MB, within 8 % of what chunked full-duplex PCIe delivers (about 44 GB/s per direction), so rows are the default.
+    Where the fused unit-box kernel applies and grad_host is addressable by the device (torch pin_memory), the kernel stores the
+    gradient into grad_host itself and the D2H leg disappears (1.71-1.77 ms, profiles/r1q_host_pipeline.md)."""
 
     def __init__(self, n, T, chunk_rows=512, max_batch=4096, frames_per_slice=0, device=None):
         import ctypes

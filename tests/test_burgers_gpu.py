@@ -172,15 +172,20 @@ def test_full_size_config2_properties():
     assert abs(l2.item() - tot) < 1e-4 * tot
 
 
-@pytest.mark.parametrize("frames_per_slice", [0, 1, 3])
+@pytest.mark.parametrize("frames_per_slice", [0, 1, 3, -1])
 @pytest.mark.parametrize("B,chunk_rows,n,T", [(512, 128, 128, 8), (300, 128, 128, 5), (40, 16, 50, 3), (64, 256, 128, 4)])
-def test_host_pipeline_equals_resident_call(B, chunk_rows, n, T, frames_per_slice):
+def test_host_pipeline_equals_resident_call(B, chunk_rows, n, T, frames_per_slice, monkeypatch):
     """pdec_burgers_pair_loss_host (chunked H2D / kernel / D2H over three streams) == the resident single launch:
     gradient bit for bit when the chunk scale is a power of two, else to rounding of the 1/B scale; losses to 1e-6;
     ragged last chunk, a batch smaller than one chunk, the general-n kernel and two calls in a row (slot re-use).
     frames_per_slice > 0: the frame-sliced mode (windows of pairs through pdec_burgers_pair_loss_window; n = 128 only, other
-    sizes fall back to row chunks): gradient bit for bit."""
+    sizes fall back to row chunks): gradient bit for bit.
+    frames_per_slice == 0 takes the direct-gradient path where it applies (the kernel stores into the page-locked host array itself);
+    -1 = row chunks with the staged device-to-host copies (PDEC_PIPE_STAGED_D2H)."""
     ops = _ops()
+    if frames_per_slice < 0:
+        monkeypatch.setenv("PDEC_PIPE_STAGED_D2H", "1")
+        frames_per_slice = 0
     rng = np.random.RandomState(B + T)
     s = np.stack([R.gaussian_clash(B, n, rng) for _ in range(T + 1)]).astype(np.float32)
     s += 0.02 * rng.randn(*s.shape).astype(np.float32)
