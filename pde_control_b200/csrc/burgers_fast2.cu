@@ -215,7 +215,7 @@ __device__ __forceinline__ float sgn(float d) { return (d > 0.0f) ? 1.0f : ((d <
 // a pair; a pair below the range's / window's first one is walked "carry-only" (forward step only: its residual gradient w.r.t.
 // its target frame is the carry the first real pair needs); the step from the last frame of a row to the first frame of the
 // next one only closes the row.
-template <bool L1TERM>
+template <bool L1TERM, bool GSTRIDE>
 __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
                                                                             float2* partials, int T, int B, int t0, int t1, long long per_warp, int pieces,
                                                                             long long gf4, unsigned* done_counter, float* __restrict__ losses, float inv_B) {
@@ -250,7 +250,8 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
     const long long n_warps = (long long)gridDim.x * F2_WARPS;
     float2 acc2 = f2(0.0f, 0.0f);
     float acc1 = 0.0f;
-    for (int piece = 0; piece < pieces; ++piece) {
+    const int npieces = F2_PIECES == 1 ? 1 : pieces;                   // the default build has no piece loop
+    for (int piece = 0; piece < npieces; ++piece) {
         const long long P0 = ((long long)piece * n_warps + (long long)blockIdx.x * F2_WARPS + warp) * per_warp;
         const long long P1 = min(total, P0 + per_warp);
         if (P0 >= P1) break;
@@ -313,7 +314,7 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
 #endif
                         gin01 = __fadd2_rn(gin01, carry01);
                         gin23 = __fadd2_rn(gin23, carry23);
-                        __stcs(g4 + ((size_t)f * gf4 + (size_t)b * 32), make_float4(gin01.x, gin01.y, gin23.x, gin23.y));   // written once, never re-read here
+                        __stcs(g4 + (GSTRIDE ? (size_t)f * gf4 + (size_t)b * 32 : off), make_float4(gin01.x, gin01.y, gin23.x, gin23.y));   // written once, never re-read here
                     } else {
                         __syncwarp();
                     }
@@ -325,7 +326,7 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
             } else {
                 // close row b: frame T receives the residual gradient of the last pair (a window that ends earlier leaves its
                 // last frame to the next window); the next row starts with a zero carry and its first real pair at t0
-                if (g4 != nullptr && f == T) __stcs(g4 + ((size_t)f * gf4 + (size_t)b * 32), make_float4(carry01.x, carry01.y, carry23.x, carry23.y));
+                if (g4 != nullptr && f == T) __stcs(g4 + (GSTRIDE ? (size_t)f * gf4 + (size_t)b * 32 : off), make_float4(carry01.x, carry01.y, carry23.x, carry23.y));
                 carry01 = f2(0.0f, 0.0f); carry23 = f2(0.0f, 0.0f);
                 lo = t0;
             }
@@ -333,7 +334,7 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
             f = fcur; b = bcur; off = offcur;
             if (remaining == 0) break;
         }
-        if (f == T && g4 != nullptr) __stcs(g4 + ((size_t)f * gf4 + (size_t)b * 32), make_float4(carry01.x, carry01.y, carry23.x, carry23.y));   // range ends with its row
+        if (f == T && g4 != nullptr) __stcs(g4 + (GSTRIDE ? (size_t)f * gf4 + (size_t)b * 32 : off), make_float4(carry01.x, carry01.y, carry23.x, carry23.y));   // range ends with its row
     }
     {
         const float a2 = warp_sum(acc2.x + acc2.y);
@@ -400,7 +401,10 @@ int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials,
     int pieces = 1;
     while (pieces < F2_PIECES && per_warp / (pieces * 2) >= F2_PIECE_MIN) pieces *= 2;
     per_warp = (total + grid * F2_WARPS * pieces - 1) / (grid * F2_WARPS * pieces);
-    if (gl1 != 0.0f) burgers_pair_loss_unit_kernel<true><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB);
-    else burgers_pair_loss_unit_kernel<false><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB);
+#define F2_LAUNCH(L1, GS) burgers_pair_loss_unit_kernel<L1, GS><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB)
+    const bool strided = gf4 != (long long)B * 32;
+    if (gl1 != 0.0f) { if (strided) F2_LAUNCH(true, true); else F2_LAUNCH(true, false); }
+    else { if (strided) F2_LAUNCH(false, true); else F2_LAUNCH(false, false); }
+#undef F2_LAUNCH
     return cudaPeekAtLastError() == cudaSuccess ? PDEC_OK : PDEC_ERR_CUDA_LAUNCH;
 }
