@@ -173,7 +173,7 @@ def test_full_size_config2_properties():
 
 
 @pytest.mark.parametrize("frames_per_slice", [0, 1, 3, -1])
-@pytest.mark.parametrize("B,chunk_rows,n,T", [(512, 128, 128, 8), (300, 128, 128, 5), (40, 16, 50, 3), (64, 256, 128, 4)])
+@pytest.mark.parametrize("B,chunk_rows,n,T", [(512, 128, 128, 8), (300, 128, 128, 5), (40, 16, 50, 3), (64, 256, 128, 4), (700, 128, 128, 3)])
 def test_host_pipeline_equals_resident_call(B, chunk_rows, n, T, frames_per_slice, monkeypatch):
     """pdec_burgers_pair_loss_host (chunked H2D / kernel / D2H over three streams) == the resident single launch:
     gradient bit for bit when the chunk scale is a power of two, else to rounding of the 1/B scale; losses to 1e-6;
