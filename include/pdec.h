@@ -139,6 +139,20 @@ int pdec_burgers_pair_loss_host(pdec_host_pipeline* pipeline, const float* s_hos
                                 int substeps, int resubstep, float gl2, float gl1, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Resampling as an operator of its own  (operator-level boundary)
+ * Replaces backend.resample(inputs, sample_coords, 'linear', boundary) (PF/tf/tf_backend.py:145-154, 451-502) and the native ops
+ * Resample / ResampleGradient (PF/tf/cuda/src/resample.cc:7-23, resample_gradient.cc:6-13) for one-channel grids of rank 1 or 2.
+ * data [B, ny, nx] (rank 2) or [B, nx] (rank 1, ny ignored); coords [coords_batch, npoints, rank] in INDEX space of data (axis 0
+ * first), coords_batch = 1 (shared by the batch) or B; out [B, npoints].  mode = PDEC_MODE_* with the TF-CPU semantics of the fused
+ * kernels ('constant': exactly 0 outside [0, N-1) along any axis).
+ * _bwd: g_data [B, ny, nx] (zeroed here, then accumulated with float atomics like the reference's ResampleGradient) and/or
+ * g_coords [B, npoints, rank] (per batch element; sum over B for shared coordinates); either may be NULL. */
+int pdec_resample_fwd(const float* data, const float* coords, float* out, int B, int rank, int ny, int nx, int coords_batch,
+                      long long npoints, int mode, void* stream);
+int pdec_resample_bwd(const float* data, const float* coords, const float* g_out, float* g_data, float* g_coords, int B, int rank,
+                      int ny, int nx, int coords_batch, long long npoints, int mode, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * 2-D incompressible flow  
  * Layouts: rho[B,ny,nx], vy[B,ny+1,nx], vx[B,ny,nx+1] (PF/physics/field/staggered_grid.py:33-39), axis 0 = y.
  * Box arguments: lower/size of the DOMAIN box per axis (PF/geom/_box.py); the staggered component boxes are

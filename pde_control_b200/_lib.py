@@ -50,6 +50,8 @@ _SIGNATURES = {
     "pdec_host_pipeline_destroy": (_c.c_int, [_P]),
     "pdec_burgers_pair_loss_host": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _c.c_double,
                                                 _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_float, _c.c_float, _P]),
+    "pdec_resample_fwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_longlong, _c.c_int, _P]),
+    "pdec_resample_bwd": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_longlong, _c.c_int, _P]),
     # ---- 2-D incompressible flow ----
     "pdec_curl_2d_fwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),
     "pdec_curl_2d_bwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),

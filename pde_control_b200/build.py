@@ -24,6 +24,7 @@ SOURCES = {
     "cg.cu": [],
     "cg_tiled.cu": [],
     "cg_pair.cu": [],
+    "resample.cu": ["-fmad=false"],
     "host_pipeline.cu": [],
 }
 

@@ -3,6 +3,7 @@
 Every op runs on CUDA tensors on `torch.cuda.current_stream()`; none has a CPU fallback (a CPU tensor raises).
 Reference semantics are cited per op (PF/ = /root/reference/PhiFlow/phi/).
 """
+import numpy as np
 import torch
 
 from . import _lib
@@ -195,6 +196,47 @@ class HostPipeline(object):
 # 2-D incompressible flow.  Layouts: rho[B,ny,nx], vy[B,ny+1,nx], vx[B,ny,nx+1]; axis 0 = y.
 # box = (lower_y, lower_x, size_y, size_x) of the domain; None -> AABox(0, resolution) (dx = 1).
 # ------------------------------------------------------------------------------------------------
+
+class _Resample(torch.autograd.Function):
+    """backend.resample (tf_backend.py:145-154): out[b, p] = multilinear sample of data[b] at coords[b | 0, p]."""
+
+    @staticmethod
+    def forward(ctx, data, coords, mode):
+        B = data.shape[0]
+        rank = data.dim() - 1
+        assert rank in (1, 2) and coords.shape[-1] == rank and coords.shape[0] in (1, B), (data.shape, coords.shape)
+        data, coords = _c(data), _c(coords)
+        _req_cuda(data, coords)
+        P = int(np.prod(coords.shape[1:-1]))
+        out = torch.empty((B,) + tuple(coords.shape[1:-1]), device=data.device, dtype=torch.float32)
+        ny, nx = (1, data.shape[1]) if rank == 1 else (data.shape[1], data.shape[2])
+        with torch.cuda.device(data.device):
+            _call("pdec_resample_fwd", _lib.ptr(data), _lib.ptr(coords), _lib.ptr(out), B, rank, ny, nx, coords.shape[0], P, int(mode),
+                  _lib.stream_ptr())
+        ctx.save_for_backward(data, coords)
+        ctx.meta = (B, rank, ny, nx, P, int(mode))
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        data, coords = ctx.saved_tensors
+        B, rank, ny, nx, P, mode = ctx.meta
+        g_out = _c(g_out)
+        g_data = torch.empty_like(data) if ctx.needs_input_grad[0] else None
+        g_coords = torch.empty((B,) + tuple(coords.shape[1:]), device=data.device, dtype=torch.float32) if ctx.needs_input_grad[1] else None
+        with torch.cuda.device(data.device):
+            _call("pdec_resample_bwd", _lib.ptr(data), _lib.ptr(coords), _lib.ptr(g_out), _lib.ptr(g_data), _lib.ptr(g_coords), B, rank, ny,
+                  nx, coords.shape[0], P, mode, _lib.stream_ptr())
+        if g_coords is not None and coords.shape[0] == 1 and B > 1:
+            g_coords = g_coords.sum(0, keepdim=True)
+        return g_data, g_coords, None
+
+
+def resample(data, coords, mode=MODE_CONSTANT):
+    """Multilinear resampling of a one-channel grid data [B, ny, nx] | [B, nx] at coords [B | 1, ..., rank] (index space, axis 0 first)
+    -> [B, ...]; differentiable w.r.t. data and coords.  The operator the reference's backend exposes (tf_backend.py:145-154)."""
+    return _Resample.apply(data, coords, int(mode))
+
 
 def _box(box, ny, nx):
     if box is None:

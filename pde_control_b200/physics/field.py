@@ -132,7 +132,23 @@ class CenteredGrid(Field):
                 hi = padded.narrow(1 + d, 1, padded.shape[1 + d] - 1)
                 comps.append(lo * 0.5 + hi * 0.5)                      # interpolate_linear: x0 * (1 - w) + x1 * w, w = 0.5 (nd.py:378-392)
             return other.with_data(comps)
-        raise NotImplementedError("general resampling between grids is not on the B200 path")
+        if isinstance(other, CenteredGrid) and self.component_count == 1:
+            # generic path (Field.at, field.py:60-72): sample at the other grid's points
+            return other.copied_with(data=self.sample_at(other.points))
+        raise NotImplementedError("resampling of multi-component grids between different grids is not on the B200 path")
+
+    def sample_at(self, points):
+        """CenteredGrid.sample_at (grid.py:101-107): points [B | 1, ..., rank] in physical units -> [B, ..., 1]; local coordinates
+        times the resolution minus one half, then the backend's resample with this field's extrapolation (ops.resample)."""
+        from .. import ops
+        from .._lib import MODE_OF_EXTRAPOLATION
+        assert self.component_count == 1 and self.rank in (1, 2)
+        points = _as_tensor(points, self.data).to(self.data.device)
+        lower = torch.as_tensor(self.box.lower, device=points.device)
+        size = torch.as_tensor(self.box.size, device=points.device)
+        res = torch.as_tensor(np.asarray(self.resolution, np.float32), device=points.device)
+        coords = (points - lower) / size * res - 0.5
+        return ops.resample(self.tensor, coords, MODE_OF_EXTRAPOLATION[self.extrapolation]).unsqueeze(-1)
 
     def padded(self, widths):
         """math.pad with the field's extrapolation (grid.py:164-170); plain torch, off the hot path."""

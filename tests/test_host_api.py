@@ -177,6 +177,8 @@ def test_scene_format_round_trip(tmp_path):
 
 
 def test_control_training_learns_and_checkpoints(tmp_path):
+    torch.manual_seed(0)                     # batch order and initial weight come from the global generators
+    np.random.seed(0)
     rng = np.random.RandomState(0)
     ends = rng.randn(16, 1, 1).astype(np.float32)
     frames = np.stack([ends * t / 2 for t in range(3)], 1)                        # [16 sims, 3 frames, 1, 1]: linear walk
