@@ -227,6 +227,12 @@ int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p, int* iter
                        int closed, float accuracy, int max_iterations, int stop_mode, void* workspace, size_t workspace_bytes,
                        void* stream);
 
+/* The stencil of a domain with obstacles from its cell mask (replaces the LaplaceMatrix op, PF/tf/cuda/src/laplace_op.cc:10-17, and
+ * PoissonDomain's mask logic, solver_api.py:51-121): active [ny*nx] floats (1 fluid, 0 obstacle) -> code [ny*nx] bytes as
+ * pdec_cg_poisson_2d_masked reads them, and the face masks fy [(ny+1)*nx], fx [ny*(nx+1)] that multiply the velocity before the
+ * divergence and the pressure gradient before the subtraction (_frictionless_velocity_mask).  Any output may be NULL. */
+int pdec_laplace_matrix_2d(const float* active, unsigned char* code, float* fy, float* fx, int ny, int nx, int closed, void* stream);
+
 /* The same solve on a domain with OBSTACLES (PoissonDomain active / accessible masks, solver_api.py:51-121; matrix
  * sparse.py:157-221): `code` [ny*nx] bytes (device, shared by the batch) gives every cell its stencil: bits 0..3 = coupled to the
  * neighbour above (i-1) / below (i+1) / left (j-1) / right (j+1), i.e. active_self * active_neighbour; bits 4..7 = minus the

@@ -25,6 +25,7 @@ SOURCES = {
     "cg_tiled.cu": [],
     "cg_pair.cu": [],
     "resample.cu": ["-fmad=false"],
+    "laplace_matrix.cu": [],
     "host_pipeline.cu": [],
 }
 

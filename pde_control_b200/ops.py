@@ -643,24 +643,17 @@ class ObstacleMasks(object):
                                     (sparse.py:186-213 with active_tensor / accessible_tensor, solver_api.py:88-109)."""
 
     def __init__(self, active, closed):
-        a = active.to(torch.float32)
+        a = active.to(torch.float32).contiguous()
         assert a.dim() == 2 and a.is_cuda
+        ny, nx = a.shape
         self.closed = bool(closed)
         self.active = a
-        pad = torch.nn.functional.pad
-        ext_act = pad(a, (1, 1, 1, 1), value=0.0)
-        ext_acc = pad(a, (1, 1, 1, 1), value=0.0 if closed else 1.0)
-        up, down = ext_act[:-2, 1:-1] * a, ext_act[2:, 1:-1] * a
-        left, right = ext_act[1:-1, :-2] * a, ext_act[1:-1, 2:] * a
-        diag = (ext_acc[:-2, 1:-1] + ext_acc[2:, 1:-1] + ext_acc[1:-1, :-2] + ext_acc[1:-1, 2:]).clamp_min(1.0)
-        self.code = (up + 2 * down + 4 * left + 8 * right + 16 * diag).to(torch.uint8).contiguous()
-        if closed:
-            py, px = pad(a, (0, 0, 1, 1), value=0.0), pad(a, (1, 1, 0, 0), value=0.0)
-        else:
-            py = pad(a[None, None], (0, 0, 1, 1), mode="replicate")[0, 0]
-            px = pad(a[None, None], (1, 1, 0, 0), mode="replicate")[0, 0]
-        self.fy = torch.minimum(py[:-1], py[1:]).contiguous()
-        self.fx = torch.minimum(px[:, :-1], px[:, 1:]).contiguous()
+        self.code = torch.empty((ny, nx), dtype=torch.uint8, device=a.device)
+        self.fy = torch.empty((ny + 1, nx), dtype=torch.float32, device=a.device)
+        self.fx = torch.empty((ny, nx + 1), dtype=torch.float32, device=a.device)
+        with torch.cuda.device(a.device):
+            _call("pdec_laplace_matrix_2d", _lib.ptr(a), _lib.ptr(self.code), _lib.ptr(self.fy), _lib.ptr(self.fx), ny, nx, int(self.closed),
+                  _lib.stream_ptr())
 
 
 def cg_poisson_masked_raw(rhs, out, code, accuracy, max_iterations, guess=None, iterations=None, residual=None, stop_mode=0):

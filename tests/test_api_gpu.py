@@ -311,3 +311,41 @@ def test_masked_cg_on_chip_matches_streaming_kernel_and_dense_solve(ny, nx, clos
         ops.cg_poisson_masked_raw(r, out, masks.code, 1e-6, 4000)
         want = np.linalg.solve(A, rhs.reshape(B, -1).astype(np.float64).T).T.reshape(B, ny, nx)
         assert rel_err(out.cpu(), want) < 2e-4
+
+
+@pytest.mark.parametrize("closed", [False, True])
+def test_laplace_matrix_kernel_matches_mask_algebra(closed):
+    """pdec_laplace_matrix_2d (the LaplaceMatrix op's twin) vs the mask algebra of solver_api.py:51-121 / sparse.py:186-213 written with
+    torch pads, and vs the oracle's dense masked matrix: stencil code, face masks."""
+    from pde_control_b200 import ops
+    from oracle import restate_fluid as F
+    rng = np.random.RandomState(3 + closed)
+    pad = torch.nn.functional.pad
+    for ny, nx in ((7, 9), (32, 32), (33, 130)):
+        a = torch.tensor((rng.rand(ny, nx) > 0.3).astype(np.float32), device="cuda")
+        m = ops.ObstacleMasks(a, closed)
+        ext_act = pad(a, (1, 1, 1, 1), value=0.0)
+        ext_acc = pad(a, (1, 1, 1, 1), value=0.0 if closed else 1.0)
+        up, down = ext_act[:-2, 1:-1] * a, ext_act[2:, 1:-1] * a
+        left, right = ext_act[1:-1, :-2] * a, ext_act[1:-1, 2:] * a
+        diag = (ext_acc[:-2, 1:-1] + ext_acc[2:, 1:-1] + ext_acc[1:-1, :-2] + ext_acc[1:-1, 2:]).clamp_min(1.0)
+        code = (up + 2 * down + 4 * left + 8 * right + 16 * diag).to(torch.uint8)
+        assert torch.equal(m.code, code)
+        if closed:
+            py, px = pad(a, (0, 0, 1, 1), value=0.0), pad(a, (1, 1, 0, 0), value=0.0)
+        else:
+            py = pad(a[None, None], (0, 0, 1, 1), mode="replicate")[0, 0]
+            px = pad(a[None, None], (1, 1, 0, 0), mode="replicate")[0, 0]
+        assert torch.equal(m.fy, torch.minimum(py[:-1], py[1:])) and torch.equal(m.fx, torch.minimum(px[:, :-1], px[:, 1:]))
+        if ny * nx < 2000:
+            A, fy, fx = F.masked_operator(a.cpu().numpy().astype(np.float64), "closed" if closed else "open")
+            c = m.code.cpu().numpy().astype(np.int64).reshape(-1)
+            np.testing.assert_array_equal(np.diag(A), -(c >> 4))
+            idx = np.arange(ny * nx)
+            for bit, off in ((0, -nx), (1, nx), (2, -1), (3, 1)):
+                has = (c >> bit) & 1
+                rows = idx[has == 1]
+                assert np.all(A[rows, rows + off] == 1.0)
+            assert int(np.count_nonzero(A)) == ny * nx + int(sum(((c >> k) & 1).sum() for k in range(4)))
+            np.testing.assert_array_equal(m.fy.cpu().numpy(), fy)
+            np.testing.assert_array_equal(m.fx.cpu().numpy(), fx)
