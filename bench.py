@@ -122,9 +122,10 @@ class BurgersWorkload:
         self.losses = torch.zeros(2, device=device)
         ws_bytes = _lib.lib().pdec_burgers_pair_loss_workspace_bytes(B, n, T)
         self.ws = torch.empty((ws_bytes + 3) // 4, device=device)
-        self.host_s = torch.empty(base.shape, dtype=torch.float32).pin_memory()
+        from pde_control_b200 import hostmem
+        self.host_s = hostmem.pinned_empty(base.shape, device)             # page-locked, on the GPU's NUMA node
         self.host_s.copy_(self.s[0].cpu())
-        self.host_grad = torch.empty(base.shape, dtype=torch.float32).pin_memory()
+        self.host_grad = hostmem.pinned_empty(base.shape, device)
         self.host_losses = torch.empty(2, dtype=torch.float32).pin_memory()
         self.h2d = self.host_s.numel() * 4
         self.d2h = self.host_grad.numel() * 4 + 8
