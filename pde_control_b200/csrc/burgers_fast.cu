@@ -142,6 +142,11 @@ __device__ __forceinline__ void fast_adjoint(const FastP& p, const Gathered& G, 
         if (MODE == PDEC_MODE_CONSTANT) {
             const int prev = __shfl_up_sync(PDEC_FULL_MASK, G.base[k], 1);
             ordered = ordered && (lane == 0 || G.base[k] > prev);
+        } else if (MODE == PDEC_MODE_CIRCULAR) {
+            // periodic rows: the wrapped indices of an instruction are distinct when the UNWRAPPED floors increase strictly over the
+            // lanes and span less than one period (the ceil samples are the floors + 1: distinct among themselves as well)
+            const int prev = __shfl_up_sync(PDEC_FULL_MASK, G.base[k], 1), first = __shfl_sync(PDEC_FULL_MASK, G.base[k], 0);
+            ordered = ordered && (lane == 0 || G.base[k] > prev) && (G.base[k] - first < 128);
         } else {
             const int pf_prev = __shfl_up_sync(PDEC_FULL_MASK, G.pf[k], 1), pc_prev = __shfl_up_sync(PDEC_FULL_MASK, G.pc[k], 1);
             ordered = ordered && (lane == 0 || (G.pf[k] > pf_prev && G.pc[k] > pc_prev));
