@@ -59,7 +59,9 @@ struct Step2 {                        // what the forward step leaves for its ad
 __device__ __forceinline__ float lds_off(const float* row, unsigned off) { return *reinterpret_cast<const float*>(reinterpret_cast<const char*>(row) + off); }
 __device__ __forceinline__ float* ptr_off(float* row, unsigned off) { return reinterpret_cast<float*>(reinterpret_cast<char*>(row) + off); }
 
-// forward step of the row (u01, u23) -> (v01, v23); su = this warp's source row, mine = su + lane (own cells at mine[32 k])
+// forward step of the row (u01, u23) -> (v01, v23); su = this warp's source row, mine = su + lane (own cells at mine[32 k]).
+// PERIODIC: 'circular' rows (tf_backend.py:476-480, 532-538): taps wrap modulo 128, w1 = 1 - w0, the stencil wraps over the lanes.
+template <bool PERIODIC>
 __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float2 X23, float2 u01, float2 u23, float* su, float* mine, int lane,
                                               float2& v01, float2& v23, Step2& S) {
     mine[0] = u01.x; mine[32] = u01.y; mine[64] = u23.x; mine[96] = u23.y;
@@ -80,23 +82,41 @@ __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float
     const float2 bf01 = f2(bf[0], bf[1]), bf23 = f2(bf[2], bf[3]);
     S.w0[0] = sub2(xi01, bf01);
     S.w0[1] = sub2(xi23, bf23);
-    S.w1[0] = sub2(__fadd2_rn(bf01, one2), xi01);
-    S.w1[1] = sub2(__fadd2_rn(bf23, one2), xi23);
+    if (PERIODIC) {
+        S.w1[0] = sub2(one2, S.w0[0]);
+        S.w1[1] = sub2(one2, S.w0[1]);
+    } else {
+        S.w1[0] = sub2(__fadd2_rn(bf01, one2), xi01);
+        S.w1[1] = sub2(__fadd2_rn(bf23, one2), xi23);
+    }
     const float w0[4] = {S.w0[0].x, S.w0[0].y, S.w0[1].x, S.w0[1].y};
     const float w1[4] = {S.w1[0].x, S.w1[0].y, S.w1[1].x, S.w1[1].y};
     float adv[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const unsigned b = (unsigned)S.bi[k] < 127u ? (unsigned)S.bi[k] : (unsigned)F2_OUT;
-        S.offF[k] = b + (b & 3u) * 127u;
-        S.offC[k] = b + ((b + 1u) & 3u) * 127u + 1u;
+        if (PERIODIC) {
+            const unsigned bF = (unsigned)S.bi[k] & 127u, bC = (unsigned)(S.bi[k] + 1) & 127u;
+            S.offF[k] = bF + (bF & 3u) * 127u;
+            S.offC[k] = bC + (bC & 3u) * 127u;
+        } else {
+            const unsigned b = (unsigned)S.bi[k] < 127u ? (unsigned)S.bi[k] : (unsigned)F2_OUT;
+            S.offF[k] = b + (b & 3u) * 127u;
+            S.offC[k] = b + ((b + 1u) & 3u) * 127u + 1u;
+        }
         const float tf = lds_off(su, S.offF[k]), tc = lds_off(su, S.offC[k]);     // (u[floor], u[floor + 1]) or (0, 0)
         adv[k] = __fadd_rn(__fmul_rn(tf, w1[k]), __fmul_rn(tc, w0[k]));           // tf_backend.py:491-497
         S.du[k] = tc - tf;
     }
-    float left = __shfl_up_sync(PDEC_FULL_MASK, adv[3], 1), right = __shfl_down_sync(PDEC_FULL_MASK, adv[0], 1);
-    if (lane == 0) left = 0.0f;                                        // zero padding of the 'constant' field (nd.py:271-283)
-    if (lane == 31) right = 0.0f;
+    float left, right;
+    if (PERIODIC) {                                                    // circular padding (nd.py:271-283)
+        left = __shfl_sync(PDEC_FULL_MASK, adv[3], (lane + 31) & 31);
+        right = __shfl_sync(PDEC_FULL_MASK, adv[0], (lane + 1) & 31);
+    } else {
+        left = __shfl_up_sync(PDEC_FULL_MASK, adv[3], 1);
+        right = __shfl_down_sync(PDEC_FULL_MASK, adv[0], 1);
+        if (lane == 0) left = 0.0f;                                    // zero padding of the 'constant' field
+        if (lane == 31) right = 0.0f;
+    }
     const float2 a01 = f2(adv[0], adv[1]), a23 = f2(adv[2], adv[3]), mid = f2(adv[1], adv[2]);
     const float2 m2 = f2(-2.0f, -2.0f), c2v = f2(p.c, p.c);
     // nd.py:281-282: (up + lo) - 2 u (2 u is exact, so one fused rounding equals the reference's two); grid.py:190 and
@@ -112,11 +132,19 @@ __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float
 
 // adjoint of one step.  h = -(dL/d step output) on entry (the caller keeps the sign of the residual gradient); returns dL/d(step
 // input) in (gin01, gin23).  The accumulator row's cell words are all-zero on entry and again on exit.
+template <bool PERIODIC>
 __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, float2 h01, float2 h23, float* sacc, float* mine_acc, int lane,
                                               float2& gin01, float2& gin23) {
-    float hl = __shfl_up_sync(PDEC_FULL_MASK, h23.y, 1), hr = __shfl_down_sync(PDEC_FULL_MASK, h01.x, 1);
-    if (lane == 0) hl = 0.0f;
-    if (lane == 31) hr = 0.0f;
+    float hl, hr;
+    if (PERIODIC) {
+        hl = __shfl_sync(PDEC_FULL_MASK, h23.y, (lane + 31) & 31);
+        hr = __shfl_sync(PDEC_FULL_MASK, h01.x, (lane + 1) & 31);
+    } else {
+        hl = __shfl_up_sync(PDEC_FULL_MASK, h23.y, 1);
+        hr = __shfl_down_sync(PDEC_FULL_MASK, h01.x, 1);
+        if (lane == 0) hl = 0.0f;
+        if (lane == 31) hr = 0.0f;
+    }
     // transpose of the (symmetric, zero-padded) diffusion stencil
     const float2 mid = f2(h01.y, h23.x), m2 = f2(-2.0f, -2.0f), c2v = f2(p.c, p.c);
     const float2 q01 = __ffma2_rn(c2v, __ffma2_rn(h01, m2, __fadd2_rn(mid, f2(hl, h01.x))), h01);
@@ -129,6 +157,10 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
     for (int k = 0; k < 4; ++k) {
         const int prev = __shfl_up_sync(PDEC_FULL_MASK, S.bi[k], 1);
         ordered = ordered && (lane == 0 || S.bi[k] > prev);
+        if (PERIODIC) {      // wrapped targets are distinct when the unwrapped floors also span less than one period
+            const int first = __shfl_sync(PDEC_FULL_MASK, S.bi[k], 0);
+            ordered = ordered && ((long long)S.bi[k] - first < 128);
+        }
     }
 #ifdef F2_SKIP_SCATTER
     if (false) {
@@ -165,8 +197,8 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
         // (match_any) and take turns by rank -- same sums in a fixed order, as many rounds as the largest group
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const bool inside = (unsigned)S.bi[k] < 127u;
-            const unsigned peers = __match_any_sync(PDEC_FULL_MASK, inside ? S.bi[k] : -1 - lane);
+            const bool inside = PERIODIC || (unsigned)S.bi[k] < 127u;
+            const unsigned peers = __match_any_sync(PDEC_FULL_MASK, PERIODIC ? (S.bi[k] & 127) : (inside ? S.bi[k] : -1 - lane));
             const int rank = __popc(peers & ((1u << lane) - 1u));
             for (int r = 0; __any_sync(PDEC_FULL_MASK, inside && rank >= r); ++r) {
                 if (inside && rank == r) {
@@ -215,7 +247,7 @@ __device__ __forceinline__ float sgn(float d) { return (d > 0.0f) ? 1.0f : ((d <
 // a pair; a pair below the range's / window's first one is walked "carry-only" (forward step only: its residual gradient w.r.t.
 // its target frame is the carry the first real pair needs); the step from the last frame of a row to the first frame of the
 // next one only closes the row.
-template <bool L1TERM, bool GSTRIDE>
+template <bool L1TERM, bool GSTRIDE, bool PERIODIC>
 __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
                                                                             float2* partials, int T, int B, int t0, int t1, long long per_warp, int pieces,
                                                                             long long gf4, unsigned* done_counter, float* __restrict__ losses, float inv_B) {
@@ -294,7 +326,7 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
             if (remaining - (real ? 1 : 0) > 0) pre = __ldcs(s4 + offn);      // in flight during this step's arithmetic
 #endif
             if (!closing) {
-                step2_forward(p, X01, X23, u01, u23, su, mine, lane, v01, v23, S);
+                step2_forward<PERIODIC>(p, X01, X23, u01, u23, su, mine, lane, v01, v23, S);
                 const float2 d01 = sub2(n01, v01), d23 = sub2(n23, v23);     // burgers.py:29
                 float2 gd01 = __fmul2_rn(d01, gl2v), gd23 = __fmul2_rn(d23, gl2v);
                 if (L1TERM) {
@@ -310,7 +342,7 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
 #if defined(F2_SKIP_ADJ)
                         gin01 = gd01; gin23 = gd23;
 #else
-                        step2_adjoint(p, S, gd01, gd23, sacc, mine_acc, lane, gin01, gin23);      // dL/dv = -gd
+                        step2_adjoint<PERIODIC>(p, S, gd01, gd23, sacc, mine_acc, lane, gin01, gin23);      // dL/dv = -gd
 #endif
                         gin01 = __fadd2_rn(gin01, carry01);
                         gin23 = __fadd2_rn(gin23, carry23);
@@ -380,8 +412,8 @@ using namespace pdec;
 // partials must hold max(32, B * T) float2 (pdec_burgers_pair_loss_workspace_bytes).  [t0, t1) = window of pairs (0, T = all):
 // losses <- the window's share of (L2, L1); grad_s frames t0..t1-1 (and T when t1 == T) <- their complete gradient
 // grad_frame_stride: floats between consecutive frames of grad_s (0: dense, B * 128)
-int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int t0, int t1, double dt, double viscosity, float gl2,
-                                float gl1, long long grad_frame_stride, unsigned* done_counter, float* losses, cudaStream_t st) {
+int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int t0, int t1, int periodic, double dt, double viscosity,
+                                float gl2, float gl1, long long grad_frame_stride, unsigned* done_counter, float* losses, cudaStream_t st) {
     if (t0 < 0 || t1 > T || t0 >= t1) return PDEC_ERR_INVALID_ARGUMENT;
     if (grad_frame_stride != 0 && (grad_frame_stride < (long long)B * 128 || (grad_frame_stride & 3))) return PDEC_ERR_INVALID_ARGUMENT;
     const long long gf4 = grad_frame_stride ? grad_frame_stride / 4 : (long long)B * 32;
@@ -401,10 +433,12 @@ int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials,
     int pieces = 1;
     while (pieces < F2_PIECES && per_warp / (pieces * 2) >= F2_PIECE_MIN) pieces *= 2;
     per_warp = (total + grid * F2_WARPS * pieces - 1) / (grid * F2_WARPS * pieces);
-#define F2_LAUNCH(L1, GS) burgers_pair_loss_unit_kernel<L1, GS><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB)
+#define F2_LAUNCH(L1, GS, PER) burgers_pair_loss_unit_kernel<L1, GS, PER><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB)
+#define F2_PICK(L1, GS) do { if (periodic) F2_LAUNCH(L1, GS, true); else F2_LAUNCH(L1, GS, false); } while (0)
     const bool strided = gf4 != (long long)B * 32;
-    if (gl1 != 0.0f) { if (strided) F2_LAUNCH(true, true); else F2_LAUNCH(true, false); }
-    else { if (strided) F2_LAUNCH(false, true); else F2_LAUNCH(false, false); }
+    if (gl1 != 0.0f) { if (strided) F2_PICK(true, true); else F2_PICK(true, false); }
+    else { if (strided) F2_PICK(false, true); else F2_PICK(false, false); }
+#undef F2_PICK
 #undef F2_LAUNCH
     return cudaPeekAtLastError() == cudaSuccess ? PDEC_OK : PDEC_ERR_CUDA_LAUNCH;
 }

@@ -226,3 +226,34 @@ def test_edge_cases_empty_batch_and_bad_arguments():
         ops.burgers_step(torch.zeros(2, 1, device="cuda"), 0.1, 0.1)          # n < 2
     with pytest.raises(PdecError):
         ops.burgers_step(torch.zeros(1, 100000, device="cuda"), 0.1, 0.1)     # row does not fit shared memory
+
+
+def test_periodic_unit_kernel_forward_is_bit_exact_and_matches_v1(monkeypatch):
+    """The periodic ('circular') twin of the fused unit kernel: (1) the force loss of a trajectory produced by the general step kernel
+    with the same mode is EXACTLY zero (the two forward steps agree bit for bit: wrapped taps, w1 = 1 - w0, wrapped stencil);
+    (2) losses and gradients agree to rounding with the v1 kernel (PDEC_BURGERS_FAST_V1), on rows that cross the
+    seam in both directions and on rows with shocks (folded back-trace: ranked scatter)."""
+    ops = _ops()
+    from pde_control_b200._lib import MODE_CIRCULAR
+    rng = np.random.RandomState(5)
+    B, n, T = 600, 128, 6
+    u0 = np.stack([R.gaussian_clash(1, n, rng)[0] for _ in range(B)]).astype(np.float32)
+    u0[::3] += 1.5                                    # drift to the right across the seam
+    u0[1::3] -= 1.5                                   # and to the left
+    u0[2::7] *= 6.0                                   # steep: several cells per cell, folds
+    u0c = torch.tensor(u0, device="cuda")
+    frames = ops.burgers_trajectory(u0c, T, 0.03, 0.003, mode=MODE_CIRCULAR, substeps=1)
+    s = torch.cat([u0c[None], frames]).contiguous()
+    l2, l1 = ops.burgers_pair_loss(s, 0.03, 0.003, mode=MODE_CIRCULAR)
+    assert l2.item() == 0.0 and l1.item() == 0.0
+    sp = (s + 0.05 * torch.randn(s.shape, device="cuda", generator=torch.Generator(device="cuda").manual_seed(1))).requires_grad_(True)
+    l2a, l1a = ops.burgers_pair_loss(sp, 0.03, 0.003, mode=MODE_CIRCULAR)
+    l2a.backward()
+    ga = sp.grad.clone()
+    sp.grad = None
+    monkeypatch.setenv("PDEC_BURGERS_FAST_V1", "1")
+    l2b, l1b = ops.burgers_pair_loss(sp, 0.03, 0.003, mode=MODE_CIRCULAR)
+    l2b.backward()
+    # the two kernels cut the (row, pair) space differently, so the loss sums are grouped differently
+    assert abs(l2a.item() - l2b.item()) <= 2e-6 * abs(l2b.item()) and abs(l1a.item() - l1b.item()) <= 2e-6 * abs(l1b.item())
+    assert rel_err(ga.cpu(), sp.grad.cpu()) < 2e-6
