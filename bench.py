@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- headline measurement of the B200-native PDE-Control physics path.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload burgers|fluid]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload burgers|burgers_periodic|fluid]
 
 Metric (BASELINE.json): forward+adjoint cell-updates/s.  One "step" = one pass of the hot path over one batch:
 
@@ -102,6 +102,7 @@ class BurgersWorkload:
     dtype = "f32"
     dominant_kernel = "burgers_pair_loss_unit_kernel"
     ncu_traffic_bytes = 129.0e6     # steady state: dram read 66.1 MB + write 62.9 MB per launch, profiles/r1k_burgers_summary.md
+    mode = 0                        # PDEC_MODE_CONSTANT: the reference's Burgers domain (OPEN boundaries -> 'constant' extrapolation)
 
     def __init__(self, device, rank, B=4096, n=128, T=32):
         import torch
@@ -146,7 +147,7 @@ class BurgersWorkload:
             T1, B, n = self.s[0].shape
             st = _lib.stream_ptr()
             self._fn = _lib.lib().pdec_burgers_pair_loss
-            self._args = [(_lib.ptr(self.s[j]), _lib.ptr(self.grad[j]), _lib.ptr(self.losses), T1 - 1, B, n, 0, float(DT), float(VISC),
+            self._args = [(_lib.ptr(self.s[j]), _lib.ptr(self.grad[j]), _lib.ptr(self.losses), T1 - 1, B, n, self.mode, float(DT), float(VISC),
                            0.0, 1.0, 1, 0, 1.0, 0.0, _lib.ptr(self.ws), self.ws.numel() * 4, st) for j in range(self.nsets)]
         rc = self._fn(*self._args[k])
         if rc != 0:
@@ -158,7 +159,7 @@ class BurgersWorkload:
         pdec_burgers_pair_loss_host): per 512-row chunk H2D of the frames, the fused kernel, D2H of the gradient, the three
         legs overlapped on three streams; plus the two loss scalars.  The step ends when the host holds the results."""
         self.i += 1
-        self.pipe.pair_loss(self.host_s, self.host_grad, self.host_losses, DT, VISC)
+        self.pipe.pair_loss(self.host_s, self.host_grad, self.host_losses, DT, VISC, mode=self.mode)
         self.torch.cuda.current_stream().synchronize()
 
     def config(self):
@@ -166,8 +167,8 @@ class BurgersWorkload:
                 "l2": self.l2_policy}
 
     # ---- CPU legs (oracle port) ---------------------------------------------------------------
-    @staticmethod
-    def cpu_step(Bs, n=128, T=32, seed=1):
+    @classmethod
+    def cpu_step(cls, Bs, n=128, T=32, seed=1):
         import torch
         from oracle import restate as R
         import numpy as np
@@ -175,14 +176,23 @@ class BurgersWorkload:
         s = np.stack([R.gaussian_clash(Bs, n, rng) for _ in range(T + 1)]).astype(np.float32)
         s = torch.tensor(s, requires_grad=True)
         t0 = time.perf_counter()
-        l2, l1 = R.burgers_pair_loss(s, DT, VISC)
+        l2, l1 = R.burgers_pair_loss(s, DT, VISC, mode=R.CIRCULAR if cls.mode == 2 else R.CONSTANT)
         l2.backward()
         return time.perf_counter() - t0, T * Bs * n
+
+
+class PeriodicBurgersWorkload(BurgersWorkload):
+    """The same step on a periodic grid (the north star's wording; the reference's own Burgers scenes are not periodic)."""
+    name = "burgers_pair_loss PERIODIC res=128 T=32 B=4096/gpu (config 2 with 'circular' extrapolation)"
+    ncu_traffic_bytes = None
+    mode = 2                        # PDEC_MODE_CIRCULAR
 
 
 def _make_workload(name, device, rank):
     if name == "burgers":
         return BurgersWorkload(device, rank)
+    if name == "burgers_periodic":
+        return PeriodicBurgersWorkload(device, rank)
     if name == "fluid":
         from pde_control_b200 import bench_fluid
         return bench_fluid.FluidWorkload(device, rank)
@@ -192,6 +202,8 @@ def _make_workload(name, device, rank):
 def _cpu_class(name):
     if name == "burgers":
         return BurgersWorkload
+    if name == "burgers_periodic":
+        return PeriodicBurgersWorkload
     from pde_control_b200 import bench_fluid
     return bench_fluid.FluidWorkload
 
@@ -330,7 +342,7 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="burgers", choices=["burgers", "fluid"])
+    ap.add_argument("--workload", default="burgers", choices=["burgers", "burgers_periodic", "fluid"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
