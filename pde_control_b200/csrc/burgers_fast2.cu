@@ -39,6 +39,9 @@ struct Unit2P {
 #ifndef F2_WARPS
 #define F2_WARPS 12                   // warps per CTA
 #endif
+#ifndef F2_WAVES
+#define F2_WAVES 1                    // CTAs per resident slot: > 1 lets the hardware scheduler balance the load (measured slower)
+#endif
 #ifndef F2_PIECES
 #define F2_PIECES 1                   // most ranges per warp (power of two)
 #endif
@@ -426,7 +429,7 @@ int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials,
     p.gl2 = gl2 * invB; p.gl1 = gl1 * invB;
     const long long total = (long long)B * (t1 - t0);
     // one range per resident warp (148 SMs x F2_MINB CTAs x F2_WARPS warps), at least 4 pairs per range
-    long long grid = 148LL * F2_MINB;
+    long long grid = 148LL * F2_MINB * F2_WAVES;
     if (grid * F2_WARPS * 4 > total) grid = total / (4 * F2_WARPS) > 0 ? total / (4 * F2_WARPS) : 1;
     long long per_warp = (total + grid * F2_WARPS - 1) / (grid * F2_WARPS);
     // several shorter ranges per warp when there is enough work (each range start costs one carry-only forward step)
