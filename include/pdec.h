@@ -99,7 +99,7 @@ int pdec_burgers_pair_loss(const float* s, float* grad_s, float* losses, int T, 
  * of disjoint windows add up to the whole), grad_s frames t0 .. t1-1 (and frame T when t1 == T) <- their COMPLETE gradient
  * (frame t0 includes the residual term of the pair before the window, recomputed from frame t0-1, which must be present).
  * Only frames t0-1 .. t1 of s are read: the host pipeline below runs window k while frames of window k+1 are still in flight.
- * Supported for the fused unit-box kernel only (n = 128, PDEC_MODE_CONSTANT or PDEC_MODE_CIRCULAR, box [0, 1], one substep):
+ * Supported for the fused unit-box kernel only (n = 128, any PDEC_MODE_*, box [0, 1], one substep):
  * pdec_burgers_pair_loss_window_supported() != 0, else PDEC_ERR_UNSUPPORTED_SIZE.  Workspace as for pdec_burgers_pair_loss. */
 int pdec_burgers_pair_loss_window_supported(int n, int mode, float box_lower, float box_size, int substeps);
 int pdec_burgers_pair_loss_window(const float* s, float* grad_s, float* losses, int T, int B, int n, int t0, int t1, int mode, double dt,

@@ -313,7 +313,7 @@ static int pair_loss_chunk(int B, int T) {
 }
 
 // burgers_fast2.cu: packed-fp32 / float2-tap kernel for 'constant' rows on the unit box with one diffusion substep
-int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int t0, int t1, int periodic, double dt, double viscosity,
+int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int t0, int t1, int pad_mode, double dt, double viscosity,
                                 float gl2, float gl1, long long grad_frame_stride, unsigned* done_counter, float* losses, cudaStream_t st);
 
 // returns PDEC_OK if it handled the call, 1 if the shape is not eligible (caller uses the general kernel)
@@ -337,9 +337,9 @@ int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials,
     const int exact = (is_pow2f(size) && is_pow2f(p.dx2)) ? ((lower == 0.0f && size == 1.0f) ? 2 : 1) : 0;
     const int C = pair_loss_chunk(B, T), nchunks = (T + C - 1) / C;
     if (cudaMemsetAsync(done_counter, 0, sizeof(unsigned), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
-    if ((mode == PDEC_MODE_CONSTANT || mode == PDEC_MODE_CIRCULAR) && exact == 2 && substeps == 1 && getenv("PDEC_BURGERS_FAST_V1") == nullptr) {
-        // headline case (BASELINE configs 2 and 4) and its periodic twin
-        const int rc = pdec_burgers_pair_loss_unit(s, grad_s, partials, T, B, 0, T, mode == PDEC_MODE_CIRCULAR, dt, viscosity, gl2, gl1, 0, done_counter,
+    if (exact == 2 && substeps == 1 && getenv("PDEC_BURGERS_FAST_V1") == nullptr) {
+        // headline case (BASELINE configs 2 and 4) and its periodic / replicate twins
+        const int rc = pdec_burgers_pair_loss_unit(s, grad_s, partials, T, B, 0, T, mode, dt, viscosity, gl2, gl1, 0, done_counter,
                                                    losses, st);
         if (rc <= 0) return rc;
     }
@@ -368,7 +368,8 @@ int pdec_burgers_pair_loss_fast(const float* s, float* grad_s, float2* partials,
 
 // ---- window of frame pairs (frame-sliced host pipeline) ------------------------------------------------------------------------
 extern "C" int pdec_burgers_pair_loss_window_supported(int n, int mode, float box_lower, float box_size, int substeps) {
-    return n == 128 && (mode == PDEC_MODE_CONSTANT || mode == PDEC_MODE_CIRCULAR) && box_lower == 0.0f && box_size == 1.0f && substeps == 1;
+    return n == 128 && (mode == PDEC_MODE_CONSTANT || mode == PDEC_MODE_REPLICATE || mode == PDEC_MODE_CIRCULAR) && box_lower == 0.0f &&
+           box_size == 1.0f && substeps == 1;
 }
 
 extern "C" int pdec_burgers_pair_loss_window_strided(const float* s, float* grad_s, float* losses, int T, int B, int n, int t0, int t1, int mode,
@@ -384,7 +385,7 @@ extern "C" int pdec_burgers_pair_loss_window_strided(const float* s, float* grad
     const size_t raw = (size_t)B * (size_t)T * sizeof(float2);
     unsigned* done_counter = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(workspace) + ((raw + 255) & ~(size_t)255));
     if (cudaMemsetAsync(done_counter, 0, sizeof(unsigned), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
-    const int rc = pdec_burgers_pair_loss_unit(s, grad_s, reinterpret_cast<float2*>(workspace), T, B, t0, t1, mode == PDEC_MODE_CIRCULAR, dt, viscosity,
+    const int rc = pdec_burgers_pair_loss_unit(s, grad_s, reinterpret_cast<float2*>(workspace), T, B, t0, t1, mode, dt, viscosity,
                                                gl2, gl1, grad_frame_stride, done_counter, losses, st);
     return rc == 1 ? PDEC_ERR_UNSUPPORTED_SIZE : rc;
 }

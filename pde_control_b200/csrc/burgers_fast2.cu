@@ -63,8 +63,9 @@ __device__ __forceinline__ float lds_off(const float* row, unsigned off) { retur
 __device__ __forceinline__ float* ptr_off(float* row, unsigned off) { return reinterpret_cast<float*>(reinterpret_cast<char*>(row) + off); }
 
 // forward step of the row (u01, u23) -> (v01, v23); su = this warp's source row, mine = su + lane (own cells at mine[32 k]).
-// PERIODIC: 'circular' rows (tf_backend.py:476-480, 532-538): taps wrap modulo 128, w1 = 1 - w0, the stencil wraps over the lanes.
-template <bool PERIODIC>
+// PAD = PDEC_MODE_*.  'circular' rows (tf_backend.py:476-480, 532-538): taps wrap modulo 128, w1 = 1 - w0, the stencil wraps over the
+// lanes.  'replicate' rows (:505-518): taps clamp to [0, 127], w1 = 1 - w0 from the UNCLAMPED floor, the stencil repeats the edge cell.
+template <int PAD>
 __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float2 X23, float2 u01, float2 u23, float* su, float* mine, int lane,
                                               float2& v01, float2& v23, Step2& S) {
     mine[0] = u01.x; mine[32] = u01.y; mine[64] = u23.x; mine[96] = u23.y;
@@ -85,7 +86,7 @@ __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float
     const float2 bf01 = f2(bf[0], bf[1]), bf23 = f2(bf[2], bf[3]);
     S.w0[0] = sub2(xi01, bf01);
     S.w0[1] = sub2(xi23, bf23);
-    if (PERIODIC) {
+    if (PAD != PDEC_MODE_CONSTANT) {
         S.w1[0] = sub2(one2, S.w0[0]);
         S.w1[1] = sub2(one2, S.w0[1]);
     } else {
@@ -97,8 +98,12 @@ __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float
     float adv[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        if (PERIODIC) {
+        if (PAD == PDEC_MODE_CIRCULAR) {
             const unsigned bF = (unsigned)S.bi[k] & 127u, bC = (unsigned)(S.bi[k] + 1) & 127u;
+            S.offF[k] = bF + (bF & 3u) * 127u;
+            S.offC[k] = bC + (bC & 3u) * 127u;
+        } else if (PAD == PDEC_MODE_REPLICATE) {
+            const unsigned bF = (unsigned)min(max(S.bi[k], 0), 127), bC = (unsigned)min(max(S.bi[k], -1), 126) + 1u;
             S.offF[k] = bF + (bF & 3u) * 127u;
             S.offC[k] = bC + (bC & 3u) * 127u;
         } else {
@@ -111,14 +116,14 @@ __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float
         S.du[k] = tc - tf;
     }
     float left, right;
-    if (PERIODIC) {                                                    // circular padding (nd.py:271-283)
+    if (PAD == PDEC_MODE_CIRCULAR) {                                   // circular padding (nd.py:271-283)
         left = __shfl_sync(PDEC_FULL_MASK, adv[3], (lane + 31) & 31);
         right = __shfl_sync(PDEC_FULL_MASK, adv[0], (lane + 1) & 31);
     } else {
         left = __shfl_up_sync(PDEC_FULL_MASK, adv[3], 1);
         right = __shfl_down_sync(PDEC_FULL_MASK, adv[0], 1);
-        if (lane == 0) left = 0.0f;                                    // zero padding of the 'constant' field
-        if (lane == 31) right = 0.0f;
+        if (lane == 0) left = PAD == PDEC_MODE_REPLICATE ? adv[0] : 0.0f;      // edge cell repeated / zero padding
+        if (lane == 31) right = PAD == PDEC_MODE_REPLICATE ? adv[3] : 0.0f;
     }
     const float2 a01 = f2(adv[0], adv[1]), a23 = f2(adv[2], adv[3]), mid = f2(adv[1], adv[2]);
     const float2 m2 = f2(-2.0f, -2.0f), c2v = f2(p.c, p.c);
@@ -135,18 +140,18 @@ __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float
 
 // adjoint of one step.  h = -(dL/d step output) on entry (the caller keeps the sign of the residual gradient); returns dL/d(step
 // input) in (gin01, gin23).  The accumulator row's cell words are all-zero on entry and again on exit.
-template <bool PERIODIC>
+template <int PAD>
 __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, float2 h01, float2 h23, float* sacc, float* mine_acc, int lane,
                                               float2& gin01, float2& gin23) {
     float hl, hr;
-    if (PERIODIC) {
+    if (PAD == PDEC_MODE_CIRCULAR) {
         hl = __shfl_sync(PDEC_FULL_MASK, h23.y, (lane + 31) & 31);
         hr = __shfl_sync(PDEC_FULL_MASK, h01.x, (lane + 1) & 31);
-    } else {
+    } else {                                                           // the stencil matrix is symmetric for every padding
         hl = __shfl_up_sync(PDEC_FULL_MASK, h23.y, 1);
         hr = __shfl_down_sync(PDEC_FULL_MASK, h01.x, 1);
-        if (lane == 0) hl = 0.0f;
-        if (lane == 31) hr = 0.0f;
+        if (lane == 0) hl = PAD == PDEC_MODE_REPLICATE ? h01.x : 0.0f;
+        if (lane == 31) hr = PAD == PDEC_MODE_REPLICATE ? h23.y : 0.0f;
     }
     // transpose of the (symmetric, zero-padded) diffusion stencil
     const float2 mid = f2(h01.y, h23.x), m2 = f2(-2.0f, -2.0f), c2v = f2(p.c, p.c);
@@ -160,9 +165,15 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
     for (int k = 0; k < 4; ++k) {
         const int prev = __shfl_up_sync(PDEC_FULL_MASK, S.bi[k], 1);
         ordered = ordered && (lane == 0 || S.bi[k] > prev);
-        if (PERIODIC) {      // wrapped targets are distinct when the unwrapped floors also span less than one period
+        if (PAD == PDEC_MODE_CIRCULAR) {      // wrapped targets are distinct when the unwrapped floors also span less than one period
             const int first = __shfl_sync(PDEC_FULL_MASK, S.bi[k], 0);
             ordered = ordered && ((long long)S.bi[k] - first < 128);
+        }
+        if (PAD == PDEC_MODE_REPLICATE) {     // the CLAMPED floor taps and the clamped ceil taps must each increase strictly (one lane
+                                              // outside per instruction is harmless: its two taps coincide, but in different instructions)
+            const int cf = min(max(S.bi[k], 0), 127), cc = min(max(S.bi[k], -1), 126);
+            const int pf = __shfl_up_sync(PDEC_FULL_MASK, cf, 1), pc = __shfl_up_sync(PDEC_FULL_MASK, cc, 1);
+            ordered = ordered && (lane == 0 || (cf > pf && cc > pc));
         }
     }
 #ifdef F2_SKIP_SCATTER
@@ -200,16 +211,23 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
         // (match_any) and take turns by rank -- same sums in a fixed order, as many rounds as the largest group
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const bool inside = PERIODIC || (unsigned)S.bi[k] < 127u;
-            const unsigned peers = __match_any_sync(PDEC_FULL_MASK, PERIODIC ? (S.bi[k] & 127) : (inside ? S.bi[k] : -1 - lane));
+            const bool inside = PAD != PDEC_MODE_CONSTANT || (unsigned)S.bi[k] < 127u;
+            // group key of the floor tap; 'replicate' clamps floor and ceil taps separately, so the ceil taps get groups of their own
+            const int keyF = PAD == PDEC_MODE_CIRCULAR ? (S.bi[k] & 127) : (PAD == PDEC_MODE_REPLICATE ? min(max(S.bi[k], 0), 127) : (inside ? S.bi[k] : -1 - lane));
+            const unsigned peers = __match_any_sync(PDEC_FULL_MASK, keyF);
             const int rank = __popc(peers & ((1u << lane) - 1u));
-            for (int r = 0; __any_sync(PDEC_FULL_MASK, inside && rank >= r); ++r) {
+            int rankC = rank;
+            if (PAD == PDEC_MODE_REPLICATE) {
+                const unsigned peersC = __match_any_sync(PDEC_FULL_MASK, min(max(S.bi[k], -1), 126));
+                rankC = __popc(peersC & ((1u << lane) - 1u));
+            }
+            for (int r = 0; __any_sync(PDEC_FULL_MASK, inside && (rank >= r || rankC >= r)); ++r) {
                 if (inside && rank == r) {
                     float* af = ptr_off(sacc, S.offF[k]);
                     *af = fmaf(-q[k], w1[k], *af);
                 }
                 __syncwarp();
-                if (inside && rank == r) {
+                if (inside && rankC == r) {
 #ifdef F2_SPLIT
                     float* ac = ptr_off(sacc + F2_ROW, S.offF[k]);
 #else
@@ -250,7 +268,7 @@ __device__ __forceinline__ float sgn(float d) { return (d > 0.0f) ? 1.0f : ((d <
 // a pair; a pair below the range's / window's first one is walked "carry-only" (forward step only: its residual gradient w.r.t.
 // its target frame is the carry the first real pair needs); the step from the last frame of a row to the first frame of the
 // next one only closes the row.
-template <bool L1TERM, bool GSTRIDE, bool PERIODIC>
+template <bool L1TERM, bool GSTRIDE, int PAD>
 __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
                                                                             float2* partials, int T, int B, int t0, int t1, long long per_warp, int pieces,
                                                                             long long gf4, unsigned* done_counter, float* __restrict__ losses, float inv_B) {
@@ -329,7 +347,7 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
             if (remaining - (real ? 1 : 0) > 0) pre = __ldcs(s4 + offn);      // in flight during this step's arithmetic
 #endif
             if (!closing) {
-                step2_forward<PERIODIC>(p, X01, X23, u01, u23, su, mine, lane, v01, v23, S);
+                step2_forward<PAD>(p, X01, X23, u01, u23, su, mine, lane, v01, v23, S);
                 const float2 d01 = sub2(n01, v01), d23 = sub2(n23, v23);     // burgers.py:29
                 float2 gd01 = __fmul2_rn(d01, gl2v), gd23 = __fmul2_rn(d23, gl2v);
                 if (L1TERM) {
@@ -345,7 +363,7 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
 #if defined(F2_SKIP_ADJ)
                         gin01 = gd01; gin23 = gd23;
 #else
-                        step2_adjoint<PERIODIC>(p, S, gd01, gd23, sacc, mine_acc, lane, gin01, gin23);      // dL/dv = -gd
+                        step2_adjoint<PAD>(p, S, gd01, gd23, sacc, mine_acc, lane, gin01, gin23);      // dL/dv = -gd
 #endif
                         gin01 = __fadd2_rn(gin01, carry01);
                         gin23 = __fadd2_rn(gin23, carry23);
@@ -415,7 +433,7 @@ using namespace pdec;
 // partials must hold max(32, B * T) float2 (pdec_burgers_pair_loss_workspace_bytes).  [t0, t1) = window of pairs (0, T = all):
 // losses <- the window's share of (L2, L1); grad_s frames t0..t1-1 (and T when t1 == T) <- their complete gradient
 // grad_frame_stride: floats between consecutive frames of grad_s (0: dense, B * 128)
-int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int t0, int t1, int periodic, double dt, double viscosity,
+int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int t0, int t1, int pad_mode, double dt, double viscosity,
                                 float gl2, float gl1, long long grad_frame_stride, unsigned* done_counter, float* losses, cudaStream_t st) {
     if (t0 < 0 || t1 > T || t0 >= t1) return PDEC_ERR_INVALID_ARGUMENT;
     if (grad_frame_stride != 0 && (grad_frame_stride < (long long)B * 128 || (grad_frame_stride & 3))) return PDEC_ERR_INVALID_ARGUMENT;
@@ -437,7 +455,7 @@ int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials,
     while (pieces < F2_PIECES && per_warp / (pieces * 2) >= F2_PIECE_MIN) pieces *= 2;
     per_warp = (total + grid * F2_WARPS * pieces - 1) / (grid * F2_WARPS * pieces);
 #define F2_LAUNCH(L1, GS, PER) burgers_pair_loss_unit_kernel<L1, GS, PER><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB)
-#define F2_PICK(L1, GS) do { if (periodic) F2_LAUNCH(L1, GS, true); else F2_LAUNCH(L1, GS, false); } while (0)
+#define F2_PICK(L1, GS) do { if (pad_mode == PDEC_MODE_CIRCULAR) F2_LAUNCH(L1, GS, PDEC_MODE_CIRCULAR); else if (pad_mode == PDEC_MODE_REPLICATE) F2_LAUNCH(L1, GS, PDEC_MODE_REPLICATE); else F2_LAUNCH(L1, GS, PDEC_MODE_CONSTANT); } while (0)
     const bool strided = gf4 != (long long)B * 32;
     if (gl1 != 0.0f) { if (strided) F2_PICK(true, true); else F2_PICK(true, false); }
     else { if (strided) F2_PICK(false, true); else F2_PICK(false, false); }

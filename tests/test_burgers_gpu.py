@@ -228,13 +228,15 @@ def test_edge_cases_empty_batch_and_bad_arguments():
         ops.burgers_step(torch.zeros(1, 100000, device="cuda"), 0.1, 0.1)     # row does not fit shared memory
 
 
-def test_periodic_unit_kernel_forward_is_bit_exact_and_matches_v1(monkeypatch):
-    """The periodic ('circular') twin of the fused unit kernel: (1) the force loss of a trajectory produced by the general step kernel
+@pytest.mark.parametrize("mode_name", ["circular", "replicate"])
+def test_periodic_unit_kernel_forward_is_bit_exact_and_matches_v1(monkeypatch, mode_name):
+    """The periodic ('circular') and 'replicate' twins of the fused unit kernel: (1) the force loss of a trajectory produced by the general step kernel
     with the same mode is EXACTLY zero (the two forward steps agree bit for bit: wrapped taps, w1 = 1 - w0, wrapped stencil);
     (2) losses and gradients agree to rounding with the v1 kernel (PDEC_BURGERS_FAST_V1), on rows that cross the
     seam in both directions and on rows with shocks (folded back-trace: ranked scatter)."""
     ops = _ops()
-    from pde_control_b200._lib import MODE_CIRCULAR
+    from pde_control_b200 import _lib
+    MODE_CIRCULAR = _lib.MODE_CIRCULAR if mode_name == "circular" else _lib.MODE_REPLICATE      # the mode under test
     rng = np.random.RandomState(5)
     B, n, T = 600, 128, 6
     u0 = np.stack([R.gaussian_clash(1, n, rng)[0] for _ in range(B)]).astype(np.float32)
