@@ -184,7 +184,7 @@ class BurgersWorkload:
 class PeriodicBurgersWorkload(BurgersWorkload):
     """The same step on a periodic grid (the north star's wording; the reference's own Burgers scenes are not periodic)."""
     name = "burgers_pair_loss PERIODIC res=128 T=32 B=4096/gpu (config 2 with 'circular' extrapolation)"
-    ncu_traffic_bytes = None
+    ncu_traffic_bytes = 90.8e6      # as captured (read 70.9 MB + write 19.9 MB; the gradient's write-back outlives the launch): profiles/r1r_unit_periodic_summary.md
     mode = 2                        # PDEC_MODE_CIRCULAR
 
 
