@@ -109,7 +109,7 @@ __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float
         } else {
             const unsigned b = (unsigned)S.bi[k] < 127u ? (unsigned)S.bi[k] : (unsigned)F2_OUT;
             S.offF[k] = b + (b & 3u) * 127u;
-            S.offC[k] = b + ((b + 1u) & 3u) * 127u + 1u;
+            S.offC[k] = S.offF[k] + ((b & 3u) == 3u ? 4u - 384u : 128u);      // next cell: the next 32-word group, or word + 1 of group 0
         }
         const float tf = lds_off(su, S.offF[k]), tc = lds_off(su, S.offC[k]);     // (u[floor], u[floor + 1]) or (0, 0)
         adv[k] = __fadd_rn(__fmul_rn(tf, w1[k]), __fmul_rn(tc, w0[k]));           // tf_backend.py:491-497
@@ -290,7 +290,8 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
     float* mine = su + lane;
     float* mine_acc = sacc + lane;
     const float2 X01 = f2((float)(4 * lane) + 0.5f, (float)(4 * lane) + 1.5f), X23 = f2((float)(4 * lane) + 2.5f, (float)(4 * lane) + 3.5f);
-    const size_t f4 = (size_t)B * 32;                                 // float4 stride between frames
+    typedef unsigned off_t32;                                          // float4 offsets of s fit 32 bits (checked by the launcher): one-instruction address updates
+    const off_t32 f4 = (off_t32)B * 32;                               // float4 stride between frames
     const float4* s4 = reinterpret_cast<const float4*>(s) + lane;
     // frame (b, f) of the gradient lives at g4 + f * gf4 + b * 32: its frame stride may differ from s's (a row chunk written straight
     // into the caller's full-batch array, which may be page-locked host memory)
@@ -308,12 +309,12 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
         const long long P0 = ((long long)piece * n_warps + (long long)blockIdx.x * F2_WARPS + warp) * per_warp;
         const long long P1 = min(total, P0 + per_warp);
         if (P0 >= P1) break;
-        long long remaining = P1 - P0;                                 // real pairs still to do
+        int remaining = (int)(P1 - P0);                                // real pairs still to do
         int b = (int)(P0 / Cw);
         int lo = t0 + (int)(P0 - (long long)b * Cw);                   // first real pair of the current row
         const int row_first = g4 != nullptr && t0 > 0 ? t0 - 1 : t0;   // first frame walked in every later row
         int f = g4 != nullptr && lo > 0 ? lo - 1 : lo;                 // frame held in u (one early: carry-only pair)
-        size_t off = (size_t)f * f4 + (size_t)b * 32;                  // float4 offset of frame (b, f)
+        off_t32 off = (off_t32)f * f4 + (off_t32)b * 32;               // float4 offset of frame (b, f)
         float2 u01, u23, carry01 = f2(0.0f, 0.0f), carry23 = f2(0.0f, 0.0f), v01, v23;
         Step2 S;
         {
@@ -322,26 +323,26 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
         }
         // position of the frame after u (f <= t1 - 1 here, so it is in the same row), then the one after that is prefetched
         int fn = f + 1, bn = b;
-        size_t offn = off + f4;
+        off_t32 offn = off + f4;
         float4 pre = __ldcs(s4 + offn);                                // streamed: every frame is read once per range
 #ifdef F2_PF2
         // second load cursor, one frame further: two frames in flight per warp.  It walks the same frame sequence and may run past
         // the end of the range (never past the array): those frames are loaded and dropped
         int fl = fn, bl = bn;
-        size_t offl = offn;
-        if (fl == t1) { fl = row_first; bl += 1; offl = (size_t)row_first * f4 + (size_t)bl * 32; } else { fl += 1; offl += f4; }
+        off_t32 offl = offn;
+        if (fl == t1) { fl = row_first; bl += 1; offl = (off_t32)row_first * f4 + (off_t32)bl * 32; } else { fl += 1; offl += f4; }
         float4 pre2 = bl < B ? __ldcs(s4 + offl) : pre;
 #endif
         while (true) {
             const float2 n01 = f2(pre.x, pre.y), n23 = f2(pre.z, pre.w);
             const int fcur = fn, bcur = bn;                            // position of n
-            const size_t offcur = offn;
+            const off_t32 offcur = offn;
             const bool closing = bcur != b;                            // u = last frame of row b, n = first frame of row b + 1
             const bool real = !closing && fcur - 1 >= lo;              // (u, n) = pair fcur - 1 of row b, inside the range
-            if (fn == t1) { fn = row_first; bn += 1; offn = (size_t)row_first * f4 + (size_t)bn * 32; } else { fn += 1; offn += f4; }
+            if (fn == t1) { fn = row_first; bn += 1; offn = (off_t32)row_first * f4 + (off_t32)bn * 32; } else { fn += 1; offn += f4; }
 #ifdef F2_PF2
             pre = pre2;
-            if (fl == t1) { fl = row_first; bl += 1; offl = (size_t)row_first * f4 + (size_t)bl * 32; } else { fl += 1; offl += f4; }
+            if (fl == t1) { fl = row_first; bl += 1; offl = (off_t32)row_first * f4 + (off_t32)bl * 32; } else { fl += 1; offl += f4; }
             if (bl < B && remaining - (real ? 1 : 0) > 0) pre2 = __ldcs(s4 + offl);
 #else
             if (remaining - (real ? 1 : 0) > 0) pre = __ldcs(s4 + offn);      // in flight during this step's arithmetic
@@ -436,6 +437,7 @@ using namespace pdec;
 int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials, int T, int B, int t0, int t1, int pad_mode, double dt, double viscosity,
                                 float gl2, float gl1, long long grad_frame_stride, unsigned* done_counter, float* losses, cudaStream_t st) {
     if (t0 < 0 || t1 > T || t0 >= t1) return PDEC_ERR_INVALID_ARGUMENT;
+    if ((long long)B * 32 * ((long long)T + 1) >= (1LL << 32)) return 1;       // float4 offsets are 32-bit in the kernel: larger arrays (> 64 GB) go to the v1 kernel
     if (grad_frame_stride != 0 && (grad_frame_stride < (long long)B * 128 || (grad_frame_stride & 3))) return PDEC_ERR_INVALID_ARGUMENT;
     const long long gf4 = grad_frame_stride ? grad_frame_stride / 4 : (long long)B * 32;
     Unit2P p;
