@@ -6,6 +6,7 @@ The .so is git-ignored but travels to the GPU box with the gpurun snapshot.
 import os
 import subprocess
 import sys
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
@@ -13,7 +14,7 @@ LIB = os.path.join(HERE, "libpdec.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-          "-Xcompiler", "-fPIC", "--use_fast_math=false"]
+          "-Xcompiler", "-fPIC"]
 # per-file extra flags: the physics kernels reproduce the reference's fp32 operation order -> no FMA contraction
 SOURCES = {
     "abi.cu": [],
@@ -51,20 +52,31 @@ def build(force=False, verbose=False):
     objs = []
     headers = [os.path.join(CSRC, "pdec_common.cuh"), os.path.join(CSRC, "cg_reduce.cuh"),
                os.path.join(HERE, "..", "include", "pdec.h"), __file__]
+    jobs = []
     for src, flags in _sources():
         obj = os.path.join(objdir, os.path.basename(src) + ".o")
         objs.append(obj)
         if not force and not verbose and os.path.exists(obj) and all(
                 os.path.getmtime(d) <= os.path.getmtime(obj) for d in [src] + headers if os.path.exists(d)):
             continue        # object newer than its source and the shared headers
-        cmd = [NVCC] + [f for f in COMMON if f != "--use_fast_math=false"] + flags + ["-c", src, "-o", obj]
+        cmd = [NVCC] + COMMON + flags + ["-c", src, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
+        jobs.append((src, cmd))
+
+    def compile_one(job):
+        src, cmd = job
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))
-        if verbose:
-            print(r.stderr)
+        return src, r.stderr
+
+    # one nvcc per translation unit, all at once: the files are independent and the longest (cg.cu) bounds the build
+    with ThreadPoolExecutor(max_workers=max(1, min(len(jobs), os.cpu_count() or 1))) as pool:
+        for src, err in pool.map(compile_one, jobs):
+            if verbose:
+                print(src)
+                print(err)
     cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-lcudart"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
