@@ -34,6 +34,7 @@ extern "C" {
 #define PDEC_ERR_WORKSPACE_TOO_SMALL (-4)
 #define PDEC_ERR_NO_DEVICE (-5)
 #define PDEC_ERR_NOT_CONVERGED (-6)
+#define PDEC_ERR_STATIC_SCRATCH_TOO_SMALL (-7) /* pdec_burgers_pair_loss_static: B * T beyond PDEC_STATIC_MAX_PAIRS */
 
 /* boundary / extrapolation modes.  Reference: PF/physics/field/grid.py:240-249 (_pad_mode_str)
  * 'constant' -> zero outside, 'boundary' -> replicate, 'periodic' -> circular;
@@ -113,6 +114,21 @@ int pdec_burgers_pair_loss_window_strided(const float* s, float* grad_s, float* 
                                           double dt, double viscosity, float box_lower, float box_size, int substeps, int resubstep,
                                           float gl2, float gl1, long long grad_frame_stride, void* workspace, size_t workspace_bytes,
                                           void* stream);
+
+/* The same loss and gradient as pdec_burgers_pair_loss for callers that CANNOT ALLOCATE (code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The scratch (loss partials + the "CTAs done" counter) is a file-scope `static __device__` array of
+ * PDEC_STATIC_SCRATCH_BYTES inside the library (csrc/noalloc.cu); every GPU that loads libpdec.so holds it until the process
+ * exits.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine) and only enqueues on `stream`.
+ * Limit: B * T <= PDEC_STATIC_MAX_PAIRS frame pairs (= BASELINE config 2, s[33, 4096, 128]); beyond it the call enqueues nothing
+ * and returns PDEC_ERR_STATIC_SCRATCH_TOO_SMALL.  Every call on a device shares the one array, which keeps the last call's
+ * contents (the call clears the counter it needs at zero): calls that overlap on the GPU -- two streams, or two graph branches --
+ * RACE; serialise them.  Results are bit-identical to pdec_burgers_pair_loss on the same inputs. */
+#define PDEC_STATIC_MAX_PAIRS 131072
+#define PDEC_STATIC_SCRATCH_BYTES (PDEC_STATIC_MAX_PAIRS * 8 + 256)
+int pdec_burgers_pair_loss_static(const float* s, float* grad_s, float* losses, int T, int B, int n, int mode, double dt,
+                                  double viscosity, float box_lower, float box_size, int substeps, int resubstep, float gl2,
+                                  float gl1, void* stream);
 
 /* The same force loss fed from HOST arrays: what the reference does every optimisation step through
  * session.run(fetches, feed_dict) (src/control/control_training.py:113-142, PF/tf/session.py:30-70 copies every fed array to

@@ -10,6 +10,7 @@ LIB_PATH = os.environ.get("PDEC_LIB_PATH") or os.path.join(HERE, "libpdec.so")  
 
 MODE_CONSTANT, MODE_REPLICATE, MODE_CIRCULAR = 0, 1, 2
 EFFECT_NONE, EFFECT_GROW, EFFECT_ADD = 0, 1, 2
+STATIC_MAX_PAIRS = 131072          # PDEC_STATIC_MAX_PAIRS of include/pdec.h (pdec_burgers_pair_loss_static)
 
 # field extrapolation name -> resample/pad mode (reference: PF/physics/field/grid.py:240-249)
 MODE_OF_EXTRAPOLATION = {"constant": MODE_CONSTANT, "boundary": MODE_REPLICATE, "periodic": MODE_CIRCULAR}
@@ -39,6 +40,8 @@ _SIGNATURES = {
     "pdec_burgers_pair_loss": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _c.c_double,
                                            _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_float, _c.c_float, _P,
                                            _c.c_size_t, _P]),
+    "pdec_burgers_pair_loss_static": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _c.c_double,
+                                                  _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_float, _c.c_float, _P]),
     "pdec_burgers_pair_loss_window_supported": (_c.c_int, [_c.c_int, _c.c_int, _c.c_float, _c.c_float, _c.c_int]),
     "pdec_burgers_pair_loss_window": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double,
                                                   _c.c_double, _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_float, _c.c_float, _P,

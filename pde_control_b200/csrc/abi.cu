@@ -12,6 +12,7 @@ extern "C" const char* pdec_error_string(int code) {
         case PDEC_ERR_WORKSPACE_TOO_SMALL: return "workspace too small";
         case PDEC_ERR_NO_DEVICE: return "no CUDA device";
         case PDEC_ERR_NOT_CONVERGED: return "solver did not converge";
+        case PDEC_ERR_STATIC_SCRATCH_TOO_SMALL: return "B * T exceeds PDEC_STATIC_MAX_PAIRS, the capacity of the library's static scratch array";
         default: return "unknown error";
     }
 }
