@@ -1,9 +1,63 @@
-"""Hierarchical frame scheduling: decides in which order the OP networks predict frames and the solver executes steps.
+"""Frame schedules: in which order the OP networks predict frames and the solver executes steps.
 
-Same classes and call order as src/control/sequences.py:1-124 (PartitioningExecutor, SeqFrame, PartitionedSequence,
-StaggeredSequence, RefinedSequence, SkipSequence, LinearSequence), written around one explicit recursion `_run`.
+Behavioural contract (the executor call order) = src/control/sequences.py:40-124; the design is this repo's own.
+A schedule is DATA: `schedule(kind, n)` produces the flat list of events
+
+    ("partition", length, first_frame)      -> executor.partition(length, frames[first], frames[first + length], frames[centre])
+    ("execute", frame)                      -> executor.execute_step(frames[frame], frames[frame + 1], sequence)
+
+once, iteratively, from the step count alone (an explicit work stack, no recursion, no executor involved), and a sequence
+object is a frame table plus a replay loop over that list.  Because the plan exists before anything runs, callers can
+inspect it (`sequence.events`), count network evaluations per scope (`op_counts`), or capture the replay in a CUDA graph.
+The order is pinned event for event against the reference module in tests/test_host_api.py.
 """
 TYPE_UNKNOWN, TYPE_PLANNED, TYPE_REAL, TYPE_KEYFRAME = 0, 1, 2, 3
+
+PARTITION, EXECUTE = "partition", "execute"
+
+_STAGGERED, _REFINED, _SKIP, _LINEAR = "staggered", "refined", "skip", "linear"
+
+
+def schedule(kind, n):
+    """The event list of a length-n sequence of the given kind ('staggered', 'refined', 'skip', 'linear')."""
+    if kind == _LINEAR:
+        return [(EXECUTE, i) for i in range(n)]
+    if kind == _SKIP:
+        return [(PARTITION, n, 0)] if n > 1 else [(EXECUTE, 0)]
+    if kind not in (_STAGGERED, _REFINED):
+        raise ValueError("unknown schedule kind %r" % (kind,))
+    events = []
+    # work items, popped from the end: ("span", length, first, refresh) = resolve frames first .. first+length;
+    # ("emit", event) = an event deferred until the items pushed after it are done
+    todo = [("span", n, 0, False)]
+    while todo:
+        item = todo.pop()
+        if item[0] == "emit":
+            events.append(item[1])
+            continue
+        _, length, first, refresh = item
+        if length == 1:
+            events.append((EXECUTE, first))
+            continue
+        half = length // 2
+        events.append((PARTITION, length, first))
+        # pushed in reverse order of execution
+        todo.append(("span", half, first + half, refresh if kind == _REFINED else False))
+        if kind == _REFINED and refresh:
+            # the first half has been executed: its end frame is REAL now, so the targets ahead are predicted again from it
+            todo.append(("emit", (PARTITION, length, first + half)))
+            todo.append(("emit", (PARTITION, length, first + length)))
+        todo.append(("span", half, first, kind == _REFINED))
+    return events
+
+
+def op_counts(events):
+    """{length: number of OP_length evaluations} of an event list."""
+    counts = {}
+    for e in events:
+        if e[0] == PARTITION:
+            counts[e[1]] = counts.get(e[1], 0) + 1
+    return counts
 
 
 class SeqFrame(object):
@@ -18,50 +72,53 @@ class SeqFrame(object):
 
 
 class PartitioningExecutor(object):
-    """Callback interface of a sequence; the base class only tracks frame types (and checks the protocol)."""
+    """Consumer of a schedule.  The base class only tracks the frame types and checks the protocol: a step starts from a
+    REAL (or key) frame, a prediction needs both ends at least PLANNED."""
 
     verbose = False
 
     def create_frame(self, index, step_count):
-        key = index in (0, step_count)
-        return SeqFrame(index, TYPE_KEYFRAME if key else TYPE_UNKNOWN)
+        return SeqFrame(index, TYPE_KEYFRAME if index in (0, step_count) else TYPE_UNKNOWN)
 
     def execute_step(self, initial_frame, target_frame, sequence):
         if self.verbose:
-            print("Execute -> %d" % (initial_frame.index + 1))
-        assert initial_frame.type >= TYPE_REAL
-        target_frame.type = max(TYPE_REAL, target_frame.type)
+            print("Execute -> %d" % target_frame.index)
+        assert initial_frame.type >= TYPE_REAL, "step from a frame that has not been simulated"
+        if target_frame.type < TYPE_REAL:
+            target_frame.type = TYPE_REAL
 
     def partition(self, n, initial_frame, target_frame, center_frame):
         if self.verbose:
-            print("Partition length %d sequence (from %d to %d) at frame %d" % (n, initial_frame.index, target_frame.index, center_frame.index))
-        assert initial_frame.type != TYPE_UNKNOWN and target_frame.type != TYPE_UNKNOWN
+            print("Partition length %d sequence (from %d to %d) at frame %d"
+                  % (n, initial_frame.index, target_frame.index, center_frame.index))
+        assert TYPE_UNKNOWN not in (initial_frame.type, target_frame.type), "prediction between unknown frames"
         center_frame.type = TYPE_PLANNED
 
 
 class PartitionedSequence(object):
+    """Frame table + replay of a precomputed schedule."""
+
+    kind = None         # set by the subclasses
+
     def __init__(self, step_count, executor):
-        self.step_count, self.executor = step_count, executor
+        self.step_count = step_count
+        self.executor = executor
+        self.events = schedule(self.kind, step_count)
         self._frames = [executor.create_frame(i, step_count) for i in range(step_count + 1)]
+        self._keep(self._frames)
+
+    def _keep(self, frames):
+        """Hook: drop the frames a schedule never touches."""
 
     def execute(self):
-        self.partition_execute(self.step_count, 0)
-
-    def partition_execute(self, n, start_frame_index, **kwargs):
-        if n == 1:
-            self.leaf_execute(self._frames[start_frame_index], self._frames[start_frame_index + 1], **kwargs)
-        else:
-            self.branch_execute(n, start_frame_index, **kwargs)
-
-    def leaf_execute(self, start_frame, end_frame, **kwargs):
-        self.executor.execute_step(start_frame, end_frame, self)
-
-    def branch_execute(self, n, start_frame_index, **kwargs):
-        raise NotImplementedError()
-
-    def partition(self, n, start_frame_index):
-        f = self._frames
-        self.executor.partition(n, f[start_frame_index], f[start_frame_index + n], f[start_frame_index + n // 2])
+        frames, executor = self._frames, self.executor
+        for event in self.events:
+            if event[0] == EXECUTE:
+                i = event[1]
+                executor.execute_step(frames[i], frames[i + 1], self)
+            else:
+                _, length, first = event
+                executor.partition(length, frames[first], frames[first + length], frames[first + length // 2])
 
     def __getitem__(self, item):
         return self._frames[item]
@@ -74,46 +131,26 @@ class PartitionedSequence(object):
 
 
 class StaggeredSequence(PartitionedSequence):
-    """Predict the centre, then fully resolve the first half before touching the second."""
-
-    def branch_execute(self, n, start_frame_index, **kwargs):
-        half = n // 2
-        self.partition(n, start_frame_index)
-        for offset in (0, half):
-            self.partition_execute(half, start_frame_index + offset)
+    """Predict the centre, resolve the first half completely, then the second half."""
+    kind = _STAGGERED
 
 
 class RefinedSequence(PartitionedSequence):
-    """Like Staggered, but after executing a first half the targets ahead are re-predicted from the REAL state."""
-
-    def branch_execute(self, n, start_frame_index, update_target=False, **kwargs):
-        half = n // 2
-        self.partition(n, start_frame_index)
-        self.partition_execute(half, start_frame_index, update_target=True)
-        if update_target:
-            for start in (start_frame_index + n, start_frame_index + half):
-                self.partition(n, start)
-        self.partition_execute(half, start_frame_index + half, update_target=update_target)
+    """Staggered, plus: once a first half has been simulated, the predictions ahead are redone from the real state."""
+    kind = _REFINED
 
 
 class SkipSequence(PartitionedSequence):
-    """Only the centre frame is predicted (supervised OP training without the solver)."""
+    """Only the centre frame is predicted, nothing is simulated (supervised OP training)."""
+    kind = _SKIP
 
-    def __init__(self, sequence_length, executor):
-        PartitionedSequence.__init__(self, sequence_length, executor)
-        centre = sequence_length // 2
-        self._frames = [f if i in (0, centre, sequence_length) else None for i, f in enumerate(self._frames)]
-
-    def branch_execute(self, n, start_frame_index, **kwargs):
-        self.partition(n, start_frame_index)
+    def _keep(self, frames):
+        kept = (0, self.step_count // 2, self.step_count)
+        for i in range(len(frames)):
+            if i not in kept:
+                frames[i] = None
 
 
 class LinearSequence(PartitionedSequence):
     """No prediction: the solver steps frame by frame towards the final target."""
-
-    def execute(self):
-        for a, b in zip(self._frames[:-1], self._frames[1:]):
-            self.leaf_execute(a, b)
-
-    def branch_execute(self, n, start_frame_index, **kwargs):
-        raise AssertionError()
+    kind = _LINEAR
