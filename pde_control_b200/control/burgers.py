@@ -16,11 +16,18 @@ from .pde_base import PDE
 
 class BurgersPDE(PDE):
 
-    def __init__(self, domain, viscosity, dt):
+    def __init__(self, domain, viscosity, dt, periodic_diffusion="fft"):
+        """periodic_diffusion: how the force loss diffuses on a PERIODIC domain.  'fft' (default) = what Burgers.step does there, as
+        in the reference (diffuse switches to its spectral branch on periodic fields, PF/physics/field/util.py:30-37), so the loss
+        equals sum_t l2(s[t+1] - Burgers().step(s[t])).  'stencil' = opt-in extension: the wrapped explicit 3-point stencil, all
+        pairs in the one fused kernel launch (the north star's "explicit viscosity diffusion on a periodic 1D grid"); it is NOT
+        the reference's periodic step.  Non-periodic domains always use the explicit stencil, like the reference."""
         PDE.__init__(self)
+        assert periodic_diffusion in ("fft", "stencil")
         self.domain = domain
         self.viscosity = viscosity
         self.dt = dt
+        self.periodic_diffusion = periodic_diffusion
 
     def create_pde(self, world, control_trainable, constant_prediction_offset):
         world.reset(world.batch_size, add_default_objects=False)
@@ -34,6 +41,16 @@ class BurgersPDE(PDE):
     def total_force_loss(self, states):
         v0 = states[0].burgers.velocity
         frames = torch.stack([s.burgers.velocity.tensor for s in states])        # [T+1, B, N]
+        if v0.extrapolation == "periodic" and self.periodic_diffusion == "fft":
+            from ..physics.burgers import fourier_diffuse
+            T, B, N = frames.shape[0] - 1, frames.shape[1], frames.shape[2]
+            # all pairs at once: circular advection by the kernel (viscosity 0 adds exactly 0), spectral diffusion with cuFFT
+            advected = ops.burgers_step(frames[:-1].reshape(T * B, N), self.dt, 0.0, lower=float(v0.box.lower[0]),
+                                        size=float(v0.box.size[0]), mode=MODE_OF_EXTRAPOLATION[v0.extrapolation])
+            stepped = fourier_diffuse(advected, float(self.dt) * float(self.viscosity), float(v0.dx[0]))
+            d = frames[1:].reshape(T * B, N) - stepped
+            self.scalars["Total Force"] = d.detach().abs().sum() / B
+            return (d ** 2).sum() / 2 / B
         l2, l1 = ops.burgers_pair_loss(frames, self.dt, self.viscosity, lower=float(v0.box.lower[0]), size=float(v0.box.size[0]),
                                        mode=MODE_OF_EXTRAPOLATION[v0.extrapolation], substeps=1)
         self.scalars["Total Force"] = l1

@@ -32,14 +32,16 @@ class IncompressibleFluidPDE(PDE):
         return initial_worldstate.state_replaced(density_pred)
 
     def target_matching_loss(self, target_state, actual_state):
-        """l1 of |fft(diff)|^2 weighted by a Gaussian in frequency space (incompressible_flow.py:23-29)."""
+        """l1 of |fft(diff)|^2 weighted in frequency space (incompressible_flow.py:23-29).  `math.fftfreq(shape)` is in 'vector'
+        mode (nd.py:317-323): k has one channel per axis, the Gaussian is taken per component and l1_loss sums both channels
+        against the one-channel power spectrum -- the weight of mode (ky, kx) is G(ky) + G(kx), a cross, not G(ky) * G(kx)."""
         diff = target_state.density.data - actual_state.density.data
         f = torch.fft.fft2(diff[..., 0].to(torch.complex64))
-        power = f.real ** 2 + f.imag ** 2
+        power = f.imag ** 2 + f.real ** 2
         ky = torch.fft.fftfreq(diff.shape[1], device=diff.device)
         kx = torch.fft.fftfreq(diff.shape[2], device=diff.device)
-        k2 = ky[:, None] ** 2 + kx[None, :] ** 2
-        weights = torch.exp(-0.5 * k2 / 0.01 ** 2)
+        gauss = lambda k: torch.exp(-0.5 * k ** 2 / 0.01 ** 2)
+        weights = gauss(ky)[:, None] + gauss(kx)[None, :]
         return (power * weights).abs().sum() / diff.shape[0]
 
     def total_force_loss(self, states):

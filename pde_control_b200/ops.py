@@ -88,10 +88,10 @@ class _BurgersPairLoss(torch.autograd.Function):
     @staticmethod
     def forward(ctx, s, mode, dt, viscosity, lower, size, substeps, resubstep):
         _req_cuda(s)
+        need_grad = ctx.needs_input_grad[0]       # not s.requires_grad: forward runs with grad mode off and _c() may copy (non-contiguous s)
         s = _c(s)
         T1, B, n = s.shape
         T = T1 - 1
-        need_grad = s.requires_grad
         losses = torch.empty(2, device=s.device, dtype=torch.float32)
         L = _lib.lib()
         ws_bytes = L.pdec_burgers_pair_loss_workspace_bytes(B, n, T)

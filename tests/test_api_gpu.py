@@ -209,6 +209,53 @@ def test_periodic_burgers_takes_the_fft_diffusion_branch():
         assert rel_err(u.velocity.data[..., 0].cpu(), g["frames"][k]) < (1e-5 if k == 1 else 1e-4)
 
 
+def test_periodic_total_force_loss_equals_residuals_of_burgers_step():
+    """on a periodic domain BurgersPDE.total_force_loss must use the step Burgers.step uses there (FFT diffusion,
+    util.py:30-37): loss == sum_t l2(s[t+1] - Burgers().step(s[t])), zero on a trajectory produced by that step, gradient vs autograd
+    of the restated expression.  The fused wrapped-stencil kernel stays available as an explicit opt-in and differs."""
+    from pde_control_b200.physics import Domain, BurgersVelocity, Burgers, PERIODIC, box, StateCollection
+    from pde_control_b200.control import BurgersPDE
+    from pde_control_b200.physics.burgers import fourier_diffuse
+    from pde_control_b200 import ops, _lib
+    g = np.load(os.path.join(GOLDEN, "burgers_periodic.npz"))
+    B, N = g["frames"].shape[1:]
+    nu, dt = float(g["viscosity"]), float(g["dt"])
+    dom = Domain([N], boundaries=PERIODIC, box=box[0:1])
+    pde = BurgersPDE(dom, nu, dt)
+
+    def states_of(frames):
+        return [StateCollection([BurgersVelocity(dom, velocity=f[..., None], viscosity=nu, batch_size=B, name="burgers")]) for f in frames]
+
+    # (1) a trajectory made by the repo's own periodic step has zero implied force
+    u = BurgersVelocity(dom, velocity=g["frames"][0][..., None], viscosity=nu, batch_size=B, name="burgers")
+    traj = [u]
+    for _ in range(3):
+        traj.append(Burgers().step(traj[-1], dt=dt))
+    frames = [t.velocity.tensor for t in traj]
+    scale = float(sum((f ** 2).sum() for f in frames))
+    loss = pde.total_force_loss(states_of(frames))
+    assert float(loss) <= 1e-10 * scale
+    # (2) on arbitrary frames: == the sum of the residuals of Burgers().step, and the gradient == autograd of that expression
+    rng = np.random.RandomState(5)
+    noisy = [torch.tensor(g["frames"][k] + 0.05 * rng.randn(B, N).astype(np.float32), device="cuda", requires_grad=True) for k in range(4)]
+    loss = pde.total_force_loss(states_of(noisy))
+    loss.backward()
+    ref_frames = [f.detach().clone().requires_grad_(True) for f in noisy]
+    expected = 0
+    for a, b in zip(ref_frames[:-1], ref_frames[1:]):
+        stepped = Burgers().step(BurgersVelocity(dom, velocity=a[..., None], viscosity=nu, batch_size=B), dt=dt).velocity.tensor
+        expected = expected + ((b - stepped) ** 2).sum() / 2 / B
+    expected.backward()
+    assert abs(float(loss) - float(expected)) <= 1e-5 * float(expected)
+    for a, b in zip(noisy, ref_frames):
+        assert rel_err(a.grad.cpu(), b.grad.cpu()) < 1e-4
+    assert float(pde.scalars["Total Force"]) > 0
+    # (3) the opt-in wrapped-stencil variant is a different (explicit) diffusion: close, not equal
+    stencil = BurgersPDE(dom, nu, dt, periodic_diffusion="stencil").total_force_loss(states_of([f.detach() for f in noisy]))
+    assert abs(float(stencil) - float(expected)) > 1e-6 * float(expected)
+    assert abs(float(stencil) - float(expected)) < 0.2 * float(expected)
+
+
 @pytest.mark.parametrize("bd", ["open", "closed"])
 def test_fourier_solver_and_solver_chain(bd):
     """FourierSolver == the reference's math.fourier_poisson; FourierSolver() & SparseCG() (the reference's TF default chain,

@@ -217,3 +217,49 @@ def test_upsample2x_1d_matches_aten_linear_and_the_reference_weights():
     assert o.shape == (2, 128, 1)
     o.sum().backward()
     assert all(q.grad is not None for q in net.parameters())
+
+
+def _fluid_target_loss_inputs():
+    rng = np.random.RandomState(11)
+    a = rng.rand(3, 12, 16, 1).astype(np.float32)
+    b = rng.rand(3, 12, 16, 1).astype(np.float32)
+    return a, b
+
+
+def _fluid_target_loss_mine(a, b):
+    dom = P.Domain([12, 16])
+    pde = C.IncompressibleFluidPDE(dom, 1.0)
+    mk = lambda x: P.StateCollection([P.CenteredGrid(torch.tensor(x), box=dom.box, name="density")])
+    return float(pde.target_matching_loss(mk(a), mk(b)))
+
+
+def test_fluid_target_matching_loss_cross_shaped_weights():
+    """incompressible_flow.py:23-29 restated in NumPy: fftfreq in 'vector' mode gives one Gaussian per axis, l1_loss sums the two
+    channels -> weight G(ky) + G(kx) (the product G(ky) G(kx) is a different objective)."""
+    a, b = _fluid_target_loss_inputs()
+    diff = (a - b)[..., 0].astype(np.complex64)
+    f = np.fft.fft2(diff)
+    power = f.imag ** 2 + f.real ** 2
+    k = np.stack(np.meshgrid(np.fft.fftfreq(12), np.fft.fftfreq(16), indexing="ij"), -1).astype(np.float32)
+    w = np.exp(-0.5 * k ** 2 / 0.01 ** 2)                                  # [ny, nx, 2]
+    expected = np.abs(power[..., None] * w[None]).sum() / 3
+    mine = _fluid_target_loss_mine(a, b)
+    assert abs(mine - expected) <= 1e-5 * expected
+    product = np.abs(power * w[..., 0] * w[..., 1]).sum() / 3
+    assert abs(product - expected) > 0.1 * expected                         # the two weightings really differ on this input
+
+
+@pytest.mark.reference
+def test_fluid_target_matching_loss_vs_live_reference_math():
+    """The same expression evaluated with the reference's own math.fft / math.fftfreq / math.l1_loss (NumPy backend)."""
+    from oracle import ref_shim
+    flow = ref_shim.flow()
+    math = flow.math
+    a, b = _fluid_target_loss_inputs()
+    diff = a - b
+    diff_fft = math.fft(diff)
+    psq = math.imag(diff_fft) ** 2 + math.real(diff_fft) ** 2              # psquare, PF/physics/schroedinger.py:34-35
+    k = math.fftfreq(diff.shape[1:-1])
+    expected = float(math.l1_loss(psq * math.exp(-0.5 * k ** 2 / 0.01 ** 2)))
+    mine = _fluid_target_loss_mine(a, b)
+    assert abs(mine - expected) <= 1e-5 * abs(expected)
