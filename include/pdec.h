@@ -243,6 +243,25 @@ int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p, int* iter
                        int closed, float accuracy, int max_iterations, int stop_mode, void* workspace, size_t workspace_bytes,
                        void* stream);
 
+/* The WHOLE pressure projection in one launch (divergence_free, PF/physics/fluid.py:214-243 = with_hard_boundary_conditions
+ * solver_api.py:111-121 -> StaggeredGrid.divergence staggered_grid.py:201-209 -> poisson_solve / SparseCG sparse.py:73-111 ->
+ * p *= dx, velocity -= mask * gradient(p) fluid.py:240-242) for grids up to 128 x 128 without obstacles: the on-chip CG of
+ * pdec_cg_poisson_2d (one CTA per batch element, zero initial guess, per-element stop rule) forms its right-hand side from the
+ * staggered field in its prologue and writes the corrected field in its epilogue, so the divergence and the pressure never make
+ * a round trip through HBM and the two stencil launches around the solve disappear.  Bit-identical to the composition
+ * pdec_mask_divergence_2d_fwd -> pdec_cg_poisson_2d -> pdec_subtract_pressure_gradient_2d_fwd.
+ * p [B,ny,nx] and div [B,ny,nx] are optional outputs (NULL: not stored); iterations / residual as pdec_cg_poisson_2d.
+ * _bwd is the adjoint of the whole triple (TF autodiff of those ops + the registered CG gradient sparse.py:93-94): given
+ * dL/dv' (and optionally the upstream dL/dp, dL/ddiv, else NULL) it writes dL/dv, running the same CG on the symmetric matrix.
+ * Larger grids: pdec_project_2d_supported() == 0 and the calls return PDEC_ERR_UNSUPPORTED_SIZE; compose the three entry points. */
+int pdec_project_2d_supported(int ny, int nx);
+int pdec_project_2d_fwd(const float* vy, const float* vx, float* vy_out, float* vx_out, float* p, float* div, int* iterations,
+                        float* residual, int B, int ny, int nx, int closed, float size_y, float size_x, float accuracy,
+                        int max_iterations, void* stream);
+int pdec_project_2d_bwd(const float* g_vy_out, const float* g_vx_out, const float* g_p, const float* g_div, float* g_vy, float* g_vx,
+                        int* iterations, float* residual, int B, int ny, int nx, int closed, float size_y, float size_x,
+                        float accuracy, int max_iterations, void* stream);
+
 /* The stencil of a domain with obstacles from its cell mask (replaces the LaplaceMatrix op, PF/tf/cuda/src/laplace_op.cc:10-17, and
  * PoissonDomain's mask logic, solver_api.py:51-121): active [ny*nx] floats (1 fluid, 0 obstacle) -> code [ny*nx] bytes as
  * pdec_cg_poisson_2d_masked reads them, and the face masks fy [(ny+1)*nx], fx [ny*(nx+1)] that multiply the velocity before the

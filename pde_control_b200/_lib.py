@@ -79,6 +79,11 @@ _SIGNATURES = {
     "pdec_cg_poisson_2d_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int]),
     "pdec_cg_poisson_2d": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _c.c_int, _c.c_int,
                                        _P, _c.c_size_t, _P]),
+    "pdec_project_2d_supported": (_c.c_int, [_c.c_int, _c.c_int]),
+    "pdec_project_2d_fwd": (_c.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _c.c_float,
+                                        _c.c_float, _c.c_int, _P]),
+    "pdec_project_2d_bwd": (_c.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _c.c_float,
+                                        _c.c_float, _c.c_int, _P]),
     "pdec_laplace_matrix_2d": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _P]),
     "pdec_cg_poisson_2d_masked": (_c.c_int, [_P, _P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _c.c_int, _c.c_int,
                                               _P, _c.c_size_t, _P]),

@@ -224,6 +224,153 @@ __global__ void __launch_bounds__(128) burgers_trajectory_bwd_kernel(BurgersP p,
     }
 }
 
+// =====================================================================================================
+// Latency-bound shape (BASELINE config 1: B = 8 rows, 32 sequential steps): ONE CTA PER ROW, ONE THREAD PER CELL.
+// With a warp per row a step is a chain of ~600 dependent warp instructions on one scheduler (10.7 us per step forward +
+// adjoint at n = 128).  Here the row's cells spread over n / 32 warps on all four schedulers: a thread keeps its cell in a
+// register, neighbours and gather taps come from a shared-memory copy of the row (ping-pong buffers, one block barrier per
+// stencil pass), frames are written / read straight from the owning thread (coalesced).  Same expressions, same operation order
+// (this file compiles with -fmad=false) => the forward is bit-identical to warp_burgers_fwd and to the pair-loss kernels.
+// IEEE divisions by box size and dx^2 become exact multiplications when those are powers of two (the unit box at n = 128).
+// The adjoint's transpose of the gather stays deterministic: every warp scatters its 32 cells into a PRIVATE shared row in a
+// fixed order (warp_ordered_scatter_add) and the rows are summed in warp order -- no float atomics.
+// =====================================================================================================
+struct CtaFast {
+    float inv_size, inv_dx2;       // used when the flags say the reciprocal is exact
+    int size_pow2, dx2_pow2;
+};
+
+__device__ __forceinline__ float cta_backtrace_xi(const BurgersP& p, const CtaFast& f, float x0, float u) {
+    const float x = x0 - u * p.dt;
+    const float local = f.size_pow2 ? (x - p.lower) * f.inv_size : (x - p.lower) / p.size;
+    return local * p.nf - 0.5f;
+}
+__device__ __forceinline__ float cta_div_dx2(const BurgersP& p, const CtaFast& f, float v) { return f.dx2_pow2 ? v * f.inv_dx2 : v / p.dx2; }
+
+template <int MODE>
+__global__ void __launch_bounds__(1024) burgers_trajectory_fwd_cta_kernel(BurgersP p, CtaFast f, const float* __restrict__ u0,
+                                                                          const float* __restrict__ force, float* __restrict__ frames,
+                                                                          int B, int nsteps, int store_all) {
+    extern __shared__ __align__(16) float smem[];
+    const int n = p.n, i = threadIdx.x, b = blockIdx.x;
+    const bool in = i < n;
+    float* su[2] = {smem, smem + p.nrow};
+    float* sa[2] = {smem + 2 * p.nrow, smem + 3 * p.nrow};
+    const size_t row = (size_t)b * n;
+    float u = in ? u0[row + i] : 0.0f;
+    const float fo = (in && p.effect_mode != PDEC_EFFECT_NONE) ? force[row + i] : 0.0f;
+    const float x0 = in ? cell_center_local(i, n) * p.size + p.lower : 0.0f;
+    if (in) su[0][i] = u;
+    __syncthreads();
+    for (int t = 0; t < nsteps; ++t) {
+        const float* cur = su[t & 1];
+        float v = 0.0f;
+        if (in) {
+            const float xi = cta_backtrace_xi(p, f, x0, u);
+            int fi, ci;
+            float w0, w1;
+            interp_setup<MODE>(xi, n, fi, ci, w0, w1);
+            v = cur[fi] * w1 + cur[ci] * w0;
+        }
+        if (p.resubstep) {          // NumPy semantics: every substep sees the updated field
+            for (int k = 0; k < p.substeps; ++k) {
+                float* buf = sa[k & 1];
+                if (in) buf[i] = v;
+                __syncthreads();
+                if (in) v = v + p.a * cta_div_dx2(p, f, lap_raw<MODE>(buf, i, n));
+            }
+        } else {                    // TF semantics: the same laplacian added `substeps` times
+            if (in) sa[0][i] = v;
+            __syncthreads();
+            if (in) {
+                const float lap = cta_div_dx2(p, f, lap_raw<MODE>(sa[0], i, n));
+                for (int k = 0; k < p.substeps; ++k) v = v + p.a * lap;
+            }
+        }
+        if (in) {
+            if (p.effect_mode == PDEC_EFFECT_GROW) v = v + fo * p.dt;
+            else if (p.effect_mode == PDEC_EFFECT_ADD) v = v + fo;
+            u = v;
+            if (store_all) frames[((size_t)t * B + b) * n + i] = v;
+            else if (t == nsteps - 1) frames[row + i] = v;
+            su[(t + 1) & 1][i] = v;
+        }
+        __syncthreads();
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(1024) burgers_trajectory_bwd_cta_kernel(BurgersP p, CtaFast f, const float* __restrict__ u0,
+                                                                          const float* __restrict__ frames, const float* __restrict__ g_frames,
+                                                                          float* __restrict__ g_u0, float* __restrict__ g_force, int B, int nsteps,
+                                                                          int g_all) {
+    extern __shared__ __align__(16) float smem[];
+    const int n = p.n, i = threadIdx.x, b = blockIdx.x, lane = i & 31, w = i >> 5, nwarps = blockDim.x >> 5;
+    const bool in = i < n;
+    float* su = smem;
+    float* sg[2] = {smem + p.nrow, smem + 2 * p.nrow};
+    float* sacc = smem + 3 * p.nrow;                        // [nwarps][nrow] private scatter rows
+    float* mine = sacc + (size_t)w * p.nrow;
+    const size_t row = (size_t)b * n;
+    const float x0 = in ? cell_center_local(i, n) * p.size + p.lower : 0.0f;
+    const bool want_gf = (g_force != nullptr) && p.effect_mode != PDEC_EFFECT_NONE;
+    float gf = 0.0f;
+    float lam = in ? (g_all ? g_frames[((size_t)(nsteps - 1) * B + b) * n + i] : g_frames[row + i]) : 0.0f;
+    // the saved input row of step t and the extra gradient of frame t are fetched one step ahead
+    float u_next = in ? (nsteps == 1 ? u0[row + i] : frames[((size_t)(nsteps - 2) * B + b) * n + i]) : 0.0f;
+    float gx_next = (in && g_all && nsteps > 1) ? g_frames[((size_t)(nsteps - 2) * B + b) * n + i] : 0.0f;
+    for (int t = nsteps - 1; t >= 0; --t) {
+        const float u = u_next, gextra = gx_next;
+        if (in && t > 0) {
+            u_next = (t == 1) ? u0[row + i] : frames[((size_t)(t - 2) * B + b) * n + i];
+            gx_next = (g_all && t > 1) ? g_frames[((size_t)(t - 2) * B + b) * n + i] : 0.0f;
+        }
+        float g = lam;
+        if (want_gf) gf += (p.effect_mode == PDEC_EFFECT_GROW) ? g * p.dt : g;
+        // diffusion adjoint: the 3-point stencil matrix is symmetric for all three pad modes (same expression as warp_burgers_bwd)
+        const int passes = p.resubstep ? p.substeps : 1;
+        const float ka = p.resubstep ? p.a : p.a * (float)p.substeps;
+        for (int k = 0; k < passes; ++k) {
+            float* buf = sg[k & 1];
+            if (in) buf[i] = g;
+            if (k == 0 && in) su[i] = u;                    // the saved row rides on the first barrier
+            __syncthreads();
+            if (in) {
+                const float up = row_at<MODE>(buf, i + 1, n), lo = row_at<MODE>(buf, i - 1, n);
+                g = g + (cta_div_dx2(p, f, ka * up) + cta_div_dx2(p, f, ka * lo) - 2.0f * cta_div_dx2(p, f, ka * g));
+            }
+        }
+        // advection adjoint: transpose of the gather into this warp's private row + derivative through the back-trace
+        for (int q = lane; q < n; q += 32) mine[q] = 0.0f;
+        __syncwarp();
+        int fi = 0, ci = 0;
+        float w0 = 0.0f, w1 = 0.0f, gxi = 0.0f;
+        if (in) {
+            const float xi = cta_backtrace_xi(p, f, x0, u);
+            interp_setup<MODE>(xi, n, fi, ci, w0, w1);
+            gxi = g * (su[ci] - su[fi]) * p.dxi_du;
+        }
+        // 'constant': an out-of-range sample reads the same cell with weights +w and -w: exactly zero
+        const bool contributes = in && !(MODE == PDEC_MODE_CONSTANT && fi == ci);
+        warp_ordered_scatter_add(mine, fi, g * w1, contributes);
+        warp_ordered_scatter_add(mine, ci, g * w0, contributes);
+        __syncthreads();
+        if (in) {
+            float acc = 0.0f;
+            for (int q = 0; q < nwarps; ++q) acc += sacc[(size_t)q * p.nrow + i];      // fixed warp order
+            lam = acc + gxi;
+            if (g_all && t > 0) lam += gextra;
+        }
+        // no barrier needed here: the next step's first shared write (sg / su) is ordered behind this step's reads of sacc by its own
+        // barrier only for OTHER buffers -- sacc is rewritten (zeroed) before that barrier, so close the step explicitly
+        __syncthreads();
+    }
+    if (in) {
+        g_u0[row + i] = lam;
+        if (g_force != nullptr) g_force[row + i] = gf;
+    }
+}
+
 // ---- kernel: fused force loss + gradient over T frame pairs ------------------
 // One warp walks one batch row b through t = 0..T-1.  Every frame s[t,b,:] is read from HBM exactly once
 // (3-slot cp.async ring: current, next, prefetch) and every gradient row is written exactly once:
@@ -361,6 +508,25 @@ static int sm_count() {
     return sms > 0 ? sms : 148;
 }
 
+// one CTA per row / one thread per cell pays while every row's CTA is resident at once with room to spare (few rows: the
+// latency-bound regime); beyond that the warp-per-row kernels have the better throughput
+static bool cta_shape(int B, int n) {
+    const int warps = (n + 31) / 32;
+    return n <= 1024 && (long long)B * warps <= (long long)sm_count() * 8;
+}
+static bool is_pow2(float v) {
+    int e;
+    return v > 0.0f && frexpf(v, &e) == 0.5f && e > -100 && e < 100;
+}
+static CtaFast cta_fast(const BurgersP& p) {
+    CtaFast f;
+    f.size_pow2 = is_pow2(p.size) ? 1 : 0;
+    f.dx2_pow2 = is_pow2(p.dx2) ? 1 : 0;
+    f.inv_size = f.size_pow2 ? 1.0f / p.size : 0.0f;      // exact reciprocals: x / 2^k == x * 2^-k bit for bit (no overflow at these scales)
+    f.inv_dx2 = f.dx2_pow2 ? 1.0f / p.dx2 : 0.0f;
+    return f;
+}
+
 // grid for a warp-per-row kernel with `wpc` warps per CTA and `smem` bytes per CTA
 static int rows_grid(int B, int wpc, size_t smem) {
     const int ctas_needed = (B + wpc - 1) / wpc;
@@ -401,12 +567,24 @@ extern "C" int pdec_burgers_trajectory_fwd(const float* u0, const float* force, 
     if (B < 0 || nsteps < 1) return PDEC_ERR_INVALID_ARGUMENT;
     if (B == 0) return PDEC_OK;
     if (!u0 || !frames || (effect_mode != PDEC_EFFECT_NONE && !force)) return PDEC_ERR_INVALID_ARGUMENT;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cta_shape(B, n)) {          // few rows: one CTA per row, one thread per cell (latency-bound regime)
+        const CtaFast f = cta_fast(p);
+        const int threads = (n + 31) & ~31;
+        const size_t csmem = (size_t)4 * p.nrow * sizeof(float);
+#define LAUNCH_FWD_CTA(M) burgers_trajectory_fwd_cta_kernel<M><<<B, threads, csmem, st>>>(p, f, u0, force, frames, B, nsteps, store_all)
+        if (mode == PDEC_MODE_CONSTANT) LAUNCH_FWD_CTA(PDEC_MODE_CONSTANT);
+        else if (mode == PDEC_MODE_REPLICATE) LAUNCH_FWD_CTA(PDEC_MODE_REPLICATE);
+        else LAUNCH_FWD_CTA(PDEC_MODE_CIRCULAR);
+#undef LAUNCH_FWD_CTA
+        PDEC_CHECK_LAUNCH();
+        return PDEC_OK;
+    }
     const int wpc = pick_wpc(p.nrow, 5);
     if (wpc == 0) return PDEC_ERR_UNSUPPORTED_SIZE;
     const size_t smem = ((size_t)p.nrow * (1 + (size_t)wpc * 5)) * sizeof(float);
     const int vec4 = (n % 4 == 0) && aligned16(u0) && aligned16(frames) && (force == nullptr || aligned16(force));
     const int grid = rows_grid(B, wpc, smem);
-    cudaStream_t st = (cudaStream_t)stream;
 #define LAUNCH_FWD(M)                                                                                          \
     do {                                                                                                       \
         rc = set_smem(burgers_trajectory_fwd_kernel<M>, smem);                                                 \
@@ -431,13 +609,30 @@ extern "C" int pdec_burgers_trajectory_bwd(const float* u0, const float* frames,
     if (B < 0 || nsteps < 1) return PDEC_ERR_INVALID_ARGUMENT;
     if (B == 0) return PDEC_OK;
     if (!u0 || !g_frames || !g_u0 || (nsteps > 1 && !frames)) return PDEC_ERR_INVALID_ARGUMENT;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cta_shape(B, n)) {
+        const CtaFast f = cta_fast(p);
+        const int threads = (n + 31) & ~31;
+        const size_t csmem = (size_t)(3 + threads / 32) * p.nrow * sizeof(float);
+#define LAUNCH_BWD_CTA(M)                                                                                      \
+    do {                                                                                                       \
+        rc = set_smem(burgers_trajectory_bwd_cta_kernel<M>, csmem);                                            \
+        if (rc != PDEC_OK) return rc;                                                                          \
+        burgers_trajectory_bwd_cta_kernel<M><<<B, threads, csmem, st>>>(p, f, u0, frames, g_frames, g_u0, g_force, B, nsteps, g_all); \
+    } while (0)
+        if (mode == PDEC_MODE_CONSTANT) LAUNCH_BWD_CTA(PDEC_MODE_CONSTANT);
+        else if (mode == PDEC_MODE_REPLICATE) LAUNCH_BWD_CTA(PDEC_MODE_REPLICATE);
+        else LAUNCH_BWD_CTA(PDEC_MODE_CIRCULAR);
+#undef LAUNCH_BWD_CTA
+        PDEC_CHECK_LAUNCH();
+        return PDEC_OK;
+    }
     const int wpc = pick_wpc(p.nrow, 6);
     if (wpc == 0) return PDEC_ERR_UNSUPPORTED_SIZE;
     const size_t smem = ((size_t)p.nrow * (1 + (size_t)wpc * 6)) * sizeof(float);
     const int vec4 = (n % 4 == 0) && aligned16(u0) && aligned16(g_frames) && aligned16(g_u0) &&
                      (frames == nullptr || aligned16(frames)) && (g_force == nullptr || aligned16(g_force));
     const int grid = rows_grid(B, wpc, smem);
-    cudaStream_t st = (cudaStream_t)stream;
 #define LAUNCH_BWD(M)                                                                                          \
     do {                                                                                                       \
         rc = set_smem(burgers_trajectory_bwd_kernel<M>, smem);                                                 \

@@ -387,10 +387,29 @@ __device__ __forceinline__ void block_reduce_pair(float& a, float& b, float* red
     block_reduce_pair_end<WARPS>(a, b, red, second_is_max);
 }
 
-template <int WARPS, bool FULL, bool FUSED>
+// PROJ != 0: the whole pressure projection in this ONE launch (divergence_free, PF/physics/fluid.py:214-243).  The right-hand side
+// is formed from the staggered field in the prologue and the corrected field is written in the epilogue, so neither the divergence nor
+// the pressure makes a round trip through HBM and the two stencil launches around the solve disappear:
+//   PROJ_FWD: rhs = div(mask v)                      out = mask v - mask grad(x dx0) / dx       (F4 -> F5 -> F6)
+//   PROJ_BWD: rhs = grad^T(g) [+ add_rhs]            out = mask g + mask div^T(x [+ add_x])     (F6^T -> F5 -> F4^T; A symmetric)
+// Every expression keeps the operation order (and roundings: explicit _rn intrinsics, no contraction) of the stand-alone kernels
+// in fluid.cu, so the fused launch is bit-identical to the three-launch composition.
+constexpr int PROJ_NONE = 0, PROJ_FWD = 1, PROJ_BWD = 2;
+struct ProjArgs {
+    const float* in_y;      // [B, ny+1, nx]  v_y (fwd) / dL/dv'_y (bwd)
+    const float* in_x;      // [B, ny, nx+1]
+    float* out_y;           // [B, ny+1, nx]  v'_y (fwd) / dL/dv_y (bwd)
+    float* out_x;           // [B, ny, nx+1]
+    const float* add_rhs;   // bwd: upstream dL/dp or nullptr
+    const float* add_x;     // bwd: upstream dL/ddiv or nullptr
+    float* store_rhs;       // fwd: divergence output or nullptr
+    float dx0, dxy, dxx;    // p *= dx0 (fluid.py:240), gradient / dxy, / dxx (staggered_grid.py:219-231)
+};
+
+template <int WARPS, bool FULL, bool FUSED, int PROJ = PROJ_NONE>
 __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __restrict__ rhs, const float* __restrict__ guess, float* __restrict__ out,
                                                                  int* __restrict__ iters, float* __restrict__ resid, int ny, int nx, int closed,
-                                                                 float accuracy, int max_it) {
+                                                                 float accuracy, int max_it, const ProjArgs pa = ProjArgs()) {
     constexpr int ROWS = 8 * WARPS;
     extern __shared__ __align__(16) float smem_dyn[];
     __shared__ __align__(16) float redA[32], redB[32], red5[2][80];
@@ -410,10 +429,42 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
     for (int ky = 0; ky < 8; ++ky) drow[ky] = cf * ((i0 + ky == 0 ? 1.0f : 0.0f) + (i0 + ky == ny - 1 ? 1.0f : 0.0f));
     const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     for (int q = threadIdx.x; q < (2 * WARPS + 2) * 32; q += 32 * WARPS) sm_e[q] = zero4;
+    // staggered component bases of this batch element and the boundary-face mask (closed: solid boundary faces are 0)
+    // (recomputed in the epilogue instead of being kept live across the iteration loop, whose register budget is full)
+    auto fmask = [&](int idx, int n) -> float { return (closed && (idx == 0 || idx == n)) ? 0.0f : 1.0f; };
 #pragma unroll
     for (int ky = 0; ky < 8; ++ky) {
         float4 g4 = zero4, r4 = zero4;
-        if (FULL) {
+        if (PROJ != PROJ_NONE) {
+            float rv[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            const int i = i0 + ky;
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx) {
+                const int j = j0 + kx;
+                if (i < ny && j < nx) {
+                    if (!FULL) valid |= 1u << (ky * 4 + kx);
+                    const float* y = pa.in_y + (size_t)blockIdx.x * (ny + 1) * nx;
+                    const float* x = pa.in_x + (size_t)blockIdx.x * ny * (nx + 1);
+                    float v;
+                    if (PROJ == PROJ_FWD) {          // mask_divergence_fwd_kernel
+                        const float dy = __fsub_rn(__fmul_rn(y[(size_t)(i + 1) * nx + j], fmask(i + 1, ny)), __fmul_rn(y[(size_t)i * nx + j], fmask(i, ny)));
+                        const float dx = __fsub_rn(__fmul_rn(x[(size_t)i * (nx + 1) + j + 1], fmask(j + 1, nx)), __fmul_rn(x[(size_t)i * (nx + 1) + j], fmask(j, nx)));
+                        v = __fadd_rn(dy, dx);
+                        if (pa.store_rhs != nullptr) pa.store_rhs[base + (size_t)i * nx + j] = v;
+                    } else {                         // subtract_gradient_bwd_kernel, the g_p output (interior faces only)
+                        float acc = 0.0f;
+                        if (i >= 1) acc = __fsub_rn(acc, __fdiv_rn(y[(size_t)i * nx + j], pa.dxy));
+                        if (i + 1 < ny) acc = __fadd_rn(acc, __fdiv_rn(y[(size_t)(i + 1) * nx + j], pa.dxy));
+                        if (j >= 1) acc = __fsub_rn(acc, __fdiv_rn(x[(size_t)i * (nx + 1) + j], pa.dxx));
+                        if (j + 1 < nx) acc = __fadd_rn(acc, __fdiv_rn(x[(size_t)i * (nx + 1) + j + 1], pa.dxx));
+                        v = __fmul_rn(acc, pa.dx0);
+                        if (pa.add_rhs != nullptr) v = __fadd_rn(v, pa.add_rhs[base + (size_t)i * nx + j]);
+                    }
+                    rv[kx] = v;
+                }
+            }
+            r4 = make_float4(rv[0], rv[1], rv[2], rv[3]);
+        } else if (FULL) {
             r4 = *reinterpret_cast<const float4*>(rhs + base + (size_t)(i0 + ky) * nx + j0);
             if (guess != nullptr) g4 = *reinterpret_cast<const float4*>(guess + base + (size_t)(i0 + ky) * nx + j0);
         } else {
@@ -558,21 +609,79 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
             ++it;
         }
     }
+    if (PROJ == PROJ_NONE || out != nullptr) {
 #pragma unroll
-    for (int ky = 0; ky < 8; ++ky) {
-        const float4 x4 = sm_x[(i0 + ky) * 32 + tx];
-        if (FULL) {
-            *reinterpret_cast<float4*>(out + base + (size_t)(i0 + ky) * nx + j0) = x4;
-        } else {
-            const float xv[4] = {x4.x, x4.y, x4.z, x4.w};
+        for (int ky = 0; ky < 8; ++ky) {
+            const float4 x4 = sm_x[(i0 + ky) * 32 + tx];
+            if (FULL) {
+                *reinterpret_cast<float4*>(out + base + (size_t)(i0 + ky) * nx + j0) = x4;
+            } else {
+                const float xv[4] = {x4.x, x4.y, x4.z, x4.w};
 #pragma unroll
-            for (int kx = 0; kx < 4; ++kx)
-                if (valid & (1u << (ky * 4 + kx))) out[base + (size_t)(i0 + ky) * nx + j0 + kx] = xv[kx];
+                for (int kx = 0; kx < 4; ++kx)
+                    if (valid & (1u << (ky * 4 + kx))) out[base + (size_t)(i0 + ky) * nx + j0 + kx] = xv[kx];
+            }
         }
     }
     if (threadIdx.x == 0) {
         if (iters) iters[blockIdx.x] = it;
         if (resid) resid[blockIdx.x] = rmax;
+    }
+    if (PROJ != PROJ_NONE) {
+        // epilogue: the corrected staggered field from the solution, which is complete in shared memory after this barrier.
+        // A thread writes the faces on the low side of its cells; the owners of the last row / column also write face ny / nx.
+        __syncthreads();
+        const float* xs = reinterpret_cast<const float*>(sm_x);          // x(i, j) = xs[i * 128 + j]
+        const size_t base_y = (size_t)blockIdx.x * (ny + 1) * nx, base_x = (size_t)blockIdx.x * ny * (nx + 1);
+        const float* y = pa.in_y + base_y;
+        const float* x = pa.in_x + base_x;
+        auto sol = [&](int i, int j) -> float {
+            float v = xs[i * 128 + j];
+            if (PROJ == PROJ_BWD && pa.add_x != nullptr) v = __fadd_rn(v, pa.add_x[base + (size_t)i * nx + j]);
+            return v;
+        };
+        auto face_y = [&](int i, int j) {
+            const size_t o = (size_t)i * nx + j;
+            const float mk = fmask(i, ny);
+            float res;
+            if (PROJ == PROJ_FWD) {              // subtract_gradient_fwd_kernel: replicate pad -> boundary-face gradient 0
+                float gr = 0.0f;
+                if (i >= 1 && i < ny) gr = __fdiv_rn(__fsub_rn(__fmul_rn(sol(i, j), pa.dx0), __fmul_rn(sol(i - 1, j), pa.dx0)), pa.dxy);
+                res = __fsub_rn(__fmul_rn(y[o], mk), __fmul_rn(gr, mk));
+            } else {                             // subtract_gradient_bwd (g * mask) + mask_divergence_bwd ((lo - hi) * mask)
+                const float lo = i >= 1 ? sol(i - 1, j) : 0.0f, hi = i < ny ? sol(i, j) : 0.0f;
+                res = __fadd_rn(__fmul_rn(y[o], mk), __fmul_rn(__fsub_rn(lo, hi), mk));
+            }
+            pa.out_y[base_y + o] = res;
+        };
+        auto face_x = [&](int i, int j) {
+            const size_t o = (size_t)i * (nx + 1) + j;
+            const float mk = fmask(j, nx);
+            float res;
+            if (PROJ == PROJ_FWD) {
+                float gr = 0.0f;
+                if (j >= 1 && j < nx) gr = __fdiv_rn(__fsub_rn(__fmul_rn(sol(i, j), pa.dx0), __fmul_rn(sol(i, j - 1), pa.dx0)), pa.dxx);
+                res = __fsub_rn(__fmul_rn(x[o], mk), __fmul_rn(gr, mk));
+            } else {
+                const float lo = j >= 1 ? sol(i, j - 1) : 0.0f, hi = j < nx ? sol(i, j) : 0.0f;
+                res = __fadd_rn(__fmul_rn(x[o], mk), __fmul_rn(__fsub_rn(lo, hi), mk));
+            }
+            pa.out_x[base_x + o] = res;
+        };
+#pragma unroll
+        for (int ky = 0; ky < 8; ++ky) {
+            const int i = i0 + ky;
+            if (i >= ny) break;
+#pragma unroll
+            for (int kx = 0; kx < 4; ++kx) {
+                const int j = j0 + kx;
+                if (j >= nx) break;
+                face_y(i, j);
+                face_x(i, j);
+                if (i == ny - 1) face_y(ny, j);
+                if (j == nx - 1) face_x(i, nx);
+            }
+        }
     }
 }
 
@@ -959,8 +1068,60 @@ static int launch_block(const float* rhs, const float* guess, float* p, int* ite
                         : (full ? cg_block_kernel<WARPS, true, false> : cg_block_kernel<WARPS, false, false>);
     if (smem > 48 * 1024 && cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
         return PDEC_ERR_CUDA_LAUNCH;
-    kernel<<<B, 32 * WARPS, smem, st>>>(rhs, guess, p, iterations, residual, ny, nx, closed, accuracy, max_iterations);
+    kernel<<<B, 32 * WARPS, smem, st>>>(rhs, guess, p, iterations, residual, ny, nx, closed, accuracy, max_iterations, ProjArgs());
     return PDEC_OK;
+}
+
+// the fused projection (PROJ_FWD / PROJ_BWD) on the two-reduction loop, one CTA per batch element
+template <int WARPS, int PROJ>
+static int launch_block_proj(float* p, int* iterations, float* residual, int B, int ny, int nx, int closed, float accuracy, int max_iterations,
+                             const ProjArgs& pa, cudaStream_t st) {
+    const size_t smem = (size_t)(8 * WARPS * 32 + (2 * WARPS + 2) * 32) * sizeof(float4);
+    const bool full = ny == 8 * WARPS && nx == 128 && (p == nullptr || (reinterpret_cast<uintptr_t>(p) & 15) == 0);
+    auto kernel = full ? cg_block_kernel<WARPS, true, false, PROJ> : cg_block_kernel<WARPS, false, false, PROJ>;
+    if (smem > 48 * 1024 && cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return PDEC_ERR_CUDA_LAUNCH;
+    kernel<<<B, 32 * WARPS, smem, st>>>(nullptr, nullptr, p, iterations, residual, ny, nx, closed, accuracy, max_iterations, pa);
+    return PDEC_OK;
+}
+
+template <int PROJ>
+static int project_2d(float* p, int* iterations, float* residual, int B, int ny, int nx, int closed, float size_y, float size_x, float accuracy,
+                      int max_iterations, ProjArgs pa, void* stream) {
+    if (B < 0 || ny < 2 || nx < 2 || max_iterations < 0 || !(size_y > 0.0f) || !(size_x > 0.0f)) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!pa.in_y || !pa.in_x || !pa.out_y || !pa.out_x) return PDEC_ERR_INVALID_ARGUMENT;
+    if (ny > 128 || nx > 128) return PDEC_ERR_UNSUPPORTED_SIZE;          // larger grids: compose the stand-alone entry points
+    pa.dxy = (float)((double)size_y / ny);
+    pa.dxx = (float)((double)size_x / nx);
+    pa.dx0 = pa.dxy;
+    cudaStream_t st = (cudaStream_t)stream;
+    closed = closed ? 1 : 0;
+    int rc;
+    if (ny > 64) rc = launch_block_proj<16, PROJ>(p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, pa, st);
+    else if (ny > 32) rc = launch_block_proj<8, PROJ>(p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, pa, st);
+    else rc = launch_block_proj<4, PROJ>(p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, pa, st);
+    if (rc != PDEC_OK) return rc;
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+extern "C" int pdec_project_2d_supported(int ny, int nx) { return ny >= 2 && nx >= 2 && ny <= 128 && nx <= 128; }
+
+extern "C" int pdec_project_2d_fwd(const float* vy, const float* vx, float* vy_out, float* vx_out, float* p, float* div, int* iterations,
+                                   float* residual, int B, int ny, int nx, int closed, float size_y, float size_x, float accuracy,
+                                   int max_iterations, void* stream) {
+    ProjArgs pa = {};
+    pa.in_y = vy; pa.in_x = vx; pa.out_y = vy_out; pa.out_x = vx_out; pa.store_rhs = div;
+    return project_2d<PROJ_FWD>(p, iterations, residual, B, ny, nx, closed, size_y, size_x, accuracy, max_iterations, pa, stream);
+}
+
+extern "C" int pdec_project_2d_bwd(const float* g_vy_out, const float* g_vx_out, const float* g_p, const float* g_div, float* g_vy, float* g_vx,
+                                   int* iterations, float* residual, int B, int ny, int nx, int closed, float size_y, float size_x,
+                                   float accuracy, int max_iterations, void* stream) {
+    ProjArgs pa = {};
+    pa.in_y = g_vy_out; pa.in_x = g_vx_out; pa.out_y = g_vy; pa.out_x = g_vx; pa.add_rhs = g_p; pa.add_x = g_div;
+    return project_2d<PROJ_BWD>(nullptr, iterations, residual, B, ny, nx, closed, size_y, size_x, accuracy, max_iterations, pa, stream);
 }
 
 template <int THREADS, int CPT = 16>

@@ -619,10 +619,65 @@ def normalize_to(target, source, epsilon=1e-5):
     return _Normalize.apply(target, source, float(epsilon))
 
 
+class _Project(torch.autograd.Function):
+    """divergence_free (PF/physics/fluid.py:214-243) as ONE launch per direction: mask + divergence in the prologue of the on-chip CG,
+    pressure-gradient subtraction in its epilogue (pdec_project_2d_fwd / _bwd).  Outputs (v'_y, v'_x, p, div, iterations); the
+    backward launch is the adjoint of the whole triple with the second CG solve inside (sparse.py:93-94)."""
+
+    @staticmethod
+    def forward(ctx, vy, vx, closed, size_y, size_x, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations):
+        _req_cuda(vy, vx)
+        vy, vx = _c(vy), _c(vx)
+        B, ny, nx = vx.shape[0], vx.shape[1], vy.shape[2]
+        oy, ox = torch.empty_like(vy), torch.empty_like(vx)
+        p = torch.empty((B, ny, nx), device=vy.device, dtype=torch.float32)
+        div = torch.empty_like(p)
+        iters = torch.zeros(B, device=vy.device, dtype=torch.int32)
+        with torch.cuda.device(vy.device):
+            _call("pdec_project_2d_fwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(oy), _lib.ptr(ox), _lib.ptr(p), _lib.ptr(div), _lib.ptr(iters),
+                  None, B, ny, nx, int(closed), size_y, size_x, float(accuracy if accuracy is not None else 0.0), int(max_iterations),
+                  _lib.stream_ptr())
+        ctx.cfg = (B, ny, nx, int(closed), size_y, size_x, float(gradient_accuracy if gradient_accuracy is not None else 0.0),
+                   int(max_gradient_iterations))
+        ctx.mark_non_differentiable(iters)
+        # p and div are returned for inspection: when nothing downstream uses them backward gets None for their gradients
+        # (no zero tensors are materialised), which the kernel takes as "no upstream term"
+        ctx.set_materialize_grads(False)
+        return oy, ox, p, div, iters
+
+    @staticmethod
+    def backward(ctx, g_oy, g_ox, g_p, g_div, _gi):
+        B, ny, nx, closed, size_y, size_x, accuracy, max_it = ctx.cfg
+        dev = next(t.device for t in (g_oy, g_ox, g_p, g_div) if t is not None)
+        g_oy = torch.zeros((B, ny + 1, nx), device=dev) if g_oy is None else _c(g_oy)
+        g_ox = torch.zeros((B, ny, nx + 1), device=dev) if g_ox is None else _c(g_ox)
+        g_p = None if g_p is None else _c(g_p)
+        g_div = None if g_div is None else _c(g_div)
+        g_vy, g_vx = torch.empty_like(g_oy), torch.empty_like(g_ox)
+        with torch.cuda.device(g_oy.device):
+            _call("pdec_project_2d_bwd", _lib.ptr(g_oy), _lib.ptr(g_ox), _lib.ptr(g_p), _lib.ptr(g_div), _lib.ptr(g_vy), _lib.ptr(g_vx),
+                  None, None, B, ny, nx, closed, size_y, size_x, accuracy, max_it, _lib.stream_ptr())
+        return g_vy, g_vx, None, None, None, None, None, None, None
+
+
+
+def _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations):
+    b = _box(box, vx.shape[1], vy.shape[2])
+    ga = accuracy if gradient_accuracy is None else gradient_accuracy
+    gi = max_iterations if max_gradient_iterations is None else max_gradient_iterations
+    return _Project.apply(vy, vx, bool(closed), b[2], b[3], accuracy, int(max_iterations), ga, int(gi))
+
+
 def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
-                    max_gradient_iterations=None, guess=None, slab=None):
+                    max_gradient_iterations=None, guess=None, slab=None, fused=True):
     """divergence_free (PF/physics/fluid.py:214-243) without obstacles -> (vy', vx', pressure, iterations, divergence).
+    Grids up to 128 x 128 with a zero initial guess take ONE launch (the projection fused around the on-chip CG, _Project);
+    otherwise divergence, solve and gradient subtraction are three operators (fused=False forces that path: A/B and tests).
     slab: a SlabSolver -> the pressure solve is decomposed over its process group."""
+    ny, nx = vx.shape[1], vy.shape[2]
+    if fused and slab is None and guess is None and _lib.lib().pdec_project_2d_supported(ny, nx):
+        oy, ox, p, div, iters = _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations)
+        return oy, ox, p, iters, div
     div = mask_divergence(vy, vx, closed)
     if slab is not None:
         p, iters, _ = _PressureSolveSlab.apply(div, slab, bool(closed), accuracy, int(max_iterations))

@@ -250,10 +250,10 @@ def test_periodic_total_force_loss_equals_residuals_of_burgers_step():
     for a, b in zip(noisy, ref_frames):
         assert rel_err(a.grad.cpu(), b.grad.cpu()) < 1e-4
     assert float(pde.scalars["Total Force"]) > 0
-    # (3) the opt-in wrapped-stencil variant is a different (explicit) diffusion: close, not equal
+    # (3) the opt-in wrapped-stencil variant is a different (explicit) diffusion -- on this scene dt * nu / dx^2 is beyond the explicit
+    # stencil's stability limit, so it amplifies the noise the spectral branch damps: it must NOT be what a periodic domain gets by default
     stencil = BurgersPDE(dom, nu, dt, periodic_diffusion="stencil").total_force_loss(states_of([f.detach() for f in noisy]))
-    assert abs(float(stencil) - float(expected)) > 1e-6 * float(expected)
-    assert abs(float(stencil) - float(expected)) < 0.2 * float(expected)
+    assert abs(float(stencil) - float(expected)) > 1e-3 * float(expected)
 
 
 @pytest.mark.parametrize("bd", ["open", "closed"])

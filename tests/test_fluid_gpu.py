@@ -313,6 +313,33 @@ def test_controlled_variant_and_force_loss_vs_golden_and_oracle():
     assert rel_err(pc.grad.cpu(), po.grad) < 1e-3 and rel_err(rc.grad.cpu(), ro.grad) < 1e-3
 
 
+@pytest.mark.parametrize("closed", [False, True])
+@pytest.mark.parametrize("B,ny,nx", [(3, 128, 128), (2, 64, 128), (2, 100, 90), (1, 37, 50), (2, 16, 24)])
+def test_fused_projection_is_bit_identical_to_the_three_operator_composition(closed, B, ny, nx):
+    """pdec_project_2d_fwd / _bwd (divergence in the prologue of the on-chip CG, gradient subtraction in its epilogue) against
+    pdec_mask_divergence_2d -> pdec_cg_poisson_2d -> pdec_subtract_pressure_gradient_2d and their adjoints: same bits, forward and
+    reverse, including upstream gradients on the pressure and the divergence outputs, on a non-square box."""
+    ops = _ops()
+    rng = np.random.RandomState(ny * 7 + nx + int(closed))
+    vy = (rng.randn(B, ny + 1, nx) * 0.5).astype(np.float32)
+    vx = (rng.randn(B, ny, nx + 1) * 0.5).astype(np.float32)
+    box = (0.0, 0.0, float(ny) * 1.5, float(nx) * 0.75)
+    w = [torch.tensor(rng.randn(*s).astype(np.float32), device="cuda") for s in ((B, ny + 1, nx), (B, ny, nx + 1), (B, ny, nx), (B, ny, nx))]
+    res = []
+    for fused, use_p in ((True, True), (False, True), (True, False), (False, False)):
+        t = [torch.tensor(a, device="cuda", requires_grad=True) for a in (vy, vx)]
+        oy, ox, p, iters, div = ops.divergence_free(t[0], t[1], closed, box, accuracy=1e-5, max_iterations=1500, fused=fused)
+        loss = (oy * w[0]).sum() + (ox * w[1]).sum()
+        if use_p:
+            loss = loss + 0.3 * (p * w[2]).sum() + 0.7 * (div * w[3]).sum()
+        loss.backward()
+        res.append([oy.detach(), ox.detach(), p.detach(), div.detach(), iters, t[0].grad, t[1].grad])
+    for a, b in ((res[0], res[1]), (res[2], res[3])):
+        for x, y in zip(a, b):
+            assert torch.equal(x, y)
+    assert int(res[0][4].max()) < 1500
+
+
 def test_adjoint_is_bit_reproducible_and_batch_independent():
     ops = _ops()
     rng = np.random.RandomState(6)
