@@ -3,6 +3,8 @@
 Every op runs on CUDA tensors on `torch.cuda.current_stream()`; none has a CPU fallback (a CPU tensor raises).
 Reference semantics are cited per op (PF/ = /root/reference/PhiFlow/phi/).
 """
+import os
+
 import numpy as np
 import torch
 
@@ -619,6 +621,9 @@ def normalize_to(target, source, epsilon=1e-5):
     return _Normalize.apply(target, source, float(epsilon))
 
 
+_FUSED_PROJECTION = bool(os.environ.get("PDEC_FUSED_PROJECTION"))      # default of divergence_free(fused=None); A/B switch (scripts/diag)
+
+
 class _Project(torch.autograd.Function):
     """divergence_free (PF/physics/fluid.py:214-243) as ONE launch per direction: mask + divergence in the prologue of the on-chip CG,
     pressure-gradient subtraction in its epilogue (pdec_project_2d_fwd / _bwd).  Outputs (v'_y, v'_x, p, div, iterations); the
@@ -669,12 +674,17 @@ def _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, m
 
 
 def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
-                    max_gradient_iterations=None, guess=None, slab=None, fused=True):
+                    max_gradient_iterations=None, guess=None, slab=None, fused=None):
     """divergence_free (PF/physics/fluid.py:214-243) without obstacles -> (vy', vx', pressure, iterations, divergence).
-    Grids up to 128 x 128 with a zero initial guess take ONE launch (the projection fused around the on-chip CG, _Project);
-    otherwise divergence, solve and gradient subtraction are three operators (fused=False forces that path: A/B and tests).
+    Default: divergence, solve and gradient subtraction are three launches.  fused=True (grids up to 128 x 128, zero guess) takes ONE
+    launch per direction (the projection fused around the on-chip CG, _Project): bit-identical, two launches and two 4 MiB round trips
+    fewer -- and MEASURED SLOWER at config 3 (14.19 against 13.37 ms per 16-step trajectory, profiles/r2f_fused_projection.md: the
+    prologue / epilogue perturb the register allocation of the iteration loop by 9 instructions in 482, which costs more than the two
+    stencil launches did inside a CUDA graph), so it is an option (PDEC_FUSED_PROJECTION=1 makes it the default), not the default.
     slab: a SlabSolver -> the pressure solve is decomposed over its process group."""
     ny, nx = vx.shape[1], vy.shape[2]
+    if fused is None:
+        fused = _FUSED_PROJECTION
     if fused and slab is None and guess is None and _lib.lib().pdec_project_2d_supported(ny, nx):
         oy, ox, p, div, iters = _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations)
         return oy, ox, p, iters, div

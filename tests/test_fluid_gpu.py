@@ -326,7 +326,7 @@ def test_fused_projection_is_bit_identical_to_the_three_operator_composition(clo
     box = (0.0, 0.0, float(ny) * 1.5, float(nx) * 0.75)
     w = [torch.tensor(rng.randn(*s).astype(np.float32), device="cuda") for s in ((B, ny + 1, nx), (B, ny, nx + 1), (B, ny, nx), (B, ny, nx))]
     res = []
-    for fused, use_p in ((True, True), (False, True), (True, False), (False, False)):
+    for fused, use_p in ((True, True), (False, True), (True, False), (False, False)):      # fused=False is the default path
         t = [torch.tensor(a, device="cuda", requires_grad=True) for a in (vy, vx)]
         oy, ox, p, iters, div = ops.divergence_free(t[0], t[1], closed, box, accuracy=1e-5, max_iterations=1500, fused=fused)
         loss = (oy * w[0]).sum() + (ox * w[1]).sum()
