@@ -1,0 +1,401 @@
+"""Fluid workloads of bench.py: BASELINE config 3 (128 x 128, 16 projected steps + adjoint, B = 64; CG at the reference's default
+accuracy, CG at the accuracy that holds the parity tolerances, and the opt-in direct solver), the notebook variant of config 3
+(CFE potential -> curl -> density advection, force loss on the staggered velocity) and config 5 (2048 x 2048, slab-decomposed, N >= 2)."""
+import os
+import time
+
+import numpy as np
+import torch
+
+from . import inputs
+
+
+def _rel(a, b):
+    a = a.detach().cpu().double()
+    b = b.detach().cpu().double()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+class FluidConfig3(object):
+    dtype = "f32"
+    STEPS, N, B = 16, 128, 64
+    MAX_IT = 2000
+    VARIANTS = {
+        # key: (accuracy, direct, label)
+        "fluid_config3": (1e-7, False, "SparseCG(accuracy=1e-7): the CG accuracy that holds the 1e-4 / 1e-3 parity tolerances"),
+        "fluid_config3_ref_accuracy": (1e-5, False, "SparseCG(accuracy=1e-5): the reference's default accuracy (its own CG does not pin the "
+                                                    "gradient to 1e-3 there, tests/test_parity_at_size_gpu.py)"),
+        "fluid_config3_direct": (None, True, "SparseSciPy (exact fast-diagonalisation solve, opt-in)"),
+    }
+
+    def __init__(self, device, rank, world, key="fluid_config3", closed=False):
+        from pde_control_b200 import graphs
+        self.key, self.dev, self.world, self.closed = key, device, world, closed
+        self.accuracy, self.direct, self.label = self.VARIANTS[key]
+        B, n = self.B, self.N
+        rho0, vy0, vx0, target = inputs.fluid_config3_inputs(B, n, rank)
+        self.host_in = [torch.tensor(a).pin_memory() for a in (rho0, vy0, vx0)]
+        self.args = [t.to(device) for t in self.host_in] + [torch.tensor(target, device=device)]
+        fn = graphs.fluid_trajectory(self.STEPS, 1.0, closed, accuracy=self.accuracy if self.accuracy else 1e-5, max_iterations=self.MAX_IT,
+                                     direct=self.direct)
+        self.graphed = graphs.GraphedFunction(fn, self.args, grad_inputs=(0, 1, 2))
+        self.host_out = [torch.empty_like(t).pin_memory() for t in self.host_in]
+        self.host_loss = torch.empty(1).pin_memory()
+        self.cell_updates = B * n * n * self.STEPS
+        self.h2d = sum(t.numel() * 4 for t in self.host_in)
+        self.d2h = self.h2d + 4
+        self.graphed.replay()
+        torch.cuda.synchronize()
+        its = self.graphed.outputs[4].float()
+        self.mean_it, self.max_it = float(its.mean()), int(its.max())
+        self.sum_max_it = float(its.max(dim=1).values.sum())            # a CG launch lasts as long as its slowest batch element
+        # per projected step: 3 advection kernels + divergence + solve + gradient subtraction forward (6), and in the adjoint
+        # subtraction^T + solve + divergence^T + 2 x (memset + prep + gather-transpose) (9); plus a few torch kernels for the loss
+        self.launches_per_step = self.STEPS * 15 + 6
+
+    def step(self):
+        self.graphed.replay()
+
+    def step_e2e(self):
+        outs, grads = self.graphed(*(self.host_in + [self.args[3]]))
+        for dst, src in zip(self.host_out, grads):
+            dst.copy_(src, non_blocking=True)
+        self.host_loss.copy_(outs[0].reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    def config(self):
+        return {"workload": "incompressible_flow %dx%d steps=%d B=%d/gpu %s, fwd + adjoint of l2_loss(rho_%d - target) (BASELINE config 3), %s"
+                            % (self.N, self.N, self.STEPS, self.B, "CLOSED" if self.closed else "OPEN", self.STEPS, self.label),
+                "batch_per_gpu": self.B, "resolution": [self.N, self.N], "steps": self.STEPS, "cg_accuracy": self.accuracy,
+                "cg_mean_iterations_forward": self.mean_it, "cg_max_iterations_forward": self.max_it, "cuda_graph": True,
+                "l2": "working set (3 fields in, 3 out, 16 saved steps: ~200 MB) exceeds L2 across a trajectory; the CG vectors of one solve "
+                      "(4 x 4 MiB) never leave the chip; inputs identical each step",
+                "parallelism": "batch-sharded x%d" % self.world}
+
+    def roofline(self, ms_per_step, peak, peak_src):
+        cells = self.B * self.N * self.N
+        non_cg = 128.0 * self.cell_updates                   # 56 B forward + 72 B adjoint per cell-update around the solves
+        solve_io = 8.0 * cells * 2 * self.STEPS              # a solve reads its right-hand side and writes its solution once
+        hbm = (non_cg + solve_io) / (ms_per_step * 1e-3) / 1e9
+        out = {"bound": "hbm", "achieved": hbm, "peak": peak, "unit": "GB/s", "frac": hbm / peak, "traffic": 4.23e6,
+               "peak_source": peak_src, "algorithmic_bytes_per_cell_update": 128.0 + 16.0,
+               "kernel": "poisson_direct_kernel" if self.direct else "cg_block_kernel",
+               "note": "compulsory HBM bytes only (fields around the solves + rhs in / solution out): the solver's vectors stay on chip by "
+                       "design, so the step is NOT HBM-bound and this fraction is small on purpose; the bound that applies is `on_chip`"}
+        if self.direct:
+            flops = 2.0 * 4 * self.N ** 3 * self.B * 2 * self.STEPS
+            fp32_peak = 148 * 128 * 2 * 1.965e9
+            out["on_chip"] = {"bound": "fp32 FFMA issue", "achieved_TFLOPs": flops / (ms_per_step * 1e-3) / 1e12,
+                              "peak_TFLOPs_64_of_148_SMs": fp32_peak * 64 / 148 / 1e12,
+                              "note": "four 128^3 fp32 products per solve and element, one CTA per element (64 of 148 SMs); achieved counts the "
+                                      "whole step's time against the solves' flops"}
+        else:
+            # forward launches last sum-over-steps of the slowest element's count; the adjoint solves are about as long
+            floor_us = 0.78
+            out["on_chip"] = {"bound": "fp32 issue of the iteration (16384 cells x 12 instructions / 128 lanes = 0.78 us per iteration per SM)",
+                              "floor_us_per_iteration": floor_us, "forward_iterations_mean": self.mean_it,
+                              "forward_iterations_sum_of_per_step_max": self.sum_max_it,
+                              "us_per_iteration_if_all_time_were_cg": ms_per_step * 1e3 / max(2.0 * self.sum_max_it, 1.0),
+                              "sm_used_of_148": 64}
+            out["on_chip"]["frac"] = floor_us / out["on_chip"]["us_per_iteration_if_all_time_were_cg"]
+            streaming = (128.0 * self.cell_updates + 36.0 * cells * 2 * self.mean_it * self.STEPS) / (ms_per_step * 1e-3) / 1e9
+            out["streaming_equivalent"] = {"GBps": streaming, "frac_of_hbm_peak": streaming / peak,
+                                           "note": "what a streaming CG (36 B per cell and iteration, SURVEY 8d; the reference's "
+                                                   "pressure_solve_op.cu.cc streams every vector every iteration) would have to move in this time"}
+        return out
+
+    def parity(self, elements=(0, 63)):
+        """Two batch elements of the timed inputs through the exact oracle (fp64 sparse direct solve, autograd with the registered second
+        solve) against the graph's own outputs for those elements: final density, and the gradients w.r.t. rho0, vy0, vx0 (x B / 2: the
+        loss is normalised by the batch size)."""
+        from oracle import restate as R
+        from oracle import restate_fluid as F
+        self.graphed(*self.args)
+        torch.cuda.synchronize()
+        outs, grads = self.graphed.outputs, self.graphed.grads
+        sel = list(elements)
+        geo = F.Geometry(self.N, self.N)
+        t = [a[sel].cpu().clone().requires_grad_(True) for a in self.args[:3]]
+        s = tuple(t)
+        for _ in range(self.STEPS):
+            s = F.incompressible_step(*s, 1.0, geo, "closed" if self.closed else "open")[:3]
+        R.l2_loss(s[0] - self.args[3][sel].cpu()).backward()
+        scale = float(self.B) / len(sel)
+        out = {"checked": True, "against": "oracle.restate_fluid (fp64 direct pressure solve) on batch elements %s of the timed inputs" % sel,
+               "max_rel_state": max(_rel(outs[k][sel], s[k - 1]) for k in (1, 2, 3)),
+               "max_rel_grad": max(_rel(grads[k][sel] * scale, t[k].grad) for k in range(3)),
+               "tolerance": {"state": 1e-4, "grad": 1e-3}}
+        out["ok"] = out["max_rel_state"] < 1e-4 and out["max_rel_grad"] < 1e-3
+        return out
+
+    # ---- CPU legs ---------------------------------------------------------------------------------
+    def cpu_baseline(self, budget_s=12.0, Bs=2):
+        """The oracle PORT with the reference's algorithm: restated fp32 CG at the reference's default accuracy 1e-5 (PF/math/blas.py:5-64)
+        forward and, as the registered gradient, in the adjoint (sparse.py:93-94); whole 16-step trajectory + gradient."""
+        from oracle import restate as R
+        from oracle import restate_fluid as F
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        geo = F.Geometry(self.N, self.N)
+        bd = "closed" if self.closed else "open"
+
+        def solver(div, boundary):
+            class S(torch.autograd.Function):
+                @staticmethod
+                def forward(ctx, d):
+                    return F.conjugate_gradient(d, boundary, 1e-5, 2000)[0]
+
+                @staticmethod
+                def backward(ctx, g):
+                    return F.conjugate_gradient(g, boundary, 1e-5, 2000)[0]
+            return S.apply(div)
+
+        arrs = [a[:Bs].cpu() for a in self.args[:3]]
+        tgt = self.args[3][:Bs].cpu()
+
+        def once(steps):
+            t = [a.clone().requires_grad_(True) for a in arrs]
+            t0 = time.perf_counter()
+            s = tuple(t)
+            for _ in range(steps):
+                s = F.incompressible_step(*s, 1.0, geo, bd, solver=solver)[:3]
+            R.l2_loss(s[0] - tgt).backward()
+            return time.perf_counter() - t0
+        once(1)
+        elapsed, reps = 0.0, 0
+        while elapsed < budget_s and reps < 5:
+            elapsed += once(self.STEPS)
+            reps += 1
+        return {"value": reps * Bs * self.N * self.N * self.STEPS / elapsed, "unit": "cell-updates/s", "cores": cores, "kind": "port",
+                "sample": "%d x the 16-step trajectory + gradient on batch %d of the timed inputs: oracle.restate_fluid with the restated fp32 "
+                          "CG at accuracy 1e-5 forward and adjoint (torch CPU, %d threads)" % (reps, Bs, cores)}
+
+    @classmethod
+    def reference_forward(cls, Bs=2, budget_s=10.0):
+        """The reference's OWN IncompressibleFlow.step (NumPy backend, SparseCG) forward only, on `Bs` elements of the same inputs."""
+        from oracle import ref_shim
+        if not ref_shim.available():
+            return None
+        pf = ref_shim.flow()
+        from oracle.make_golden_fluid import staggered_tensor
+        rho0, vy0, vx0, _ = inputs.fluid_config3_inputs(cls.B, cls.N, 0)
+        dom = pf.Domain([cls.N, cls.N], boundaries=pf.OPEN)
+        from phi.physics.pressuresolver.sparse import SparseCG
+        physics = pf.IncompressibleFlow(pressure_solver=SparseCG(accuracy=1e-5, max_iterations=2000))
+
+        def once(steps):
+            state = pf.Fluid(dom, density=rho0[:Bs, ..., None].copy(), velocity=staggered_tensor(vy0[:Bs], vx0[:Bs]), batch_size=Bs)
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                state = physics.step(state, dt=1.0)
+            return time.perf_counter() - t0
+        once(1)
+        elapsed, reps, steps = 0.0, 0, 4
+        while elapsed < budget_s and reps < 3:
+            elapsed += once(steps)
+            reps += 1
+        return {"value": reps * steps * Bs * cls.N * cls.N / elapsed, "unit": "cell-updates/s (FORWARD ONLY)", "cores": 1,
+                "kind": "reference-forward",
+                "sample": "%d x %d steps of the unmodified reference's IncompressibleFlow.step (NumPy/SciPy backend, SparseCG(1e-5)) on batch %d "
+                          "of the timed inputs" % (reps, steps, Bs)}
+
+
+class FluidNotebook(object):
+    """The path the reference's IncompressibleFluidPDE actually runs (src/control/pde/incompressible_flow.py:31-59): per step
+    CFE potential -> staggered_curl_2d -> semi-Lagrangian density advection; losses = l2(rho_T - target) + mean over frame pairs of
+    l2(semi_lagrangian(v_t, v_t) - v_t+1) (total_force_loss); gradient w.r.t. every potential frame and rho_0.  No pressure solve."""
+    key = "fluid_notebook"
+    dtype = "f32"
+    dominant_kernel = "advect_staggered_bwd_kernel"
+    algorithmic_bytes_per_cell_update = 72.0        # SURVEY 8d, notebook variant
+    STEPS, N, B = 16, 128, 64
+
+    def __init__(self, device, rank, world):
+        from pde_control_b200 import graphs, ops
+        self.dev, self.world = device, world
+        B, n, T = self.B, self.N, self.STEPS
+        rho0, phi, target = inputs.fluid_notebook_inputs(B, n, T, rank)
+        self.host_in = [torch.tensor(rho0).pin_memory(), torch.tensor(phi).pin_memory()]
+        self.args = [t.to(device) for t in self.host_in] + [torch.tensor(target, device=device)]
+        self.fn = self.make_fn(ops, T)
+        self.graphed = graphs.GraphedFunction(self.fn, self.args, grad_inputs=(0, 1))
+        self.host_out = [torch.empty_like(t).pin_memory() for t in self.host_in]
+        self.host_loss = torch.empty(1).pin_memory()
+        self.cell_updates = B * n * n * T
+        self.h2d = sum(t.numel() * 4 for t in self.host_in)
+        self.d2h = self.h2d + 4
+        self.launches_per_step = T * 12
+
+    @staticmethod
+    def make_fn(ops, T, dt=1.0):
+        from pde_control_b200._lib import MODE_CONSTANT, MODE_REPLICATE
+
+        def fn(rho, phi, target):
+            B = rho.shape[0]
+            vs = []
+            for t in range(T):
+                vy, vx = ops.curl_2d(phi[t], MODE_CONSTANT)                       # U-Net output sampled like the density: 'constant'
+                rho = ops.advect_centered(rho, vy, vx, dt, MODE_CONSTANT)
+                vs.append((vy, vx))
+            d = rho - target
+            loss = (d * d).sum() / (2 * B)
+            force = 0
+            for (ay, ax), (by, bx) in zip(vs[:-1], vs[1:]):                       # total_force_loss: velocities from the curl extrapolate 'boundary'
+                sy, sx = ops.advect_staggered(ay, ax, dt, MODE_REPLICATE)
+                force = force + ((sy - by) ** 2).sum() / (2 * B) + ((sx - bx) ** 2).sum() / (2 * B)
+            return loss + force / (T - 1), rho
+        return fn
+
+    def step(self):
+        self.graphed.replay()
+
+    def step_e2e(self):
+        outs, grads = self.graphed(*(self.host_in + [self.args[2]]))
+        for dst, src in zip(self.host_out, grads):
+            dst.copy_(src, non_blocking=True)
+        self.host_loss.copy_(outs[0].reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    def config(self):
+        return {"workload": "notebook fluid variant %dx%d steps=%d B=%d/gpu: potential -> curl -> density advection + staggered force loss, fwd + "
+                            "adjoint w.r.t. all potentials and rho_0 (IncompressibleFluidPDE path, no pressure solve)" % (self.N, self.N, self.STEPS, self.B),
+                "batch_per_gpu": self.B, "resolution": [self.N, self.N], "steps": self.STEPS, "cuda_graph": True,
+                "l2": "64 MiB of potentials + saved fields per trajectory: larger than nothing in particular, smaller than L2 (126 MB) -- stated: "
+                      "inputs identical each step, partly L2 resident",
+                "parallelism": "batch-sharded x%d" % self.world}
+
+    def roofline(self, ms_per_step, peak, peak_src):
+        achieved = self.algorithmic_bytes_per_cell_update * self.cell_updates / (ms_per_step * 1e-3) / 1e9
+        return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "algorithmic_bytes_per_cell_update": self.algorithmic_bytes_per_cell_update,
+                "kernel": self.dominant_kernel,
+                "note": "72 B per cell-update = SURVEY 8d's figure for FUSED curl+advection and a fused force loss; the kernels here are still one "
+                        "per operator (curl, advect, staggered advect, their gather-transpose adjoints), so the real traffic is ~3x that"}
+
+    def parity(self, elements=(0, 63)):
+        from oracle import restate as R
+        from oracle import restate_fluid as F
+        self.graphed(*self.args)
+        torch.cuda.synchronize()
+        outs, grads = self.graphed.outputs, self.graphed.grads
+        sel = list(elements)
+        geo = F.Geometry(self.N, self.N)
+        T = self.STEPS
+        rho = self.args[0][sel].cpu().clone().requires_grad_(True)
+        phi = self.args[1][:, sel].cpu().clone().requires_grad_(True)
+        r, vys, vxs = rho, [], []
+        for t in range(T):
+            r, vy, vx = F.controlled_step(r, phi[t], 1.0, geo)
+            vys.append(vy)
+            vxs.append(vx)
+        loss = R.l2_loss(r - self.args[2][sel].cpu())
+        force = 0
+        for k in range(T - 1):
+            force = force + F.force_loss([vys[k], vys[k + 1]], [vxs[k], vxs[k + 1]], 1.0, geo)
+        (loss + force / (T - 1)).backward()
+        scale = float(self.B) / len(sel)
+        out = {"checked": True, "against": "oracle.restate_fluid.controlled_step / force_loss on batch elements %s of the timed inputs" % sel,
+               "max_rel_state": _rel(outs[1][sel], r),
+               "max_rel_grad": max(_rel(grads[0][sel] * scale, rho.grad), _rel(grads[1][:, sel] * scale, phi.grad)),
+               "tolerance": {"state": 1e-4, "grad": 1e-3}}
+        out["ok"] = out["max_rel_state"] < 1e-4 and out["max_rel_grad"] < 1e-3
+        return out
+
+    def cpu_baseline(self, budget_s=8.0, Bs=4):
+        from oracle import restate as R
+        from oracle import restate_fluid as F
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        geo = F.Geometry(self.N, self.N)
+        T = self.STEPS
+        rho0, phi0, tgt = self.args[0][:Bs].cpu(), self.args[1][:, :Bs].cpu(), self.args[2][:Bs].cpu()
+
+        def once():
+            rho, phi = rho0.clone().requires_grad_(True), phi0.clone().requires_grad_(True)
+            t0 = time.perf_counter()
+            r, vys, vxs = rho, [], []
+            for t in range(T):
+                r, vy, vx = F.controlled_step(r, phi[t], 1.0, geo)
+                vys.append(vy)
+                vxs.append(vx)
+            loss = R.l2_loss(r - tgt)
+            for k in range(T - 1):
+                loss = loss + F.force_loss([vys[k], vys[k + 1]], [vxs[k], vxs[k + 1]], 1.0, geo) / (T - 1)
+            loss.backward()
+            return time.perf_counter() - t0
+        once()
+        elapsed, reps = 0.0, 0
+        while elapsed < budget_s and reps < 10:
+            elapsed += once()
+            reps += 1
+        return {"value": reps * Bs * self.N * self.N * T / elapsed, "unit": "cell-updates/s", "cores": cores, "kind": "port",
+                "sample": "%d x the same 16-step trajectory + gradient on batch %d of the timed inputs with oracle.restate_fluid (torch CPU fp32, %d "
+                          "threads)" % (reps, Bs, cores)}
+
+
+class Config5Slab(object):
+    """BASELINE config 5 (N >= 2): 2048 x 2048, B = 1, projected steps forward + adjoint, the pressure solve slab-decomposed over the
+    ranks with the per-iteration exchange over NVLink peer memory (ops.SlabSolver -> pdec_cg_poisson_2d_slab).  The reference's
+    max_iterations = 2000 would cap the solve at this size (~4500 iterations to 1e-5), so max_iterations = 20000 and counts are reported."""
+    key = "config5_slab"
+    dtype = "f32"
+    N, STEPS = 2048, 2
+
+    def __init__(self, device, rank, world):
+        from pde_control_b200 import ops
+        self.ops, self.dev, self.rank, self.world = ops, device, rank, world
+        n = self.N
+        g = torch.Generator(device=device)
+        g.manual_seed(3)                                    # the same (replicated) fields on every rank
+
+        def smooth(x, passes=6):
+            for _ in range(passes):
+                x = (x + torch.roll(x, 1, -1) + torch.roll(x, -1, -1) + torch.roll(x, 1, -2) + torch.roll(x, -1, -2)) / 5
+            return x / x.abs().max()
+        self.rho0 = (smooth(torch.randn(1, n, n, device=device, generator=g)) > 0.2).float()
+        self.vy0 = smooth(torch.randn(1, n + 1, n, device=device, generator=g))
+        self.vx0 = smooth(torch.randn(1, n, n + 1, device=device, generator=g))
+        self.target = (smooth(torch.randn(1, n, n, device=device, generator=g)) > 0.2).float()
+        self.solver = ops.SlabSolver(1, n, n)
+        self.cell_updates = n * n * self.STEPS             # the ranks share ONE domain: strong scaling
+        self.its = []
+
+    def step(self):
+        ops = self.ops
+        s = (self.rho0.clone().requires_grad_(True), self.vy0.clone().requires_grad_(True), self.vx0.clone().requires_grad_(True))
+        leaves, its = s, []
+        for _ in range(self.STEPS):
+            out = ops.incompressible_step(*s, 0.8, False, accuracy=1e-5, max_iterations=20000, slab=self.solver)
+            s = out[:3]
+            its.append(out[4])
+        self.loss = ((s[0] - self.target) ** 2).sum() / 2
+        self.grads = torch.autograd.grad(self.loss, leaves)
+        self.its = its
+
+    def config(self):
+        return {"workload": "incompressible_flow 2048x2048 B=1 steps=%d OPEN fwd + adjoint, row slabs over %d GPUs, CG to 1e-5 (BASELINE config 5)"
+                            % (self.STEPS, self.world), "resolution": [self.N, self.N], "steps": self.STEPS,
+                "parallelism": "slab CG x%d over NVLink peer memory; advection / divergence / gradient replicated, pressure all-gathered (NCCL)"
+                               % self.world, "scaling": "strong"}
+
+    def solve_parity(self):
+        """One 2048^2 right-hand side through the slab solver against its own fp64 residual, |A p - rhs|_inf, and a solve-time figure."""
+        ops = self.ops
+        rhs = ops.mask_divergence(self.vy0, self.vx0, False)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        p, iters, resid = self.solver.solve(rhs, False, 1e-5, 20000)
+        e1.record()
+        torch.cuda.synchronize()
+        pd = torch.nn.functional.pad(p.double(), (1, 1, 1, 1))
+        Ap = pd[:, 2:, 1:-1] + pd[:, :-2, 1:-1] + pd[:, 1:-1, 2:] + pd[:, 1:-1, :-2] - 4.0 * p.double()
+        true_res = float((Ap - rhs.double()).abs().max())
+        k = int(iters.max())
+        ms = e0.elapsed_time(e1)
+        return {"checked": True, "against": "fp64 evaluation of A p - rhs of the slab solve (rhs = divergence of the timed velocity)",
+                "iterations": k, "recurrence_residual": float(resid.max()), "true_residual_inf": true_res, "rhs_inf": float(rhs.abs().max()),
+                "tolerance": {"true_residual_inf": 1e-3}, "ok": k > 0 and true_res < 1e-3, "ms_per_solve": ms, "us_per_iteration": ms * 1e3 / max(k, 1)}
+
+    def close(self):
+        self.solver.close()

@@ -262,6 +262,21 @@ int pdec_project_2d_bwd(const float* g_vy_out, const float* g_vx_out, const floa
                         int* iterations, float* residual, int B, int ny, int nx, int closed, float size_y, float size_x,
                         float accuracy, int max_iterations, void* stream);
 
+/* EXACT pressure solve by fast diagonalisation (opt-in, next to the CG): replaces the reference's direct solver class SparseSciPy
+ * (PF/physics/pressuresolver/sparse.py:14-37, scipy spsolve on the matrix of sparse.py:114-221; the reference's default on its NumPy
+ * backend, solver_api.py:144-148).  Rectangular domains up to 128 x 128 without obstacles: A = T_y (x) I + I (x) T_x with closed-form
+ * eigenvectors per axis (sine basis on OPEN, cosine basis on CLOSED domains), p = E_y [(E_y^T rhs E_x) / (l_y + l_x)] E_x^T as four
+ * on-chip 128^3 fp32 products per batch element (one CTA each).  No iteration count, no accuracy knob; on a CLOSED domain the
+ * mean-free solution (what CG reaches from a zero guess).  The same call is its own adjoint (A symmetric, sparse.py:93-94).
+ * `spectral`: pdec_poisson_direct_2d_spectral_bytes() bytes of device memory owned by the caller, filled ONCE per (ny, nx, closed)
+ * by pdec_poisson_direct_2d_setup (eigenvectors evaluated in fp64 on the device) and read-only afterwards (shareable by streams).
+ * A binder with other boundary rules (per-side mixed) may fill the block itself: five [128][128] float matrices, zero padded --
+ * E_y (E[k][m]: cell k, eigenvector m), E_x, E_x^T, E_y^T, inv[j][i] = 1 / (l_x(j) + l_y(i)) (0 for a singular mode). */
+size_t pdec_poisson_direct_2d_spectral_bytes(void);
+int pdec_poisson_direct_2d_supported(int ny, int nx);
+int pdec_poisson_direct_2d_setup(void* spectral, size_t spectral_bytes, int ny, int nx, int closed, void* stream);
+int pdec_poisson_direct_2d(const float* rhs, float* p, int B, int ny, int nx, const void* spectral, void* stream);
+
 /* The stencil of a domain with obstacles from its cell mask (replaces the LaplaceMatrix op, PF/tf/cuda/src/laplace_op.cc:10-17, and
  * PoissonDomain's mask logic, solver_api.py:51-121): active [ny*nx] floats (1 fluid, 0 obstacle) -> code [ny*nx] bytes as
  * pdec_cg_poisson_2d_masked reads them, and the face masks fy [(ny+1)*nx], fx [ny*(nx+1)] that multiply the velocity before the

@@ -28,6 +28,7 @@ SOURCES = {
     "resample.cu": ["-fmad=false"],
     "laplace_matrix.cu": [],
     "host_pipeline.cu": [],
+    "poisson_direct.cu": [],
     "noalloc.cu": [],               # static-scratch entry point: host wrapper only, no kernel of its own
 }
 

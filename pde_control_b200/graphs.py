@@ -66,7 +66,7 @@ class GraphedFunction(object):
         return self.replay()
 
 
-def fluid_trajectory(steps, dt, closed, accuracy=1e-5, max_iterations=2000, box=None, loss=None):
+def fluid_trajectory(steps, dt, closed, accuracy=1e-5, max_iterations=2000, box=None, loss=None, direct=False):
     """fn(rho, vy, vx[, target]) for GraphedFunction: `steps` projected IncompressibleFlow steps (PF/physics/fluid.py:90-114); returns
     (loss, rho, vy, vx, cg_iterations [steps, B]) with loss = l2_loss(rho_final - target) (PF/math/nd.py:111-124) unless `loss` is given."""
     from . import ops
@@ -74,7 +74,8 @@ def fluid_trajectory(steps, dt, closed, accuracy=1e-5, max_iterations=2000, box=
     def fn(rho, vy, vx, target=None):
         iters = []
         for _ in range(steps):
-            rho, vy, vx, _p, it = ops.incompressible_step(rho, vy, vx, dt, closed, box=box, accuracy=accuracy, max_iterations=max_iterations)
+            rho, vy, vx, _p, it = ops.incompressible_step(rho, vy, vx, dt, closed, box=box, accuracy=accuracy, max_iterations=max_iterations,
+                                                          direct=direct)
             iters.append(it)
         if loss is not None:
             value = loss(rho, vy, vx, target)

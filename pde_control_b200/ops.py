@@ -403,6 +403,62 @@ def cg_poisson_raw(rhs, out, closed, accuracy, max_iterations, guess=None, itera
               _lib.stream_ptr())
 
 
+_SPECTRAL = {}
+
+
+def _spectral_block(device, ny, nx, closed):
+    """Eigenvector matrices + reciprocal eigenvalue sums of the (ny, nx, closed) Poisson matrix, built once on the device."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), int(ny), int(nx), bool(closed))
+    blk = _SPECTRAL.get(key)
+    if blk is None:
+        L = _lib.lib()
+        nbytes = L.pdec_poisson_direct_2d_spectral_bytes()
+        blk = torch.empty(nbytes // 4, device=device, dtype=torch.float32)
+        with torch.cuda.device(device):
+            _call("pdec_poisson_direct_2d_setup", _lib.ptr(blk), nbytes, int(ny), int(nx), int(bool(closed)), _lib.stream_ptr())
+        # built on the current stream; other streams (graph branches) only ever read it after this one has been joined
+        torch.cuda.current_stream(device).synchronize()
+        _SPECTRAL[key] = blk
+    return blk
+
+
+def poisson_direct_raw(rhs, out, closed):
+    B, ny, nx = rhs.shape
+    blk = _spectral_block(rhs.device, ny, nx, closed)
+    with torch.cuda.device(rhs.device):
+        _call("pdec_poisson_direct_2d", _lib.ptr(rhs), _lib.ptr(out), B, ny, nx, _lib.ptr(blk), _lib.stream_ptr())
+
+
+class _PressureSolveDirect(torch.autograd.Function):
+    """Exact solve by fast diagonalisation (pdec_poisson_direct_2d; the reference's SparseSciPy, sparse.py:14-37).  Backward = the same
+    solve of the incoming gradient (A symmetric, sparse.py:93-94)."""
+
+    @staticmethod
+    def forward(ctx, div, closed):
+        _req_cuda(div)
+        div = _c(div)
+        p = torch.empty_like(div)
+        poisson_direct_raw(div, p, closed)
+        ctx.closed = closed
+        return p
+
+    @staticmethod
+    def backward(ctx, g_p):
+        g_p = _c(g_p)
+        g_div = torch.empty_like(g_p)
+        poisson_direct_raw(g_p, g_div, ctx.closed)
+        return g_div, None
+
+
+def pressure_solve_direct(div, closed):
+    """Exact pressure [B, ny, nx] of a rectangular domain without obstacles, grids up to 128 x 128; differentiable w.r.t. div."""
+    return _PressureSolveDirect.apply(div, bool(closed))
+
+
+def direct_solver_supported(ny, nx):
+    return bool(_lib.lib().pdec_poisson_direct_2d_supported(int(ny), int(nx)))
+
+
 class SlabComm(object):
     """Peer-visible communication buffers of the slab-decomposed CG (include/pdec.h, pdec_slab_comm): one buffer per rank,
     allocated by the library (cudaMalloc), exchanged as CUDA IPC handles over `torch.distributed` and mapped into every
@@ -674,15 +730,21 @@ def _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, m
 
 
 def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
-                    max_gradient_iterations=None, guess=None, slab=None, fused=None):
+                    max_gradient_iterations=None, guess=None, slab=None, fused=None, direct=False):
     """divergence_free (PF/physics/fluid.py:214-243) without obstacles -> (vy', vx', pressure, iterations, divergence).
     Default: divergence, solve and gradient subtraction are three launches.  fused=True (grids up to 128 x 128, zero guess) takes ONE
     launch per direction (the projection fused around the on-chip CG, _Project): bit-identical, two launches and two 4 MiB round trips
     fewer -- and MEASURED SLOWER at config 3 (14.19 against 13.37 ms per 16-step trajectory, profiles/r2f_fused_projection.md: the
     prologue / epilogue perturb the register allocation of the iteration loop by 9 instructions in 482, which costs more than the two
     stencil launches did inside a CUDA graph), so it is an option (PDEC_FUSED_PROJECTION=1 makes it the default), not the default.
-    slab: a SlabSolver -> the pressure solve is decomposed over its process group."""
+    slab: a SlabSolver -> the pressure solve is decomposed over its process group.
+    direct=True: the exact fast-diagonalisation solve instead of CG (pressure_solve_direct; iterations are reported as 0)."""
     ny, nx = vx.shape[1], vy.shape[2]
+    if direct:
+        div = mask_divergence(vy, vx, closed)
+        p = pressure_solve_direct(div, closed)
+        oy, ox = subtract_pressure_gradient(vy, vx, p, closed, box)
+        return oy, ox, p, torch.zeros(vy.shape[0], device=vy.device, dtype=torch.int32), div
     if fused is None:
         fused = _FUSED_PROJECTION
     if fused and slab is None and guess is None and _lib.lib().pdec_project_2d_supported(ny, nx):
@@ -775,14 +837,15 @@ def divergence_free_masked(vy, vx, masks, box=None, accuracy=1e-5, max_iteration
 
 
 def incompressible_step(rho, vy, vx, dt, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
-                        max_gradient_iterations=None, conserve_density=True, slab=None):
+                        max_gradient_iterations=None, conserve_density=True, slab=None, direct=False, fused=None):
     """IncompressibleFlow.step (PF/physics/fluid.py:90-114), default flags, no obstacles / effects / buoyancy.
-    Field modes follow Material.extrapolation_mode / vector_extrapolation_mode: open -> constant, closed -> replicate."""
+    Field modes follow Material.extrapolation_mode / vector_extrapolation_mode: open -> constant, closed -> replicate.
+    direct=True: exact fast-diagonalisation pressure solve instead of CG (see divergence_free)."""
     mode = MODE_REPLICATE if closed else MODE_CONSTANT
     rho2 = advect_centered(rho, vy, vx, dt, mode, box)
     ay, ax = advect_staggered(vy, vx, dt, mode, box)
     if closed and conserve_density:
         rho2 = normalize_to(rho2, rho)
     oy, ox, p, iters, _ = divergence_free(ay, ax, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations,
-                                         slab=slab)
+                                         slab=slab, direct=direct, fused=fused)
     return rho2, oy, ox, p, iters

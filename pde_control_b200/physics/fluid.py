@@ -43,6 +43,23 @@ class SparseCG(_Chainable):
         return (p.unsqueeze(-1) if field.dim() == 4 else p), iters
 
 
+class SparseSciPy(_Chainable):
+    """The reference's DIRECT solver class (pressuresolver/sparse.py:14-37: scipy spsolve of the sparse matrix; its default on the NumPy
+    backend, solver_api.py:144-148).  Here: the exact fast-diagonalisation solve on the GPU (pdec_poisson_direct_2d) for rectangular
+    domains up to 128 x 128 without obstacles -- no iteration count, no accuracy knob; the gradient is a second exact solve.  Other
+    shapes, obstacles: use SparseCG."""
+
+    accuracy = 0.0
+    max_iterations = 0
+
+    def solve(self, field, domain, guess=None):
+        t = field[..., 0] if field.dim() == 4 else field
+        if not ops.direct_solver_supported(t.shape[1], t.shape[2]):
+            raise NotImplementedError("SparseSciPy (direct solve) covers grids up to 128 x 128; use SparseCG")
+        p = ops.pressure_solve_direct(t, _closed(domain))
+        return (p.unsqueeze(-1) if field.dim() == 4 else p), None
+
+
 class _SolverChain(object):
     """solver1 & solver2 (solver_api.py:161-174): each solver's result is the next one's initial guess.  The reference's default
     on the TensorFlow backend is FourierSolver() & SparseCG() (solver_api.py:149-155)."""
@@ -159,14 +176,28 @@ def divergence_free(velocity, domain=None, obstacles=(), pressure_solver=None, r
         domain = Domain(velocity.resolution, OPEN, box=velocity.box)
     solver = pressure_solver or SparseCG()
     vy, vx = velocity.tensors
+    guess = None
+    if isinstance(solver, _SolverChain):
+        # solver1 & solver2 (solver_api.py:161-174; the reference's TF default is FourierSolver() & SparseCG()): the leading solvers turn
+        # the divergence into an initial guess for the last one
+        div0 = ops.mask_divergence(vy, vx, _closed(domain)).detach()
+        for lead in solver.solvers[:-1]:
+            guess, _ = lead.solve(div0, domain, guess)
+        solver = solver.solvers[-1]
+    if isinstance(solver, FourierSolver):
+        raise NotImplementedError("FourierSolver alone is exact on periodic domains only: chain it, FourierSolver() & SparseCG()")
     if len(obstacles) > 0:
         assert velocity.rank == 2
+        if not isinstance(solver, SparseCG):
+            raise NotImplementedError("domains with obstacles are solved with SparseCG")
         masks = obstacle_masks(obstacles, velocity, domain)
         oy, ox, p, iters, div = ops.divergence_free_masked(vy, vx, masks, _box4(velocity.box), solver.accuracy, solver.max_iterations,
                                                            solver.gradient_accuracy, solver.max_gradient_iterations)
+    elif isinstance(solver, SparseSciPy):
+        oy, ox, p, iters, div = ops.divergence_free(vy, vx, _closed(domain), _box4(velocity.box), direct=True)
     else:
         oy, ox, p, iters, div = ops.divergence_free(vy, vx, _closed(domain), _box4(velocity.box), solver.accuracy, solver.max_iterations,
-                                                    solver.gradient_accuracy, solver.max_gradient_iterations)
+                                                    solver.gradient_accuracy, solver.max_gradient_iterations, guess=guess)
     result = velocity.with_tensors([oy, ox])
     if not return_info:
         return result

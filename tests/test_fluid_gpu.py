@@ -183,6 +183,44 @@ def test_cg_solves_the_restated_operator(bd, ny, nx):
     assert rel_err(got, direct) < 2e-4
 
 
+@pytest.mark.parametrize("bd", ["open", "closed"])
+@pytest.mark.parametrize("ny,nx", [(128, 128), (64, 64), (17, 23), (100, 90), (40, 32), (2, 2), (128, 6)])
+def test_direct_solver_vs_fp64_sparse_solve_and_reference_pressures(bd, ny, nx):
+    """pdec_poisson_direct_2d (fast diagonalisation; the reference's SparseSciPy, sparse.py:14-37) against the fp64 sparse LU of the
+    restated matrix: solution 1e-5, A p == rhs, rhs without the compatibility condition on CLOSED domains included (the singular mode is
+    dropped, like the bordered system of the oracle); gradient = the same solve (symmetric); at 40 x 32 also the reference's own pressures."""
+    ops = _ops()
+    rng = np.random.RandomState(ny * 131 + nx)
+    B = 3
+    rhs = _smooth(rng, (B, ny, nx), 1.0, passes=2) if min(ny, nx) > 4 else rng.randn(B, ny, nx).astype(np.float32)
+    if (ny, nx) == (40, 32):
+        rhs = np.load(os.path.join(GOLDEN, "poisson_40x32.npz"))["rhs_" + bd].astype(np.float32)
+    t = torch.tensor(rhs, device="cuda", requires_grad=True)
+    p = ops.pressure_solve_direct(t, bd == "closed")
+    w = torch.tensor(rng.randn(B, ny, nx).astype(np.float32), device="cuda")
+    (p * w).sum().backward()
+    direct = F.pressure_solve(torch.tensor(rhs), bd).numpy()
+    got = p.detach().cpu().numpy()
+    if bd == "closed":
+        assert float(np.abs(got.mean((1, 2))).max()) < 1e-4 * float(np.abs(got).max())        # the mean-free solution
+        direct, got = _demean(direct), _demean(got)
+    assert rel_err(got, direct) < 1e-5
+    # A p == rhs (minus its mean on closed domains: that component is outside the range of A)
+    target = rhs - rhs.mean((1, 2), keepdims=True) if bd == "closed" else rhs
+    assert float((F.laplace_apply(p.detach().cpu().double(), bd) - torch.tensor(target).double()).abs().max()) < 2e-5 * max(1.0, float(p.abs().max()))
+    gdirect = F.pressure_solve(w.cpu(), bd).numpy()
+    ggot = t.grad.cpu().numpy()
+    if bd == "closed":
+        gdirect, ggot = _demean(gdirect), _demean(ggot)
+    assert rel_err(ggot, gdirect) < 1e-5
+    if (ny, nx) == (40, 32):
+        ref = np.load(os.path.join(GOLDEN, "poisson_40x32.npz"))["p_" + bd]                # reference SparseCG(1e-6) pressures
+        mine = p.detach().cpu().numpy()
+        if bd == "closed":
+            ref, mine = _demean(ref), _demean(mine)
+        assert rel_err(mine, ref) < 1e-5
+
+
 def test_cg_iteration_semantics_guess_and_batch_independence():
     ops = _ops()
     rng = np.random.RandomState(1)

@@ -62,12 +62,12 @@ def _oracle_run(arrs, tgt, bd, solver=None):
     return traj, [x.grad for x in t]
 
 
-def _cuda_run(arrs, tgt, bd, accuracy):
+def _cuda_run(arrs, tgt, bd, accuracy, direct=False):
     from pde_control_b200 import ops
     t = [torch.tensor(a, device="cuda", requires_grad=True) for a in arrs]
     s, traj, iters = tuple(t), [], []
     for _ in range(16):
-        out = ops.incompressible_step(*s, 1.0, bd == "closed", accuracy=accuracy, max_iterations=2000)
+        out = ops.incompressible_step(*s, 1.0, bd == "closed", accuracy=accuracy, max_iterations=2000, direct=direct)
         s = out[:3]
         iters.append(out[4])
         traj.append([x.detach().cpu() for x in s])
@@ -101,6 +101,18 @@ def test_config3_trajectory_vs_oracle_at_size(bd):
     assert max_it < 2000
     assert state < 1e-4, (state, grad)
     assert grad < 1e-3, (state, grad)
+
+
+@pytest.mark.parametrize("bd", ["open", "closed"])
+def test_config3_trajectory_with_the_direct_solver_vs_oracle_at_size(bd):
+    """The same trajectory with the exact fast-diagonalisation solver (physics.SparseSciPy / direct=True): no accuracy knob, the
+    tolerances hold with an order of magnitude to spare."""
+    arrs, tgt = _inputs_at_size()
+    traj_o, grads_o = _oracle_run(arrs, tgt, bd)
+    traj_c, grads_c, _ = _cuda_run(arrs, tgt, bd, None, direct=True)
+    state, grad = _dist(traj_c, grads_c, traj_o, grads_o)
+    assert state < 1e-4 and grad < 1e-3, (state, grad)
+    assert state < 3e-5 and grad < 1e-4, (state, grad)
 
 
 @pytest.mark.parametrize("bd", ["open", "closed"])
