@@ -334,38 +334,45 @@ class FluidNotebook(object):
 
 
 class Config5Slab(object):
-    """BASELINE config 5 (N >= 2): 2048 x 2048, B = 1, projected steps forward + adjoint, the pressure solve slab-decomposed over the
-    ranks with the per-iteration exchange over NVLink peer memory (ops.SlabSolver -> pdec_cg_poisson_2d_slab).  The reference's
-    max_iterations = 2000 would cap the solve at this size (~4500 iterations to 1e-5), so max_iterations = 20000 and counts are reported."""
+    """BASELINE config 5 (N >= 2): 2048 x 2048, B = 1, projected steps forward + adjoint on a row-slab decomposed domain
+    (pde_control_b200/slab.py): NOTHING is replicated -- halo rows of rho / vy / vx for the advection and one halo row of the pressure
+    travel over NVLink peer memory (pdec_halo_push_rows / _pull_rows), the pressure solve is the slab CG with its per-iteration exchange
+    inside the kernel (pdec_cg_poisson_2d_slab); no NCCL call on the data path.  The reference's max_iterations = 2000 would cap the
+    solve at this size (~3000-4500 iterations to 1e-5), so max_iterations = 20000 and the counts are reported."""
     key = "config5_slab"
     dtype = "f32"
-    N, STEPS = 2048, 2
+    N, STEPS, HALO = 2048, 2, 4
 
     def __init__(self, device, rank, world):
-        from pde_control_b200 import ops
-        self.ops, self.dev, self.rank, self.world = ops, device, rank, world
+        import torch.distributed as dist
+        from pde_control_b200 import ops, slab
+        self.ops, self.dev, self.rank, self.world, self.dist = ops, device, rank, world, dist
         n = self.N
         g = torch.Generator(device=device)
-        g.manual_seed(3)                                    # the same (replicated) fields on every rank
+        g.manual_seed(3)                                    # every rank builds the same global fields, then keeps only its slab
 
         def smooth(x, passes=6):
             for _ in range(passes):
                 x = (x + torch.roll(x, 1, -1) + torch.roll(x, -1, -1) + torch.roll(x, 1, -2) + torch.roll(x, -1, -2)) / 5
             return x / x.abs().max()
-        self.rho0 = (smooth(torch.randn(1, n, n, device=device, generator=g)) > 0.2).float()
-        self.vy0 = smooth(torch.randn(1, n + 1, n, device=device, generator=g))
-        self.vx0 = smooth(torch.randn(1, n, n + 1, device=device, generator=g))
-        self.target = (smooth(torch.randn(1, n, n, device=device, generator=g)) > 0.2).float()
-        self.solver = ops.SlabSolver(1, n, n)
+        rho0 = (smooth(torch.randn(1, n, n, device=device, generator=g)) > 0.2).float()
+        vy0 = smooth(torch.randn(1, n + 1, n, device=device, generator=g))
+        vx0 = smooth(torch.randn(1, n, n + 1, device=device, generator=g))
+        target = (smooth(torch.randn(1, n, n, device=device, generator=g)) > 0.2).float()
+        self.stepper = slab.SlabStepper(1, n, n, halo=self.HALO)
+        lay = self.stepper.layout
+        self.local = [t.clone() for t in self.stepper.scatter(rho0, vy0, vx0)]
+        self.target = target[:, lay.r0:lay.r1].contiguous()
+        del rho0, vy0, vx0, target
+        torch.cuda.empty_cache()
         self.cell_updates = n * n * self.STEPS             # the ranks share ONE domain: strong scaling
         self.its = []
 
     def step(self):
-        ops = self.ops
-        s = (self.rho0.clone().requires_grad_(True), self.vy0.clone().requires_grad_(True), self.vx0.clone().requires_grad_(True))
-        leaves, its = s, []
+        leaves = [t.clone().requires_grad_(True) for t in self.local]
+        s, its = tuple(leaves), []
         for _ in range(self.STEPS):
-            out = ops.incompressible_step(*s, 0.8, False, accuracy=1e-5, max_iterations=20000, slab=self.solver)
+            out = self.stepper.step(*s, 0.8, False, accuracy=1e-5, max_iterations=20000)
             s = out[:3]
             its.append(out[4])
         self.loss = ((s[0] - self.target) ** 2).sum() / 2
@@ -373,29 +380,38 @@ class Config5Slab(object):
         self.its = its
 
     def config(self):
-        return {"workload": "incompressible_flow 2048x2048 B=1 steps=%d OPEN fwd + adjoint, row slabs over %d GPUs, CG to 1e-5 (BASELINE config 5)"
-                            % (self.STEPS, self.world), "resolution": [self.N, self.N], "steps": self.STEPS,
-                "parallelism": "slab CG x%d over NVLink peer memory; advection / divergence / gradient replicated, pressure all-gathered (NCCL)"
-                               % self.world, "scaling": "strong"}
+        return {"workload": "incompressible_flow 2048x2048 B=1 steps=%d OPEN fwd + adjoint, row slabs over %d GPUs, CG to 1e-5 (BASELINE config 5); "
+                            "ms_per_step = one %d-step trajectory" % (self.STEPS, self.world, self.STEPS),
+                "resolution": [self.N, self.N], "steps": self.STEPS, "halo_rows": self.HALO,
+                "parallelism": "row slabs x%d: advection halos and the pressure halo over NVLink peer memory, slab CG with in-kernel exchange; "
+                               "nothing replicated, no NCCL on the data path" % self.world, "scaling": "strong"}
+
+    def extra(self):
+        its = [int(i.max()) for i in self.its]
+        return {"cg_iterations_forward": its, "halo_violations": int(self.stepper.halo_violations.item()), "halo_status": int(self.stepper.ex.status.item()),
+                "loss_local": float(self.loss.detach())}
 
     def solve_parity(self):
-        """One 2048^2 right-hand side through the slab solver against its own fp64 residual, |A p - rhs|_inf, and a solve-time figure."""
-        ops = self.ops
-        rhs = ops.mask_divergence(self.vy0, self.vx0, False)
+        """One 2048^2 right-hand side (the divergence of the timed velocity) through the slab solver, gathered, against its own fp64
+        residual |A p - rhs|_inf; and a solve-time figure.  Collective: every rank calls it."""
+        from pde_control_b200 import slab
+        ops, st = self.ops, self.stepper
+        div = ops.mask_divergence(self.local[1], self.local[2], False)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        p, iters, resid = self.solver.solve(rhs, False, 1e-5, 20000)
+        p, iters = slab._SlabSolve.apply(div, st, 0, 1e-5, 20000)
         e1.record()
         torch.cuda.synchronize()
-        pd = torch.nn.functional.pad(p.double(), (1, 1, 1, 1))
-        Ap = pd[:, 2:, 1:-1] + pd[:, :-2, 1:-1] + pd[:, 1:-1, 2:] + pd[:, 1:-1, :-2] - 4.0 * p.double()
-        true_res = float((Ap - rhs.double()).abs().max())
+        P, R = st.gather(p).double(), st.gather(div).double()
+        pd = torch.nn.functional.pad(P, (1, 1, 1, 1))
+        Ap = pd[:, 2:, 1:-1] + pd[:, :-2, 1:-1] + pd[:, 1:-1, 2:] + pd[:, 1:-1, :-2] - 4.0 * P
+        true_res = float((Ap - R).abs().max())
         k = int(iters.max())
         ms = e0.elapsed_time(e1)
-        return {"checked": True, "against": "fp64 evaluation of A p - rhs of the slab solve (rhs = divergence of the timed velocity)",
-                "iterations": k, "recurrence_residual": float(resid.max()), "true_residual_inf": true_res, "rhs_inf": float(rhs.abs().max()),
+        return {"checked": True, "against": "fp64 evaluation of A p - rhs of the gathered slab solve (rhs = divergence of the timed velocity)",
+                "iterations": k, "true_residual_inf": true_res, "rhs_inf": float(R.abs().max()),
                 "tolerance": {"true_residual_inf": 1e-3}, "ok": k > 0 and true_res < 1e-3, "ms_per_solve": ms, "us_per_iteration": ms * 1e3 / max(k, 1)}
 
     def close(self):
-        self.solver.close()
+        self.stepper.close()

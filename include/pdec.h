@@ -43,6 +43,13 @@ extern "C" {
 #define PDEC_MODE_REPLICATE 1
 #define PDEC_MODE_CIRCULAR 2
 
+/* The `closed` argument of the 2-D entry points (which sides of the domain are SOLID; Domain boundaries, PF/physics/domain.py:13-35 with
+ * Material.solid, material.py:8-58): 0 = every side OPEN, 1 = every side CLOSED, or per side -- the reference's
+ * Domain(..., boundaries=[(lower_y, upper_y), (lower_x, upper_x)]) -- with PDEC_CLOSED_SIDES(ylo, yhi, xlo, xhi), each 0 / 1.
+ * A solid side zeroes its boundary faces (solver_api.py:111-121) and does not count as an accessible neighbour in the matrix diagonal
+ * (sparse.py:186-213); an open side counts. */
+#define PDEC_CLOSED_SIDES(ylo, yhi, xlo, xhi) (0x10 | ((ylo) ? 1 : 0) | ((yhi) ? 2 : 0) | ((xlo) ? 4 : 0) | ((xhi) ? 8 : 0))
+
 /* FieldEffect modes, PF/physics/field/effect.py:48-53 */
 #define PDEC_EFFECT_NONE 0
 #define PDEC_EFFECT_GROW 1 /* u += f*dt */
@@ -317,6 +324,24 @@ int pdec_cg_slab_comm_init(void* comm, int B, int nx, void* stream);
 int pdec_cg_poisson_2d_slab(const float* rhs, float* p, int* iterations, float* residual, int B, int ny_local, int nx,
                             int ny_global, int row0, int closed, float accuracy, int max_iterations, const pdec_slab_comm* comm,
                             void* workspace, size_t workspace_bytes, void* stream);
+/* Halo rows of row-slab decomposed fields, exchanged over NVLink peer memory (SURVEY 8e / 8b "halo pack/unpack for slabs").  The reference
+ * has no distributed code; these entries are what a slab-decomposed IncompressibleFlow.step (PF/physics/fluid.py:90-114) needs around
+ * advect.semi_lagrangian (advect.py:24-40: rows within max|v| dt / dx + 1 of a seam) and StaggeredGrid.gradient (staggered_grid.py:219-231:
+ * one row of the pressure).  field [B, rows_total, row_len] (row_len = nx, or nx + 1 for the x-face component).
+ * _push_rows STORES rows [row_first, row_first + nrows) of every batch element straight into the NEIGHBOUR's inbox (peer_inbox = the
+ * neighbour's inbox as mapped into this process: pdec_comm_alloc / pdec_comm_open); _pull_rows waits for the rows the neighbour pushed
+ * and writes (accumulate = 0) or adds (accumulate = 1: the adjoint of an exchange is the reverse exchange, summed) them to rows
+ * [row_first, row_first + nrows) of its own field.  side: 0 = the rows travel UP (they arrive from the rank below and become a lower
+ * halo), 1 = DOWN.  Both ends pass the same `seq` (>= 1, incremented by the host for every exchange on an inbox; a sender is never more
+ * than one exchange ahead, which the two parity slots of the inbox absorb).  Every float travels in an 8-byte word with its sequence
+ * number: no fence, no NCCL call, no host round trip.  status (device int, may be NULL) <- -1 if a word did not arrive within ~10 s.
+ * An inbox holds pdec_halo_inbox_bytes(B, row_len, max_rows) bytes, zeroed ONCE by pdec_halo_inbox_init before any peer pushes. */
+size_t pdec_halo_inbox_bytes(int B, int row_len, int max_rows);
+int pdec_halo_inbox_init(void* inbox, int B, int row_len, int max_rows, void* stream);
+int pdec_halo_push_rows(const float* field, int B, int rows_total, int row_len, int row_first, int nrows, void* peer_inbox, int side,
+                        unsigned seq, int max_rows, void* stream);
+int pdec_halo_pull_rows(float* field, int B, int rows_total, int row_len, int row_first, int nrows, const void* my_inbox, int side,
+                        unsigned seq, int accumulate, int max_rows, int* status, void* stream);
 /* peer-visible device allocations for the above: cudaMalloc + CUDA IPC handle (64 bytes, exchanged by the host program) */
 int pdec_comm_alloc(size_t bytes, void** ptr, unsigned char* handle64);
 int pdec_comm_open(const unsigned char* handle64, void** ptr);

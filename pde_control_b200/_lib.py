@@ -97,6 +97,11 @@ _SIGNATURES = {
     "pdec_cg_slab_comm_init": (_c.c_int, [_P, _c.c_int, _c.c_int, _P]),
     "pdec_cg_poisson_2d_slab": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_float,
                                             _c.c_int, _P, _P, _c.c_size_t, _P]),
+    "pdec_halo_inbox_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int]),
+    "pdec_halo_inbox_init": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_int, _P]),
+    "pdec_halo_push_rows": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P, _c.c_int, _c.c_uint, _c.c_int, _P]),
+    "pdec_halo_pull_rows": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P, _c.c_int, _c.c_uint, _c.c_int, _c.c_int,
+                                        _P, _P]),
     "pdec_comm_alloc": (_c.c_int, [_c.c_size_t, _c.POINTER(_P), _c.POINTER(_c.c_ubyte)]),
     "pdec_comm_open": (_c.c_int, [_c.POINTER(_c.c_ubyte), _c.POINTER(_P)]),
     "pdec_comm_close": (_c.c_int, [_P]),

@@ -24,11 +24,11 @@ SOURCES = {
     "fluid.cu": ["-fmad=false"],
     "cg.cu": [],
     "cg_tiled.cu": [],
-    "cg_pair.cu": [],
     "resample.cu": ["-fmad=false"],
     "laplace_matrix.cu": [],
     "host_pipeline.cu": [],
     "poisson_direct.cu": [],
+    "halo.cu": [],
     "noalloc.cu": [],               # static-scratch entry point: host wrapper only, no kernel of its own
 }
 

@@ -27,9 +27,10 @@ namespace pdec {
 __device__ __forceinline__ unsigned cell_nibble(int i, int j, int ny, int nx) {
     return (i > 0 ? 1u : 0u) | (i < ny - 1 ? 2u : 0u) | (j > 0 ? 4u : 0u) | (j < nx - 1 ? 8u : 0u);
 }
-__device__ __forceinline__ float cell_diag(unsigned nib, int closed) {
-    if (!closed) return -4.0f;
-    const float d = -(float)__popc(nib);
+// diagonal = -(accessible neighbours) clamped <= -1 (sparse.py:186-213): an in-domain neighbour always counts, the outside counts on
+// OPEN sides only.  `sides` = 4-bit mask of SOLID sides in the nibble's bit order (y-lower, y-upper, x-lower, x-upper)
+__device__ __forceinline__ float cell_diag(unsigned nib, unsigned sides) {
+    const float d = -(float)(4 - __popc(~nib & 0xFu & sides));
     return fminf(d, -1.0f);
 }
 // sum in the column order of the sorted sparse row (sparse.py:173-176): i-1, j-1, centre, j+1, i+1
@@ -162,157 +163,9 @@ __global__ void __launch_bounds__(THREADS, 1) cg_smem_kernel(const float* __rest
 }
 
 // -------------------------------------------------------------------------------------------------------------
-// cg_tile_kernel: the production one-CTA-per-element kernel for grids up to 128 x 128.
-// Thread (tx, ty) of a 32 x TY block owns the cells (i = 4*ty + ky, j = tx + 32*kx), kx, ky < 4: a warp always touches 32
-// consecutive columns of one row (conflict-free shared memory, affine offsets).  r, Am and the thread's OWN m values live in
-// registers; shared memory holds m with a one-cell halo ring (pitch nx+2) and x.  The halo ring removes every boundary
-// predicate from the 5-point stencil: it stays 0 for the open operator (p = 0 outside) and mirrors the border cell for the
-// closed one (sum of in-domain neighbours - count * centre == sum of 4 - 4 * centre with mirrored ghosts).
-// Per cell and iteration: 4 LDS + 1 LDS/STS pair (x) + 1 STS (m) and ~12 FP32 ops; beta = (r.Am)/(m.Am) is formed once
-// per iteration (the reference divides per element, blas.py:54 -- same value up to rounding; CG iterates are not the
-// parity oracle).
-// -------------------------------------------------------------------------------------------------------------
-template <int TY, bool FULL>
-__global__ void __launch_bounds__(32 * TY, 1) cg_tile_kernel(const float* __restrict__ rhs, const float* __restrict__ guess, float* __restrict__ out,
-                                                             int* __restrict__ iters, float* __restrict__ resid, int ny, int nx, int closed,
-                                                             float accuracy, int max_it) {
-    constexpr int THREADS = 32 * TY;
-    extern __shared__ __align__(16) float smem_dyn[];
-    __shared__ float redA[2][32], redB[2][32];
-    const int pitch = nx + 2;
-    const int padded = (ny + 2) * pitch;
-    float* sm_m = smem_dyn;                 // [(ny+2) x pitch], halo ring
-    float* sm_x = smem_dyn + padded;        // same indexing (halo unused)
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const size_t base = (size_t)blockIdx.x * ny * nx;
-    float r[16], am[16], m[16];
-    unsigned valid = 0u;                    // bit (ky*4+kx): the cell exists
-    for (int q = threadIdx.x; q < padded; q += THREADS) { sm_m[q] = 0.0f; sm_x[q] = 0.0f; }
-    __syncthreads();
-#pragma unroll
-    for (int ky = 0; ky < 4; ++ky)
-#pragma unroll
-        for (int kx = 0; kx < 4; ++kx) {
-            const int c = ky * 4 + kx, i = 4 * ty + ky, j = tx + 32 * kx;
-            r[c] = 0.0f; am[c] = 0.0f; m[c] = 0.0f;
-            if (i < ny && j < nx) {
-                valid |= 1u << c;
-                r[c] = rhs[base + (size_t)i * nx + j];
-                if (guess != nullptr) {
-                    const float g0 = guess[base + (size_t)i * nx + j];
-                    const int off = (i + 1) * pitch + j + 1;
-                    sm_x[off] = g0;
-                    sm_m[off] = g0;
-                    if (closed) {
-                        if (i == 0) sm_m[off - pitch] = g0;
-                        if (i == ny - 1) sm_m[off + pitch] = g0;
-                        if (j == 0) sm_m[off - 1] = g0;
-                        if (j == nx - 1) sm_m[off + 1] = g0;
-                    }
-                }
-            }
-        }
-    const int off0 = (4 * ty + 1) * pitch + tx + 1, sy = pitch;
-    if (guess != nullptr) {                 // momentum = k - A x0   (blas.py:24-26)
-        __syncthreads();
-#pragma unroll
-        for (int ky = 0; ky < 4; ++ky)
-#pragma unroll
-            for (int kx = 0; kx < 4; ++kx) {
-                const int c = ky * 4 + kx;
-                if (FULL || (valid & (1u << c))) {
-                    const int off = off0 + ky * sy + kx * 32;
-                    r[c] -= (sm_m[off - pitch] + sm_m[off - 1]) + (sm_m[off + 1] + sm_m[off + pitch]) - 4.0f * sm_m[off];
-                }
-            }
-        __syncthreads();
-    }
-    float rmax = 0.0f, dummy = 0.0f;
-    auto publish_m = [&]() {                // own m -> shared memory (+ mirrored ghosts for the closed operator)
-#pragma unroll
-        for (int ky = 0; ky < 4; ++ky)
-#pragma unroll
-            for (int kx = 0; kx < 4; ++kx) {
-                const int c = ky * 4 + kx;
-                if (FULL || (valid & (1u << c))) {
-                    const int off = off0 + ky * sy + kx * 32;
-                    sm_m[off] = m[c];
-                    if (closed) {
-                        const int i = 4 * ty + ky, j = tx + 32 * kx;
-                        if (i == 0) sm_m[off - pitch] = m[c];
-                        if (i == ny - 1) sm_m[off + pitch] = m[c];
-                        if (j == 0) sm_m[off - 1] = m[c];
-                        if (j == nx - 1) sm_m[off + 1] = m[c];
-                    }
-                }
-            }
-    };
-    auto matvec = [&]() {                   // vertical neighbours inside the thread's 4-row strip come from registers
-#pragma unroll
-        for (int ky = 0; ky < 4; ++ky)
-#pragma unroll
-            for (int kx = 0; kx < 4; ++kx) {
-                const int c = ky * 4 + kx;
-                if (FULL || (valid & (1u << c))) {
-                    const int off = off0 + ky * sy + kx * 32;
-                    const float up = (FULL && ky > 0) ? m[c - 4 >= 0 ? c - 4 : 0] : sm_m[off - pitch];
-                    const float dn = (FULL && ky < 3) ? m[c + 4 <= 15 ? c + 4 : 15] : sm_m[off + pitch];
-                    am[c] = (up + sm_m[off - 1]) + (sm_m[off + 1] + dn) - 4.0f * m[c];
-                }
-            }
-    };
-#pragma unroll
-    for (int c = 0; c < 16; ++c) { m[c] = r[c]; rmax = fmaxf(rmax, fabsf(r[c])); }
-    publish_m();
-    block_reduce2<THREADS>(dummy, rmax, redB, true);     // its __syncthreads also orders publish_m before the matvec
-    matvec();
-    int it = 0;
-    while (it < max_it && (accuracy <= 0.0f || rmax >= accuracy)) {
-        float s1 = 0.0f, s2 = 0.0f;
-#pragma unroll
-        for (int c = 0; c < 16; ++c) { s1 += m[c] * am[c]; s2 += m[c] * r[c]; }
-        block_reduce2<THREADS>(s1, s2, redA, false);
-        const float tmp = s1, a = div_no_nan(s2, tmp);
-        float s3 = 0.0f, mx = 0.0f;
-#pragma unroll
-        for (int ky = 0; ky < 4; ++ky)
-#pragma unroll
-            for (int kx = 0; kx < 4; ++kx) {
-                const int c = ky * 4 + kx;
-                if (FULL || (valid & (1u << c))) {
-                    const int off = off0 + ky * sy + kx * 32;
-                    sm_x[off] += a * m[c];
-                    r[c] -= a * am[c];
-                    s3 += r[c] * am[c];
-                    mx = fmaxf(mx, fabsf(r[c]));
-                }
-            }
-        block_reduce2<THREADS>(s3, mx, redB, true);
-        const float beta = div_no_nan(s3, tmp);
-#pragma unroll
-        for (int c = 0; c < 16; ++c) m[c] = r[c] - beta * m[c];
-        publish_m();                        // all stencil reads of the old m completed before reduction A's barrier
-        __syncthreads();
-        matvec();
-        rmax = mx;
-        ++it;
-    }
-#pragma unroll
-    for (int ky = 0; ky < 4; ++ky)
-#pragma unroll
-        for (int kx = 0; kx < 4; ++kx) {
-            const int c = ky * 4 + kx, i = 4 * ty + ky, j = tx + 32 * kx;
-            if (FULL || (valid & (1u << c))) out[base + (size_t)i * nx + j] = sm_x[off0 + ky * sy + kx * 32];
-        }
-    if (threadIdx.x == 0) {
-        if (iters) iters[blockIdx.x] = it;
-        if (resid) resid[blockIdx.x] = rmax;
-    }
-}
-
-// -------------------------------------------------------------------------------------------------------------
 // cg_block_kernel: production one-CTA-per-element kernel for grids up to 128 x 128 (second generation).
-// cg_tile_kernel is bound by shared-memory instruction issue (88 LDS/STS per thread and iteration + 40 reduction shuffles on
+// An earlier tile kernel (4 x 4 cells per thread, vectors in shared memory) was bound by shared-memory instruction issue (88 LDS/STS per
+// thread and iteration + 40 reduction shuffles on
 // 32 warps).  Here a thread owns a BLOCK of 8 rows x 4 consecutive columns (cells i = 8*warp + ky, j = 4*lane + kx):
 //   * r, Am, m of the 32 cells stay in registers (96 registers; 16 warps x 128 registers fill the register file);
 //   * left/right neighbours come from registers or ONE shuffle per row and side; up/down neighbours from registers except
@@ -422,16 +275,17 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
     unsigned valid = 0u;
     // diagonal = dcol[kx] + drow[ky]
     float dcol[4], drow[8];
-    const float cf = closed ? 1.0f : 0.0f;
+    // `closed` = 4-bit mask of solid sides (pdec_closed_sides): a cell on a solid side has one accessible neighbour fewer
 #pragma unroll
-    for (int kx = 0; kx < 4; ++kx) dcol[kx] = -4.0f + cf * ((j0 + kx == 0 ? 1.0f : 0.0f) + (j0 + kx == nx - 1 ? 1.0f : 0.0f));
+    for (int kx = 0; kx < 4; ++kx) dcol[kx] = -4.0f + ((j0 + kx == 0 && (closed & 4)) ? 1.0f : 0.0f) + ((j0 + kx == nx - 1 && (closed & 8)) ? 1.0f : 0.0f);
 #pragma unroll
-    for (int ky = 0; ky < 8; ++ky) drow[ky] = cf * ((i0 + ky == 0 ? 1.0f : 0.0f) + (i0 + ky == ny - 1 ? 1.0f : 0.0f));
+    for (int ky = 0; ky < 8; ++ky) drow[ky] = ((i0 + ky == 0 && (closed & 1)) ? 1.0f : 0.0f) + ((i0 + ky == ny - 1 && (closed & 2)) ? 1.0f : 0.0f);
     const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     for (int q = threadIdx.x; q < (2 * WARPS + 2) * 32; q += 32 * WARPS) sm_e[q] = zero4;
     // staggered component bases of this batch element and the boundary-face mask (closed: solid boundary faces are 0)
     // (recomputed in the epilogue instead of being kept live across the iteration loop, whose register budget is full)
-    auto fmask = [&](int idx, int n) -> float { return (closed && (idx == 0 || idx == n)) ? 0.0f : 1.0f; };
+    auto fmask_y = [&](int idx) -> float { return ((idx == 0 && (closed & 1)) || (idx == ny && (closed & 2))) ? 0.0f : 1.0f; };
+    auto fmask_x = [&](int idx) -> float { return ((idx == 0 && (closed & 4)) || (idx == nx && (closed & 8))) ? 0.0f : 1.0f; };
 #pragma unroll
     for (int ky = 0; ky < 8; ++ky) {
         float4 g4 = zero4, r4 = zero4;
@@ -447,8 +301,8 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
                     const float* x = pa.in_x + (size_t)blockIdx.x * ny * (nx + 1);
                     float v;
                     if (PROJ == PROJ_FWD) {          // mask_divergence_fwd_kernel
-                        const float dy = __fsub_rn(__fmul_rn(y[(size_t)(i + 1) * nx + j], fmask(i + 1, ny)), __fmul_rn(y[(size_t)i * nx + j], fmask(i, ny)));
-                        const float dx = __fsub_rn(__fmul_rn(x[(size_t)i * (nx + 1) + j + 1], fmask(j + 1, nx)), __fmul_rn(x[(size_t)i * (nx + 1) + j], fmask(j, nx)));
+                        const float dy = __fsub_rn(__fmul_rn(y[(size_t)(i + 1) * nx + j], fmask_y(i + 1)), __fmul_rn(y[(size_t)i * nx + j], fmask_y(i)));
+                        const float dx = __fsub_rn(__fmul_rn(x[(size_t)i * (nx + 1) + j + 1], fmask_x(j + 1)), __fmul_rn(x[(size_t)i * (nx + 1) + j], fmask_x(j)));
                         v = __fadd_rn(dy, dx);
                         if (pa.store_rhs != nullptr) pa.store_rhs[base + (size_t)i * nx + j] = v;
                     } else {                         // subtract_gradient_bwd_kernel, the g_p output (interior faces only)
@@ -642,7 +496,7 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
         };
         auto face_y = [&](int i, int j) {
             const size_t o = (size_t)i * nx + j;
-            const float mk = fmask(i, ny);
+            const float mk = fmask_y(i);
             float res;
             if (PROJ == PROJ_FWD) {              // subtract_gradient_fwd_kernel: replicate pad -> boundary-face gradient 0
                 float gr = 0.0f;
@@ -656,7 +510,7 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
         };
         auto face_x = [&](int i, int j) {
             const size_t o = (size_t)i * (nx + 1) + j;
-            const float mk = fmask(j, nx);
+            const float mk = fmask_x(j);
             float res;
             if (PROJ == PROJ_FWD) {
                 float gr = 0.0f;
@@ -684,10 +538,6 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_block_kernel(const float* __
         }
     }
 }
-
-// cg_pair.cu: one batch element on a cluster of two CTAs (128 x 128, zero guess)
-int cg_pair_launch(const float* rhs, float* p, int* iterations, float* residual, int B, int closed, float accuracy, int max_iterations,
-                   bool p2p, cudaStream_t st);
 
 // -------------------------------------------------------------------------------------------------------------
 // cg_block_masked_kernel: the on-chip block kernel for a domain with obstacles (any ny <= 8 * WARPS, nx <= 128, zero guess).
@@ -1040,24 +890,6 @@ extern "C" size_t pdec_cg_poisson_2d_workspace_bytes(int B, int ny, int nx) {
     return streaming > tiled ? streaming : tiled;
 }
 
-template <int TY, bool FULL>
-static int launch_tile_(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
-                       int closed, float accuracy, int max_iterations, cudaStream_t st) {
-    const size_t smem = (size_t)2 * (ny + 2) * (nx + 2) * sizeof(float);
-    auto kernel = cg_tile_kernel<TY, FULL>;
-    if (smem > 48 * 1024 && cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
-        return PDEC_ERR_CUDA_LAUNCH;
-    kernel<<<B, 32 * TY, smem, st>>>(rhs, guess, p, iterations, residual, ny, nx, closed, accuracy, max_iterations);
-    return PDEC_OK;
-}
-
-template <int TY>
-static int launch_tile(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
-                       int closed, float accuracy, int max_iterations, cudaStream_t st) {
-    if (ny == 4 * TY && nx == 128) return launch_tile_<TY, true>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
-    return launch_tile_<TY, false>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
-}
-
 template <int WARPS>
 static int launch_block(const float* rhs, const float* guess, float* p, int* iterations, float* residual, int B, int ny, int nx,
                         int closed, float accuracy, int max_iterations, cudaStream_t st, bool fused) {
@@ -1096,7 +928,7 @@ static int project_2d(float* p, int* iterations, float* residual, int B, int ny,
     pa.dxx = (float)((double)size_x / nx);
     pa.dx0 = pa.dxy;
     cudaStream_t st = (cudaStream_t)stream;
-    closed = closed ? 1 : 0;
+    closed = (int)pdec_closed_sides(closed);
     int rc;
     if (ny > 64) rc = launch_block_proj<16, PROJ>(p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, pa, st);
     else if (ny > 32) rc = launch_block_proj<8, PROJ>(p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, pa, st);
@@ -1153,31 +985,16 @@ extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p
     const bool on_chip = !whole_batch && (long long)ny * nx <= PDEC_CG_SMEM_MAX_CELLS;
     if (!on_chip && workspace_bytes < pdec_cg_poisson_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
     cudaStream_t st = (cudaStream_t)stream;
-    closed = closed ? 1 : 0;
+    const int closed_arg = closed;                    // forwarded unchanged to the tiled entry, which normalises it itself
+    closed = (int)pdec_closed_sides(closed);
     const long long N = (long long)ny * nx;
     int rc = PDEC_OK;
-    if (on_chip && ny == 128 && nx == 128 && guess == nullptr && (variant == 6 || variant == 7)) {
-        // two SMs per element (cg_pair.cu; 6 = hardware cluster barriers, 7 = mbarrier hand-shake).  Measured SLOWER than one CTA per
-        // element (1.90 / 2.47 us per iteration against 1.78, profiles/r1p_cg_pair.md): selector only, never the default
-        rc = cg_pair_launch(rhs, p, iterations, residual, B, closed, accuracy, max_iterations, variant == 7, st);
-        if (rc != PDEC_OK) return rc;
-        PDEC_CHECK_LAUNCH();
-        return PDEC_OK;
-    }
     if (on_chip && ny <= 128 && nx <= 128 && (variant == 0 || variant == 4 || variant == 5 || variant >= 6)) {
         // the one-reduction loop (variant 5) saves a barrier but costs a fifth dot product: measured slower (profiles/r1e_*)
         const bool fused = variant == 5;
         if (ny > 64) rc = launch_block<16>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st, fused);
         else if (ny > 32) rc = launch_block<8>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st, fused);
         else rc = launch_block<4>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st, fused);
-        if (rc != PDEC_OK) return rc;
-        PDEC_CHECK_LAUNCH();
-        return PDEC_OK;
-    }
-    if (on_chip && ny <= 128 && nx <= 128 && variant == 3) {
-        if (ny > 64) rc = launch_tile<32>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
-        else if (ny > 32) rc = launch_tile<16>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
-        else rc = launch_tile<8>(rhs, guess, p, iterations, residual, B, ny, nx, closed, accuracy, max_iterations, st);
         if (rc != PDEC_OK) return rc;
         PDEC_CHECK_LAUNCH();
         return PDEC_OK;
@@ -1198,7 +1015,7 @@ extern "C" int pdec_cg_poisson_2d(const float* rhs, const float* guess, float* p
     // medium grids: a grid of on-chip tiles with one grid-wide barrier per iteration (cg_tiled.cu); it declines what it cannot
     // keep resident (or an initial guess / the whole-batch rule), which then streams through L2 with the cooperative kernel below
     if (!whole_batch && guess == nullptr && variant == 0) {
-        rc = pdec_cg_poisson_2d_slab(rhs, p, iterations, residual, B, ny, nx, ny, 0, closed, accuracy, max_iterations, nullptr, workspace,
+        rc = pdec_cg_poisson_2d_slab(rhs, p, iterations, residual, B, ny, nx, ny, 0, closed_arg, accuracy, max_iterations, nullptr, workspace,
                                      workspace_bytes, stream);
         if (rc != PDEC_ERR_UNSUPPORTED_SIZE) return rc;
     }

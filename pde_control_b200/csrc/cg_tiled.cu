@@ -155,13 +155,13 @@ __global__ void __launch_bounds__(32 * WARPS, 1) cg_tiled_kernel(CgTiled P) {
     float r[32], am[32], m[32];
     unsigned valid = 0u;
     float dcol[4], drow[8];
-    const float cf = P.closed ? 1.0f : 0.0f;
+    // P.closed = 4-bit mask of solid sides of the GLOBAL domain (pdec_closed_sides)
 #pragma unroll
-    for (int kx = 0; kx < 4; ++kx) dcol[kx] = -4.0f + cf * ((j0 + kx == 0 ? 1.0f : 0.0f) + (j0 + kx == nx - 1 ? 1.0f : 0.0f));
+    for (int kx = 0; kx < 4; ++kx) dcol[kx] = -4.0f + ((j0 + kx == 0 && (P.closed & 4)) ? 1.0f : 0.0f) + ((j0 + kx == nx - 1 && (P.closed & 8)) ? 1.0f : 0.0f);
 #pragma unroll
     for (int ky = 0; ky < 8; ++ky) {
         const int gi = P.row0 + i0 + ky;
-        drow[ky] = cf * ((gi == 0 ? 1.0f : 0.0f) + (gi == P.ny_glob - 1 ? 1.0f : 0.0f));
+        drow[ky] = ((gi == 0 && (P.closed & 1)) ? 1.0f : 0.0f) + ((gi == P.ny_glob - 1 && (P.closed & 2)) ? 1.0f : 0.0f);
     }
     const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     for (int q = tid; q < (2 * WARPS + 2) * 32; q += THREADS) sm_e[q] = zero4;
@@ -542,7 +542,7 @@ extern "C" int pdec_cg_poisson_2d_slab(const float* rhs, float* p, int* iteratio
     cudaStream_t st = (cudaStream_t)stream;
     CgTiled P;
     P.rhs = rhs; P.out = p; P.iters = iterations; P.resid = residual;
-    P.B = B; P.ny_loc = ny_local; P.nx = nx; P.ny_glob = ny_global; P.row0 = row0; P.closed = closed ? 1 : 0; P.max_it = max_iterations;
+    P.B = B; P.ny_loc = ny_local; P.nx = nx; P.ny_glob = ny_global; P.row0 = row0; P.closed = (int)pdec_closed_sides(closed); P.max_it = max_iterations;
     P.accuracy = accuracy;
     P.tiles_y = tl.tiles_y; P.tiles_x = tl.tiles_x; P.tile_rows = tl.tile_rows;
     P.rank = rank; P.nranks = nranks;

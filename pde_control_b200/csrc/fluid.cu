@@ -376,32 +376,35 @@ __global__ void __launch_bounds__(256) curl_bwd_kernel(const float* __restrict__
 }
 
 // ---- masked divergence (solver_api.py:111-121, staggered_grid.py:201-209) ----------------------------
-__device__ __forceinline__ float face_mask(int idx, int n, int closed) { return (closed && (idx == 0 || idx == n)) ? 0.0f : 1.0f; }
+// boundary faces of a SOLID side are zeroed (with_hard_boundary_conditions, solver_api.py:111-121); `closed` = 4-bit side mask
+// (pdec_closed_sides): bits 0 / 1 = lower / upper side along y, bits 2 / 3 along x
+__device__ __forceinline__ float face_mask_y(int idx, int n, unsigned closed) { return ((idx == 0 && (closed & 1u)) || (idx == n && (closed & 2u))) ? 0.0f : 1.0f; }
+__device__ __forceinline__ float face_mask_x(int idx, int n, unsigned closed) { return ((idx == 0 && (closed & 4u)) || (idx == n && (closed & 8u))) ? 0.0f : 1.0f; }
 
 __global__ void __launch_bounds__(256) mask_divergence_fwd_kernel(const float* __restrict__ vy, const float* __restrict__ vx, float* __restrict__ div,
-                                                                  int ny, int nx, int closed) {
+                                                                  int ny, int nx, unsigned closed) {
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     if (i >= ny || j >= nx) return;
     const float* y = vy + (size_t)b * (ny + 1) * nx;
     const float* x = vx + (size_t)b * ny * (nx + 1);
-    const float dy = y[(size_t)(i + 1) * nx + j] * face_mask(i + 1, ny, closed) - y[(size_t)i * nx + j] * face_mask(i, ny, closed);
-    const float dx = x[(size_t)i * (nx + 1) + j + 1] * face_mask(j + 1, nx, closed) - x[(size_t)i * (nx + 1) + j] * face_mask(j, nx, closed);
+    const float dy = y[(size_t)(i + 1) * nx + j] * face_mask_y(i + 1, ny, closed) - y[(size_t)i * nx + j] * face_mask_y(i, ny, closed);
+    const float dx = x[(size_t)i * (nx + 1) + j + 1] * face_mask_x(j + 1, nx, closed) - x[(size_t)i * (nx + 1) + j] * face_mask_x(j, nx, closed);
     div[(size_t)b * ny * nx + (size_t)i * nx + j] = dy + dx;
 }
 
 __global__ void __launch_bounds__(256) mask_divergence_bwd_kernel(const float* __restrict__ g_div, float* __restrict__ g_vy, float* __restrict__ g_vx,
-                                                                  int ny, int nx, int closed, int accumulate) {
+                                                                  int ny, int nx, unsigned closed, int accumulate) {
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     const float* d = g_div + (size_t)b * ny * nx;
     if (i <= ny && j < nx) {
         const float lo = (i >= 1) ? d[(size_t)(i - 1) * nx + j] : 0.0f, hi = (i < ny) ? d[(size_t)i * nx + j] : 0.0f;
-        const float v = (lo - hi) * face_mask(i, ny, closed);
+        const float v = (lo - hi) * face_mask_y(i, ny, closed);
         float* p = g_vy + (size_t)b * (ny + 1) * nx + (size_t)i * nx + j;
         *p = accumulate ? *p + v : v;
     }
     if (i < ny && j <= nx) {
         const float lo = (j >= 1) ? d[(size_t)i * nx + j - 1] : 0.0f, hi = (j < nx) ? d[(size_t)i * nx + j] : 0.0f;
-        const float v = (lo - hi) * face_mask(j, nx, closed);
+        const float v = (lo - hi) * face_mask_x(j, nx, closed);
         float* p = g_vx + (size_t)b * ny * (nx + 1) + (size_t)i * (nx + 1) + j;
         *p = accumulate ? *p + v : v;
     }
@@ -409,20 +412,20 @@ __global__ void __launch_bounds__(256) mask_divergence_bwd_kernel(const float* _
 
 // ---- pressure-gradient subtraction (fluid.py:240-242, staggered_grid.py:219-231) ---------------------
 __global__ void __launch_bounds__(256) subtract_gradient_fwd_kernel(const float* __restrict__ vy, const float* __restrict__ vx, const float* __restrict__ p,
-                                                                    float* __restrict__ oy, float* __restrict__ ox, int ny, int nx, int closed,
+                                                                    float* __restrict__ oy, float* __restrict__ ox, int ny, int nx, unsigned closed,
                                                                     float dx0, float dxy, float dxx) {
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     const float* q = p + (size_t)b * ny * nx;
     if (i <= ny && j < nx) {
         const size_t o = (size_t)b * (ny + 1) * nx + (size_t)i * nx + j;
-        const float m = face_mask(i, ny, closed);
+        const float m = face_mask_y(i, ny, closed);
         float gr = 0.0f;                                   // replicate pad: boundary-face gradient is 0
         if (i >= 1 && i < ny) gr = (q[(size_t)i * nx + j] * dx0 - q[(size_t)(i - 1) * nx + j] * dx0) / dxy;
         oy[o] = vy[o] * m - gr * m;
     }
     if (i < ny && j <= nx) {
         const size_t o = (size_t)b * ny * (nx + 1) + (size_t)i * (nx + 1) + j;
-        const float m = face_mask(j, nx, closed);
+        const float m = face_mask_x(j, nx, closed);
         float gr = 0.0f;
         if (j >= 1 && j < nx) gr = (q[(size_t)i * nx + j] * dx0 - q[(size_t)i * nx + j - 1] * dx0) / dxx;
         ox[o] = vx[o] * m - gr * m;
@@ -430,18 +433,18 @@ __global__ void __launch_bounds__(256) subtract_gradient_fwd_kernel(const float*
 }
 
 __global__ void __launch_bounds__(256) subtract_gradient_bwd_kernel(const float* __restrict__ g_oy, const float* __restrict__ g_ox, float* __restrict__ g_vy,
-                                                                    float* __restrict__ g_vx, float* __restrict__ g_p, int ny, int nx, int closed,
+                                                                    float* __restrict__ g_vx, float* __restrict__ g_p, int ny, int nx, unsigned closed,
                                                                     float dx0, float dxy, float dxx, int accumulate) {
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     const float* gy = g_oy + (size_t)b * (ny + 1) * nx;
     const float* gx = g_ox + (size_t)b * ny * (nx + 1);
     if (g_vy != nullptr && i <= ny && j < nx) {
-        const float v = gy[(size_t)i * nx + j] * face_mask(i, ny, closed);
+        const float v = gy[(size_t)i * nx + j] * face_mask_y(i, ny, closed);
         float* p = g_vy + (size_t)b * (ny + 1) * nx + (size_t)i * nx + j;
         *p = accumulate ? *p + v : v;
     }
     if (g_vx != nullptr && i < ny && j <= nx) {
-        const float v = gx[(size_t)i * (nx + 1) + j] * face_mask(j, nx, closed);
+        const float v = gx[(size_t)i * (nx + 1) + j] * face_mask_x(j, nx, closed);
         float* p = g_vx + (size_t)b * ny * (nx + 1) + (size_t)i * (nx + 1) + j;
         *p = accumulate ? *p + v : v;
     }
@@ -708,7 +711,7 @@ extern "C" int pdec_mask_divergence_2d_fwd(const float* vy, const float* vx, flo
     if (B < 0 || ny < 2 || nx < 2 || B > 65535) return PDEC_ERR_INVALID_ARGUMENT;
     if (B == 0) return PDEC_OK;
     if (!vy || !vx || !div) return PDEC_ERR_INVALID_ARGUMENT;
-    mask_divergence_fwd_kernel<<<tiles(ny, nx, B), kBlock, 0, (cudaStream_t)stream>>>(vy, vx, div, ny, nx, closed ? 1 : 0);
+    mask_divergence_fwd_kernel<<<tiles(ny, nx, B), kBlock, 0, (cudaStream_t)stream>>>(vy, vx, div, ny, nx, pdec_closed_sides(closed));
     PDEC_CHECK_LAUNCH();
     return PDEC_OK;
 }
@@ -718,7 +721,7 @@ extern "C" int pdec_mask_divergence_2d_bwd(const float* g_div, float* g_vy, floa
     if (B < 0 || ny < 2 || nx < 2 || B > 65535) return PDEC_ERR_INVALID_ARGUMENT;
     if (B == 0) return PDEC_OK;
     if (!g_div || !g_vy || !g_vx) return PDEC_ERR_INVALID_ARGUMENT;
-    mask_divergence_bwd_kernel<<<tiles(ny + 1, nx + 1, B), kBlock, 0, (cudaStream_t)stream>>>(g_div, g_vy, g_vx, ny, nx, closed ? 1 : 0, accumulate);
+    mask_divergence_bwd_kernel<<<tiles(ny + 1, nx + 1, B), kBlock, 0, (cudaStream_t)stream>>>(g_div, g_vy, g_vx, ny, nx, pdec_closed_sides(closed), accumulate);
     PDEC_CHECK_LAUNCH();
     return PDEC_OK;
 }
@@ -729,7 +732,7 @@ extern "C" int pdec_subtract_pressure_gradient_2d_fwd(const float* vy, const flo
     if (B == 0) return PDEC_OK;
     if (!vy || !vx || !p || !vy_out || !vx_out) return PDEC_ERR_INVALID_ARGUMENT;
     const float dxy = (float)((double)size_y / ny), dxx = (float)((double)size_x / nx);
-    subtract_gradient_fwd_kernel<<<tiles(ny + 1, nx + 1, B), kBlock, 0, (cudaStream_t)stream>>>(vy, vx, p, vy_out, vx_out, ny, nx, closed ? 1 : 0,
+    subtract_gradient_fwd_kernel<<<tiles(ny + 1, nx + 1, B), kBlock, 0, (cudaStream_t)stream>>>(vy, vx, p, vy_out, vx_out, ny, nx, pdec_closed_sides(closed),
                                                                                                  dxy, dxy, dxx);
     PDEC_CHECK_LAUNCH();
     return PDEC_OK;
@@ -743,7 +746,7 @@ extern "C" int pdec_subtract_pressure_gradient_2d_bwd(const float* g_vy_out, con
     if (!g_vy_out || !g_vx_out) return PDEC_ERR_INVALID_ARGUMENT;
     const float dxy = (float)((double)size_y / ny), dxx = (float)((double)size_x / nx);
     subtract_gradient_bwd_kernel<<<tiles(ny + 1, nx + 1, B), kBlock, 0, (cudaStream_t)stream>>>(g_vy_out, g_vx_out, g_vy, g_vx, g_p, ny, nx,
-                                                                                                 closed ? 1 : 0, dxy, dxy, dxx, accumulate_v);
+                                                                                                 pdec_closed_sides(closed), dxy, dxy, dxx, accumulate_v);
     PDEC_CHECK_LAUNCH();
     return PDEC_OK;
 }

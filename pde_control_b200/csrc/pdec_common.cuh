@@ -6,6 +6,12 @@
 
 #define PDEC_FULL_MASK 0xffffffffu
 
+// `closed` argument of the 2-D entry points -> 4-bit side mask (bit 0: y-lower side solid, 1: y-upper, 2: x-lower, 3: x-upper).
+// 0 = OPEN everywhere, 1 (or any value without bit 4) = CLOSED everywhere, PDEC_CLOSED_SIDES(...) = per side (include/pdec.h).
+__host__ __device__ __forceinline__ unsigned pdec_closed_sides(int closed) {
+    return (closed & 0x10) ? (unsigned)(closed & 0xF) : (closed ? 0xFu : 0u);
+}
+
 namespace pdec {
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }

@@ -28,19 +28,24 @@ constexpr int DS_MAT = DS_N * DS_N;       // floats per spectral matrix
 // spectral block layout (floats): [0] Ey  (Ey[k][m], columns = eigenvectors of T_y)   [1] Ex   [2] Ex^T   [3] Ey^T
 //                                 [4] inv (inv[j][i] = 1 / (l_x(j) + l_y(i)), 0 for padding and for the singular mode)
 
-// 1-D eigenpairs: ends OPEN (outside contributes 0, diagonal -2) or CLOSED (diagonal -1 at the ends)
-__device__ __forceinline__ double eig_vec(int i, int k, int n, int closed) {
+// 1-D eigenpairs of tridiag(1, d, 1), d = -2 except -1 at an end whose side is SOLID (one accessible neighbour fewer); an OPEN end sees
+// a zero outside.  ends = (lower solid) | (upper solid) << 1.  Orthonormal closed forms: open-open: sine basis; solid-solid: cosine basis
+// (DCT-II); mixed: quarter-wave sines anchored at the open end.
+__device__ __forceinline__ double eig_vec(int i, int k, int n, int ends) {
     const double pi = 3.14159265358979323846;
-    if (closed) {
+    if (ends == 3) {
         const double c = k == 0 ? sqrt(1.0 / n) : sqrt(2.0 / n);
         return c * cos(pi * (i + 0.5) * k / n);
     }
-    return sqrt(2.0 / (n + 1)) * sin(pi * (i + 1.0) * (k + 1.0) / (n + 1));
+    if (ends == 0) return sqrt(2.0 / (n + 1)) * sin(pi * (i + 1.0) * (k + 1.0) / (n + 1));
+    const double theta = pi * (2.0 * k + 1.0) / (2.0 * n + 1.0), c = sqrt(4.0 / (2.0 * n + 1.0));
+    return c * sin((ends == 2 ? (i + 1.0) : (double)(n - i)) * theta);        // ends == 2: open below, solid above; ends == 1: mirrored
 }
-__device__ __forceinline__ double eig_val(int k, int n, int closed) {
+__device__ __forceinline__ double eig_val(int k, int n, int ends) {
     const double pi = 3.14159265358979323846;
-    if (closed) return -2.0 + 2.0 * cos(pi * k / n);
-    return -2.0 + 2.0 * cos(pi * (k + 1.0) / (n + 1));
+    if (ends == 3) return -2.0 + 2.0 * cos(pi * k / n);
+    if (ends == 0) return -2.0 + 2.0 * cos(pi * (k + 1.0) / (n + 1));
+    return -2.0 + 2.0 * cos(pi * (2.0 * k + 1.0) / (2.0 * n + 1.0));
 }
 
 __global__ void __launch_bounds__(256) poisson_direct_setup_kernel(float* __restrict__ spec, int ny, int nx, int closed) {
@@ -48,15 +53,16 @@ __global__ void __launch_bounds__(256) poisson_direct_setup_kernel(float* __rest
     if (idx >= DS_MAT) return;
     const int a = idx / DS_N, b = idx % DS_N;
     // E[k][m]: row = cell index k, column = eigenvector m
-    const float ey = (a < ny && b < ny) ? (float)eig_vec(a, b, ny, closed) : 0.0f;
-    const float ex = (a < nx && b < nx) ? (float)eig_vec(a, b, nx, closed) : 0.0f;
+    const int ends_y = closed & 3, ends_x = (closed >> 2) & 3;          // `closed` = 4-bit side mask (pdec_closed_sides)
+    const float ey = (a < ny && b < ny) ? (float)eig_vec(a, b, ny, ends_y) : 0.0f;
+    const float ex = (a < nx && b < nx) ? (float)eig_vec(a, b, nx, ends_x) : 0.0f;
     spec[0 * DS_MAT + idx] = ey;
     spec[1 * DS_MAT + idx] = ex;
     spec[2 * DS_MAT + b * DS_N + a] = ex;
     spec[3 * DS_MAT + b * DS_N + a] = ey;
     float inv = 0.0f;
     if (a < nx && b < ny) {              // inv[j = a][i = b]
-        const double l = eig_val(a, nx, closed) + eig_val(b, ny, closed);
+        const double l = eig_val(a, nx, ends_x) + eig_val(b, ny, ends_y);
         // the one singular mode (constants on a closed domain) -> 0; every other eigenvalue sum is <= -2 (1 - cos(pi / 128)) ~ -6e-4
         inv = (fabs(l) < 1e-9) ? 0.0f : (float)(1.0 / l);
     }
@@ -161,7 +167,7 @@ extern "C" int pdec_poisson_direct_2d_setup(void* spectral, size_t spectral_byte
     if (!spectral) return PDEC_ERR_INVALID_ARGUMENT;
     if (!pdec_poisson_direct_2d_supported(ny, nx)) return PDEC_ERR_UNSUPPORTED_SIZE;
     if (spectral_bytes < pdec_poisson_direct_2d_spectral_bytes()) return PDEC_ERR_WORKSPACE_TOO_SMALL;
-    poisson_direct_setup_kernel<<<(DS_MAT + 255) / 256, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float*>(spectral), ny, nx, closed ? 1 : 0);
+    poisson_direct_setup_kernel<<<(DS_MAT + 255) / 256, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float*>(spectral), ny, nx, (int)pdec_closed_sides(closed));
     PDEC_CHECK_LAUNCH();
     return PDEC_OK;
 }

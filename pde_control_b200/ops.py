@@ -240,6 +240,17 @@ def resample(data, coords, mode=MODE_CONSTANT):
     return _Resample.apply(data, coords, int(mode))
 
 
+def closed_code(closed):
+    """The C-ABI's `closed` argument: False / True (every side OPEN / CLOSED), an int code, or four flags (y-lower, y-upper, x-lower,
+    x-upper side solid) -> PDEC_CLOSED_SIDES (include/pdec.h)."""
+    if isinstance(closed, (tuple, list)):
+        ylo, yhi, xlo, xhi = (bool(c) for c in closed)
+        if ylo == yhi == xlo == xhi:
+            return int(ylo)
+        return 0x10 | int(ylo) | int(yhi) << 1 | int(xlo) << 2 | int(xhi) << 3
+    return int(closed)
+
+
 def _box(box, ny, nx):
     if box is None:
         return (0.0, 0.0, float(ny), float(nx))
@@ -385,7 +396,7 @@ class _MaskDivergence(torch.autograd.Function):
 
 
 def mask_divergence(vy, vx, closed):
-    return _MaskDivergence.apply(vy, vx, bool(closed))
+    return _MaskDivergence.apply(vy, vx, closed_code(closed))
 
 
 CG_STOP_PER_ELEMENT, CG_STOP_WHOLE_BATCH = 0, 1
@@ -399,7 +410,7 @@ def cg_poisson_raw(rhs, out, closed, accuracy, max_iterations, guess=None, itera
     ws = _lib.workspace(rhs.device, nbytes)
     with torch.cuda.device(rhs.device):
         _call("pdec_cg_poisson_2d", _lib.ptr(rhs), _lib.ptr(guess), _lib.ptr(out), _lib.ptr(iterations), _lib.ptr(residual), B, ny, nx,
-              int(closed), float(accuracy if accuracy is not None else 0.0), int(max_iterations), int(stop_mode), _lib.ptr(ws), nbytes,
+              closed_code(closed), float(accuracy if accuracy is not None else 0.0), int(max_iterations), int(stop_mode), _lib.ptr(ws), nbytes,
               _lib.stream_ptr())
 
 
@@ -408,14 +419,14 @@ _SPECTRAL = {}
 
 def _spectral_block(device, ny, nx, closed):
     """Eigenvector matrices + reciprocal eigenvalue sums of the (ny, nx, closed) Poisson matrix, built once on the device."""
-    key = (device.index if device.index is not None else torch.cuda.current_device(), int(ny), int(nx), bool(closed))
+    key = (device.index if device.index is not None else torch.cuda.current_device(), int(ny), int(nx), closed_code(closed))
     blk = _SPECTRAL.get(key)
     if blk is None:
         L = _lib.lib()
         nbytes = L.pdec_poisson_direct_2d_spectral_bytes()
         blk = torch.empty(nbytes // 4, device=device, dtype=torch.float32)
         with torch.cuda.device(device):
-            _call("pdec_poisson_direct_2d_setup", _lib.ptr(blk), nbytes, int(ny), int(nx), int(bool(closed)), _lib.stream_ptr())
+            _call("pdec_poisson_direct_2d_setup", _lib.ptr(blk), nbytes, int(ny), int(nx), closed_code(closed), _lib.stream_ptr())
         # built on the current stream; other streams (graph branches) only ever read it after this one has been joined
         torch.cuda.current_stream(device).synchronize()
         _SPECTRAL[key] = blk
@@ -452,7 +463,7 @@ class _PressureSolveDirect(torch.autograd.Function):
 
 def pressure_solve_direct(div, closed):
     """Exact pressure [B, ny, nx] of a rectangular domain without obstacles, grids up to 128 x 128; differentiable w.r.t. div."""
-    return _PressureSolveDirect.apply(div, bool(closed))
+    return _PressureSolveDirect.apply(div, closed_code(closed))
 
 
 def direct_solver_supported(ny, nx):
@@ -516,7 +527,7 @@ def cg_poisson_slab_raw(rhs, out, closed, accuracy, max_iterations, ny_global=No
     ws = _lib.workspace(rhs.device, nbytes)
     with torch.cuda.device(rhs.device):
         _call("pdec_cg_poisson_2d_slab", _lib.ptr(rhs), _lib.ptr(out), _lib.ptr(iterations), _lib.ptr(residual), B, ny, nx,
-              int(ny if ny_global is None else ny_global), int(row0), int(closed), float(accuracy if accuracy is not None else 0.0),
+              int(ny if ny_global is None else ny_global), int(row0), closed_code(closed), float(accuracy if accuracy is not None else 0.0),
               int(max_iterations), None if comm is None else ctypes.cast(ctypes.pointer(comm.struct), ctypes.c_void_p),
               _lib.ptr(ws), nbytes, _lib.stream_ptr())
 
@@ -552,7 +563,7 @@ def pressure_solve(div, closed, accuracy=1e-5, max_iterations=2000, gradient_acc
     """Returns (pressure, iterations[B] int32, residual[B]); only the pressure is differentiable (w.r.t. div)."""
     ga = accuracy if gradient_accuracy is None else gradient_accuracy
     gi = max_iterations if max_gradient_iterations is None else max_gradient_iterations
-    return _PressureSolve.apply(div, bool(closed), accuracy, int(max_iterations), ga, int(gi), guess, int(stop_mode))
+    return _PressureSolve.apply(div, closed_code(closed), accuracy, int(max_iterations), ga, int(gi), guess, int(stop_mode))
 
 
 class SlabSolver(object):
@@ -638,7 +649,7 @@ class _SubtractPressureGradient(torch.autograd.Function):
 
 def subtract_pressure_gradient(vy, vx, p, closed, box=None):
     b = _box(box, p.shape[1], p.shape[2])
-    return _SubtractPressureGradient.apply(vy, vx, p, bool(closed), b[2], b[3])
+    return _SubtractPressureGradient.apply(vy, vx, p, closed_code(closed), b[2], b[3])
 
 
 class _Normalize(torch.autograd.Function):
@@ -726,7 +737,7 @@ def _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, m
     b = _box(box, vx.shape[1], vy.shape[2])
     ga = accuracy if gradient_accuracy is None else gradient_accuracy
     gi = max_iterations if max_gradient_iterations is None else max_gradient_iterations
-    return _Project.apply(vy, vx, bool(closed), b[2], b[3], accuracy, int(max_iterations), ga, int(gi))
+    return _Project.apply(vy, vx, closed_code(closed), b[2], b[3], accuracy, int(max_iterations), ga, int(gi))
 
 
 def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
@@ -752,7 +763,7 @@ def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000
         return oy, ox, p, iters, div
     div = mask_divergence(vy, vx, closed)
     if slab is not None:
-        p, iters, _ = _PressureSolveSlab.apply(div, slab, bool(closed), accuracy, int(max_iterations))
+        p, iters, _ = _PressureSolveSlab.apply(div, slab, closed_code(closed), accuracy, int(max_iterations))
     else:
         p, iters, _ = pressure_solve(div, closed, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations, guess)
     oy, ox = subtract_pressure_gradient(vy, vx, p, closed, box)

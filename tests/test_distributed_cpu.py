@@ -104,3 +104,69 @@ def test_two_rank_slab_cg_single_exchange_formulation_matches_plain_cg(tmp_path)
             assert abs(int(iters[b]) - k) <= 1
             assert np.abs(got[b] - ref[0].numpy()).max() < 1e-7 * max(1.0, np.abs(ref.numpy()).max())
         assert exchanges == max(iters) + 2               # one exchange per iteration (+ the set-up pass and the final test)
+
+
+def _halo_worker(rank, world, port, out_dir):
+    """SlabLayout (pde_control_b200/slab.py: the index arithmetic of the peer-memory halo exchange) driven by a NumPy transport over gloo:
+    the haloed arrays must be the global array's rows, and the reverse exchange must be the exact transpose of the forward one."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from pde_control_b200.slab import SlabLayout, CENTRED, YFACE
+
+    def exchange(lay, local, kind, H, reverse=False, g=None):
+        """forward: local slab -> haloed array.  reverse: gradient of the haloed array g -> gradient of the slab (accumulated)."""
+        hlo, hhi = lay.halo_widths(H)
+        plan = lay.plan(kind, H)
+        if not reverse:
+            out = np.zeros((hlo + local.shape[0] + hhi,) + local.shape[1:], local.dtype)
+            out[hlo:hlo + local.shape[0]] = local
+            reqs = [dist.isend(torch.tensor(local[e["send_first"]:e["send_first"] + e["n"]].copy()), e["peer"]) for e in plan]
+            for e in plan:
+                buf = torch.empty((e["n"],) + local.shape[1:], dtype=torch.float64)
+                dist.recv(buf, e["peer"])
+                out[e["recv_first"]:e["recv_first"] + e["n"]] = buf.numpy()
+            for r in reqs:
+                r.wait()
+            return out
+        n_local = lay.local_rows(kind)
+        back = g[hlo:hlo + n_local].copy()
+        reqs = [dist.isend(torch.tensor(g[e["recv_first"]:e["recv_first"] + e["n"]].copy()), e["peer"]) for e in plan]
+        for e in plan:
+            buf = torch.empty((e["n"],) + g.shape[1:], dtype=torch.float64)
+            dist.recv(buf, e["peer"])
+            back[e["send_first"]:e["send_first"] + e["n"]] += buf.numpy()
+        for r in reqs:
+            r.wait()
+        return back
+
+    ny, nx, H = 24, 5, 3
+    lay = SlabLayout(ny, world, rank)
+    ok = True
+    dots = []
+    for kind, nrows in ((CENTRED, ny), (YFACE, ny + 1)):
+        glob = np.random.RandomState(nrows).randn(nrows, nx)        # the same global array on every rank
+        rng = np.random.RandomState(100 + rank)
+        local = glob[lay.r0:lay.r0 + lay.local_rows(kind)]
+        haloed = exchange(lay, local, kind, H)
+        hlo, hhi = lay.halo_widths(H)
+        ok = ok and np.array_equal(haloed, glob[lay.r0 - hlo:lay.r0 + lay.local_rows(kind) + hhi])
+        # <E x, y> summed over the ranks == <x, E^T y> summed over the ranks
+        y = rng.randn(*haloed.shape)
+        x = rng.randn(*local.shape)
+        lhs = float((exchange(lay, x, kind, H) * y).sum())
+        rhs = float((x * exchange(lay, None, kind, H, reverse=True, g=y)).sum())
+        t = torch.tensor([lhs, rhs], dtype=torch.float64)
+        dist.all_reduce(t)
+        dots.append(t.tolist())
+    np.save(os.path.join(out_dir, "halo_%d.npy" % rank), np.array([float(ok)] + [v for d in dots for v in d]))
+    dist.destroy_process_group()
+
+
+def test_slab_layout_halo_exchange_and_its_transpose_over_gloo(tmp_path):
+    for world in (2, 3):
+        port = _free_port()
+        mp.spawn(_halo_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+        for rank in range(world):
+            r = np.load(tmp_path / ("halo_%d.npy" % rank))
+            assert r[0] == 1.0, "haloed array != rows of the global array"
+            assert abs(r[1] - r[2]) < 1e-9 * max(1.0, abs(r[1])) and abs(r[3] - r[4]) < 1e-9 * max(1.0, abs(r[3]))
