@@ -25,12 +25,29 @@ def staggered_tensor(vy, vx):
     return t
 
 
-def fluid_step_case(pf, ny, nx, B, boundary, seed, steps, dt, solver="direct", buoyancy=0.0, density_effect=False, obstacles=()):
+BOUNDARY_SPECS = {
+    # name -> per axis a material name or a (lower, upper) pair (Domain boundaries, PF/physics/domain.py:13-35)
+    "open": "OPEN", "closed": "CLOSED", "no_slip": "NO_SLIP",
+    "open_top": [("CLOSED", "OPEN"), "CLOSED"],                 # the reference's own example: a box open at the top
+    "open_y_half_open_x": ["OPEN", ("CLOSED", "OPEN")],
+}
+
+
+def ref_boundaries(pf, name):
+    from phi.physics import material as M
+    spec = BOUNDARY_SPECS[name]
+    get = lambda n: getattr(M, n)
+    if isinstance(spec, str):
+        return get(spec)
+    return [get(e) if isinstance(e, str) else (get(e[0]), get(e[1])) for e in spec]
+
+
+def fluid_step_case(pf, ny, nx, B, boundary, seed, steps, dt, solver="direct", buoyancy=0.0, density_effect=False, obstacles=(),
+                    conserve_density=True):
     rng = np.random.RandomState(seed)
     rho = np.abs(_smooth(rng, (B, ny, nx), 1.0))
     vy, vx = random_staggered(rng, B, ny, nx, 1.5)
-    material = pf.OPEN if boundary == "open" else pf.CLOSED
-    dom = pf.Domain([ny, nx], boundaries=material)
+    dom = pf.Domain([ny, nx], boundaries=ref_boundaries(pf, boundary))
     fluid = pf.Fluid(dom, density=rho[..., None].copy(), velocity=staggered_tensor(vy, vx), batch_size=B, buoyancy_factor=buoyancy)
     effects = []
     if density_effect:          # a GROW effect on the density (what Inflow is, effect.py:62) given as a plain grid
@@ -38,7 +55,7 @@ def fluid_step_case(pf, ny, nx, B, boundary, seed, steps, dt, solver="direct", b
         src[:, ny // 4:ny // 2, nx // 3:2 * nx // 3] = 0.25
         effects = [pf.FieldEffect(pf.CenteredGrid(src, box=dom.box), ["density"], pf.GROW)]
     psolver = pf.SparseSciPy() if solver == "direct" else pf.SparseCG(accuracy=1e-7, max_iterations=5000)
-    phys = pf.IncompressibleFlow(pressure_solver=psolver)
+    phys = pf.IncompressibleFlow(pressure_solver=psolver, conserve_density=conserve_density)
     out = dict(rho0=rho, vy0=vy, vx0=vx, dt=dt, boundary=boundary, steps=steps, buoyancy=buoyancy)
     obs = [pf.Obstacle(pf.box[y0:y1, x0:x1]) for (y0, y1, x0, x1) in obstacles]
     if obstacles:
@@ -167,6 +184,13 @@ def main(pf, out_dir):
                         **fluid_step_case(pf, 32, 32, 2, "open", 17, 2, 0.5, obstacles=[(8, 14, 10, 20), (20, 26, 0, 5)]))
     np.savez_compressed(os.path.join(out_dir, "fluid_obstacle_closed_24x32.npz"),
                         **fluid_step_case(pf, 24, 32, 2, "closed", 19, 2, 0.5, obstacles=[(6, 12, 10, 20), (16, 24, 27, 32)]))
+    # SURVEY 8f N3 remainder: NO_SLIP (velocity extrapolated with 0 outside) and per-side mixed boundaries.  The reference's own
+    # conserve_density test (np.all over a ragged list, fluid.py:100) fails under NumPy 2 for mixed boundaries: conserve_density=False
+    np.savez_compressed(os.path.join(out_dir, "fluid_noslip_24x20.npz"), **fluid_step_case(pf, 24, 20, 2, "no_slip", 31, 3, 0.6, buoyancy=0.1))
+    np.savez_compressed(os.path.join(out_dir, "fluid_mixed_open_top_24x20.npz"),
+                        **fluid_step_case(pf, 24, 20, 2, "open_top", 37, 3, 0.6, buoyancy=0.1, conserve_density=False))
+    np.savez_compressed(os.path.join(out_dir, "fluid_mixed_half_open_x_20x24.npz"),
+                        **fluid_step_case(pf, 20, 24, 2, "open_y_half_open_x", 41, 3, 0.6, conserve_density=False))
     for name in EFFECT_SCENES:          # Inflow / Accelerator / FIX effects, sphere and union obstacles
         np.savez_compressed(os.path.join(out_dir, name + ".npz"), **effects_case(pf, name))
     np.savez_compressed(os.path.join(out_dir, "fluid_controlled_64.npz"), **controlled_case(pf, 64, 64, 2, 9, 1.0))

@@ -512,3 +512,177 @@ def incompressible_step_effects(rho, vy, vx, dt, geo, boundary, buoyancy=0.0, gr
     else:
         vy2, vx2, p, div = divergence_free(ay, ax, geo, boundary)
     return rho2, vy2, vx2, p
+
+
+# ---- SURVEY 8f N3 remainder: NO_SLIP and per-side mixed boundaries (test infrastructure only) --------------------------------
+# A Domain's boundaries may differ per side (PF/physics/domain.py:13-35).  Fields then carry a per-side extrapolation and
+#   * sampling goes through CenteredGrid._padded_resample (grid.py:211-216): pad ONE cell on every side with the side's mode, resample
+#     the padded array with 'replicate' at coordinates shifted by one cell;
+#   * paddings run in passes (backend_helper.py:22-36): every 'replicate' side first, then every 'constant' side;
+#   * solid sides zero their boundary faces (solver_api.py:111-121) and do not count as accessible neighbours (sparse.py:186-213).
+# `sides` below = [(lower, upper) per axis] of CONSTANT / REPLICATE; `solid` = (y-lower, y-upper, x-lower, x-upper) booleans.
+
+def sides_of(solid, friction=0):
+    """(density sides, velocity sides) from the per-side solid flags: Material.extrapolation_mode / vector_extrapolation_mode."""
+    rho = [(REPLICATE if solid[0] else CONSTANT, REPLICATE if solid[1] else CONSTANT),
+           (REPLICATE if solid[2] else CONSTANT, REPLICATE if solid[3] else CONSTANT)]
+    vel = [tuple(REPLICATE if (m == REPLICATE and friction == 0) else CONSTANT for m in pair) for pair in rho]
+    return rho, vel
+
+
+def _uniform(sides):
+    modes = {m for pair in sides for m in pair}
+    return modes.pop() if len(modes) == 1 else None
+
+
+def pad_sides(t, widths, sides):
+    """math.pad of a [B, ny, nx] array with per-side modes, in the reference's pass order."""
+    for single in (REPLICATE, CONSTANT):
+        for axis in (0, 1):
+            lo = widths[axis][0] if sides[axis][0] == single else 0
+            hi = widths[axis][1] if sides[axis][1] == single else 0
+            if lo or hi:
+                t = pad_axis(t, 1 + axis, lo, hi, single)
+    return t
+
+
+def sample_sides(field, iy, ix, sides):
+    """CenteredGrid.sample_at at index coordinates (iy, ix): one mode -> the backend's resample; per-side -> _padded_resample."""
+    mode = _uniform(sides)
+    if mode is not None:
+        return resample(field, torch.stack([iy, ix], -1), mode)
+    padded = pad_sides(field, [[1, 1], [1, 1]], sides)
+    return resample(padded, torch.stack([iy + 1.0, ix + 1.0], -1), REPLICATE)
+
+
+def _other_component_at_sides(v_other, other_axis, geo, sides, dtp):
+    """_other_component_at with the component padded per side along the target's axis."""
+    target_axis = 1 - other_axis
+    res_o, lo_o, sz_o = geo.component(other_axis)
+    _res_t, lo_t, _sz_t = geo.component(target_axis)
+    widths = [[0, 0], [0, 0]]
+    widths[target_axis] = [1, 1]
+    padded = pad_sides(v_other, widths, sides)
+    lo_p = lo_o.astype(np.float64).copy()
+    lo_p[target_axis] -= geo.dx[target_axis]
+    sz_p = sz_o.astype(np.float64).copy()
+    sz_p[target_axis] += 2 * geo.dx[target_axis]
+    res_p = list(res_o)
+    res_p[target_axis] += 2
+    lo_p, sz_p = lo_p.astype(np.float32), sz_p.astype(np.float32)
+    t = padded
+    for axis in (0, 1):
+        wu, wl = _half_weights(lo_p, sz_p, res_p, lo_t, axis, dtp)
+        t = (t[:, 1:, :] * wu + t[:, :-1, :] * wl) if axis == 0 else (t[:, :, 1:] * wu + t[:, :, :-1] * wl)
+    return t
+
+
+def advect_sides(rho, vy, vx, dt, geo, rho_sides, v_sides):
+    """F1 + F2 with per-side extrapolations -> (rho', advected vy, advected vx)."""
+    dtp = rho.dtype
+    dt_ = torch.tensor(dt, dtype=dtp)
+    py, px = _points(geo.res, geo.lower, geo.size, dtp)
+    cy, cx = velocity_at_centers(vy, vx, geo)
+    iy = _index_coords(py[None, :, None] - cy * dt_, geo.lower, geo.size, geo.res, 0, dtp)
+    ix = _index_coords(px[None, None, :] - cx * dt_, geo.lower, geo.size, geo.res, 1, dtp)
+    rho2 = sample_sides(rho, iy, ix, rho_sides)
+    out = []
+    for c, vc in ((0, vy), (1, vx)):
+        res_c, lo_c, sz_c = geo.component(c)
+        qy, qx = _points(res_c, lo_c, sz_c, dtp)
+        other = _other_component_at_sides(vx if c == 0 else vy, 1 - c, geo, v_sides, dtp)
+        uy, ux = (vc, other) if c == 0 else (other, vc)
+        iy = _index_coords(qy[None, :, None] - uy * dt_, lo_c, sz_c, res_c, 0, dtp)
+        ix = _index_coords(qx[None, None, :] - ux * dt_, lo_c, sz_c, res_c, 1, dtp)
+        out.append(sample_sides(vc, iy, ix, v_sides))
+    return rho2, out[0], out[1]
+
+
+_LU_SIDES = {}
+
+
+def _solve_sides_np(rhs, solid):
+    """fp64 sparse LU of the matrix with per-side boundary rules; singular (constants) only if every side is solid."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+    B, ny, nx = rhs.shape
+    key = (ny, nx, tuple(bool(s) for s in solid))
+    singular = all(solid)
+    if key not in _LU_SIDES:
+        N = ny * nx
+        idx = np.arange(N).reshape(ny, nx)
+        rows, cols, vals = [], [], []
+        acc = np.zeros((ny, nx))
+        for sl_a, sl_b in ((np.s_[1:, :], np.s_[:-1, :]), (np.s_[:, 1:], np.s_[:, :-1])):
+            a, b = idx[sl_a].ravel(), idx[sl_b].ravel()
+            rows += [a, b]
+            cols += [b, a]
+            vals += [np.ones(a.size), np.ones(a.size)]
+            acc[sl_a] += 1
+            acc[sl_b] += 1
+        # the outside counts as an accessible neighbour on OPEN sides
+        acc[0, :] += 0 if solid[0] else 1
+        acc[-1, :] += 0 if solid[1] else 1
+        acc[:, 0] += 0 if solid[2] else 1
+        acc[:, -1] += 0 if solid[3] else 1
+        rows.append(idx.ravel())
+        cols.append(idx.ravel())
+        vals.append(np.minimum(-acc.ravel(), -1.0))
+        A = sp.csc_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))), shape=(N, N))
+        if singular:
+            one = sp.csc_matrix(np.ones((N, 1)))
+            A = sp.bmat([[A, one], [one.T, None]], format="csc")
+        _LU_SIDES[key] = spl.splu(A)
+    lu = _LU_SIDES[key]
+    out = np.empty((B, ny, nx))
+    for b in range(B):
+        v = rhs[b].astype(np.float64).ravel()
+        if singular:
+            v = np.concatenate([v, [0.0]])
+        out[b] = lu.solve(v)[:ny * nx].reshape(ny, nx)
+    return out
+
+
+class _PressureSolveSides(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, div, solid):
+        ctx.solid = solid
+        return torch.from_numpy(_solve_sides_np(div.detach().numpy(), solid)).to(div.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        return torch.from_numpy(_solve_sides_np(g.detach().numpy(), ctx.solid)).to(g.dtype), None
+
+
+def divergence_free_sides(vy, vx, geo, solid):
+    my, mx = torch.ones_like(vy), torch.ones_like(vx)
+    if solid[0]:
+        my[:, 0, :] = 0
+    if solid[1]:
+        my[:, -1, :] = 0
+    if solid[2]:
+        mx[:, :, 0] = 0
+    if solid[3]:
+        mx[:, :, -1] = 0
+    vy, vx = vy * my, vx * mx
+    div = divergence(vy, vx)
+    p = _PressureSolveSides.apply(div, tuple(bool(s) for s in solid))
+    dtp = p.dtype
+    q = p * torch.tensor(float(geo.dx[0]), dtype=dtp)
+    qy, qx = pad_axis(q, 1, 1, 1, REPLICATE), pad_axis(q, 2, 1, 1, REPLICATE)
+    gy = (qy[:, 1:, :] - qy[:, :-1, :]) / torch.tensor(float(geo.dx[0]), dtype=dtp)
+    gx = (qx[:, :, 1:] - qx[:, :, :-1]) / torch.tensor(float(geo.dx[1]), dtype=dtp)
+    return vy - gy * my, vx - gx * mx, p, div
+
+
+def incompressible_step_sides(rho, vy, vx, dt, geo, solid, friction=0, buoyancy=0.0, gravity=-9.81, conserve_density=True):
+    """IncompressibleFlow.step (fluid.py:90-114) on a domain whose sides are solid per `solid` (NO_SLIP: all solid, friction 1)."""
+    rho_sides, v_sides = sides_of(solid, friction)
+    rho2, ay, ax = advect_sides(rho, vy, vx, dt, geo, rho_sides, v_sides)
+    if conserve_density and all(solid):
+        rho2 = normalize_to(rho2, rho)
+    if buoyancy != 0.0:
+        ly, _lx = centered_to_faces(rho2 * (-gravity * buoyancy * dt), REPLICATE)
+        ay = ay + ly
+    vy2, vx2, p, _div = divergence_free_sides(ay, ax, geo, solid)
+    return rho2, vy2, vx2, p

@@ -102,17 +102,83 @@ NO_SLIP = STICKY = Material("sticky", solid=True, friction=1)
 PERIODIC = Material("periodic", solid=False, periodic=True)
 
 
+def _collapse(values):
+    """struct collapse (PF/struct/tensorop.py): (a, a) -> a per axis, and one value if every axis agrees."""
+    per_axis = tuple(v[0] if v[0] == v[1] else (v[0], v[1]) for v in values)
+    if all(isinstance(v, str) or isinstance(v, (bool, np.bool_)) for v in per_axis) and len(set(per_axis)) == 1:
+        return per_axis[0]
+    return per_axis
+
+
+class MixedBoundaries(tuple):
+    """Per-axis / per-side boundary materials, Domain(..., boundaries=[(lower_y, upper_y), x_material]) (PF/physics/domain.py:13-35).
+    Offers Material's derived properties mapped over the sides (the reference's @mappable struct properties, material.py:60-98): a
+    property is one value where all sides agree, else a tuple per axis whose entries are a value or a (lower, upper) pair."""
+
+    def __new__(cls, boundaries, rank):
+        axes = []
+        assert len(boundaries) == rank, "one boundary entry per spatial dimension (highest dimension first)"
+        for b in boundaries:
+            if isinstance(b, Material):
+                axes.append((b, b))
+            else:
+                lo, hi = b
+                assert isinstance(lo, Material) and isinstance(hi, Material)
+                axes.append((lo, hi))
+        return tuple.__new__(cls, axes)
+
+    def _map(self, attr):
+        return _collapse([(getattr(lo, attr), getattr(hi, attr)) for lo, hi in self])
+
+    extrapolation_mode = property(lambda self: self._map("extrapolation_mode"))
+    accessible_extrapolation_mode = property(lambda self: self._map("accessible_extrapolation_mode"))
+    vector_extrapolation_mode = property(lambda self: self._map("vector_extrapolation_mode"))
+
+    @property
+    def solid(self):
+        """True only if EVERY side is solid (what np.all(Material.solid(boundaries)) asks, fluid.py:100)."""
+        return all(lo.solid and hi.solid for lo, hi in self)
+
+    @property
+    def periodic(self):
+        return any(lo.periodic or hi.periodic for lo, hi in self)
+
+    @property
+    def solid_sides(self):
+        """Flat per-side flags, axis-major: (y-lower, y-upper, x-lower, x-upper) in 2-D -- the C-ABI's PDEC_CLOSED_SIDES order."""
+        return tuple(bool(m.solid) for lo, hi in self for m in (lo, hi))
+
+    def __repr__(self):
+        return "[%s]" % ", ".join(repr(lo) if lo is hi else "(%r, %r)" % (lo, hi) for lo, hi in self)
+
+
+def extrapolation_sides(extrapolation, rank):
+    """An extrapolation (one mode, or per axis a mode or a (lower, upper) pair) -> [(lower_mode, upper_mode)] per axis."""
+    if isinstance(extrapolation, str):
+        return [(extrapolation, extrapolation)] * rank
+    assert len(extrapolation) == rank
+    return [(e, e) if isinstance(e, str) else (e[0], e[1]) for e in extrapolation]
+
+
 class Domain(object):
-    """Resolution + boundaries + box (PF/physics/domain.py:13-35).  Only a single Material for all faces is supported
-    (per-side mixed boundaries are outside the hot path: SURVEY 8f N3)."""
+    """Resolution + boundaries + box (PF/physics/domain.py:13-35).  `boundaries`: one Material for all faces, or per axis (highest
+    dimension first) a Material or a (lower, upper) pair -- e.g. [(CLOSED, OPEN), CLOSED] = a box open at the top."""
 
     def __init__(self, resolution, boundaries=OPEN, box=None):
         self.resolution = np.atleast_1d(np.asarray(resolution, np.int64))
         if not isinstance(boundaries, Material):
-            raise NotImplementedError("per-axis / per-side boundaries are not on the B200 path: %s" % (boundaries,))
+            mixed = MixedBoundaries(boundaries, len(self.resolution))
+            uniform = all(lo is mixed[0][0] and hi is mixed[0][0] for lo, hi in mixed)
+            boundaries = mixed[0][0] if uniform else mixed
         self.boundaries = boundaries
         self.box = AABox.to_box(box, resolution_hint=self.resolution)
         assert self.box.rank == len(self.resolution), "box rank %d does not match resolution %s" % (self.box.rank, self.resolution)
+
+    @property
+    def solid_sides(self):
+        if isinstance(self.boundaries, MixedBoundaries):
+            return self.boundaries.solid_sides
+        return (bool(self.boundaries.solid),) * (2 * self.rank)
 
     @staticmethod
     def as_domain(domain_like):
@@ -139,7 +205,7 @@ class Domain(object):
 
     def __eq__(self, other):
         return isinstance(other, Domain) and np.array_equal(self.resolution, other.resolution) and self.box == other.box \
-            and self.boundaries is other.boundaries
+            and (self.boundaries is other.boundaries or self.boundaries == other.boundaries)
 
     def __hash__(self):
         return hash(tuple(self.resolution.tolist()))

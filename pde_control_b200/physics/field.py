@@ -11,11 +11,28 @@ projection) lives in ops.py / libpdec.so, not here.
 import numpy as np
 import torch
 
-from .domain import AABox, Domain
+from .domain import AABox, Domain, extrapolation_sides
 from .world import State
 
 GROW, ADD, FIX = "grow", "add", "fix"
 _MODES = ("periodic", "constant", "boundary")
+
+
+def _check_extrapolation(extrapolation):
+    """One mode, or per axis a mode or a (lower, upper) pair of modes (mixed boundaries, PF/physics/domain.py:13-35)."""
+    if isinstance(extrapolation, str):
+        assert extrapolation in _MODES, extrapolation
+        return extrapolation
+    out = []
+    for e in extrapolation:
+        if isinstance(e, str):
+            assert e in _MODES, e
+            out.append(e)
+        else:
+            lo, hi = e
+            assert lo in _MODES and hi in _MODES, e
+            out.append((lo, hi))
+    return tuple(out)
 
 
 def _as_tensor(data, like=None):
@@ -55,8 +72,7 @@ class CenteredGrid(Field):
             data = data.unsqueeze(0)
         self.data = data
         self.box = AABox.to_box(box, resolution_hint=self.resolution)
-        assert extrapolation in _MODES, extrapolation
-        self.extrapolation = extrapolation
+        self.extrapolation = _check_extrapolation(extrapolation)
 
     @staticmethod
     def sample(value, domain, batch_size=None, name=None, device="cuda"):
@@ -143,6 +159,8 @@ class CenteredGrid(Field):
         from .. import ops
         from .._lib import MODE_OF_EXTRAPOLATION
         assert self.component_count == 1 and self.rank in (1, 2)
+        if not isinstance(self.extrapolation, str):
+            return self._padded_resample(points)
         points = _as_tensor(points, self.data).to(self.data.device)
         lower = torch.as_tensor(self.box.lower, device=points.device)
         size = torch.as_tensor(self.box.size, device=points.device)
@@ -150,19 +168,39 @@ class CenteredGrid(Field):
         coords = (points - lower) / size * res - 0.5
         return ops.resample(self.tensor, coords, MODE_OF_EXTRAPOLATION[self.extrapolation]).unsqueeze(-1)
 
+    def _padded_resample(self, points):
+        """sample_at for a per-side extrapolation (grid.py:211-216): pad ONE cell on every side with the side's own mode, then resample
+        the padded array with 'replicate' at coordinates shifted by that cell.  (Not the same as 'constant' sampling: between the last
+        cell and a zero-padded ring the value is interpolated towards 0 instead of dropping to exactly 0.)"""
+        from .. import ops
+        from .._lib import MODE_REPLICATE
+        padded = self.padded([[1, 1]] * self.rank).tensor.contiguous()
+        points = _as_tensor(points, self.data).to(self.data.device)
+        lower = torch.as_tensor(self.box.lower, device=points.device)
+        size = torch.as_tensor(self.box.size, device=points.device)
+        res = torch.as_tensor(np.asarray(self.resolution, np.float32), device=points.device)
+        coords = (points - lower) / size * res + 0.5
+        return ops.resample(padded, coords, MODE_REPLICATE).unsqueeze(-1)
+
     def padded(self, widths):
-        """math.pad with the field's extrapolation (grid.py:164-170); plain torch, off the hot path."""
+        """math.pad with the field's extrapolation (grid.py:164-170); plain torch, off the hot path.  Per-side modes are padded in the
+        reference's pass order (backend_helper.py:22-36): all 'circular' sides first, then 'replicate', then 'constant'."""
         if isinstance(widths, int):
             widths = [[widths, widths]] * self.rank
-        mode = {"constant": "constant", "boundary": "replicate", "periodic": "circular"}[self.extrapolation]
+        widths = [[int(lo), int(hi)] for lo, hi in widths]
+        names = {"constant": "constant", "boundary": "replicate", "periodic": "circular"}
+        sides = extrapolation_sides(self.extrapolation, self.rank)
         t = self.data.movedim(-1, 1)                           # [B, C, spatial...]
-        pad = []
-        for lo, hi in reversed(widths):
-            pad += [int(lo), int(hi)]
-        if self.rank == 1 and mode != "constant":
-            t = torch.nn.functional.pad(t, pad, mode=mode)
-        else:
-            t = torch.nn.functional.pad(t, pad, mode=mode) if mode != "constant" else torch.nn.functional.pad(t, pad)
+        for single in ("periodic", "boundary", "constant"):
+            pad, any_width = [], False
+            for ax in reversed(range(self.rank)):
+                lo = widths[ax][0] if sides[ax][0] == single else 0
+                hi = widths[ax][1] if sides[ax][1] == single else 0
+                pad += [lo, hi]
+                any_width = any_width or lo > 0 or hi > 0
+            if not any_width:
+                continue
+            t = torch.nn.functional.pad(t, pad) if single == "constant" else torch.nn.functional.pad(t, pad, mode=names[single])
         w = np.asarray(widths, np.float64)
         new_box = AABox(self.box.lower - w[:, 0] * self.dx, self.box.upper + w[:, 1] * self.dx)
         return self.copied_with(data=t.movedim(1, -1), box=new_box)
@@ -190,8 +228,7 @@ class StaggeredGrid(Field):
 
     def __init__(self, data, box=None, name=None, extrapolation="boundary", tags=(), age=0.0, batch_size=None):
         Field.__init__(self, name=name, tags=tags, age=age, batch_size=batch_size)
-        assert extrapolation in _MODES, extrapolation
-        self.extrapolation = extrapolation
+        self.extrapolation = _check_extrapolation(extrapolation)
         if isinstance(data, torch.Tensor) or isinstance(data, np.ndarray):
             components = unstack_staggered_tensor(_as_tensor(data))
         else:

@@ -13,7 +13,7 @@ import torch
 from .. import ops
 from .._lib import MODE_OF_EXTRAPOLATION
 from .burgers import DomainState
-from .domain import Domain, OPEN
+from .domain import Domain, OPEN, MixedBoundaries
 from .field import CenteredGrid, StaggeredGrid, effect_applied
 from .world import Physics, State, StateDependency, Gravity
 
@@ -100,6 +100,8 @@ def _closed(domain):
     m = domain.boundaries
     if m.periodic:
         raise NotImplementedError("periodic pressure solves are not on the B200 path (SURVEY 8f N4)")
+    if isinstance(m, MixedBoundaries):
+        return tuple(domain.solid_sides)          # per-side solid flags -> PDEC_CLOSED_SIDES (ops.closed_code)
     return bool(m.solid)
 
 
@@ -113,16 +115,58 @@ def poisson_solve(input_field, poisson_domain, solver=None, guess=None):
 
 def semi_lagrangian(field, velocity_field, dt):
     """advect.semi_lagrangian (advect.py:24-40) for the two cases on the path: a centred scalar field advected by a
-    staggered velocity, and a staggered velocity advected by itself."""
+    staggered velocity, and a staggered velocity advected by itself.  Uniform extrapolations take the fused kernels; per-side (mixed
+    boundary) extrapolations take the reference's generic route, operator by operator (_semi_lagrangian_generic)."""
+    mixed = not isinstance(field.extrapolation, str) or not isinstance(velocity_field.extrapolation, str)
     if isinstance(field, StaggeredGrid):
         assert velocity_field is field or velocity_field.compatible(field), "staggered fields are self-advected on the B200 path"
+        if mixed:
+            return field.with_data([_semi_lagrangian_generic(c, field, dt) for c in field.data])
         vy, vx = field.tensors
         ay, ax = ops.advect_staggered(vy, vx, dt, MODE_OF_EXTRAPOLATION[field.extrapolation], _box4(field.box))
         return field.with_tensors([ay, ax])
     assert isinstance(field, CenteredGrid) and isinstance(velocity_field, StaggeredGrid) and field.rank == 2
+    if mixed:
+        return field.copied_with(data=_semi_lagrangian_generic(field, velocity_field, dt))
     vy, vx = velocity_field.tensors
     out = ops.advect_centered(field.tensor, vy, vx, dt, MODE_OF_EXTRAPOLATION[field.extrapolation], _box4(field.box))
     return field.with_tensor(out)
+
+
+def _staggered_at_grid(velocity, grid):
+    """StaggeredGrid.at(points of a CenteredGrid on the same lattice) (staggered_grid.py:126-137 -> CenteredGrid.at fast path,
+    grid.py:112-123): every component is padded (its own extrapolation, per side) by what the target box needs, cropped and linearly
+    interpolated at the fractional offset -- 0.5 along every axis where the two lattices are staggered against each other.
+    Returns [B, *grid.resolution, rank]."""
+    comps = []
+    for comp in velocity.data:
+        lower = np.ceil(np.maximum(0, comp.box.lower - grid.box.lower) / comp.dx - 1e-9).astype(int)
+        upper = np.ceil(np.maximum(0, grid.box.upper - comp.box.upper) / comp.dx - 1e-9).astype(int)
+        src = comp.padded([[int(a), int(b)] for a, b in zip(lower, upper)]) if (lower.sum() + upper.sum()) > 0 else comp
+        origin = (grid.box.lower - src.box.lower) / src.dx                    # in cells of the padded component
+        data = src.data
+        for ax in range(grid.rank):
+            o = int(np.floor(origin[ax] + 1e-9))
+            frac = float(origin[ax] - o)
+            n = int(grid.resolution[ax])
+            if abs(frac) < 1e-6:
+                data = data.narrow(1 + ax, o, n)
+            else:
+                assert abs(frac - 0.5) < 1e-6, "grids of one lattice are staggered by half a cell"
+                lo, hi = data.narrow(1 + ax, o, n), data.narrow(1 + ax, o + 1, n)
+                data = lo * 0.5 + hi * 0.5                                   # interpolate_linear: x0 (1 - w) + x1 w (nd.py:378-392)
+        comps.append(data)
+    return torch.cat(comps, -1)
+
+
+def _semi_lagrangian_generic(grid, velocity, dt):
+    """x0 = grid.points; v = velocity.at(x0); data = grid.sample_at(x0 - v dt) (advect.py:33-37) for one CenteredGrid (a scalar field or one
+    staggered component); plain torch + the resample operator.  Returns the new data [B, ..., 1]."""
+    v = _staggered_at_grid(velocity, grid)
+    x = grid.points.to(v.device) - v * float(dt)
+    B = v.shape[0]
+    sampled = grid.sample_at(x.reshape(B, -1, grid.rank))
+    return sampled.reshape(grid.data.shape)
 
 
 def staggered_curl_2d(grid):
@@ -188,6 +232,8 @@ def divergence_free(velocity, domain=None, obstacles=(), pressure_solver=None, r
         raise NotImplementedError("FourierSolver alone is exact on periodic domains only: chain it, FourierSolver() & SparseCG()")
     if len(obstacles) > 0:
         assert velocity.rank == 2
+        if isinstance(domain.boundaries, MixedBoundaries):
+            raise NotImplementedError("obstacles inside a domain with per-side mixed boundaries")
         if not isinstance(solver, SparseCG):
             raise NotImplementedError("domains with obstacles are solved with SparseCG")
         masks = obstacle_masks(obstacles, velocity, domain)
@@ -264,7 +310,7 @@ class IncompressibleFlow(Physics):
             velocity, solve_info = divergence_free(velocity, fluid.domain, obstacles, self.pressure_solver, return_info=True)
         new_density = semi_lagrangian(density, velocity, dt)
         velocity = advected_velocity = semi_lagrangian(velocity, velocity, dt)
-        if self.conserve_density and fluid.domain.boundaries.solid:
+        if self.conserve_density and fluid.domain.boundaries.solid:       # every side solid (np.all(Material.solid(boundaries)), fluid.py:100)
             new_density = new_density.with_tensor(ops.normalize_to(new_density.tensor, density.tensor))
         density = new_density
         for effect in density_effects:

@@ -205,3 +205,28 @@ def test_fourier_poisson_matches_reference(bd):
     """FourierSolver's guess (math.fourier_poisson) vs the live reference."""
     g = _load("poisson_40x32")
     assert rel_err(F.fourier_poisson(torch.tensor(g["rhs_" + bd])), g["fft_" + bd]) < 1e-5
+
+
+_SIDE_CASES = {"fluid_noslip_24x20": ((1, 1, 1, 1), 1, True), "fluid_mixed_open_top_24x20": ((1, 0, 1, 1), 0, False),
+               "fluid_mixed_half_open_x_20x24": ((0, 0, 1, 0), 0, False)}
+
+
+@pytest.mark.parametrize("name", sorted(_SIDE_CASES))
+def test_no_slip_and_mixed_boundaries_match_reference_golden(name):
+    """SURVEY 8f N3 remainder: NO_SLIP (Material.vector_extrapolation_mode 'constant' on a solid domain, material.py:88-98) and per-side
+    mixed boundaries Domain(..., [(CLOSED, OPEN), CLOSED]) (domain.py:13-35; sampling through _padded_resample, grid.py:211-216) against
+    goldens from the live reference (conserve_density=False for the mixed cases: the reference's own flag test fails under NumPy 2)."""
+    solid, friction, conserve = _SIDE_CASES[name]
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    B, ny, nx = g["rho0"].shape
+    geo = F.Geometry(ny, nx)
+    for k in range(1, int(g["steps"]) + 1):
+        prev = [torch.tensor(g["%s%d" % (n, k - 1)]) for n in ("rho", "vy", "vx")]
+        out = F.incompressible_step_sides(*prev, float(g["dt"]), geo, solid, friction=friction, buoyancy=float(g["buoyancy"]),
+                                          conserve_density=conserve)
+        for a, n in zip(out[:3], ("rho", "vy", "vx")):
+            assert rel_err(a, g["%s%d" % (n, k)]) < 1e-5, (name, k, n)
+        p, pref = out[3].numpy(), g["p%d" % k]
+        if all(solid):
+            p, pref = p - p.mean((1, 2), keepdims=True), pref - pref.mean((1, 2), keepdims=True)
+        assert rel_err(p, pref) < 1e-4
