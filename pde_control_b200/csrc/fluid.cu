@@ -196,9 +196,11 @@ __device__ __forceinline__ float gather_transpose(const float* __restrict__ XY, 
     float acc = 0.0f;
     if (MODE == PDEC_MODE_CIRCULAR) {
         Ry = min(Ry, ry / 2); Rx = min(Rx, rx / 2);
-        for (int di = -Ry; di <= Ry; ++di) {
+        // a window that covers the whole ring visits every source ONCE: on an even ring -R and +R are the same cell
+        const int hy = 2 * Ry >= ry ? Ry - 1 : Ry, hx = 2 * Rx >= rx ? Rx - 1 : Rx;
+        for (int di = -Ry; di <= hy; ++di) {
             const int a = map_index<MODE>(i + di, ry);
-            for (int dj = -Rx; dj <= Rx; ++dj) {
+            for (int dj = -Rx; dj <= hx; ++dj) {
                 const int c = map_index<MODE>(j + dj, rx);
                 const size_t o = (size_t)a * rx + c;
                 float ty = __ldg(XY + o) - (float)i, tx = __ldg(XX + o) - (float)j;

@@ -66,23 +66,51 @@ class GraphedFunction(object):
         return self.replay()
 
 
-def fluid_trajectory(steps, dt, closed, accuracy=1e-5, max_iterations=2000, box=None, loss=None, direct=False):
+def fluid_trajectory(steps, dt, closed, accuracy=1e-5, max_iterations=2000, box=None, loss=None, direct=False, groups=1):
     """fn(rho, vy, vx[, target]) for GraphedFunction: `steps` projected IncompressibleFlow steps (PF/physics/fluid.py:90-114); returns
-    (loss, rho, vy, vx, cg_iterations [steps, B]) with loss = l2_loss(rho_final - target) (PF/math/nd.py:111-124) unless `loss` is given."""
-    from . import ops
+    (loss, rho, vy, vx, cg_iterations [steps, B]) with loss = l2_loss(rho_final - target) (PF/math/nd.py:111-124) unless `loss` is given.
 
-    def fn(rho, vy, vx, target=None):
+    groups > 1: the batch is cut into that many sub-batches whose trajectories run on PARALLEL streams (parallel branches of the captured
+    graph).  Batch elements never interact, but a CG launch lasts as long as its slowest element: with one launch per step for the whole
+    batch every step waits for the slowest of all B elements, with sub-batches only for the slowest of its own group, and the groups drift
+    apart instead of idling (64 one-CTA solves still fit the 148 SMs at once).  Per-element results are bit-identical; the loss is summed
+    group by group."""
+    from . import ops
+    streams = []
+
+    def run(rho, vy, vx, target):
         iters = []
         for _ in range(steps):
             rho, vy, vx, _p, it = ops.incompressible_step(rho, vy, vx, dt, closed, box=box, accuracy=accuracy, max_iterations=max_iterations,
                                                           direct=direct)
             iters.append(it)
-        if loss is not None:
-            value = loss(rho, vy, vx, target)
+        return rho, vy, vx, torch.stack(iters)
+
+    def fn(rho, vy, vx, target=None):
+        B = rho.shape[0]
+        if groups <= 1 or B < 2 * groups:
+            rho2, vy2, vx2, iters = run(rho, vy, vx, target)
         else:
-            d = rho if target is None else rho - target
-            value = (d * d).sum() / (2 * rho.shape[0])
-        return value, rho, vy, vx, torch.stack(iters)
+            main = torch.cuda.current_stream(rho.device)
+            while len(streams) < groups:
+                streams.append(torch.cuda.Stream(rho.device))
+            bounds = [B * g // groups for g in range(groups + 1)]
+            parts = []
+            for g in range(groups):
+                lo, hi = bounds[g], bounds[g + 1]
+                streams[g].wait_stream(main)
+                with torch.cuda.stream(streams[g]):
+                    parts.append(run(rho[lo:hi], vy[lo:hi], vx[lo:hi], target))
+            for g in range(groups):
+                main.wait_stream(streams[g])
+            rho2, vy2, vx2 = (torch.cat([p[k] for p in parts]) for k in range(3))
+            iters = torch.cat([p[3] for p in parts], 1)
+        if loss is not None:
+            value = loss(rho2, vy2, vx2, target)
+        else:
+            d = rho2 if target is None else rho2 - target
+            value = (d * d).sum() / (2 * B)
+        return value, rho2, vy2, vx2, iters
 
     return fn
 

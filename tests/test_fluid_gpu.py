@@ -99,6 +99,31 @@ def test_advect_staggered_forward_and_adjoint(mode, shape, box, vscale):
     assert rel_err(yc.grad.cpu(), yo.grad) < 1e-3 and rel_err(xc.grad.cpu(), xo.grad) < 1e-3
 
 
+def test_circular_adjoint_with_back_traces_beyond_half_the_ring():
+    """on an EVEN periodic grid a gather-transpose window clamped to half the ring must visit every source once (offsets
+    -R and +R are the same cell).  Velocities large enough that the window covers the whole ring, against the oracle's autograd."""
+    ops = _ops()
+    rng = np.random.RandomState(77)
+    B, ny, nx = 2, 16, 12
+    rho, vy, vx = _fields(rng, B, ny, nx, 14.0)            # |v| dt up to ~11 cells: beyond ny / 2 and nx / 2
+    geo = F.Geometry(ny, nx)
+    (ro, yo, xo), (rc, yc, xc) = _pair([rho, vy, vx])
+    oo = F.advect_centered(ro, yo, xo, 0.8, geo, R.CIRCULAR)
+    oc = ops.advect_centered(rc, yc, xc, 0.8, R.CIRCULAR, None)
+    assert rel_err(oc.detach().cpu(), oo.detach()) < 1e-4
+    w = rng.randn(B, ny, nx).astype(np.float32)
+    (oo * torch.tensor(w)).sum().backward()
+    (oc * torch.tensor(w).cuda()).sum().backward()
+    assert rel_err(rc.grad.cpu(), ro.grad) < 1e-3
+    (yo2, xo2), (yc2, xc2) = _pair([vy, vx])
+    ayo, axo = F.advect_staggered(yo2, xo2, 0.8, geo, R.CIRCULAR)
+    ayc, axc = ops.advect_staggered(yc2, xc2, 0.8, R.CIRCULAR, None)
+    wy, wx = rng.randn(*vy.shape).astype(np.float32), rng.randn(*vx.shape).astype(np.float32)
+    _backward_weighted([ayo, axo], [torch.tensor(wy), torch.tensor(wx)])
+    _backward_weighted([ayc, axc], [torch.tensor(wy).cuda(), torch.tensor(wx).cuda()])
+    assert rel_err(yc2.grad.cpu(), yo2.grad) < 1e-3 and rel_err(xc2.grad.cpu(), xo2.grad) < 1e-3
+
+
 @pytest.mark.parametrize("bd", ["open", "closed"])
 def test_divergence_and_gradient_subtraction_forward_and_adjoint(bd):
     ops = _ops()
