@@ -28,7 +28,11 @@ class ControlTraining(object):
     def __init__(self, n, pde, datapath, val_range, train_range, trace_to_channel=None, obs_loss_frames=(-1,),
                  trainable_networks=("CFE", "OP2"), sequence_class=StaggeredSequence, batch_size=16, view_size=16,
                  learning_rate=1e-3, learning_rate_half_life=1000, dt=1.0, new_graph=True, device="cuda", reg_scale=1.0,
-                 process_group=None):
+                 process_group=None, cuda_graph=False):
+        """cuda_graph=True (fixed batch shape, one GPU): the whole optimisation step -- the frame sequence with its network evaluations
+        and solver kernels, the losses, backward and the Adam update -- is captured ONCE into a CUDA graph after three eager steps and
+        replayed afterwards; per step only the batch is copied into static tensors and the learning rate written into a device scalar.
+        The analogue of the reference's one static TF graph per app (src/control/control_training.py:50-84) run by session.run."""
         self.initial_learning_rate = self.float_learning_rate = learning_rate
         self.learning_rate_half_life = learning_rate_half_life
         self.diffphys = sequence_class is not None
@@ -60,6 +64,8 @@ class ControlTraining(object):
         self._train_iter = None if self._train is None else self._train.batches(batch_size)
         self.all_states = None
         self.sequence = None
+        self.cuda_graph = bool(cuda_graph)
+        self._graph = None
 
     # ---- graph replacement: one forward pass of the sequence --------------------------------------------------
     def _fill(self, worldstate, batch, frame):
@@ -145,6 +151,8 @@ class ControlTraining(object):
         self.prepare()
         if self.learning_rate_half_life is not None:
             self.float_learning_rate = self.initial_learning_rate * 0.5 ** (self.steps / float(self.learning_rate_half_life))
+        if self.cuda_graph:
+            return self._graphed_step()
         params = self._trainable_parameters()
         if self.optimizer is None:
             self.optimizer = torch.optim.Adam(params, lr=self.float_learning_rate)
@@ -160,6 +168,55 @@ class ControlTraining(object):
         self.steps += 1
         self.scalars = {k: float(v.detach() if isinstance(v, torch.Tensor) else v) for k, v in scalars.items()}
         self.scalars["Loss"] = float(objective.detach())
+        return self.scalars
+
+    # ---- the optimisation step as one CUDA graph --------------------------------------------------------------------------------
+    _GRAPH_WARMUP = 3
+
+    def _graphed_step(self):
+        assert self.world_size == 1, "cuda_graph=True is a single-GPU feature (the gradient all-reduce re-binds .grad every step)"
+        assert self.device.type == "cuda"
+        host = self._batch(self._train, next(self._train_iter))
+        if self._graph is None:
+            params = self._trainable_parameters()
+            self._lr = torch.tensor(float(self.float_learning_rate), device=self.device)
+            self.optimizer = torch.optim.Adam(params, lr=self._lr, capturable=True)
+            self._static = {k: torch.empty(v.shape, dtype=torch.float32, device=self.device) for k, v in host.items()}
+            self._side = torch.cuda.Stream(self.device)
+            self._eager_steps = 0
+        self._lr.fill_(float(self.float_learning_rate))
+        for k, v in host.items():
+            self._static[k].copy_(torch.as_tensor(v, dtype=torch.float32), non_blocking=False)
+
+        def one_step():
+            self.optimizer.zero_grad(set_to_none=True)
+            loss, reg, scalars = self.forward(self._static)
+            objective = loss if reg is None else loss + reg * self.reg_scale
+            objective.backward()
+            self.optimizer.step()
+            out = {k: (v.detach() if isinstance(v, torch.Tensor) else float(v)) for k, v in scalars.items()}
+            out["Loss"] = objective.detach()
+            return out
+
+        if self._graph is None and self._eager_steps < self._GRAPH_WARMUP:
+            # eager steps on the side stream the capture will use (autograd binds gradient sinks to the stream of first use)
+            self._side.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(self._side):
+                out = one_step()
+            torch.cuda.current_stream(self.device).wait_stream(self._side)
+            self._eager_steps += 1
+        else:
+            if self._graph is None:
+                # capture: Adam runs BEFORE it is captured at least once (state initialised above); the capture itself executes
+                # nothing, so this step's work happens in the replay right below
+                torch.cuda.synchronize(self.device)
+                self._graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self._graph, stream=self._side):
+                    self._graph_out = one_step()
+            self._graph.replay()
+            out = self._graph_out
+        self.steps += 1
+        self.scalars = {k: float(v) for k, v in out.items()}
         return self.scalars
 
     progress = step

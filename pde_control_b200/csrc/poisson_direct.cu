@@ -14,7 +14,7 @@
 //
 // Kernel: 512 threads, thread (warp w, lane tx) owns the 8 x 4 output block rows 8w.., columns 4tx.. of every product (the layout of
 // cg_block_kernel).  Each product is a LEFT multiplication C = M B with B in shared memory (row-major, LDS.128 per k, conflict free)
-// and M read k-major from global memory (two broadcast LDG.128 per k, L1 resident: the spectral block is shared by all CTAs); right
+// and M staged k-major into a two-slot shared-memory ring by cp.async, 32 rows at a time (two broadcast LDS.128 per k); right
 // multiplications are left multiplications of the transpose, so stages 1 and 3 store their result transposed.  6 shared-memory
 // wavefronts per 32 FFMA per warp and k: FFMA-bound.
 #include "pdec_common.cuh"
@@ -69,24 +69,51 @@ __global__ void __launch_bounds__(256) poisson_direct_setup_kernel(float* __rest
     spec[4 * DS_MAT + idx] = inv;
 }
 
-// C(8 x 4 block of this thread) = sum_k Mk[k][8w .. 8w+7] * Bs[k][4tx .. 4tx+3]
-__device__ __forceinline__ void left_multiply(const float* __restrict__ Mk, const float* Bs, int K, int w, int tx, float (&acc)[8][4]) {
+constexpr int DS_CHUNK = 32;              // rows of M per staged chunk (16 KB); 4 chunks per product, 16 per solve
+constexpr int DS_CHUNKS = 4 * (DS_N / DS_CHUNK);
+
+// chunk g of the solve = rows [c * 32, c * 32 + 32) of spectral matrix `stage` (g = stage * 4 + c), contiguous in global memory:
+// every thread copies two 16-byte pieces into the ring slot g & 1 (cp.async, L2 -> shared without registers)
+__device__ __forceinline__ void stage_chunk(const float* __restrict__ spec, float* ring, int g) {
+    if (g < DS_CHUNKS) {
+        const float* src = spec + (size_t)(g / (DS_N / DS_CHUNK)) * DS_MAT + (size_t)(g % (DS_N / DS_CHUNK)) * DS_CHUNK * DS_N;
+        float* dst = ring + (g & 1) * DS_CHUNK * DS_N;
+        const int q = threadIdx.x * 8;
+        cp_async16(dst + q, src + q);
+        cp_async16(dst + q + 4, src + q + 4);
+    }
+    cp_async_commit();                      // an empty group at the tail keeps the wait count uniform
+}
+
+// C(8 x 4 block of this thread) = sum_k M[k][8w .. 8w+7] * Bs[k][4tx .. 4tx+3], M streamed through the two-slot ring:
+// while chunk g is multiplied, chunk g + 1 is in flight (ncu on the first version, M read with LDG: 4.1 long-scoreboard stalls per
+// issue, 49 % issue slots used -- the broadcast loads missed L1 two times in three).  g0 = first chunk of this product.
+__device__ __forceinline__ void left_multiply(const float* __restrict__ spec, const float* ring, const float* Bs, int K, int g0, int w, int tx,
+                                              float (&acc)[8][4]) {
 #pragma unroll
     for (int r = 0; r < 8; ++r)
 #pragma unroll
         for (int c = 0; c < 4; ++c) acc[r][c] = 0.0f;
-    const float4* m4 = reinterpret_cast<const float4*>(Mk) + 2 * w;
     const float4* b4 = reinterpret_cast<const float4*>(Bs) + tx;
+    for (int c = 0; c < DS_N / DS_CHUNK; ++c) {
+        const int g = g0 + c;
+        cp_async_wait<1>();                 // chunk g has landed (this thread's pieces) ...
+        __syncthreads();                    // ... and everybody else's
+        const float4* m4 = reinterpret_cast<const float4*>(ring + (g & 1) * DS_CHUNK * DS_N) + 2 * w;
+        const int k0 = c * DS_CHUNK, kn = min(DS_CHUNK, K - k0);
 #pragma unroll 4
-    for (int k = 0; k < K; ++k) {
-        const float4 a0 = __ldg(m4 + k * (DS_N / 4)), a1 = __ldg(m4 + k * (DS_N / 4) + 1);
-        const float4 b = b4[k * (DS_PITCH / 4)];
-        const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-        const float bv[4] = {b.x, b.y, b.z, b.w};
+        for (int kk = 0; kk < kn; ++kk) {
+            const float4 a0 = m4[kk * (DS_N / 4)], a1 = m4[kk * (DS_N / 4) + 1];          // broadcast LDS.128
+            const float4 b = b4[(k0 + kk) * (DS_PITCH / 4)];
+            const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float bv[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
-        for (int r = 0; r < 8; ++r)
+            for (int r = 0; r < 8; ++r)
 #pragma unroll
-            for (int c = 0; c < 4; ++c) acc[r][c] = fmaf(av[r], bv[c], acc[r][c]);
+                for (int cc = 0; cc < 4; ++cc) acc[r][cc] = fmaf(av[r], bv[cc], acc[r][cc]);
+        }
+        __syncthreads();                    // the slot is free again
+        stage_chunk(spec, const_cast<float*>(ring), g + 2);
     }
 }
 
@@ -105,6 +132,9 @@ __global__ void __launch_bounds__(512, 1) poisson_direct_kernel(const float* __r
     extern __shared__ __align__(16) float smem[];
     float* buf0 = smem;
     float* buf1 = smem + DS_N * DS_PITCH;
+    float* ring = smem + 2 * DS_N * DS_PITCH;          // two 16 KB slots for the spectral matrices
+    stage_chunk(spec, ring, 0);
+    stage_chunk(spec, ring, 1);
     const int tx = threadIdx.x & 31, w = threadIdx.x >> 5;
     const size_t base = (size_t)blockIdx.x * ny * nx;
     const bool vec = (nx & 3) == 0 && ((reinterpret_cast<uintptr_t>(rhs) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
@@ -126,11 +156,11 @@ __global__ void __launch_bounds__(512, 1) poisson_direct_kernel(const float* __r
     __syncthreads();
     float acc[8][4];
     // 1: U = Ey^T R            -> stored transposed: buf1 = U^T [nx][ny]
-    left_multiply(spec + 0 * DS_MAT, buf0, ny, w, tx, acc);
+    left_multiply(spec, ring, buf0, ny, 0 * (DS_N / DS_CHUNK), w, tx, acc);
     store_transposed(buf1, w, tx, acc);
     __syncthreads();
     // 2: V^T = Ex^T U^T, scaled by 1 / (l_x + l_y)  -> buf0 = S^T [nx][ny]
-    left_multiply(spec + 1 * DS_MAT, buf1, nx, w, tx, acc);
+    left_multiply(spec, ring, buf1, nx, 1 * (DS_N / DS_CHUNK), w, tx, acc);
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         const float4 s = __ldg(reinterpret_cast<const float4*>(spec + 4 * DS_MAT + (8 * w + r) * DS_N) + tx);
@@ -139,11 +169,11 @@ __global__ void __launch_bounds__(512, 1) poisson_direct_kernel(const float* __r
     }
     __syncthreads();
     // 3: W^T = Ex S^T          -> stored transposed: buf1 = W [ny][nx]
-    left_multiply(spec + 2 * DS_MAT, buf0, nx, w, tx, acc);
+    left_multiply(spec, ring, buf0, nx, 2 * (DS_N / DS_CHUNK), w, tx, acc);
     store_transposed(buf1, w, tx, acc);
     __syncthreads();
     // 4: P = Ey W              -> global
-    left_multiply(spec + 3 * DS_MAT, buf1, ny, w, tx, acc);
+    left_multiply(spec, ring, buf1, ny, 3 * (DS_N / DS_CHUNK), w, tx, acc);
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         const int i = 8 * w + r, j = 4 * tx;
@@ -177,7 +207,7 @@ extern "C" int pdec_poisson_direct_2d(const float* rhs, float* p, int B, int ny,
     if (!pdec_poisson_direct_2d_supported(ny, nx)) return PDEC_ERR_UNSUPPORTED_SIZE;
     if (B == 0) return PDEC_OK;
     if (!rhs || !p || !spectral) return PDEC_ERR_INVALID_ARGUMENT;
-    const size_t smem = (size_t)2 * DS_N * DS_PITCH * sizeof(float);
+    const size_t smem = ((size_t)2 * DS_N * DS_PITCH + 2 * DS_CHUNK * DS_N) * sizeof(float);
     if (cudaFuncSetAttribute(poisson_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
     poisson_direct_kernel<<<B, 512, smem, (cudaStream_t)stream>>>(rhs, p, reinterpret_cast<const float*>(spectral), ny, nx);
     PDEC_CHECK_LAUNCH();

@@ -346,6 +346,43 @@ def test_control_training_burgers_runs_the_fused_force_loss():
     assert rel_err(states[0].burgers.velocity.data.cpu(), data["u"][:2, 0]) == 0.0
 
 
+def test_control_training_cuda_graph_replays_the_eager_optimisation_step():
+    """ControlTraining(cuda_graph=True): after three eager steps the whole optimisation step (frame sequence with the OP networks, fused
+    force loss + adjoint, backward, Adam) is captured once and replayed.  Same data order, same initial weights: the graphed run follows the
+    eager one (Adam's capturable kernels round like the eager ones up to 1e-6) and costs less host time per step."""
+    import time
+    from pde_control_b200 import ops, datagen
+    from pde_control_b200.physics import Domain, box
+    from pde_control_b200.control import ControlTraining, BurgersPDE, StaggeredSequence
+    rng = np.random.RandomState(0)
+    n, sims, N = 8, 32, 128
+    u0 = torch.tensor(datagen.gaussian_clash(sims, N, rng)).cuda()
+    f = torch.tensor(datagen.gaussian_force(sims, N, rng)).cuda()
+    frames = torch.cat([u0[None], ops.burgers_trajectory(u0, n, 0.03, 0.003, force=f, substeps=4, resubstep=True)])
+    data = {"u": frames.permute(1, 0, 2)[..., None].cpu().numpy()}
+    runs = {}
+    for graphed in (False, True):
+        torch.manual_seed(0)
+        np.random.seed(0)
+        pde = BurgersPDE(Domain([N], box=box[0:1]), 0.003, 0.03)
+        app = ControlTraining(n, pde, data, None, range(sims), trace_to_channel=lambda _: "u", obs_loss_frames=[],
+                              trainable_networks=["OP2", "OP4", "OP8"], sequence_class=StaggeredSequence, batch_size=16,
+                              learning_rate=1e-3, dt=0.03, cuda_graph=graphed)
+        losses = [app.step()["Loss"] for _ in range(6)]
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        losses += [app.step()["Loss"] for _ in range(6)]
+        torch.cuda.synchronize()
+        runs[graphed] = (losses, [p.detach().clone() for p in pde.networks.parameters()], (time.perf_counter() - t0) / 6, app)
+    assert runs[True][3]._graph is not None and runs[False][3]._graph is None
+    for a, b in zip(runs[True][0], runs[False][0]):
+        assert abs(a - b) <= 1e-4 * abs(b), (runs[True][0], runs[False][0])
+    for a, b in zip(runs[True][1], runs[False][1]):
+        assert rel_err(a.cpu(), b.cpu()) < 1e-3
+    assert "Total Force" in runs[True][3].scalars
+    assert runs[True][2] < runs[False][2]                     # replay is cheaper than ~100 eager launches + the Python world machinery
+
+
 def test_control_training_fluid_cfe_and_op():
     from pde_control_b200 import datagen
     from pde_control_b200.physics import Domain
