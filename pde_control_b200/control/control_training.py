@@ -177,7 +177,7 @@ class ControlTraining(object):
         assert self.world_size == 1, "cuda_graph=True is a single-GPU feature (the gradient all-reduce re-binds .grad every step)"
         assert self.device.type == "cuda"
         host = self._batch(self._train, next(self._train_iter))
-        if self._graph is None:
+        if not hasattr(self, "_static"):
             params = self._trainable_parameters()
             self._lr = torch.tensor(float(self.float_learning_rate), device=self.device)
             self.optimizer = torch.optim.Adam(params, lr=self._lr, capturable=True)
