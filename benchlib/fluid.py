@@ -95,8 +95,12 @@ class FluidConfig3(object):
                                       "counts the step's time (advection adjoints included) against the solves' flops"}
         else:
             # forward launches last sum-over-steps of the slowest element's count; the adjoint solves are about as long
-            floor_us = 0.78
-            out["on_chip"] = {"bound": "fp32 issue of the iteration (16384 cells x 12 instructions / 128 lanes = 0.78 us per iteration per SM)",
+            # 323 fma-pipe instructions (224 FFMA + 93 FADD + 6 FMUL) per warp and iteration, 4 warps per scheduler, one register-operand
+            # fma-pipe instruction per 2 cycles per scheduler (B300_MICROARCH "Pipe rates": rt_SMSP = 2; ncu: fma pipe 37 % of cycles against
+            # a saturation of 50 %): 2584 cycles = 1.31 us at 1.965 GHz.  (Round 1 quoted 0.78 us assuming one instruction per cycle.)
+            floor_us = 1.31
+            out["on_chip"] = {"bound": "fp32 fma pipe of the iteration (323 fma-pipe instructions per warp x 4 warps per scheduler x 2 cycles = 1.31 us "
+                                       "per iteration per SM)",
                               "floor_us_per_iteration": floor_us, "forward_iterations_mean": self.mean_it,
                               "forward_iterations_sum_of_per_step_max": self.sum_max_it,
                               "us_per_iteration_if_all_time_were_cg": ms_per_step * 1e3 / max(2.0 * self.sum_max_it, 1.0),
