@@ -21,7 +21,7 @@ median repetition; `e2e` = the same through the public API with pinned HOST buff
 
 `--impl reference`: the reference arm on the host cores (rank 0 only): the oracle PORT (PyTorch-CPU fp32 restatement incl. the adjoint --
 the reference's reverse mode is TF-1.14 graph autodiff, not installable) at the SAME batch as the GPU arm, and, as
-`cpu_baseline.reference_forward`, the reference's own unmodified NumPy code (forward only), staged under oracle/_ref.
+`cpu_baseline.reference_forward`, the reference's own unmodified NumPy code (forward only), staged under baseline/_ref.
 """
 import argparse
 import json

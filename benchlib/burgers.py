@@ -140,7 +140,7 @@ class BurgersConfig2(object):
 
     @classmethod
     def reference_forward(cls, Bs=64, budget_s=8.0):
-        """The reference's OWN code (unmodified PhiFlow, NumPy backend, staged under oracle/_ref on the GPU box): forward only -- it has
+        """The reference's OWN code (unmodified PhiFlow, NumPy backend, staged under baseline/_ref on the GPU box): forward only -- it has
         no reverse mode without TensorFlow.  Per frame pair: Burgers().step on a BurgersVelocity state + the residual's l2_loss."""
         from oracle import ref_shim
         if not ref_shim.available():

@@ -1,7 +1,7 @@
 """TEST INFRASTRUCTURE ONLY -- runtime shim that imports the UNMODIFIED reference
 (PhiFlow 1.4.0 NumPy/SciPy backend) read-only from /root/reference.
 
-In the build container the reference is /root/reference; on the GPU box it is the unmodified copy under oracle/_ref/
+In the build container the reference is /root/reference; on the GPU box it is the unmodified copy under baseline/_ref/
 (git-ignored, staged by oracle/stage_reference.py at build time).
 Used by oracle/make_golden.py to generate tests/golden/*.npz and by the CPU tests that
 validate the restatement in oracle/restate.py against the real reference.
@@ -17,13 +17,13 @@ import sys
 
 def _root():
     """/root/reference in the build container; on the GPU box the unmodified copy staged by oracle/stage_reference.py under the
-    git-ignored oracle/_ref/ (travels with the gpurun snapshot)."""
+    git-ignored baseline/_ref/ (travels with the gpurun snapshot)."""
     env = os.environ.get("PDEC_REFERENCE_ROOT")
     if env:
         return env
     if os.path.isdir("/root/reference/PhiFlow/phi"):
         return "/root/reference"
-    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+    return os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "_ref")
 
 
 REFERENCE_ROOT = _root()

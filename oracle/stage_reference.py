@@ -1,11 +1,11 @@
 """TEST / BASELINE INFRASTRUCTURE ONLY -- stages the UNMODIFIED reference for the GPU box.
 
 /root/reference exists only in the build container.  `stage()` copies, byte for byte and without edits,
-  /root/reference/PhiFlow/phi/**/*.py (+ VERSION)      -> oracle/_ref/PhiFlow/phi/        (PhiFlow 1.4.0, NumPy/SciPy backend)
-  /root/reference/src/control/sequences.py             -> oracle/_ref/src/control/sequences.py   (TensorFlow-free scheduler module)
-into the git-ignored directory oracle/_ref/ (listed in .gitignore, NOT in .gpurunignore: it travels with the gpurun snapshot like
+  /root/reference/PhiFlow/phi/**/*.py (+ VERSION)      -> baseline/_ref/PhiFlow/phi/        (PhiFlow 1.4.0, NumPy/SciPy backend)
+  /root/reference/src/control/sequences.py             -> baseline/_ref/src/control/sequences.py   (TensorFlow-free scheduler module)
+into the git-ignored directory baseline/_ref/ (listed in .gitignore, NOT in .gpurunignore: it travels with the gpurun snapshot like
 the built libpdec.so, and never enters the history -- no reference source is committed to this repository).
-oracle/ref_shim.py falls back to oracle/_ref when /root/reference is absent, so that on the GPU box
+oracle/ref_shim.py falls back to baseline/_ref when /root/reference is absent, so that on the GPU box
   * `bench.py --impl reference` times the reference's OWN forward path (Burgers.step / IncompressibleFlow.step, NumPy backend), and
   * the `reference`-marked tests run against the live reference there too.
 Called from __graft_entry__.build(); a no-op when /root/reference is absent (the GPU box uses what was staged here).
@@ -14,7 +14,7 @@ import os
 import shutil
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-STAGED = os.path.join(HERE, "_ref")
+STAGED = os.path.join(os.path.dirname(HERE), "baseline", "_ref")        # the contract's place for the UNMODIFIED reference
 SOURCE = "/root/reference"
 
 
