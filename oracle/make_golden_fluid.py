@@ -194,4 +194,5 @@ def main(pf, out_dir):
     for name in EFFECT_SCENES:          # Inflow / Accelerator / FIX effects, sphere and union obstacles
         np.savez_compressed(os.path.join(out_dir, name + ".npz"), **effects_case(pf, name))
     np.savez_compressed(os.path.join(out_dir, "fluid_controlled_64.npz"), **controlled_case(pf, 64, 64, 2, 9, 1.0))
+    np.savez_compressed(os.path.join(out_dir, "fluid_controlled_128.npz"), **controlled_case(pf, 128, 128, 1, 15, 1.0))      # config-3 size
     np.savez_compressed(os.path.join(out_dir, "poisson_40x32.npz"), **poisson_cases(pf))
