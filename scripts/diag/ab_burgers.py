@@ -8,8 +8,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 WORKER = r'''
 import sys, os, json
 sys.path.insert(0, %r)
-import torch, bench
-wl = bench.BurgersWorkload(torch.device("cuda", 0), 0)
+import torch
+from benchlib.burgers import BurgersConfig2
+wl = BurgersConfig2(torch.device("cuda", 0), 0, 1)
 for _ in range(10): wl.step()
 torch.cuda.synchronize()
 best = 1e9
