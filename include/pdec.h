@@ -168,12 +168,15 @@ int pdec_burgers_pair_loss_host(pdec_host_pipeline* pipeline, const float* s_hos
  * data [B, ny, nx] (rank 2) or [B, nx] (rank 1, ny ignored); coords [coords_batch, npoints, rank] in INDEX space of data (axis 0
  * first), coords_batch = 1 (shared by the batch) or B; out [B, npoints].  mode = PDEC_MODE_* with the TF-CPU semantics of the fused
  * kernels ('constant': exactly 0 outside [0, N-1) along any axis).
- * _bwd: g_data [B, ny, nx] (zeroed here, then accumulated with float atomics like the reference's ResampleGradient) and/or
- * g_coords [B, npoints, rank] (per batch element; sum over B for shared coordinates); either may be NULL. */
+ * _bwd: g_data [B, ny, nx] and/or g_coords [B, npoints, rank] (per batch element; sum over B for shared coordinates); either may be
+ * NULL.  g_data is accumulated WITHOUT float atomics (the reference's ResampleGradient uses them): 64-bit fixed-point integer atomics
+ * with a power-of-two scale from max|g_out| -- the sum does not depend on the order, two runs are bit-identical; workspace =
+ * pdec_resample_bwd_workspace_bytes() bytes of device scratch (needed when g_data != NULL). */
 int pdec_resample_fwd(const float* data, const float* coords, float* out, int B, int rank, int ny, int nx, int coords_batch,
                       long long npoints, int mode, void* stream);
+size_t pdec_resample_bwd_workspace_bytes(int B, int rank, int ny, int nx);
 int pdec_resample_bwd(const float* data, const float* coords, const float* g_out, float* g_data, float* g_coords, int B, int rank,
-                      int ny, int nx, int coords_batch, long long npoints, int mode, void* stream);
+                      int ny, int nx, int coords_batch, long long npoints, int mode, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * 2-D incompressible flow  

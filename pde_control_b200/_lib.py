@@ -54,7 +54,9 @@ _SIGNATURES = {
     "pdec_burgers_pair_loss_host": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _c.c_double,
                                                 _c.c_float, _c.c_float, _c.c_int, _c.c_int, _c.c_float, _c.c_float, _P]),
     "pdec_resample_fwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_longlong, _c.c_int, _P]),
-    "pdec_resample_bwd": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_longlong, _c.c_int, _P]),
+    "pdec_resample_bwd_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int, _c.c_int]),
+    "pdec_resample_bwd": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_longlong, _c.c_int, _P,
+                                      _c.c_size_t, _P]),
     # ---- 2-D incompressible flow ----
     "pdec_curl_2d_fwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),
     "pdec_curl_2d_bwd": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),

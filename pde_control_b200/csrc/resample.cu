@@ -9,8 +9,11 @@
 // indices only; 'circular' wraps.  Combination order of the corners: over axis 0 first, then axis 1 (:491-497).
 // Layout: data [B, ny, nx] (rank 2) or [B, nx] (rank 1), one channel; coords [Bc, P, rank] in INDEX space of data (what
 // CenteredGrid.sample_at passes, grid.py:101-107), Bc = 1 (shared by the batch) or B; out [B, P].
-// Reverse mode: g_data by atomicAdd of the four corner weights (like the reference's ResampleGradient: the order of float additions
-// is not fixed; the fused kernels of the hot path use their own deterministic transposes), g_coords [B, P, rank] per batch element.
+// Reverse mode: g_coords [B, P, rank] per batch element; g_data is the transpose of a gather at ARBITRARY points, so there is no window
+// to bound a gather-transpose with (the fused kernels of the hot path have one).  It is accumulated DETERMINISTICALLY all the same, without
+// float atomics (the reference's ResampleGradient, resample_gradient.cu.cc:80-134, uses them): every contribution is converted to 64-bit
+// fixed point with a power-of-two scale taken from max|g_out| (an order-independent integer atomicMax) and added with integer atomics --
+// integer addition is associative, the sum does not depend on the order -- then converted back.  Resolution: max|g_out| * 2^-40 per term.
 #include "pdec_common.cuh"
 
 namespace pdec {
@@ -40,10 +43,37 @@ __global__ void __launch_bounds__(256) resample_fwd_kernel(const float* __restri
     out[(long long)b * P + p] = v;
 }
 
+// workspace header: word 0 = bits of max|g_out| (non-negative floats order like their bit patterns)
+__global__ void __launch_bounds__(256) resample_absmax_kernel(const float* __restrict__ g, long long n, unsigned* __restrict__ header) {
+    float m = 0.0f;
+    for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < n; q += (long long)gridDim.x * 256) {
+        const float v = fabsf(g[q]);
+        if (v == v && v < 3.0e38f) m = fmaxf(m, v);                 // NaN / inf gradients do not set the scale
+    }
+    m = warp_max(m);
+    __shared__ float sm[8];
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x < 8) {
+        m = sm[threadIdx.x];
+        for (int o = 4; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffu, m, o));
+        if (threadIdx.x == 0) atomicMax(header, __float_as_uint(m));
+    }
+}
+
+// scale = 2^(bits - exponent of max|g|): every |contribution| <= max|g| maps below 2^bits
+__device__ __forceinline__ float fixed_scale(const unsigned* header, int bits) {
+    const float m = __uint_as_float(header[0]);
+    if (!(m > 0.0f)) return 0.0f;
+    int e;
+    frexpf(m, &e);                                                  // m = f * 2^e, f in [0.5, 1)
+    return ldexpf(1.0f, min(max(bits - e, -120), 120));
+}
+
 template <int MODE, int RANK>
 __global__ void __launch_bounds__(256) resample_bwd_kernel(const float* __restrict__ data, const float* __restrict__ coords, const float* __restrict__ g_out,
-                                                           float* __restrict__ g_data, float* __restrict__ g_coords, int ny, int nx, long long P,
-                                                           int shared_coords) {
+                                                           unsigned long long* __restrict__ acc, float* __restrict__ g_coords, int ny, int nx, long long P,
+                                                           int shared_coords, const unsigned* __restrict__ header, int bits) {
     const long long p = (long long)blockIdx.x * 256 + threadIdx.x;
     const int b = blockIdx.y;
     if (p >= P) return;
@@ -54,16 +84,23 @@ __global__ void __launch_bounds__(256) resample_bwd_kernel(const float* __restri
     float w0x, w1x, w0y = 0.0f, w1y = 1.0f;
     interp_setup<MODE>(c[RANK - 1], nx, fx, cx, w0x, w1x);
     if (RANK == 2) interp_setup<MODE>(c[0], ny, fy, cy, w0y, w1y);
-    if (g_data != nullptr) {
-        float* gd = g_data + (size_t)b * ny * nx;
-        if (RANK == 1) {
-            atomicAdd(gd + fx, g * w1x);
-            atomicAdd(gd + cx, g * w0x);
-        } else {
-            atomicAdd(gd + (size_t)fy * nx + fx, g * w1x * w1y);
-            atomicAdd(gd + (size_t)cy * nx + fx, g * w1x * w0y);
-            atomicAdd(gd + (size_t)fy * nx + cx, g * w0x * w1y);
-            atomicAdd(gd + (size_t)cy * nx + cx, g * w0x * w0y);
+    if (acc != nullptr) {
+        const float scale = fixed_scale(header, bits);
+        unsigned long long* gd = acc + (size_t)b * ny * nx;
+        auto add = [&](size_t idx, float v) {                       // two's-complement add: order independent
+            const float sv = v * scale;
+            if (sv == sv && fabsf(sv) < 9.0e18f) atomicAdd(gd + idx, (unsigned long long)__float2ll_rn(sv));
+        };
+        if (scale > 0.0f) {
+            if (RANK == 1) {
+                add(fx, g * w1x);
+                add(cx, g * w0x);
+            } else {
+                add((size_t)fy * nx + fx, g * w1x * w1y);
+                add((size_t)cy * nx + fx, g * w1x * w0y);
+                add((size_t)fy * nx + cx, g * w0x * w1y);
+                add((size_t)cy * nx + cx, g * w0x * w0y);
+            }
         }
     }
     if (g_coords != nullptr) {
@@ -78,6 +115,14 @@ __global__ void __launch_bounds__(256) resample_bwd_kernel(const float* __restri
             gc[1] = g * (f1 - f0);
         }
     }
+}
+
+__global__ void __launch_bounds__(256) resample_unfix_kernel(const unsigned long long* __restrict__ acc, float* __restrict__ g_data, long long n,
+                                                             const unsigned* __restrict__ header, int bits) {
+    const float scale = fixed_scale(header, bits);
+    const double inv = scale > 0.0f ? 1.0 / (double)scale : 0.0;
+    for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < n; q += (long long)gridDim.x * 256)
+        g_data[q] = (float)((double)(long long)acc[q] * inv);
 }
 
 }  // namespace pdec
@@ -112,26 +157,55 @@ extern "C" int pdec_resample_fwd(const float* data, const float* coords, float* 
     return PDEC_OK;
 }
 
+extern "C" size_t pdec_resample_bwd_workspace_bytes(int B, int rank, int ny, int nx) {
+    if (rank == 1) ny = 1;
+    return 256 + sizeof(unsigned long long) * (size_t)(B > 0 ? B : 1) * (size_t)(ny > 0 ? ny : 1) * (size_t)(nx > 0 ? nx : 1);
+}
+
 extern "C" int pdec_resample_bwd(const float* data, const float* coords, const float* g_out, float* g_data, float* g_coords, int B, int rank,
-                                 int ny, int nx, int coords_batch, long long npoints, int mode, void* stream) {
+                                 int ny, int nx, int coords_batch, long long npoints, int mode, void* workspace, size_t workspace_bytes,
+                                 void* stream) {
     if (!resample_args_ok(data, coords, B, rank, ny, nx, coords_batch, npoints, mode) || !g_out) return PDEC_ERR_INVALID_ARGUMENT;
     if (B == 0) return PDEC_OK;
     if (B > 65535) return PDEC_ERR_UNSUPPORTED_SIZE;
     cudaStream_t st = (cudaStream_t)stream;
     if (rank == 1) ny = 1;
-    if (g_data && cudaMemsetAsync(g_data, 0, sizeof(float) * (size_t)B * ny * nx, st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
-    if (npoints == 0 || (!g_data && !g_coords)) return PDEC_OK;
+    const long long cells = (long long)B * ny * nx;
+    if (g_data) {
+        if (!workspace) return PDEC_ERR_INVALID_ARGUMENT;
+        if (workspace_bytes < pdec_resample_bwd_workspace_bytes(B, rank, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+        if (cudaMemsetAsync(workspace, 0, pdec_resample_bwd_workspace_bytes(B, rank, ny, nx), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+    }
+    if (npoints == 0 || (!g_data && !g_coords)) {
+        if (g_data && cudaMemsetAsync(g_data, 0, sizeof(float) * (size_t)cells, st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+        return PDEC_OK;
+    }
+    unsigned* header = reinterpret_cast<unsigned*>(workspace);
+    unsigned long long* acc = g_data ? reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(workspace) + 256) : nullptr;
+    // up to 4 * npoints terms can land on one cell: keep the sum below 2^62
+    int bits = 40, terms = 2;
+    for (long long t = 4 * npoints; t > 1 && terms < 62; t >>= 1) ++terms;
+    if (bits > 62 - terms) bits = 62 - terms;
+    const long long total = (long long)B * npoints;
+    if (g_data) {
+        const int blocks = (int)((total + 255) / 256 > 1184 ? 1184 : (total + 255) / 256);
+        resample_absmax_kernel<<<blocks, 256, 0, st>>>(g_out, total, header);
+    }
     const dim3 grid((unsigned)((npoints + 255) / 256), (unsigned)B);
     const int shared = coords_batch == 1 ? 1 : 0;
-#define RS_BWD(M)                                                                                                                          \
-    do {                                                                                                                                   \
-        if (rank == 1) resample_bwd_kernel<M, 1><<<grid, 256, 0, st>>>(data, coords, g_out, g_data, g_coords, ny, nx, npoints, shared);     \
-        else resample_bwd_kernel<M, 2><<<grid, 256, 0, st>>>(data, coords, g_out, g_data, g_coords, ny, nx, npoints, shared);               \
+#define RS_BWD(M)                                                                                                                                      \
+    do {                                                                                                                                               \
+        if (rank == 1) resample_bwd_kernel<M, 1><<<grid, 256, 0, st>>>(data, coords, g_out, acc, g_coords, ny, nx, npoints, shared, header, bits);      \
+        else resample_bwd_kernel<M, 2><<<grid, 256, 0, st>>>(data, coords, g_out, acc, g_coords, ny, nx, npoints, shared, header, bits);                \
     } while (0)
     if (mode == PDEC_MODE_CONSTANT) RS_BWD(PDEC_MODE_CONSTANT);
     else if (mode == PDEC_MODE_REPLICATE) RS_BWD(PDEC_MODE_REPLICATE);
     else RS_BWD(PDEC_MODE_CIRCULAR);
 #undef RS_BWD
+    if (g_data) {
+        const int blocks = (int)((cells + 255) / 256 > 1184 ? 1184 : (cells + 255) / 256);
+        resample_unfix_kernel<<<blocks, 256, 0, st>>>(acc, g_data, cells, header, bits);
+    }
     PDEC_CHECK_LAUNCH();
     return PDEC_OK;
 }

@@ -226,9 +226,11 @@ class _Resample(torch.autograd.Function):
         g_out = _c(g_out)
         g_data = torch.empty_like(data) if ctx.needs_input_grad[0] else None
         g_coords = torch.empty((B,) + tuple(coords.shape[1:]), device=data.device, dtype=torch.float32) if ctx.needs_input_grad[1] else None
+        nbytes = _lib.lib().pdec_resample_bwd_workspace_bytes(B, rank, ny, nx)
+        ws = _lib.workspace(data.device, nbytes)
         with torch.cuda.device(data.device):
             _call("pdec_resample_bwd", _lib.ptr(data), _lib.ptr(coords), _lib.ptr(g_out), _lib.ptr(g_data), _lib.ptr(g_coords), B, rank, ny,
-                  nx, coords.shape[0], P, mode, _lib.stream_ptr())
+                  nx, coords.shape[0], P, mode, _lib.ptr(ws), nbytes, _lib.stream_ptr())
         if g_coords is not None and coords.shape[0] == 1 and B > 1:
             g_coords = g_coords.sum(0, keepdim=True)
         return g_data, g_coords, None

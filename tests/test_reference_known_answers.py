@@ -145,6 +145,19 @@ def test_resample_operator_vs_oracle(mode, rank, shared):
     assert rel_err(got.detach().cpu(), want.detach()) < 1e-6
     assert rel_err(dg.grad.cpu(), dc.grad) < 1e-5
     assert rel_err(cg.grad.cpu(), cc.grad) < 1e-5
+    # the data gradient is a scatter at arbitrary points: fixed-point integer atomics, so it is bit-reproducible (no float atomics);
+    # many points on one cell, gradients spanning 12 orders of magnitude
+    big = torch.tensor(np.tile(coords[:, :8], (1, 500, 1)), device="cuda")
+    wbig = torch.tensor((rng.randn(B, big.shape[1]) * 10.0 ** rng.uniform(-6, 6, size=(B, big.shape[1]))).astype(np.float32), device="cuda")
+    grads = []
+    for _ in range(3):
+        d2 = torch.tensor(data, device="cuda", requires_grad=True)
+        (ops.resample(d2, big, cmode) * wbig).sum().backward()
+        grads.append(d2.grad.clone())
+    assert torch.equal(grads[0], grads[1]) and torch.equal(grads[0], grads[2])
+    d3 = torch.tensor(data, requires_grad=True)
+    (R.resample(d3.double(), big.cpu().double(), mode) * wbig.cpu().double()).sum().backward()
+    assert rel_err(grads[0].cpu(), d3.grad) < 1e-5
 
 
 @pytest.mark.gpu
