@@ -743,7 +743,7 @@ def _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, m
 
 
 def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
-                    max_gradient_iterations=None, guess=None, slab=None, fused=None, direct=False):
+                    max_gradient_iterations=None, guess=None, slab=None, fused=None, direct=False, stop_mode=CG_STOP_PER_ELEMENT):
     """divergence_free (PF/physics/fluid.py:214-243) without obstacles -> (vy', vx', pressure, iterations, divergence).
     Default: divergence, solve and gradient subtraction are three launches.  fused=True (grids up to 128 x 128, zero guess) takes ONE
     launch per direction (the projection fused around the on-chip CG, _Project): bit-identical, two launches and two 4 MiB round trips
@@ -760,14 +760,14 @@ def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000
         return oy, ox, p, torch.zeros(vy.shape[0], device=vy.device, dtype=torch.int32), div
     if fused is None:
         fused = _FUSED_PROJECTION
-    if fused and slab is None and guess is None and _lib.lib().pdec_project_2d_supported(ny, nx):
+    if fused and slab is None and guess is None and stop_mode == CG_STOP_PER_ELEMENT and _lib.lib().pdec_project_2d_supported(ny, nx):
         oy, ox, p, div, iters = _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations)
         return oy, ox, p, iters, div
     div = mask_divergence(vy, vx, closed)
     if slab is not None:
         p, iters, _ = _PressureSolveSlab.apply(div, slab, closed_code(closed), accuracy, int(max_iterations))
     else:
-        p, iters, _ = pressure_solve(div, closed, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations, guess)
+        p, iters, _ = pressure_solve(div, closed, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations, guess, stop_mode)
     oy, ox = subtract_pressure_gradient(vy, vx, p, closed, box)
     return oy, ox, p, iters, div
 

@@ -27,8 +27,15 @@ class SparseCG(_Chainable):
     """Conjugate-gradient pressure solver parameters (sparse.py:42-71).  'mirror' gradient iterations are treated as
     'same' (the device decides the iteration count)."""
 
-    def __init__(self, accuracy=1e-5, gradient_accuracy="same", max_iterations=2000, max_gradient_iterations="same", autodiff=False):
+    def __init__(self, accuracy=1e-5, gradient_accuracy="same", max_iterations=2000, max_gradient_iterations="same", autodiff=False,
+                 stop_mode="per_element"):
+        """stop_mode: 'per_element' (default here: every batch element stops on ITS max|r| < accuracy -- on chip, and batch shards on
+        different GPUs then behave like the whole batch) or 'whole_batch' (the reference's rule, PF/math/blas.py:33-37: all elements
+        iterate until the batch-wide max|r| < accuracy; runs on the streaming cooperative kernel for B > 1).  The SOLUTION is the parity
+        oracle either way (converged elements only move below the tolerance); iteration counts differ."""
         assert not autodiff, "autodiff through the CG loop is not provided: the gradient is a second solve (sparse.py:93-94)"
+        assert stop_mode in ("per_element", "whole_batch")
+        self.stop_mode = ops.CG_STOP_WHOLE_BATCH if stop_mode == "whole_batch" else ops.CG_STOP_PER_ELEMENT
         self.accuracy = accuracy
         self.gradient_accuracy = accuracy if gradient_accuracy == "same" else gradient_accuracy
         self.max_iterations = max_iterations
@@ -39,7 +46,7 @@ class SparseCG(_Chainable):
         t = field[..., 0] if field.dim() == 4 else field
         g = None if guess is None else (guess[..., 0] if guess.dim() == 4 else guess)
         p, iters, _ = ops.pressure_solve(t, _closed(domain), self.accuracy, self.max_iterations, self.gradient_accuracy,
-                                         self.max_gradient_iterations, g)
+                                         self.max_gradient_iterations, g, self.stop_mode)
         return (p.unsqueeze(-1) if field.dim() == 4 else p), iters
 
 
@@ -243,7 +250,8 @@ def divergence_free(velocity, domain=None, obstacles=(), pressure_solver=None, r
         oy, ox, p, iters, div = ops.divergence_free(vy, vx, _closed(domain), _box4(velocity.box), direct=True)
     else:
         oy, ox, p, iters, div = ops.divergence_free(vy, vx, _closed(domain), _box4(velocity.box), solver.accuracy, solver.max_iterations,
-                                                    solver.gradient_accuracy, solver.max_gradient_iterations, guess=guess)
+                                                    solver.gradient_accuracy, solver.max_gradient_iterations, guess=guess,
+                                                    stop_mode=getattr(solver, "stop_mode", ops.CG_STOP_PER_ELEMENT))
     result = velocity.with_tensors([oy, ox])
     if not return_info:
         return result

@@ -242,6 +242,29 @@ def test_no_slip_and_per_side_mixed_boundaries_match_reference_golden(name, boun
         assert rel_err(a.grad.cpu(), b.grad) < 1e-3
 
 
+def test_sparse_cg_stop_modes_and_solver_chain_through_divergence_free():
+    """SparseCG(stop_mode='whole_batch') is the reference's rule (blas.py:33-37) -- every element runs the batch's
+    iteration count, same solution within the tolerance; FourierSolver() & SparseCG() (the reference's TF default chain) is accepted by
+    IncompressibleFlow / divergence_free and its Fourier guess reaches the CG."""
+    from pde_control_b200 import physics as P
+    rng = np.random.RandomState(3)
+    B, n = 3, 32
+    dom = P.Domain([n, n], boundaries=P.CLOSED)
+    v = P.StaggeredGrid([torch.tensor(rng.randn(B, n + 1, n, 1).astype(np.float32) * [[[[0.1]]], [[[1.0]]], [[[3.0]]]], device="cuda").float(),
+                         torch.tensor(rng.randn(B, n, n + 1, 1).astype(np.float32), device="cuda")], box=dom.box, batch_size=B)
+    res = {}
+    for name, solver in (("element", P.SparseCG(accuracy=1e-6)), ("batch", P.SparseCG(accuracy=1e-6, stop_mode="whole_batch")),
+                         ("chain", P.FourierSolver() & P.SparseCG(accuracy=1e-6))):
+        out, info = P.divergence_free(v, dom, pressure_solver=solver, return_info=True)
+        res[name] = (out, info["iterations"])
+    it_e, it_b = res["element"][1].cpu().numpy(), res["batch"][1].cpu().numpy()
+    assert len(set(it_b.tolist())) == 1 and it_b[0] >= it_e.max() - 2 and it_e.min() < it_e.max()
+    for name in ("batch", "chain"):
+        for a, b in zip(res[name][0].data, res["element"][0].data):
+            assert rel_err(a.data.cpu(), b.data.cpu()) < 1e-5
+    assert int(res["chain"][1].max()) > 0
+
+
 def test_periodic_burgers_takes_the_fft_diffusion_branch():
     """PERIODIC Burgers through World (circular advection kernel + FFT diffusion + GROW effect) vs the live reference."""
     from pde_control_b200.physics import World, Domain, BurgersVelocity, Burgers, PERIODIC, box, FieldEffect, CenteredGrid
