@@ -491,3 +491,62 @@ def test_edge_cases():
     out = ops.advect_centered(rho, vy, vx, 1.0, R.CONSTANT)
     out.sum().backward()
     assert float(out.abs().max()) == 0.0 and bool(torch.isfinite(rho.grad).all()) and float(rho.grad.abs().max()) == 0.0
+
+
+def test_edge_cases_of_the_round_2_entry_points():
+    """C-ABI return codes and empty / ragged inputs of pdec_project_2d_*, pdec_poisson_direct_2d*, pdec_halo_* and the per-side closed codes:
+    empty batches are no-ops, sizes beyond the on-chip kernels are refused with PDEC_ERR_UNSUPPORTED_SIZE (-2), bad arguments with -1,
+    too-small buffers with -4 -- never a crash, never a silent fallback."""
+    from pde_control_b200 import _lib, ops
+    L = _lib.lib()
+    st = _lib.stream_ptr()
+    dev = torch.device("cuda")
+    vy, vx = torch.zeros(1, 9, 8, device=dev), torch.zeros(1, 8, 9, device=dev)
+    oy, ox = torch.empty_like(vy), torch.empty_like(vx)
+    P = _lib.ptr
+    # fused projection
+    assert L.pdec_project_2d_supported(128, 128) == 1 and L.pdec_project_2d_supported(129, 64) == 0 and L.pdec_project_2d_supported(1, 8) == 0
+    assert L.pdec_project_2d_fwd(P(vy), P(vx), P(oy), P(ox), None, None, None, None, 0, 8, 8, 0, 8.0, 8.0, 1e-5, 100, st) == 0        # B = 0
+    assert L.pdec_project_2d_fwd(P(vy), P(vx), P(oy), P(ox), None, None, None, None, 1, 200, 8, 0, 200.0, 8.0, 1e-5, 100, st) == -2
+    assert L.pdec_project_2d_fwd(None, P(vx), P(oy), P(ox), None, None, None, None, 1, 8, 8, 0, 8.0, 8.0, 1e-5, 100, st) == -1
+    assert L.pdec_project_2d_bwd(P(vy), P(vx), None, None, P(oy), P(ox), None, None, 1, 8, 8, 1, 8.0, -1.0, 1e-5, 100, st) == -1   # size <= 0
+    # a zero field projects to zero in zero iterations, with every per-side code
+    it = torch.full((1,), -1, dtype=torch.int32, device=dev)
+    for code in (0, 1, 0x10 | 0b0101, 0x10 | 0b1010):
+        assert L.pdec_project_2d_fwd(P(vy), P(vx), P(oy), P(ox), None, None, P(it), None, 1, 8, 8, code, 8.0, 8.0, 1e-5, 100, st) == 0
+        torch.cuda.synchronize()
+        assert int(it[0]) == 0 and float(oy.abs().max()) == 0.0 and float(ox.abs().max()) == 0.0
+    # direct solver
+    nbytes = L.pdec_poisson_direct_2d_spectral_bytes()
+    spec = torch.empty(nbytes // 4, device=dev)
+    assert L.pdec_poisson_direct_2d_supported(128, 128) == 1 and L.pdec_poisson_direct_2d_supported(130, 8) == 0
+    assert L.pdec_poisson_direct_2d_setup(P(spec), nbytes - 4, 8, 8, 0, st) == -4
+    assert L.pdec_poisson_direct_2d_setup(P(spec), nbytes, 300, 8, 0, st) == -2
+    assert L.pdec_poisson_direct_2d_setup(P(spec), nbytes, 8, 8, 0x10 | 0b0110, st) == 0
+    rhs, p = torch.zeros(0, 8, 8, device=dev), torch.zeros(0, 8, 8, device=dev)
+    assert L.pdec_poisson_direct_2d(P(rhs), P(p), 0, 8, 8, P(spec), st) == 0                                              # empty batch
+    assert L.pdec_poisson_direct_2d(None, None, 1, 8, 8, P(spec), st) == -1
+    assert ops.pressure_solve_direct(torch.zeros(0, 8, 8, device=dev), False).shape == (0, 8, 8)
+    # a ragged shape (rows and columns not multiples of the thread tiles) against the fp64 solve, mixed sides
+    rng = np.random.RandomState(9)
+    r = rng.randn(2, 13, 27).astype(np.float32)
+    got = ops.pressure_solve_direct(torch.tensor(r, device=dev), (True, False, False, True)).cpu().numpy()
+    want = F._solve_sides_np(r, (True, False, False, True))
+    assert rel_err(got, want) < 1e-5
+    # halo exchange: argument checks (the transport itself needs two GPUs: tests/test_slab_multi_gpu.py)
+    assert L.pdec_halo_inbox_bytes(2, 16, 4) == 4 * 2 * 4 * 16 * 8 and L.pdec_halo_inbox_bytes(0, 16, 4) == 0
+    f = torch.zeros(2, 8, 16, device=dev)
+    box = torch.zeros(L.pdec_halo_inbox_bytes(2, 16, 4) // 4, device=dev)
+    assert L.pdec_halo_inbox_init(P(box), 2, 16, 4, st) == 0
+    assert L.pdec_halo_push_rows(P(f), 2, 8, 16, 0, 0, P(box), 0, 1, 4, st) == 0              # zero rows: nothing to do
+    assert L.pdec_halo_push_rows(P(f), 2, 8, 16, 6, 4, P(box), 0, 1, 4, st) == -1             # rows beyond the field
+    assert L.pdec_halo_push_rows(P(f), 2, 8, 16, 0, 5, P(box), 0, 1, 4, st) == -1             # more rows than the inbox holds
+    assert L.pdec_halo_push_rows(P(f), 2, 8, 16, 0, 2, P(box), 0, 0, 4, st) == -1             # sequence number 0 is "never written"
+    # a rank may push to ITSELF (one process): rows arrive, tag-checked, and accumulate in reverse mode
+    f[:, :2] = torch.arange(32, device=dev, dtype=torch.float32).reshape(1, 2, 16) + 1.0
+    assert L.pdec_halo_push_rows(P(f), 2, 8, 16, 0, 2, P(box), 1, 7, 4, st) == 0
+    g = torch.ones(2, 8, 16, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    assert L.pdec_halo_pull_rows(P(g), 2, 8, 16, 6, 2, P(box), 1, 7, 1, 4, P(status), st) == 0
+    torch.cuda.synchronize()
+    assert int(status[0]) == 0 and torch.equal(g[:, 6:], f[:, :2] + 1.0) and float(g[:, :6].min()) == 1.0
