@@ -23,6 +23,7 @@ struct FluidGeo {
     int ny, nx;
     float lo[2], sz[2];          // domain box (centred grids)
     float clo[2][2], csz[2][2];  // staggered component boxes [component][axis]  (staggered_grid.py:49-53)
+    float inv[2], cinv[2][2];    // exact reciprocals of sz / csz where those are powers of two, else 0
     float c_wu[2], c_wl[2];      // component c -> cell centres along axis c      (grid.py:112-120)
     float s_wu[2][2], s_wl[2][2];// component 1-c -> face centres of component c, [c][axis]
     float dt;
@@ -49,6 +50,26 @@ __device__ __forceinline__ float point_coord(int i, int n, float lower, float si
 }
 __device__ __forceinline__ float index_coord(float x, float lower, float size, float resf) {
     return ((x - lower) / size) * resf - 0.5f;          // _box.py:50-52, grid.py:104-105
+}
+// the same with the division replaced by the exact reciprocal when `inv` != 0 (size a power of two: x / 2^k == x * 2^-k bit for bit)
+__device__ __forceinline__ float index_coord_fast(float x, float lower, float size, float inv, float resf) {
+    const float local = inv != 0.0f ? (x - lower) * inv : (x - lower) / size;
+    return local * resf - 0.5f;
+}
+
+// Sample-point coordinates of this block's 8 rows and 32 columns, computed ONCE per block into shared memory.  point_coord evaluates
+// numpy.linspace in float64 (two double divisions per call): per thread that was ~40 % of the advection kernels' instructions
+// (ncu, profiles/r2n_solver_kernels_summary.md: 400 thread instructions per cell).  Same function, same bits.
+__device__ __forceinline__ void block_points(int ry, int rx, const float* lo, const float* sz, float* s_py, float* s_px) {
+    const int t = threadIdx.y * 32 + threadIdx.x;
+    if (t < 8) {
+        const int i = blockIdx.y * 8 + t;
+        s_py[t] = i < ry ? point_coord(i, ry, lo[0], sz[0]) : 0.0f;
+    } else if (t >= 32 && t < 64) {
+        const int j = blockIdx.x * 32 + t - 32;
+        s_px[t - 32] = j < rx ? point_coord(j, rx, lo[1], sz[1]) : 0.0f;
+    }
+    __syncthreads();
 }
 
 // Resolution of the grid a VARIANT advects (= samples from and writes to).
@@ -82,15 +103,16 @@ __device__ __forceinline__ void velocity_at(const FluidGeo& g, const float* __re
 // Back-traced index coordinates of sample (i, j) of the VARIANT's grid.
 template <int VARIANT, int VMODE>
 __device__ __forceinline__ void backtrace(const FluidGeo& g, const float* __restrict__ vy, const float* __restrict__ vx,
-                                          int i, int j, int ry, int rx, float& xiy, float& xix) {
+                                          int i, int j, int ry, int rx, float py, float px, float& xiy, float& xix) {
     float uy, ux;
     velocity_at<VARIANT, VMODE>(g, vy, vx, i, j, uy, ux);
     const float *lo = (VARIANT == V_CENTERED) ? g.lo : g.clo[VARIANT - 1];
     const float *sz = (VARIANT == V_CENTERED) ? g.sz : g.csz[VARIANT - 1];
-    const float y = point_coord(i, ry, lo[0], sz[0]) - uy * g.dt;    // advect.py:35
-    const float x = point_coord(j, rx, lo[1], sz[1]) - ux * g.dt;
-    xiy = index_coord(y, lo[0], sz[0], (float)ry);
-    xix = index_coord(x, lo[1], sz[1], (float)rx);
+    const float *inv = (VARIANT == V_CENTERED) ? g.inv : g.cinv[VARIANT - 1];
+    const float y = py - uy * g.dt;                                  // advect.py:35; (py, px) = point_coord of (i, j), from block_points
+    const float x = px - ux * g.dt;
+    xiy = index_coord_fast(y, lo[0], sz[0], inv[0], (float)ry);
+    xix = index_coord_fast(x, lo[1], sz[1], inv[1], (float)rx);
 }
 
 // Bilinear sample, TF op order (tf_backend.py:491-497): combine over y first, then x.
@@ -119,10 +141,12 @@ __global__ void __launch_bounds__(256) advect_fwd_kernel(FluidGeo g, const float
     int ry, rx;
     variant_res<VARIANT>(g.ny, g.nx, ry, rx);
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    __shared__ float s_py[8], s_px[32];
+    block_points(ry, rx, (VARIANT == V_CENTERED) ? g.lo : g.clo[VARIANT - 1], (VARIANT == V_CENTERED) ? g.sz : g.csz[VARIANT - 1], s_py, s_px);
     if (i >= ry || j >= rx) return;
     const size_t sy = (size_t)(g.ny + 1) * g.nx, sx = (size_t)g.ny * (g.nx + 1), sf = (size_t)ry * rx;
     float xiy, xix, d0, d1;
-    backtrace<VARIANT, VMODE>(g, vy + b * sy, vx + b * sx, i, j, ry, rx, xiy, xix);
+    backtrace<VARIANT, VMODE>(g, vy + b * sy, vx + b * sx, i, j, ry, rx, s_py[threadIdx.y], s_px[threadIdx.x], xiy, xix);
     out[b * sf + (size_t)i * rx + j] = sample2d<FMODE, false>(field + b * sf, ry, rx, xiy, xix, d0, d1);
 }
 
@@ -145,9 +169,11 @@ __global__ void __launch_bounds__(256) advect_bwd_prep_kernel(FluidGeo g, const 
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     const size_t sy = (size_t)(g.ny + 1) * g.nx, sx = (size_t)g.ny * (g.nx + 1), sf = (size_t)ry * rx;
     int dispy = 0, dispx = 0;
+    __shared__ float s_py[8], s_px[32];
+    block_points(ry, rx, (VARIANT == V_CENTERED) ? g.lo : g.clo[VARIANT - 1], (VARIANT == V_CENTERED) ? g.sz : g.csz[VARIANT - 1], s_py, s_px);
     if (i < ry && j < rx) {
         float xiy, xix, dy, dx;
-        backtrace<VARIANT, VMODE>(g, vy + b * sy, vx + b * sx, i, j, ry, rx, xiy, xix);
+        backtrace<VARIANT, VMODE>(g, vy + b * sy, vx + b * sx, i, j, ry, rx, s_py[threadIdx.y], s_px[threadIdx.x], xiy, xix);
         sample2d<FMODE, true>(field + b * sf, ry, rx, xiy, xix, dy, dx);
         const float go = gout[b * sf + (size_t)i * rx + j];
         const float *sz = (VARIANT == V_CENTERED) ? g.sz : g.csz[VARIANT - 1];
@@ -560,6 +586,11 @@ static int make_geo(FluidGeo& g, int B, int ny, int nx, double dt, float lower_y
             g.clo[c][a] = lo_c;
             g.csz[c][a] = up_c - lo_c;
         }
+    auto exact_inv = [](float v) { int e; return (v > 0.0f && frexpf(v, &e) == 0.5f && e > -100 && e < 100) ? 1.0f / v : 0.0f; };
+    for (int a = 0; a < 2; ++a) {
+        g.inv[a] = exact_inv(g.sz[a]);
+        for (int c = 0; c < 2; ++c) g.cinv[c][a] = exact_inv(g.csz[c][a]);
+    }
     for (int c = 0; c < 2; ++c) half_weights(g.clo[c][c], g.csz[c][c], res[c] + 1, g.lo[c], g.c_wu[c], g.c_wl[c]);
     for (int c = 0; c < 2; ++c) {
         const int d = 1 - c;   // the other component, padded by one cell on both sides along axis c
