@@ -249,8 +249,7 @@ class FluidNotebook(object):
             loss = (d * d).sum() / (2 * B)
             force = 0
             for (ay, ax), (by, bx) in zip(vs[:-1], vs[1:]):                       # total_force_loss: velocities from the curl extrapolate 'boundary'
-                sy, sx = ops.advect_staggered(ay, ax, dt, MODE_REPLICATE)
-                force = force + ((sy - by) ** 2).sum() / (2 * B) + ((sx - bx) ** 2).sum() / (2 * B)
+                force = force + ops.staggered_force_loss(ay, ax, by, bx, dt, MODE_REPLICATE)
             return loss + force / (T - 1), rho
         return fn
 
@@ -277,8 +276,9 @@ class FluidNotebook(object):
         return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "peak_source": peak_src, "algorithmic_bytes_per_cell_update": self.algorithmic_bytes_per_cell_update,
                 "kernel": self.dominant_kernel,
-                "note": "72 B per cell-update = SURVEY 8d's figure for FUSED curl+advection and a fused force loss; the kernels here are still one "
-                        "per operator (curl, advect, staggered advect, their gather-transpose adjoints), so the real traffic is ~3x that"}
+                "note": "72 B per cell-update = SURVEY 8d's figure for FUSED curl+advection and a fused force loss; the force loss is fused "
+                        "(pdec_staggered_force_loss: advect + residual + reduction, the advected field never stored), curl and density advection and "
+                        "the gather-transpose adjoints are still one kernel per operator, so the real traffic is ~2.5x that"}
 
     def parity(self, elements=(0, 63)):
         from oracle import restate as R

@@ -214,6 +214,21 @@ int pdec_advect_staggered_2d_bwd(const float* vy, const float* vx, const float* 
                                  float lower_x, float size_y, float size_x, void* workspace, size_t workspace_bytes,
                                  void* stream);
 
+/* One term of IncompFlowControl.total_force_loss fused (src/control/pde/incompressible_flow.py:31-43:
+ * l2_loss(advect.semi_lagrangian(v1, v1, dt) - v2) summed over both staggered components, l2_loss = sum(d^2) / 2 / batch):
+ * loss[0] = sum(resid_y^2) / 2 / B + sum(resid_x^2) / 2 / B with resid = advected(v) - (ty, tx); the residuals are kept for the adjoint,
+ * the advected field is never stored.  Deterministic: block partials re-reduced in float64 in a fixed order.
+ * _bwd: seed = resid * (g_loss[0] / B) (g_loss is a DEVICE scalar, so the call can sit in a CUDA graph), then the adjoint of the
+ * staggered advection into g_vy / g_vx; g_ty / g_tx (= -seed) may be NULL.  workspace of _bwd: pdec_advect_2d_workspace_bytes. */
+size_t pdec_staggered_force_loss_workspace_bytes(int B, int ny, int nx);
+int pdec_staggered_force_loss_fwd(const float* vy, const float* vx, const float* ty, const float* tx, float* resid_y, float* resid_x,
+                                  float* loss, int B, int ny, int nx, int mode, double dt, float lower_y, float lower_x, float size_y,
+                                  float size_x, void* workspace, size_t workspace_bytes, void* stream);
+int pdec_staggered_force_loss_bwd(const float* vy, const float* vx, const float* resid_y, const float* resid_x, const float* g_loss,
+                                  float* seed_y, float* seed_x, float* g_vy, float* g_vx, float* g_ty, float* g_tx, int B, int ny, int nx,
+                                  int mode, double dt, float lower_y, float lower_x, float size_y, float size_x, void* workspace,
+                                  size_t workspace_bytes, void* stream);
+
 /* PoissonDomain.with_hard_boundary_conditions (PF/physics/pressuresolver/solver_api.py:111-121, no obstacles: faces on a
  * solid domain boundary are zeroed when closed != 0) fused with StaggeredGrid.divergence(physical_units=False)
  * (staggered_grid.py:201-209). */

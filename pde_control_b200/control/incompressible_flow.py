@@ -6,7 +6,7 @@ the force loss self-advects the staggered velocity; the target loss (FFT-weighte
 import numpy as np
 import torch
 
-from ..physics import CenteredGrid, Physics, StateDependency, staggered_curl_2d, semi_lagrangian
+from ..physics import CenteredGrid, Physics, StateDependency, staggered_curl_2d, semi_lagrangian, staggered_force_loss
 from .networks import UNet
 from .pde_base import PDE
 
@@ -49,10 +49,7 @@ class IncompressibleFluidPDE(PDE):
         for s1, s2 in zip(states[:-1], states[1:]):
             if hasattr(s1.density, "velocity") and hasattr(s2.density, "velocity"):
                 v1, v2 = s1.density.velocity, s2.density.velocity
-                adv = semi_lagrangian(v1, v1, self.dt)
-                for a, b in zip(adv.data, v2.data):
-                    d = a.data - b.data
-                    loss = loss + (d ** 2).sum() / 2 / d.shape[0]
+                loss = loss + staggered_force_loss(v1, v2, self.dt)     # l2_loss(semi_lagrangian(v1, v1, dt) - v2), one fused term
                 count += 1
         return None if count == 0 else loss / count
 

@@ -150,6 +150,78 @@ __global__ void __launch_bounds__(256) advect_fwd_kernel(FluidGeo g, const float
     out[b * sf + (size_t)i * rx + j] = sample2d<FMODE, false>(field + b * sf, ry, rx, xiy, xix, d0, d1);
 }
 
+// ---- fused staggered force loss (control/incompressible_flow total_force_loss: l2_loss(semi_lagrangian(v1, v1, dt) - v2)) ----------------
+// One launch per component: back-trace, sample, subtract the next frame's velocity, keep the residual (the adjoint's seed) and the block's
+// sum of squares.  The advected field itself never reaches HBM.  Partials are re-reduced in a fixed order (no float atomics).
+__device__ __forceinline__ float block_sum_2d(float v, float* sh) {
+    const int t = threadIdx.y * 32 + threadIdx.x;
+    v = warp_sum(v);
+    if ((t & 31) == 0) sh[t >> 5] = v;
+    __syncthreads();
+    float r = 0.0f;
+    if (t < 32) {
+        r = t < 8 ? sh[t] : 0.0f;
+        r = warp_sum(r);
+    }
+    return r;                                                         // valid in thread 0
+}
+
+template <int VARIANT, int M>
+__global__ void __launch_bounds__(256) advect_residual_kernel(FluidGeo g, const float* __restrict__ vy, const float* __restrict__ vx,
+                                                              const float* __restrict__ target, float* __restrict__ resid,
+                                                              float* __restrict__ partials) {
+    int ry, rx;
+    variant_res<VARIANT>(g.ny, g.nx, ry, rx);
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    __shared__ float s_py[8], s_px[32], sh[8];
+    block_points(ry, rx, g.clo[VARIANT - 1], g.csz[VARIANT - 1], s_py, s_px);
+    float d = 0.0f;
+    if (i < ry && j < rx) {
+        const size_t sy = (size_t)(g.ny + 1) * g.nx, sx = (size_t)g.ny * (g.nx + 1), sf = (size_t)ry * rx;
+        const float* field = (VARIANT == V_COMP_Y ? vy + b * sy : vx + b * sx);
+        float xiy, xix, d0, d1;
+        backtrace<VARIANT, M>(g, vy + b * sy, vx + b * sx, i, j, ry, rx, s_py[threadIdx.y], s_px[threadIdx.x], xiy, xix);
+        const size_t at = b * sf + (size_t)i * rx + j;
+        d = sample2d<M, false>(field, ry, rx, xiy, xix, d0, d1) - __ldg(target + at);
+        resid[at] = d;
+    }
+    const float s = block_sum_2d(d * d, sh);
+    if (threadIdx.x == 0 && threadIdx.y == 0) partials[((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = s;
+}
+
+// loss = sum(partials of component y) / 2 / B + sum(partials of component x) / 2 / B, each sum in float64 and a fixed order
+__global__ void __launch_bounds__(1024) force_loss_finish_kernel(const float* __restrict__ partials, int n0, int n1, int B, float* __restrict__ loss) {
+    __shared__ double sh[2][1024];
+    double a0 = 0.0, a1 = 0.0;
+    for (int i = threadIdx.x; i < n0; i += 1024) a0 += (double)partials[i];
+    for (int i = threadIdx.x; i < n1; i += 1024) a1 += (double)partials[n0 + i];
+    sh[0][threadIdx.x] = a0; sh[1][threadIdx.x] = a1;
+    __syncthreads();
+    for (int w = 512; w > 0; w >>= 1) {
+        if (threadIdx.x < w) { sh[0][threadIdx.x] += sh[0][threadIdx.x + w]; sh[1][threadIdx.x] += sh[1][threadIdx.x + w]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) loss[0] = (float)(sh[0][0] / 2.0 / (double)B) + (float)(sh[1][0] / 2.0 / (double)B);
+}
+
+// seeds of the adjoint: g_a = resid * (g_loss / B) for both components, and the target's gradient -g_a (optional)
+__global__ void __launch_bounds__(256) force_loss_seed_kernel(const float* __restrict__ ry_, const float* __restrict__ rx_, const float* __restrict__ g_loss,
+                                                              float inv_B, float* __restrict__ gy, float* __restrict__ gx, float* __restrict__ g_ty,
+                                                              float* __restrict__ g_tx, size_t n0, size_t n1) {
+    const float k = g_loss[0] * inv_B;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n0 + n1; i += (size_t)gridDim.x * blockDim.x) {
+        if (i < n0) {
+            const float v = ry_[i] * k;
+            gy[i] = v;
+            if (g_ty) g_ty[i] = -v;
+        } else {
+            const float v = rx_[i - n0] * k;
+            gx[i - n0] = v;
+            if (g_tx) g_tx[i - n0] = -v;
+        }
+    }
+}
+
 // ---- adjoint pass A: coordinates, coordinate gradients, displacement bound ----------------------------
 // Effective coordinate for the transpose: 'constant' -> NaN marks "contributes nothing"; 'replicate' -> clamped.
 template <int MODE>
@@ -790,6 +862,60 @@ extern "C" int pdec_advect_staggered_2d_bwd(const float* vy, const float* vx, co
 #undef CALL
     PDEC_CHECK_LAUNCH();
     return PDEC_OK;
+}
+
+// ---- fused staggered force loss ------------------------------------------------------------------------
+static size_t force_loss_blocks(int B, int ny, int nx, size_t& n0) {
+    const dim3 t0 = tiles(ny + 1, nx, B), t1 = tiles(ny, nx + 1, B);
+    n0 = (size_t)t0.x * t0.y * t0.z;
+    return n0 + (size_t)t1.x * t1.y * t1.z;
+}
+
+extern "C" size_t pdec_staggered_force_loss_workspace_bytes(int B, int ny, int nx) {
+    size_t n0;
+    return force_loss_blocks(B > 0 ? B : 1, ny, nx, n0) * sizeof(float);
+}
+
+extern "C" int pdec_staggered_force_loss_fwd(const float* vy, const float* vx, const float* ty, const float* tx, float* resid_y, float* resid_x,
+                                             float* loss, int B, int ny, int nx, int mode, double dt, float lower_y, float lower_x, float size_y,
+                                             float size_x, void* workspace, size_t workspace_bytes, void* stream) {
+    FluidGeo g;
+    int rc = make_geo(g, B, ny, nx, dt, lower_y, lower_x, size_y, size_x);
+    if (rc != PDEC_OK) return rc;
+    if (bad_mode(mode)) return PDEC_ERR_INVALID_ARGUMENT;
+    if (!loss) return PDEC_ERR_INVALID_ARGUMENT;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (B == 0) return cudaMemsetAsync(loss, 0, sizeof(float), st) == cudaSuccess ? PDEC_OK : PDEC_ERR_CUDA_LAUNCH;
+    if (!vy || !vx || !ty || !tx || !resid_y || !resid_x || !workspace) return PDEC_ERR_INVALID_ARGUMENT;
+    if (workspace_bytes < pdec_staggered_force_loss_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+    size_t n0;
+    const size_t n = force_loss_blocks(B, ny, nx, n0);
+    if (n > 0x7fffffffULL) return PDEC_ERR_INVALID_ARGUMENT;
+    float* partials = reinterpret_cast<float*>(workspace);
+#define CALL(M)                                                                                                                \
+    advect_residual_kernel<V_COMP_Y, M><<<tiles(ny + 1, nx, B), kBlock, 0, st>>>(g, vy, vx, ty, resid_y, partials);            \
+    advect_residual_kernel<V_COMP_X, M><<<tiles(ny, nx + 1, B), kBlock, 0, st>>>(g, vy, vx, tx, resid_x, partials + n0)
+    MODE_SWITCH(mode, CALL);
+#undef CALL
+    force_loss_finish_kernel<<<1, 1024, 0, st>>>(partials, (int)n0, (int)(n - n0), B, loss);
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+extern "C" int pdec_staggered_force_loss_bwd(const float* vy, const float* vx, const float* resid_y, const float* resid_x, const float* g_loss,
+                                             float* seed_y, float* seed_x, float* g_vy, float* g_vx, float* g_ty, float* g_tx, int B, int ny, int nx,
+                                             int mode, double dt, float lower_y, float lower_x, float size_y, float size_x, void* workspace,
+                                             size_t workspace_bytes, void* stream) {
+    if (B < 0) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!resid_y || !resid_x || !g_loss || !seed_y || !seed_x) return PDEC_ERR_INVALID_ARGUMENT;
+    const size_t n0 = (size_t)B * (ny + 1) * nx, n1 = (size_t)B * ny * (nx + 1);
+    size_t blocks = (n0 + n1 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    force_loss_seed_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(resid_y, resid_x, g_loss, 1.0f / (float)B, seed_y, seed_x, g_ty, g_tx, n0, n1);
+    PDEC_CHECK_LAUNCH();
+    return pdec_advect_staggered_2d_bwd(vy, vx, seed_y, seed_x, g_vy, g_vx, 0, B, ny, nx, mode, dt, lower_y, lower_x, size_y, size_x, workspace,
+                                        workspace_bytes, stream);
 }
 
 extern "C" int pdec_mask_divergence_2d_fwd(const float* vy, const float* vx, float* div, int B, int ny, int nx, int closed, void* stream) {

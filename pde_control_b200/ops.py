@@ -371,6 +371,53 @@ def advect_staggered(vy, vx, dt, mode=MODE_REPLICATE, box=None):
     return _AdvectStaggered.apply(vy, vx, float(dt), int(mode), _box(box, vx.shape[1], vy.shape[2]))
 
 
+class _StaggeredForceLoss(torch.autograd.Function):
+    """l2_loss(advect.semi_lagrangian(v1, v1, dt) - v2) over both staggered components, one fused term of total_force_loss
+    (src/control/pde/incompressible_flow.py:31-43).  The residual is the only array kept for the adjoint."""
+
+    @staticmethod
+    def forward(ctx, vy, vx, ty, tx, dt, mode, box):
+        _req_cuda(vy, vx, ty, tx)
+        vy, vx, ty, tx = _c(vy), _c(vx), _c(ty), _c(tx)
+        B, ny1, nx = vy.shape
+        ny = ny1 - 1
+        assert vx.shape == (B, ny, nx + 1) and ty.shape == vy.shape and tx.shape == vx.shape, (vy.shape, vx.shape, ty.shape, tx.shape)
+        ry, rx = torch.empty_like(vy), torch.empty_like(vx)
+        loss = torch.empty((), device=vy.device, dtype=torch.float32)
+        nbytes = _lib.lib().pdec_staggered_force_loss_workspace_bytes(B, ny, nx)
+        ws = _lib.workspace(vy.device, nbytes)
+        with torch.cuda.device(vy.device):
+            _call("pdec_staggered_force_loss_fwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(ty), _lib.ptr(tx), _lib.ptr(ry), _lib.ptr(rx),
+                  _lib.ptr(loss), B, ny, nx, mode, dt, *box, _lib.ptr(ws), nbytes, _lib.stream_ptr())
+        ctx.save_for_backward(vy, vx, ry, rx)
+        ctx.cfg = (dt, mode, box)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g_loss):
+        vy, vx, ry, rx = ctx.saved_tensors
+        dt, mode, box = ctx.cfg
+        B, ny1, nx = vy.shape
+        ny = ny1 - 1
+        g_loss = _c(g_loss.to(torch.float32))
+        want_t = ctx.needs_input_grad[2] or ctx.needs_input_grad[3]
+        sy, sx = torch.empty_like(vy), torch.empty_like(vx)
+        g_vy, g_vx = torch.empty_like(vy), torch.empty_like(vx)
+        g_ty, g_tx = (torch.empty_like(vy), torch.empty_like(vx)) if want_t else (None, None)
+        nbytes = _lib.lib().pdec_advect_2d_workspace_bytes(B, ny, nx)
+        ws = _lib.workspace(vy.device, nbytes)
+        with torch.cuda.device(vy.device):
+            _call("pdec_staggered_force_loss_bwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(ry), _lib.ptr(rx), _lib.ptr(g_loss), _lib.ptr(sy),
+                  _lib.ptr(sx), _lib.ptr(g_vy), _lib.ptr(g_vx), _lib.ptr(g_ty) if want_t else 0, _lib.ptr(g_tx) if want_t else 0, B, ny, nx,
+                  mode, dt, *box, _lib.ptr(ws), nbytes, _lib.stream_ptr())
+        return g_vy, g_vx, g_ty, g_tx, None, None, None
+
+
+def staggered_force_loss(vy, vx, ty, tx, dt, mode=MODE_REPLICATE, box=None):
+    """sum((advected(vy) - ty)^2) / 2 / B + sum((advected(vx) - tx)^2) / 2 / B as a 0-d tensor."""
+    return _StaggeredForceLoss.apply(vy, vx, ty, tx, float(dt), int(mode), _box(box, vx.shape[1], vy.shape[2]))
+
+
 class _MaskDivergence(torch.autograd.Function):
     """with_hard_boundary_conditions + divergence(physical_units=False) (solver_api.py:111-121, staggered_grid.py:201-209)."""
 

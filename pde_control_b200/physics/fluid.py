@@ -140,6 +140,20 @@ def semi_lagrangian(field, velocity_field, dt):
     return field.with_tensor(out)
 
 
+def staggered_force_loss(v1, v2, dt):
+    """math.l2_loss(advect.semi_lagrangian(v1, v1, dt) - v2) for two StaggeredGrids of one lattice (one term of total_force_loss,
+    src/control/pde/incompressible_flow.py:37-38): the fused kernel where v1's extrapolation is uniform, else the operator route."""
+    if isinstance(v1.extrapolation, str) and v1.rank == 2 and v1.compatible(v2):
+        vy, vx = v1.tensors
+        ty, tx = v2.tensors
+        return ops.staggered_force_loss(vy, vx, ty, tx, dt, MODE_OF_EXTRAPOLATION[v1.extrapolation], _box4(v1.box))
+    adv, loss = semi_lagrangian(v1, v1, dt), 0
+    for a, b in zip(adv.data, v2.data):
+        d = a.data - b.data
+        loss = loss + (d ** 2).sum() / 2 / d.shape[0]
+    return loss
+
+
 def _staggered_at_grid(velocity, grid):
     """StaggeredGrid.at(points of a CenteredGrid on the same lattice) (staggered_grid.py:126-137 -> CenteredGrid.at fast path,
     grid.py:112-123): every component is padded (its own extrapolation, per side) by what the target box needs, cropped and linearly

@@ -99,6 +99,58 @@ def test_advect_staggered_forward_and_adjoint(mode, shape, box, vscale):
     assert rel_err(yc.grad.cpu(), yo.grad) < 1e-3 and rel_err(xc.grad.cpu(), xo.grad) < 1e-3
 
 
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("shape,box,vscale", [((2, 33, 40), None, 2.5), ((3, 128, 128), None, 1.5), ((2, 24, 18), (0.5, -1.0, 3.0, 4.5), 0.4)])
+def test_fused_staggered_force_loss_vs_oracle_and_vs_the_operator_composition(mode, shape, box, vscale):
+    """pdec_staggered_force_loss_fwd / _bwd (one term of total_force_loss, src/control/pde/incompressible_flow.py:31-43): loss and the
+    gradients w.r.t. BOTH velocities against oracle.restate_fluid.force_loss + autograd; against advect_staggered + torch arithmetic the
+    gradient of the advected velocity is the same kernel on the same seed up to one rounding of the seed's scale."""
+    ops = _ops()
+    B, ny, nx = shape
+    rng = np.random.RandomState(7 * nx + mode)
+    _, vy, vx = _fields(rng, B, ny, nx, vscale)
+    _, ty, tx = _fields(rng, B, ny, nx, vscale)
+    geo = F.Geometry(ny, nx) if box is None else F.Geometry(ny, nx, box[:2], box[2:])
+    (yo, xo, tyo, txo), (yc, xc, tyc, txc) = _pair([vy, vx, ty, tx])
+    ay, ax = F.advect_staggered(yo, xo, 0.8, geo, mode)
+    lo = ((ay - tyo) ** 2).sum() / 2 / B + ((ax - txo) ** 2).sum() / 2 / B
+    (lo * 0.37).backward()
+    lc = ops.staggered_force_loss(yc, xc, tyc, txc, 0.8, mode, box)
+    (lc * 0.37).backward()
+    assert abs(lc.item() - lo.item()) < 2e-6 * abs(lo.item())
+    for a, b in ((yc, yo), (xc, xo), (tyc, tyo), (txc, txo)):
+        assert rel_err(a.grad.cpu(), b.grad) < 1e-3
+    # the unfused composition on the same inputs
+    (y2, x2, ty2, tx2), = [[torch.tensor(a).cuda().requires_grad_() for a in (vy, vx, ty, tx)]]
+    ay2, ax2 = ops.advect_staggered(y2, x2, 0.8, mode, box)
+    l2 = ((ay2 - ty2) ** 2).sum() / 2 / B + ((ax2 - tx2) ** 2).sum() / 2 / B
+    (l2 * 0.37).backward()
+    assert abs(lc.item() - l2.item()) < 2e-6 * abs(l2.item())
+    for a, b in ((yc, y2), (xc, x2), (tyc, ty2), (txc, tx2)):
+        assert rel_err(a.grad.cpu(), b.grad.cpu()) < 2e-6
+    # twice in a row: same bits (no atomics anywhere on the path)
+    y3, x3 = yc.detach().clone().requires_grad_(), xc.detach().clone().requires_grad_()
+    l3 = ops.staggered_force_loss(y3, x3, tyc.detach(), txc.detach(), 0.8, mode, box)
+    (l3 * 0.37).backward()
+    assert l3.item() == lc.item() and torch.equal(y3.grad, yc.grad) and torch.equal(x3.grad, xc.grad)
+
+
+def test_total_force_loss_of_the_control_module_takes_the_fused_kernel():
+    """IncompFlowControl.total_force_loss equivalent (control/incompressible_flow.py) on StaggeredGrids from the curl: same value as the
+    oracle's force_loss on the golden notebook frame."""
+    from pde_control_b200.physics import Domain, CLOSED, StaggeredGrid, staggered_force_loss
+    g = np.load(os.path.join(GOLDEN, "fluid_controlled_64.npz"))
+    dt = float(g["dt"])
+    dom = Domain([64, 64], boundaries=CLOSED)
+    vy, vx = torch.tensor(g["vy"]).cuda(), torch.tensor(g["vx"]).cuda()
+    v1 = StaggeredGrid([vy.unsqueeze(-1), vx.unsqueeze(-1)], box=dom.box, extrapolation="boundary")
+    v2 = v1.with_tensors([vy * 0.9, vx * 1.1])
+    lc = staggered_force_loss(v1, v2, dt)
+    geo = F.Geometry(64, 64)
+    lo = F.force_loss([torch.tensor(g["vy"]), torch.tensor(g["vy"]) * 0.9], [torch.tensor(g["vx"]), torch.tensor(g["vx"]) * 1.1], dt, geo)
+    assert abs(lc.item() - lo.item()) < 1e-5 * abs(lo.item())
+
+
 def test_circular_adjoint_with_back_traces_beyond_half_the_ring():
     """on an EVEN periodic grid a gather-transpose window clamped to half the ring must visit every source once (offsets
     -R and +R are the same cell).  Velocities large enough that the window covers the whole ring, against the oracle's autograd."""
