@@ -241,8 +241,9 @@ class FluidNotebook(object):
         def fn(rho, phi, target):
             B = rho.shape[0]
             vs = []
+            frames = phi.unbind(0)                                                # one stack in the backward, not T zero-filled select_backwards
             for t in range(T):
-                vy, vx = ops.curl_2d(phi[t], MODE_CONSTANT)                       # U-Net output sampled like the density: 'constant'
+                vy, vx = ops.curl_2d(frames[t], MODE_CONSTANT)                       # U-Net output sampled like the density: 'constant'
                 rho = ops.advect_centered(rho, vy, vx, dt, MODE_CONSTANT)
                 vs.append((vy, vx))
             d = rho - target
