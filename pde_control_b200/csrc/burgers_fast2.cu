@@ -34,10 +34,14 @@ struct Unit2P {
 #define F2_ROW 164
 #define F2_OUT 512                    // "floor index" given to out-of-domain samples: taps at bytes 512 and 640
 #ifndef F2_MINB
-#define F2_MINB 2                     // resident CTAs per SM (A/B on one box, us per step: 8x3 54.5, 7x4 53.5, 12x2 52.8, 4x6 55.3, 8x4 60.9 and 6x5 63.6 spill)
+#define F2_MINB 2                     // resident CTAs per SM (A/B on one box, us per step, round 1 walk: 8x3 54.5, 7x4 53.5, 12x2 52.8, 4x6 55.3, 8x4 60.9
+                                      // and 6x5 63.6 spill; round 2 row-segment walk, 72 registers: 14x2 51.2, 12x2 53.3, 7x4 53.3, 9x3 55.3, 16x2 57.8 spills)
 #endif
 #ifndef F2_WARPS
-#define F2_WARPS 12                   // warps per CTA
+#define F2_WARPS 12                   // warps per CTA (80 registers)
+#endif
+#ifndef F2_WARPS_LEAN
+#define F2_WARPS_LEAN 14              // warps per CTA of the variant that fits 72 registers without spills (no L1 term, dense gradient, 'constant')
 #endif
 #ifndef F2_WAVES
 #define F2_WAVES 1                    // CTAs per resident slot: > 1 lets the hardware scheduler balance the load (measured slower)
@@ -65,15 +69,17 @@ __device__ __forceinline__ float* ptr_off(float* row, unsigned off) { return rei
 // forward step of the row (u01, u23) -> (v01, v23); su = this warp's source row, mine = su + lane (own cells at mine[32 k]).
 // PAD = PDEC_MODE_*.  'circular' rows (tf_backend.py:476-480, 532-538): taps wrap modulo 128, w1 = 1 - w0, the stencil wraps over the
 // lanes.  'replicate' rows (:505-518): taps clamp to [0, 127], w1 = 1 - w0 from the UNCLAMPED floor, the stencil repeats the edge cell.
-template <int PAD>
+// `after_u()` runs once the frame's registers are dead (row stored, back-trace coordinates taken): the caller reloads them there.
+template <int PAD, class AfterU>
 __device__ __forceinline__ void step2_forward(const Unit2P& p, float2 X01, float2 X23, float2 u01, float2 u23, float* su, float* mine, int lane,
-                                              float2& v01, float2& v23, Step2& S) {
+                                              float2& v01, float2& v23, Step2& S, AfterU&& after_u) {
     mine[0] = u01.x; mine[32] = u01.y; mine[64] = u23.x; mine[96] = u23.y;
     __syncwarp();
     const float2 dt2 = f2(p.dt128, p.dt128), half2v = f2(-0.5f, -0.5f), one2 = f2(1.0f, 1.0f);
     // advect.py:35, _box.py:50-52, grid.py:104-105 folded (see the header): xi = ((i + 0.5) - u * 128dt) - 0.5
     const float2 xi01 = __fadd2_rn(sub2(X01, __fmul2_rn(u01, dt2)), half2v);
     const float2 xi23 = __fadd2_rn(sub2(X23, __fmul2_rn(u23, dt2)), half2v);
+    after_u();
     const float xi[4] = {xi01.x, xi01.y, xi23.x, xi23.y};
     float bf[4];
 #pragma unroll
@@ -263,21 +269,22 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
 __device__ __forceinline__ float sgn(float d) { return (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f); }
 
 // Work = the (row, pair) space B x [t0, t1) in row-major order (t0 = 0, t1 = T: the whole sequence; a narrower window serves the
-// frame-sliced host pipeline), cut into gridDim.x * F2_WARPS equal contiguous ranges, one per warp.  A warp walks the FRAMES of
-// its range -- (b, f), f = first..t1, then row b + 1 -- with the next frame always in flight.  Consecutive frames of a row form
-// a pair; a pair below the range's / window's first one is walked "carry-only" (forward step only: its residual gradient w.r.t.
-// its target frame is the carry the first real pair needs); the step from the last frame of a row to the first frame of the
-// next one only closes the row.
-template <bool L1TERM, bool GSTRIDE, int PAD>
-__global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
+// frame-sliced host pipeline), cut into gridDim.x * F2_WARPS equal contiguous ranges, one per warp.  A warp walks its range one ROW
+// SEGMENT at a time: the frames of the segment's pairs sit in two register sets that take turns as (frame, next frame), and the set of
+// the frame just consumed is reloaded a few instructions into its forward step with the frame after next -- no per-pair cursor, no
+// register moves (round 2: 299 -> 267 instructions per pair, 72 registers -> 14 warps x 2 CTAs per SM).  A segment that does not
+// start at pair 0 first walks the pair before it "carry-only" (forward step only: its residual gradient w.r.t. its target frame is
+// the carry the first real pair needs); the first frame of the next row is requested during the segment's last pair.
+template <bool L1TERM, bool GSTRIDE, int PAD, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
                                                                             float2* partials, int T, int B, int t0, int t1, long long per_warp, int pieces,
                                                                             long long gf4, unsigned* done_counter, float* __restrict__ losses, float inv_B) {
 #ifdef F2_SPLIT
-    __shared__ float smem[F2_WARPS][3][F2_ROW];
+    __shared__ float smem[WARPS][3][F2_ROW];
 #else
-    __shared__ float smem[F2_WARPS][2][F2_ROW];
+    __shared__ float smem[WARPS][2][F2_ROW];
 #endif
-    __shared__ float red2[F2_WARPS], red1[F2_WARPS];
+    __shared__ float red2[WARPS], red1[WARPS];
     __shared__ unsigned s_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* su = smem[warp][0];
@@ -301,99 +308,106 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
     const long long total = (long long)B * Cw;
     // a warp's share = `pieces` ranges of per_warp pairs, piece k of warp w at ((k * warps) + w) * per_warp: rows that take the slow
     // scatter path for all their pairs (shocks) are spread over several warps instead of landing on one
-    const long long n_warps = (long long)gridDim.x * F2_WARPS;
+    const long long n_warps = (long long)gridDim.x * WARPS;
     float2 acc2 = f2(0.0f, 0.0f);
     float acc1 = 0.0f;
     const int npieces = F2_PIECES == 1 ? 1 : pieces;                   // the default build has no piece loop
     for (int piece = 0; piece < npieces; ++piece) {
-        const long long P0 = ((long long)piece * n_warps + (long long)blockIdx.x * F2_WARPS + warp) * per_warp;
+        const long long P0 = ((long long)piece * n_warps + (long long)blockIdx.x * WARPS + warp) * per_warp;
         const long long P1 = min(total, P0 + per_warp);
         if (P0 >= P1) break;
-        int remaining = (int)(P1 - P0);                                // real pairs still to do
+        int left = (int)(P1 - P0);                                     // real pairs of the range not yet handed to a row segment
         int b = (int)(P0 / Cw);
-        int lo = t0 + (int)(P0 - (long long)b * Cw);                   // first real pair of the current row
-        const int row_first = g4 != nullptr && t0 > 0 ? t0 - 1 : t0;   // first frame walked in every later row
-        int f = g4 != nullptr && lo > 0 ? lo - 1 : lo;                 // frame held in u (one early: carry-only pair)
-        off_t32 off = (off_t32)f * f4 + (off_t32)b * 32;               // float4 offset of frame (b, f)
-        float2 u01, u23, carry01 = f2(0.0f, 0.0f), carry23 = f2(0.0f, 0.0f), v01, v23;
+        int pa = t0 + (int)(P0 - (long long)b * Cw);                   // first real pair of the current row
+        const bool want_g = g4 != nullptr;
+        const int lead = want_g && t0 > 0 ? 1 : 0;                     // later rows start one frame early (carry-only pair)
+        off_t32 off = (off_t32)(pa - (want_g && pa > 0 ? 1 : 0)) * f4 + (off_t32)b * 32;      // float4 offset of the first frame walked
+        // two frame registers, A and B, take turns as (u, target): u's registers are dead a few instructions into the forward step and
+        // are reloaded there with the frame after the target (or, at the last pair of the row, the first frame of the next row)
+        float4 A = s4[off], Bq = __ldcs(s4 + off + f4);
         Step2 S;
-        {
-            const float4 q = s4[off];
-            u01 = f2(q.x, q.y); u23 = f2(q.z, q.w);
-        }
-        // position of the frame after u (f <= t1 - 1 here, so it is in the same row), then the one after that is prefetched
-        int fn = f + 1, bn = b;
-        off_t32 offn = off + f4;
-        float4 pre = __ldcs(s4 + offn);                                // streamed: every frame is read once per range
-#ifdef F2_PF2
-        // second load cursor, one frame further: two frames in flight per warp.  It walks the same frame sequence and may run past
-        // the end of the range (never past the array): those frames are loaded and dropped
-        int fl = fn, bl = bn;
-        off_t32 offl = offn;
-        if (fl == t1) { fl = row_first; bl += 1; offl = (off_t32)row_first * f4 + (off_t32)bl * 32; } else { fl += 1; offl += f4; }
-        float4 pre2 = bl < B ? __ldcs(s4 + offl) : pre;
-#endif
-        while (true) {
-            const float2 n01 = f2(pre.x, pre.y), n23 = f2(pre.z, pre.w);
-            const int fcur = fn, bcur = bn;                            // position of n
-            const off_t32 offcur = offn;
-            const bool closing = bcur != b;                            // u = last frame of row b, n = first frame of row b + 1
-            const bool real = !closing && fcur - 1 >= lo;              // (u, n) = pair fcur - 1 of row b, inside the range
-            if (fn == t1) { fn = row_first; bn += 1; offn = (off_t32)row_first * f4 + (off_t32)bn * 32; } else { fn += 1; offn += f4; }
-#ifdef F2_PF2
-            pre = pre2;
-            if (fl == t1) { fl = row_first; bl += 1; offl = (off_t32)row_first * f4 + (off_t32)bl * 32; } else { fl += 1; offl += f4; }
-            if (bl < B && remaining - (real ? 1 : 0) > 0) pre2 = __ldcs(s4 + offl);
-#else
-            if (remaining - (real ? 1 : 0) > 0) pre = __ldcs(s4 + offn);      // in flight during this step's arithmetic
-#endif
-            if (!closing) {
-                step2_forward<PAD>(p, X01, X23, u01, u23, su, mine, lane, v01, v23, S);
-                const float2 d01 = sub2(n01, v01), d23 = sub2(n23, v23);     // burgers.py:29
-                float2 gd01 = __fmul2_rn(d01, gl2v), gd23 = __fmul2_rn(d23, gl2v);
+        while (true) {                                                 // one row segment per turn
+            int cnt = min(left, t1 - pa);                              // its real pairs: pa .. pa + cnt - 1
+            left -= cnt;
+            const bool ends_at_T = pa + cnt == T;
+            const off_t32 next_first = (off_t32)(t0 - lead) * f4 + (off_t32)(b + 1) * 32;
+            const bool more = left > 0;
+            float2 carry01 = f2(0.0f, 0.0f), carry23 = f2(0.0f, 0.0f), v01, v23;
+            if (want_g && pa > 0) {
+                // carry-only pair (pa - 1, pa): forward step only, its residual gradient w.r.t. frame pa is the carry of the first real pair
+                const float2 n01 = f2(Bq.x, Bq.y), n23 = f2(Bq.z, Bq.w);
+                step2_forward<PAD>(p, X01, X23, f2(A.x, A.y), f2(A.z, A.w), su, mine, lane, v01, v23, S, [&] { A = __ldcs(s4 + off + 2 * f4); });
+                const float2 d01 = sub2(n01, v01), d23 = sub2(n23, v23);
+                carry01 = __fmul2_rn(d01, gl2v); carry23 = __fmul2_rn(d23, gl2v);
                 if (L1TERM) {
-                    gd01.x += p.gl1 * sgn(d01.x); gd01.y += p.gl1 * sgn(d01.y);
-                    gd23.x += p.gl1 * sgn(d23.x); gd23.y += p.gl1 * sgn(d23.y);
+                    carry01.x += p.gl1 * sgn(d01.x); carry01.y += p.gl1 * sgn(d01.y);
+                    carry23.x += p.gl1 * sgn(d23.x); carry23.y += p.gl1 * sgn(d23.y);
                 }
-                if (real) {
-                    acc2 = __ffma2_rn(d01, d01, acc2);
-                    acc2 = __ffma2_rn(d23, d23, acc2);
-                    acc1 += (fabsf(d01.x) + fabsf(d01.y)) + (fabsf(d23.x) + fabsf(d23.y));
-                    if (g4 != nullptr) {
-                        float2 gin01, gin23;
-#if defined(F2_SKIP_ADJ)
-                        gin01 = gd01; gin23 = gd23;
-#else
-                        step2_adjoint<PAD>(p, S, gd01, gd23, sacc, mine_acc, lane, gin01, gin23);      // dL/dv = -gd
-#endif
-                        gin01 = __fadd2_rn(gin01, carry01);
-                        gin23 = __fadd2_rn(gin23, carry23);
-                        __stcs(g4 + (GSTRIDE ? (size_t)f * gf4 + (size_t)b * 32 : off), make_float4(gin01.x, gin01.y, gin23.x, gin23.y));   // written once, never re-read here
-                    } else {
-                        __syncwarp();
-                    }
-                    remaining -= 1;
-                } else {
-                    __syncwarp();                                      // carry-only pair: nothing stored, nothing summed
-                }
-                carry01 = gd01; carry23 = gd23;
-            } else {
-                // close row b: frame T receives the residual gradient of the last pair (a window that ends earlier leaves its
-                // last frame to the next window); the next row starts with a zero carry and its first real pair at t0
-                if (g4 != nullptr && f == T) __stcs(g4 + (GSTRIDE ? (size_t)f * gf4 + (size_t)b * 32 : off), make_float4(carry01.x, carry01.y, carry23.x, carry23.y));
-                carry01 = f2(0.0f, 0.0f); carry23 = f2(0.0f, 0.0f);
-                lo = t0;
+                __syncwarp();
+                const float4 t = A; A = Bq; Bq = t;                    // (u, target) = (frame pa, frame pa + 1) again in (A, B)
+                off += f4;
             }
-            u01 = n01; u23 = n23;
-            f = fcur; b = bcur; off = offcur;
-            if (remaining == 0) break;
+            size_t goff = GSTRIDE ? (size_t)pa * gf4 + (size_t)b * 32 : 0;       // gradient frame of u when its stride differs from s's
+            // one pair: (U, N) = (frame p, frame p + 1); U is reloaded inside; `off` = float4 offset of frame p
+#define F2_PAIR(U, N)                                                                                                                    \
+            {                                                                                                                            \
+                const float2 n01 = f2(N.x, N.y), n23 = f2(N.z, N.w);                                                                     \
+                step2_forward<PAD>(p, X01, X23, f2(U.x, U.y), f2(U.z, U.w), su, mine, lane, v01, v23, S, [&] {                           \
+                    if (cnt > 1) U = __ldcs(s4 + off + 2 * f4); else if (more) U = __ldcs(s4 + next_first);                              \
+                });                                                                                                                      \
+                const float2 d01 = sub2(n01, v01), d23 = sub2(n23, v23);     /* burgers.py:29 */                                         \
+                float2 gd01 = __fmul2_rn(d01, gl2v), gd23 = __fmul2_rn(d23, gl2v);                                                       \
+                if (L1TERM) {                                                                                                            \
+                    gd01.x += p.gl1 * sgn(d01.x); gd01.y += p.gl1 * sgn(d01.y);                                                          \
+                    gd23.x += p.gl1 * sgn(d23.x); gd23.y += p.gl1 * sgn(d23.y);                                                          \
+                }                                                                                                                        \
+                acc2 = __ffma2_rn(d01, d01, acc2);                                                                                       \
+                acc2 = __ffma2_rn(d23, d23, acc2);                                                                                       \
+                acc1 += (fabsf(d01.x) + fabsf(d01.y)) + (fabsf(d23.x) + fabsf(d23.y));                                                   \
+                if (want_g) {                                                                                                            \
+                    float2 gin01, gin23;                                                                                                 \
+                    F2_ADJOINT_CALL                                                                                                      \
+                    gin01 = __fadd2_rn(gin01, carry01);                                                                                  \
+                    gin23 = __fadd2_rn(gin23, carry23);                                                                                  \
+                    __stcs(g4 + (GSTRIDE ? goff : (size_t)off), make_float4(gin01.x, gin01.y, gin23.x, gin23.y));   /* written once */   \
+                    carry01 = gd01; carry23 = gd23;                                                                                      \
+                } else {                                                                                                                 \
+                    __syncwarp();                                                                                                        \
+                }                                                                                                                        \
+                off += f4;                                                                                                               \
+                if (GSTRIDE) goff += (size_t)gf4;                                                                                        \
+            }
+#if defined(F2_SKIP_ADJ)
+#define F2_ADJOINT_CALL gin01 = gd01; gin23 = gd23;
+#else
+#define F2_ADJOINT_CALL step2_adjoint<PAD>(p, S, gd01, gd23, sacc, mine_acc, lane, gin01, gin23);      /* dL/dv = -gd */
+#endif
+            bool in_b;                                                 // the row's last frame ended up in B (else in A); the other holds the next row's first
+            while (true) {
+                F2_PAIR(A, Bq)
+                if (--cnt == 0) { in_b = true; break; }
+                F2_PAIR(Bq, A)
+                if (--cnt == 0) { in_b = false; break; }
+            }
+#undef F2_PAIR
+#undef F2_ADJOINT_CALL
+            // `off` = the row segment's last frame.  Frame T receives the residual gradient of the last pair; a window that ends earlier leaves
+            // its last frame to the next window
+            if (want_g && ends_at_T)
+                __stcs(g4 + (GSTRIDE ? goff : (size_t)off), make_float4(carry01.x, carry01.y, carry23.x, carry23.y));
+            if (!more) break;
+            // next row: its first frame is in flight in the register set that does not hold the row's last frame
+            if (in_b) { /* A holds it */ } else { A = Bq; }
+            b += 1;
+            pa = t0;
+            off = next_first;
+            Bq = __ldcs(s4 + off + f4);
         }
-        if (f == T && g4 != nullptr) __stcs(g4 + (GSTRIDE ? (size_t)f * gf4 + (size_t)b * 32 : off), make_float4(carry01.x, carry01.y, carry23.x, carry23.y));   // range ends with its row
     }
     {
         const float a2 = warp_sum(acc2.x + acc2.y);
         acc1 = warp_sum(acc1);
-        if (lane == 0) partials[(size_t)blockIdx.x * F2_WARPS + warp] = make_float2(a2, acc1);
+        if (lane == 0) partials[(size_t)blockIdx.x * WARPS + warp] = make_float2(a2, acc1);
     }
     // second stage fused into the same launch: the CTA that finishes last adds all partials in a FIXED order
     // losses[0] = sum(d^2)/2/B (l2_loss, PF/math/nd.py:115-121), losses[1] = sum|d|/B (l1_loss, nd.py:96-108)
@@ -406,8 +420,8 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
     if (s_last) {
         __threadfence();
         float a2 = 0.0f, a1 = 0.0f;
-        const int count = (int)gridDim.x * F2_WARPS;
-        for (int i = threadIdx.x; i < count; i += 32 * F2_WARPS) {
+        const int count = (int)gridDim.x * WARPS;
+        for (int i = threadIdx.x; i < count; i += 32 * WARPS) {
             const float2 v = __ldcg(partials + i);
             a2 += v.x;
             a1 += v.y;
@@ -419,7 +433,7 @@ __global__ void __launch_bounds__(32 * F2_WARPS, F2_MINB) burgers_pair_loss_unit
         if (threadIdx.x == 0) {
             float t2 = 0.0f, t1 = 0.0f;
 #pragma unroll
-            for (int w = 0; w < F2_WARPS; ++w) { t2 += red2[w]; t1 += red1[w]; }
+            for (int w = 0; w < WARPS; ++w) { t2 += red2[w]; t1 += red1[w]; }
             losses[0] = t2 * 0.5f * inv_B;
             losses[1] = t1 * inv_B;
         }
@@ -448,18 +462,21 @@ int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials,
     const float invB = 1.0f / (float)B;
     p.gl2 = gl2 * invB; p.gl1 = gl1 * invB;
     const long long total = (long long)B * (t1 - t0);
-    // one range per resident warp (148 SMs x F2_MINB CTAs x F2_WARPS warps), at least 4 pairs per range
+    const bool strided = gf4 != (long long)B * 32;
+    const bool lean = gl1 == 0.0f && !strided && pad_mode == PDEC_MODE_CONSTANT;
+    const int warps = lean ? F2_WARPS_LEAN : F2_WARPS;
+    // one range per resident warp (148 SMs x F2_MINB CTAs x warps), at least 4 pairs per range
     long long grid = 148LL * F2_MINB * F2_WAVES;
-    if (grid * F2_WARPS * 4 > total) grid = total / (4 * F2_WARPS) > 0 ? total / (4 * F2_WARPS) : 1;
-    long long per_warp = (total + grid * F2_WARPS - 1) / (grid * F2_WARPS);
+    if (grid * warps * 4 > total) grid = total / (4 * warps) > 0 ? total / (4 * warps) : 1;
+    long long per_warp = (total + grid * warps - 1) / (grid * warps);
     // several shorter ranges per warp when there is enough work (each range start costs one carry-only forward step)
     int pieces = 1;
     while (pieces < F2_PIECES && per_warp / (pieces * 2) >= F2_PIECE_MIN) pieces *= 2;
-    per_warp = (total + grid * F2_WARPS * pieces - 1) / (grid * F2_WARPS * pieces);
-#define F2_LAUNCH(L1, GS, PER) burgers_pair_loss_unit_kernel<L1, GS, PER><<<(unsigned)grid, 32 * F2_WARPS, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB)
-#define F2_PICK(L1, GS) do { if (pad_mode == PDEC_MODE_CIRCULAR) F2_LAUNCH(L1, GS, PDEC_MODE_CIRCULAR); else if (pad_mode == PDEC_MODE_REPLICATE) F2_LAUNCH(L1, GS, PDEC_MODE_REPLICATE); else F2_LAUNCH(L1, GS, PDEC_MODE_CONSTANT); } while (0)
-    const bool strided = gf4 != (long long)B * 32;
-    if (gl1 != 0.0f) { if (strided) F2_PICK(true, true); else F2_PICK(true, false); }
+    per_warp = (total + grid * warps * pieces - 1) / (grid * warps * pieces);
+#define F2_LAUNCH(L1, GS, PER, W) burgers_pair_loss_unit_kernel<L1, GS, PER, W><<<(unsigned)grid, 32 * W, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB)
+#define F2_PICK(L1, GS) do { if (pad_mode == PDEC_MODE_CIRCULAR) F2_LAUNCH(L1, GS, PDEC_MODE_CIRCULAR, F2_WARPS); else if (pad_mode == PDEC_MODE_REPLICATE) F2_LAUNCH(L1, GS, PDEC_MODE_REPLICATE, F2_WARPS); else F2_LAUNCH(L1, GS, PDEC_MODE_CONSTANT, F2_WARPS); } while (0)
+    if (lean) F2_LAUNCH(false, false, PDEC_MODE_CONSTANT, F2_WARPS_LEAN);
+    else if (gl1 != 0.0f) { if (strided) F2_PICK(true, true); else F2_PICK(true, false); }
     else { if (strided) F2_PICK(false, true); else F2_PICK(false, false); }
 #undef F2_PICK
 #undef F2_LAUNCH
