@@ -41,7 +41,12 @@ struct Unit2P {
 #define F2_WARPS 12                   // warps per CTA (80 registers)
 #endif
 #ifndef F2_WARPS_LEAN
-#define F2_WARPS_LEAN 14              // warps per CTA of the variant that fits 72 registers without spills (no L1 term, dense gradient, 'constant')
+#define F2_WARPS_LEAN 28              // warps per CTA of the variant that fits 72 registers without spills (no L1 term, dense gradient, 'constant')
+#endif
+#ifndef F2_MINB_LEAN
+#define F2_MINB_LEAN 1                // resident CTAs per SM of that variant.  ONE CTA of 28 warps, not two of 14: the warp schedulers favour the older
+                                      // CTA, which then finishes 5 us before the younger one and leaves the SM half empty for that long (per-warp timers,
+                                      // scripts/diag/burgers_tail.py: CTAs 0..147 37 us, CTAs 148..295 42 us; one CTA: all warps 40 us).  14x2 51.2, 28x1 49.2, 24x1 51.4 us
 #endif
 #ifndef F2_WAVES
 #define F2_WAVES 1                    // CTAs per resident slot: > 1 lets the hardware scheduler balance the load (measured slower)
@@ -275,8 +280,8 @@ __device__ __forceinline__ float sgn(float d) { return (d > 0.0f) ? 1.0f : ((d <
 // register moves (round 2: 299 -> 267 instructions per pair, 72 registers -> 14 warps x 2 CTAs per SM).  A segment that does not
 // start at pair 0 first walks the pair before it "carry-only" (forward step only: its residual gradient w.r.t. its target frame is
 // the carry the first real pair needs); the first frame of the next row is requested during the segment's last pair.
-template <bool L1TERM, bool GSTRIDE, int PAD, int WARPS>
-__global__ void __launch_bounds__(32 * WARPS, F2_MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
+template <bool L1TERM, bool GSTRIDE, int PAD, int WARPS, int MINB>
+__global__ void __launch_bounds__(32 * WARPS, MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
                                                                             float2* partials, int T, int B, int t0, int t1, long long per_warp, int pieces,
                                                                             long long gf4, unsigned* done_counter, float* __restrict__ losses, float inv_B) {
 #ifdef F2_SPLIT
@@ -296,6 +301,11 @@ __global__ void __launch_bounds__(32 * WARPS, F2_MINB) burgers_pair_loss_unit_ke
     __syncwarp();
     float* mine = su + lane;
     float* mine_acc = sacc + lane;
+#ifdef F2_TIMING
+    // diagnostic build (scripts/diag/burgers_tail.py): per warp (SM id, start, end) in ns of the global timer, kept in the unused part of `partials`
+    unsigned long long t_begin;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_begin));
+#endif
     const float2 X01 = f2((float)(4 * lane) + 0.5f, (float)(4 * lane) + 1.5f), X23 = f2((float)(4 * lane) + 2.5f, (float)(4 * lane) + 3.5f);
     typedef unsigned off_t32;                                          // float4 offsets of s fit 32 bits (checked by the launcher): one-instruction address updates
     const off_t32 f4 = (off_t32)B * 32;                               // float4 stride between frames
@@ -404,6 +414,16 @@ __global__ void __launch_bounds__(32 * WARPS, F2_MINB) burgers_pair_loss_unit_ke
             Bq = __ldcs(s4 + off + f4);
         }
     }
+#ifdef F2_TIMING
+    if (lane == 0) {
+        unsigned long long t_end;
+        unsigned smid;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_end));
+        asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+        uint4* dbg = reinterpret_cast<uint4*>(partials + 65536) + (size_t)blockIdx.x * WARPS + warp;
+        *dbg = make_uint4(smid, (unsigned)(t_begin & 0xffffffffu), (unsigned)(t_end & 0xffffffffu), 0u);
+    }
+#endif
     {
         const float a2 = warp_sum(acc2.x + acc2.y);
         acc1 = warp_sum(acc1);
@@ -466,16 +486,16 @@ int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials,
     const bool lean = gl1 == 0.0f && !strided && pad_mode == PDEC_MODE_CONSTANT;
     const int warps = lean ? F2_WARPS_LEAN : F2_WARPS;
     // one range per resident warp (148 SMs x F2_MINB CTAs x warps), at least 4 pairs per range
-    long long grid = 148LL * F2_MINB * F2_WAVES;
+    long long grid = 148LL * (lean ? F2_MINB_LEAN : F2_MINB) * F2_WAVES;
     if (grid * warps * 4 > total) grid = total / (4 * warps) > 0 ? total / (4 * warps) : 1;
     long long per_warp = (total + grid * warps - 1) / (grid * warps);
     // several shorter ranges per warp when there is enough work (each range start costs one carry-only forward step)
     int pieces = 1;
     while (pieces < F2_PIECES && per_warp / (pieces * 2) >= F2_PIECE_MIN) pieces *= 2;
     per_warp = (total + grid * warps * pieces - 1) / (grid * warps * pieces);
-#define F2_LAUNCH(L1, GS, PER, W) burgers_pair_loss_unit_kernel<L1, GS, PER, W><<<(unsigned)grid, 32 * W, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB)
-#define F2_PICK(L1, GS) do { if (pad_mode == PDEC_MODE_CIRCULAR) F2_LAUNCH(L1, GS, PDEC_MODE_CIRCULAR, F2_WARPS); else if (pad_mode == PDEC_MODE_REPLICATE) F2_LAUNCH(L1, GS, PDEC_MODE_REPLICATE, F2_WARPS); else F2_LAUNCH(L1, GS, PDEC_MODE_CONSTANT, F2_WARPS); } while (0)
-    if (lean) F2_LAUNCH(false, false, PDEC_MODE_CONSTANT, F2_WARPS_LEAN);
+#define F2_LAUNCH(L1, GS, PER, W, MB) burgers_pair_loss_unit_kernel<L1, GS, PER, W, MB><<<(unsigned)grid, 32 * W, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB)
+#define F2_PICK(L1, GS) do { if (pad_mode == PDEC_MODE_CIRCULAR) F2_LAUNCH(L1, GS, PDEC_MODE_CIRCULAR, F2_WARPS, F2_MINB); else if (pad_mode == PDEC_MODE_REPLICATE) F2_LAUNCH(L1, GS, PDEC_MODE_REPLICATE, F2_WARPS, F2_MINB); else F2_LAUNCH(L1, GS, PDEC_MODE_CONSTANT, F2_WARPS, F2_MINB); } while (0)
+    if (lean) F2_LAUNCH(false, false, PDEC_MODE_CONSTANT, F2_WARPS_LEAN, F2_MINB_LEAN);
     else if (gl1 != 0.0f) { if (strided) F2_PICK(true, true); else F2_PICK(true, false); }
     else { if (strided) F2_PICK(false, true); else F2_PICK(false, false); }
 #undef F2_PICK
