@@ -34,11 +34,12 @@ struct Unit2P {
 #define F2_ROW 164
 #define F2_OUT 512                    // "floor index" given to out-of-domain samples: taps at bytes 512 and 640
 #ifndef F2_MINB
-#define F2_MINB 2                     // resident CTAs per SM (A/B on one box, us per step, round 1 walk: 8x3 54.5, 7x4 53.5, 12x2 52.8, 4x6 55.3, 8x4 60.9
-                                      // and 6x5 63.6 spill; round 2 row-segment walk, 72 registers: 14x2 51.2, 12x2 53.3, 7x4 53.3, 9x3 55.3, 16x2 57.8 spills)
+#define F2_MINB 1                     // resident CTAs per SM: one (see F2_MINB_LEAN).  A/B on one box, us per step, round 1 walk: 8x3 54.5, 7x4 53.5, 12x2 52.8,
+                                      // 4x6 55.3, 8x4 60.9 and 6x5 63.6 spill; round 2 row-segment walk, 72 registers: 14x2 51.2, 12x2 53.3, 7x4 53.3, 9x3 55.3,
+                                      // 16x2 57.8 spills; periodic rows 12x2 55.3, 24x1 53.7; replicate rows 12x2 58.7, 24x1 57.0
 #endif
 #ifndef F2_WARPS
-#define F2_WARPS 12                   // warps per CTA (80 registers)
+#define F2_WARPS 24                   // warps per CTA (80 registers)
 #endif
 #ifndef F2_WARPS_LEAN
 #define F2_WARPS_LEAN 28              // warps per CTA of the variant that fits 72 registers without spills (no L1 term, dense gradient, 'constant')

@@ -10,6 +10,7 @@ import sys, os, json
 sys.path.insert(0, %r)
 import torch
 from benchlib.burgers import BurgersConfig2
+BurgersConfig2.mode = int(os.environ.get("AB_MODE", "0"))      # 2 = periodic rows
 wl = BurgersConfig2(torch.device("cuda", 0), 0, 1)
 for _ in range(10): wl.step()
 torch.cuda.synchronize()
