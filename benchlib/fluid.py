@@ -243,8 +243,7 @@ class FluidNotebook(object):
             vs = []
             frames = phi.unbind(0)                                                # one stack in the backward, not T zero-filled select_backwards
             for t in range(T):
-                vy, vx = ops.curl_2d(frames[t], MODE_CONSTANT)                       # U-Net output sampled like the density: 'constant'
-                rho = ops.advect_centered(rho, vy, vx, dt, MODE_CONSTANT)
+                rho, vy, vx = ops.curl_advect(rho, frames[t], dt, MODE_CONSTANT, MODE_CONSTANT)   # U-Net output sampled like the density: 'constant'
                 vs.append((vy, vx))
             d = rho - target
             loss = (d * d).sum() / (2 * B)
@@ -278,8 +277,9 @@ class FluidNotebook(object):
                 "peak_source": peak_src, "algorithmic_bytes_per_cell_update": self.algorithmic_bytes_per_cell_update,
                 "kernel": self.dominant_kernel,
                 "note": "72 B per cell-update = SURVEY 8d's figure for FUSED curl+advection and a fused force loss; the force loss is fused "
-                        "(pdec_staggered_force_loss: advect + residual + reduction, the advected field never stored), curl and density advection and "
-                        "the gather-transpose adjoints are still one kernel per operator, so the real traffic is ~2.5x that"}
+                        "(pdec_staggered_force_loss: advect + residual + reduction, the advected field never stored) and so are curl + density advection "
+                        "(pdec_curl_advect_2d); the gather-transpose adjoints stay two passes (coordinates, then the transpose), so the real traffic "
+                        "is ~2.5x that"}
 
     def parity(self, elements=(0, 63)):
         from oracle import restate as R

@@ -214,6 +214,20 @@ int pdec_advect_staggered_2d_bwd(const float* vy, const float* vx, const float* 
                                  float lower_x, float size_y, float size_x, void* workspace, size_t workspace_bytes,
                                  void* stream);
 
+/* ControlledIncompressibleFlow.step fused (src/control/pde/incompressible_flow.py:53-59): velocity = staggered_curl_2d(potential)
+ * (PF/physics/field/util.py:60-67) and next density = advect.semi_lagrangian(density, velocity, dt) (advect.py:24-37) in one launch;
+ * vy / vx are written (the force loss and the adjoint read them) but not read back.  Same bits as pdec_curl_2d_fwd followed by
+ * pdec_advect_centered_2d_fwd.  potential_mode = extrapolation of the potential, mode = of the density.
+ * _bwd: g_rho <- adjoint of the sampling (may be NULL), g_phi <- transpose of the curl applied to the velocity gradient of the
+ * advection PLUS add_vy / add_vx (gradients that reached the velocity by other routes, e.g. the force-loss terms; either may be
+ * NULL).  Workspace: pdec_advect_2d_workspace_bytes. */
+int pdec_curl_advect_2d_fwd(const float* rho, const float* phi, float* vy, float* vx, float* rho_out, int B, int ny, int nx,
+                            int potential_mode, int mode, double dt, float lower_y, float lower_x, float size_y, float size_x, void* stream);
+int pdec_curl_advect_2d_bwd(const float* rho, const float* vy, const float* vx, const float* g_out, const float* add_vy,
+                            const float* add_vx, float* g_rho, float* g_phi, int B, int ny, int nx, int potential_mode, int mode,
+                            double dt, float lower_y, float lower_x, float size_y, float size_x, void* workspace,
+                            size_t workspace_bytes, void* stream);
+
 /* One term of IncompFlowControl.total_force_loss fused (src/control/pde/incompressible_flow.py:31-43:
  * l2_loss(advect.semi_lagrangian(v1, v1, dt) - v2) summed over both staggered components, l2_loss = sum(d^2) / 2 / batch):
  * loss[0] = sum(resid_y^2) / 2 / B + sum(resid_x^2) / 2 / B with resid = advected(v) - (ty, tx); the residuals are kept for the adjoint,

@@ -69,6 +69,10 @@ _SIGNATURES = {
                                                 _c.c_double, _c.c_float, _c.c_float, _c.c_float, _c.c_float, _P, _c.c_size_t, _P]),
     "pdec_advect_staggered_2d_bwd": (_c.c_int, [_P, _P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int,
                                                  _c.c_double, _c.c_float, _c.c_float, _c.c_float, _c.c_float, _P, _c.c_size_t, _P]),
+    "pdec_curl_advect_2d_fwd": (_c.c_int, [_P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double,
+                                            _c.c_float, _c.c_float, _c.c_float, _c.c_float, _P]),
+    "pdec_curl_advect_2d_bwd": (_c.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double,
+                                            _c.c_float, _c.c_float, _c.c_float, _c.c_float, _P, _c.c_size_t, _P]),
     "pdec_staggered_force_loss_workspace_bytes": (_c.c_size_t, [_c.c_int, _c.c_int, _c.c_int]),
     "pdec_staggered_force_loss_fwd": (_c.c_int, [_P, _P, _P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double,
                                                   _c.c_float, _c.c_float, _c.c_float, _c.c_float, _P, _c.c_size_t, _P]),

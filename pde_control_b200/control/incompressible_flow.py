@@ -6,7 +6,7 @@ the force loss self-advects the staggered velocity; the target loss (FFT-weighte
 import numpy as np
 import torch
 
-from ..physics import CenteredGrid, Physics, StateDependency, staggered_curl_2d, semi_lagrangian, staggered_force_loss
+from ..physics import CenteredGrid, Physics, StateDependency, staggered_curl_2d, semi_lagrangian, staggered_force_loss, curl_advect
 from .networks import UNet
 from .pde_base import PDE
 
@@ -68,7 +68,7 @@ class ControlledIncompressibleFlow(Physics):
             potential = net(torch.cat([density.data, pred.prediction.density.data], -1))
         # the U-Net output is sampled like `density` (standard_networks.py:68): same box and extrapolation
         velocity_potential = CenteredGrid(potential, box=density.box, extrapolation=density.extrapolation, batch_size=density._batch_size)
-        velocity = staggered_curl_2d(velocity_potential)
-        next_density = semi_lagrangian(density, velocity, dt).copied_with(age=density.age + dt)
+        next_density, velocity = curl_advect(density, velocity_potential, dt)         # staggered_curl_2d + semi_lagrangian, one launch
+        next_density = next_density.copied_with(age=density.age + dt)
         next_density.velocity = velocity
         return next_density

@@ -415,8 +415,9 @@ template <int FMODE>
 __global__ void __launch_bounds__(256) advect_centered_bwd_kernel(FluidGeo g, const float* __restrict__ XY, const float* __restrict__ XX,
                                                                   const float* __restrict__ GY, const float* __restrict__ GX,
                                                                   const float* __restrict__ gout, const int* __restrict__ rmax,
-                                                                  float* __restrict__ g_rho, float* __restrict__ g_vy,
-                                                                  float* __restrict__ g_vx, int accumulate) {
+                                                                  float* __restrict__ g_rho, float* g_vy, float* g_vx,
+                                                                  const float* add_vy, const float* add_vx) {
+    // add_vy / add_vx (optional, same shapes as g_vy / g_vx, may alias them): gradients that reached the velocity by other routes
     const int ny = g.ny, nx = g.nx;
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     const size_t sf = (size_t)ny * nx;
@@ -435,15 +436,15 @@ __global__ void __launch_bounds__(256) advect_centered_bwd_kernel(FluidGeo g, co
         float v = 0.0f;
         if (i >= 1) v += g.c_wu[0] * __ldg(GY + b * sf + (size_t)(i - 1) * nx + j);
         if (i <= ny - 1) v += g.c_wl[0] * __ldg(GY + b * sf + (size_t)i * nx + j);
-        float* p = g_vy + b * (size_t)(ny + 1) * nx + (size_t)i * nx + j;
-        *p = accumulate ? *p + v : v;
+        const size_t at = b * (size_t)(ny + 1) * nx + (size_t)i * nx + j;
+        g_vy[at] = add_vy != nullptr ? add_vy[at] + v : v;
     }
     if (g_vx != nullptr && i < ny && j <= nx) {
         float v = 0.0f;
         if (j >= 1) v += g.c_wu[1] * __ldg(GX + b * sf + (size_t)i * nx + j - 1);
         if (j <= nx - 1) v += g.c_wl[1] * __ldg(GX + b * sf + (size_t)i * nx + j);
-        float* p = g_vx + b * (size_t)ny * (nx + 1) + (size_t)i * (nx + 1) + j;
-        *p = accumulate ? *p + v : v;
+        const size_t at = b * (size_t)ny * (nx + 1) + (size_t)i * (nx + 1) + j;
+        g_vx[at] = add_vx != nullptr ? add_vx[at] + v : v;
     }
 }
 
@@ -491,6 +492,37 @@ __global__ void __launch_bounds__(256) curl_fwd_kernel(const float* __restrict__
     const float c = load_mapped<MODE>(f, i, j, ny, nx);
     if (j < nx) vy[(size_t)b * (ny + 1) * nx + (size_t)i * nx + j] = c - load_mapped<MODE>(f, i, j + 1, ny, nx);
     if (i < ny) vx[(size_t)b * ny * (nx + 1) + (size_t)i * (nx + 1) + j] = load_mapped<MODE>(f, i + 1, j, ny, nx) - c;
+}
+
+// staggered_curl_2d + advect.semi_lagrangian(density, curl, dt) in one launch (ControlledIncompressibleFlow.step,
+// src/control/pde/incompressible_flow.py:53-59): a thread owns lattice point (i, j), writes the two face velocities it owns and, inside
+// the domain, advects the cell: the four face values of the cell come from the potential directly (same expressions as curl_fwd_kernel,
+// same bits), so the velocity is written for the later force loss / adjoint but never read back here.
+template <int PMODE, int FMODE>
+__global__ void __launch_bounds__(256) curl_advect_fwd_kernel(FluidGeo g, const float* __restrict__ rho, const float* __restrict__ phi,
+                                                              float* __restrict__ vy, float* __restrict__ vx, float* __restrict__ out) {
+    const int ny = g.ny, nx = g.nx;
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    __shared__ float s_py[8], s_px[32];
+    block_points(ny, nx, g.lo, g.sz, s_py, s_px);
+    if (i > ny || j > nx) return;
+    const float* f = phi + (size_t)b * ny * nx;
+    const float c = load_mapped<PMODE>(f, i, j, ny, nx);
+    const float pr = load_mapped<PMODE>(f, i, j + 1, ny, nx), pd = load_mapped<PMODE>(f, i + 1, j, ny, nx);
+    const float vy0 = c - pr, vx0 = pd - c;
+    if (j < nx) vy[(size_t)b * (ny + 1) * nx + (size_t)i * nx + j] = vy0;
+    if (i < ny) vx[(size_t)b * ny * (nx + 1) + (size_t)i * (nx + 1) + j] = vx0;
+    if (i >= ny || j >= nx) return;
+    const float pdr = load_mapped<PMODE>(f, i + 1, j + 1, ny, nx);
+    const float vy1 = pd - pdr, vx1 = pdr - pr;                        // vy[i + 1][j], vx[i][j + 1]
+    const float uy = vy1 * g.c_wu[0] + vy0 * g.c_wl[0];                // StaggeredGrid.at(centres), as velocity_at<V_CENTERED>
+    const float ux = vx1 * g.c_wu[1] + vx0 * g.c_wl[1];
+    const float y = s_py[threadIdx.y] - uy * g.dt, x = s_px[threadIdx.x] - ux * g.dt;
+    const float xiy = index_coord_fast(y, g.lo[0], g.sz[0], g.inv[0], (float)ny);
+    const float xix = index_coord_fast(x, g.lo[1], g.sz[1], g.inv[1], (float)nx);
+    float d0, d1;
+    const size_t sf = (size_t)ny * nx;
+    out[b * sf + (size_t)i * nx + j] = sample2d<FMODE, false>(rho + b * sf, ny, nx, xiy, xix, d0, d1);
 }
 
 template <int MODE>
@@ -829,7 +861,7 @@ extern "C" int pdec_advect_centered_2d_bwd(const float* rho, const float* vy, co
     if (cudaMemsetAsync(rmax, 0, 4 * (size_t)B * sizeof(int), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
 #define CALL(M)                                                                                                                     \
     advect_bwd_prep_kernel<V_CENTERED, M, 0><<<tiles(ny, nx, B), kBlock, 0, st>>>(g, rho, vy, vx, g_out, W, W + sf, W + 2 * sf, W + 3 * sf, rmax); \
-    advect_centered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, W, W + sf, W + 2 * sf, W + 3 * sf, g_out, rmax, g_rho, g_vy, g_vx, accumulate_v)
+    advect_centered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, W, W + sf, W + 2 * sf, W + 3 * sf, g_out, rmax, g_rho, g_vy, g_vx, accumulate_v ? g_vy : nullptr, accumulate_v ? g_vx : nullptr)
     MODE_SWITCH(mode, CALL);
 #undef CALL
     PDEC_CHECK_LAUNCH();
@@ -859,6 +891,64 @@ extern "C" int pdec_advect_staggered_2d_bwd(const float* vy, const float* vx, co
     advect_bwd_prep_kernel<V_COMP_X, M, M><<<tiles(ny, nx + 1, B), kBlock, 0, st>>>(g, vx, vy, vx, g_ax, W1, W1 + sx, W1 + 2 * sx, W1 + 3 * sx, rmax1); \
     advect_staggered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, W0, W1, g_ay, g_ax, rmax0, rmax1, g_vy, g_vx, accumulate, B)
     MODE_SWITCH(mode, CALL);
+#undef CALL
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+// ---- fused curl + density advection ----------------------------------------------------------------------
+template <int PM>
+static void launch_curl_advect(int fmode, const FluidGeo& g, const float* rho, const float* phi, float* vy, float* vx, float* out, int B, cudaStream_t st) {
+#define CALL(M) curl_advect_fwd_kernel<PM, M><<<tiles(g.ny + 1, g.nx + 1, B), kBlock, 0, st>>>(g, rho, phi, vy, vx, out)
+    MODE_SWITCH(fmode, CALL);
+#undef CALL
+}
+
+extern "C" int pdec_curl_advect_2d_fwd(const float* rho, const float* phi, float* vy, float* vx, float* rho_out, int B, int ny, int nx,
+                                       int potential_mode, int mode, double dt, float lower_y, float lower_x, float size_y, float size_x,
+                                       void* stream) {
+    FluidGeo g;
+    int rc = make_geo(g, B, ny, nx, dt, lower_y, lower_x, size_y, size_x);
+    if (rc != PDEC_OK) return rc;
+    if (bad_mode(mode) || bad_mode(potential_mode)) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!rho || !phi || !vy || !vx || !rho_out) return PDEC_ERR_INVALID_ARGUMENT;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (potential_mode == PDEC_MODE_CONSTANT) launch_curl_advect<PDEC_MODE_CONSTANT>(mode, g, rho, phi, vy, vx, rho_out, B, st);
+    else if (potential_mode == PDEC_MODE_REPLICATE) launch_curl_advect<PDEC_MODE_REPLICATE>(mode, g, rho, phi, vy, vx, rho_out, B, st);
+    else launch_curl_advect<PDEC_MODE_CIRCULAR>(mode, g, rho, phi, vy, vx, rho_out, B, st);
+    PDEC_CHECK_LAUNCH();
+    return PDEC_OK;
+}
+
+// adjoint: g_rho <- transpose of the sampling; the velocity gradient of the advection PLUS add_vy / add_vx (what reached the curl's
+// velocity by other routes: the force-loss terms; either may be NULL) goes through the transpose of the curl into g_phi.  The summed
+// face gradients live in the workspace (pdec_advect_2d_workspace_bytes has the room behind the four centred arrays).
+extern "C" int pdec_curl_advect_2d_bwd(const float* rho, const float* vy, const float* vx, const float* g_out, const float* add_vy,
+                                       const float* add_vx, float* g_rho, float* g_phi, int B, int ny, int nx, int potential_mode, int mode,
+                                       double dt, float lower_y, float lower_x, float size_y, float size_x, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+    FluidGeo g;
+    int rc = make_geo(g, B, ny, nx, dt, lower_y, lower_x, size_y, size_x);
+    if (rc != PDEC_OK) return rc;
+    if (bad_mode(mode) || bad_mode(potential_mode)) return PDEC_ERR_INVALID_ARGUMENT;
+    if (B == 0) return PDEC_OK;
+    if (!rho || !vy || !vx || !g_out || !g_phi || !workspace) return PDEC_ERR_INVALID_ARGUMENT;
+    if (workspace_bytes < pdec_advect_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+    cudaStream_t st = (cudaStream_t)stream;
+    int* rmax = reinterpret_cast<int*>(workspace);
+    float* W = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + ws_header(B));
+    const size_t sf = (size_t)B * ny * nx;
+    float* t_vy = W + 4 * sf;                                          // B * (ny + 1) * nx
+    float* t_vx = t_vy + (size_t)B * (ny + 1) * nx;                    // B * ny * (nx + 1)
+    if (cudaMemsetAsync(rmax, 0, 4 * (size_t)B * sizeof(int), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+#define CALL(M)                                                                                                                     \
+    advect_bwd_prep_kernel<V_CENTERED, M, 0><<<tiles(ny, nx, B), kBlock, 0, st>>>(g, rho, vy, vx, g_out, W, W + sf, W + 2 * sf, W + 3 * sf, rmax); \
+    advect_centered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, W, W + sf, W + 2 * sf, W + 3 * sf, g_out, rmax, g_rho, t_vy, t_vx, add_vy, add_vx)
+    MODE_SWITCH(mode, CALL);
+#undef CALL
+#define CALL(M) curl_bwd_kernel<M><<<tiles(ny, nx, B), kBlock, 0, st>>>(t_vy, t_vx, g_phi, ny, nx)
+    MODE_SWITCH(potential_mode, CALL);
 #undef CALL
     PDEC_CHECK_LAUNCH();
     return PDEC_OK;

@@ -333,6 +333,57 @@ def advect_centered(rho, vy, vx, dt, mode=MODE_CONSTANT, box=None):
     return _AdvectCentered.apply(rho, vy, vx, float(dt), int(mode), _box(box, rho.shape[1], rho.shape[2]))
 
 
+class _CurlAdvect(torch.autograd.Function):
+    """velocity = staggered_curl_2d(potential); next = advect.semi_lagrangian(density, velocity, dt) in one launch
+    (ControlledIncompressibleFlow.step, src/control/pde/incompressible_flow.py:53-59).  The backward takes the gradients that reached
+    the velocity by other routes (the force-loss terms) and adds them inside the adjoint kernel instead of in separate launches."""
+
+    @staticmethod
+    def forward(ctx, rho, phi, dt, potential_mode, mode, box):
+        _req_cuda(rho, phi)
+        rho, phi = _c(rho), _c(phi)
+        B, ny, nx = rho.shape
+        assert phi.shape == rho.shape, (rho.shape, phi.shape)
+        out = torch.empty_like(rho)
+        vy = torch.empty((B, ny + 1, nx), device=rho.device, dtype=torch.float32)
+        vx = torch.empty((B, ny, nx + 1), device=rho.device, dtype=torch.float32)
+        with torch.cuda.device(rho.device):
+            _call("pdec_curl_advect_2d_fwd", _lib.ptr(rho), _lib.ptr(phi), _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(out), B, ny, nx,
+                  potential_mode, mode, dt, *box, _lib.stream_ptr())
+        ctx.save_for_backward(rho, vy, vx)
+        ctx.cfg = (dt, potential_mode, mode, box)
+        ctx.set_materialize_grads(False)
+        return out, vy, vx
+
+    @staticmethod
+    def backward(ctx, g_out, g_vy, g_vx):
+        rho, vy, vx = ctx.saved_tensors
+        dt, potential_mode, mode, box = ctx.cfg
+        B, ny, nx = rho.shape
+        if g_out is None:
+            if g_vy is None and g_vx is None:
+                return None, None, None, None, None, None
+            g_out = torch.zeros_like(rho)
+        g_out = _c(g_out)
+        g_vy = _c(g_vy) if g_vy is not None else None
+        g_vx = _c(g_vx) if g_vx is not None else None
+        g_rho = torch.empty_like(rho) if ctx.needs_input_grad[0] else None
+        g_phi = torch.empty_like(rho)
+        nbytes = _lib.lib().pdec_advect_2d_workspace_bytes(B, ny, nx)
+        ws = _lib.workspace(rho.device, nbytes)
+        with torch.cuda.device(rho.device):
+            _call("pdec_curl_advect_2d_bwd", _lib.ptr(rho), _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(g_out),
+                  _lib.ptr(g_vy) if g_vy is not None else 0, _lib.ptr(g_vx) if g_vx is not None else 0,
+                  _lib.ptr(g_rho) if g_rho is not None else 0, _lib.ptr(g_phi), B, ny, nx, potential_mode, mode, dt, *box,
+                  _lib.ptr(ws), nbytes, _lib.stream_ptr())
+        return g_rho, g_phi, None, None, None, None
+
+
+def curl_advect(rho, phi, dt, potential_mode=MODE_CONSTANT, mode=MODE_CONSTANT, box=None):
+    """(next density, vy, vx) of the controlled step; see _CurlAdvect."""
+    return _CurlAdvect.apply(rho, phi, float(dt), int(potential_mode), int(mode), _box(box, rho.shape[1], rho.shape[2]))
+
+
 class _AdvectStaggered(torch.autograd.Function):
     """advect.semi_lagrangian(v, v, dt) on a StaggeredGrid (advect.py:38-40)."""
 

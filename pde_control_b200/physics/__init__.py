@@ -7,7 +7,7 @@ from .field import (Field, CenteredGrid, StaggeredGrid, FieldEffect, GROW, ADD, 
                     staggered_component_box)
 from .burgers import DomainState, BurgersVelocity, Burgers
 from .fluid import (Fluid, IncompressibleFlow, INCOMPRESSIBLE_FLOW, SparseCG, poisson_solve, divergence_free, semi_lagrangian,
-                    staggered_curl_2d, gravity_tensor, Obstacle, FourierSolver, SparseSciPy, staggered_force_loss)
+                    staggered_curl_2d, gravity_tensor, Obstacle, FourierSolver, SparseSciPy, staggered_force_loss, curl_advect)
 from .geom import (Geometry, Sphere, Union, union, GeometryMask, mask, ConstantField, AnalyticField, Inflow, Accelerator, Fan,
                    ConstantVelocity, HeatSource, ColdSource)
 

@@ -197,6 +197,18 @@ def staggered_curl_2d(grid):
     return StaggeredGrid([vy.unsqueeze(-1), vx.unsqueeze(-1)], box=grid.box, batch_size=grid._batch_size)
 
 
+def curl_advect(density, potential, dt):
+    """(semi_lagrangian(density, staggered_curl_2d(potential), dt), staggered_curl_2d(potential)) -- the controlled step
+    (src/control/pde/incompressible_flow.py:56-58) -- through the fused kernel where both extrapolations are uniform."""
+    if isinstance(density.extrapolation, str) and isinstance(potential.extrapolation, str) and density.rank == 2 and potential.compatible(density):
+        out, vy, vx = ops.curl_advect(density.tensor, potential.tensor, dt, MODE_OF_EXTRAPOLATION[potential.extrapolation],
+                                      MODE_OF_EXTRAPOLATION[density.extrapolation], _box4(density.box))
+        velocity = StaggeredGrid([vy.unsqueeze(-1), vx.unsqueeze(-1)], box=potential.box, batch_size=potential._batch_size)
+        return density.with_tensor(out), velocity
+    velocity = staggered_curl_2d(potential)
+    return semi_lagrangian(density, velocity, dt), velocity
+
+
 def _box4(box):
     return tuple(float(v) for v in box.lower) + tuple(float(v) for v in box.size)
 

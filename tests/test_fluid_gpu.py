@@ -135,6 +135,47 @@ def test_fused_staggered_force_loss_vs_oracle_and_vs_the_operator_composition(mo
     assert l3.item() == lc.item() and torch.equal(y3.grad, yc.grad) and torch.equal(x3.grad, xc.grad)
 
 
+@pytest.mark.parametrize("pmode", MODES)
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("shape,box", [((2, 33, 40), None), ((3, 128, 128), None), ((2, 24, 18), (0.5, -1.0, 3.0, 4.5))])
+def test_fused_curl_advect_is_the_two_operator_composition(pmode, mode, shape, box):
+    """pdec_curl_advect_2d_fwd / _bwd (ControlledIncompressibleFlow.step, src/control/pde/incompressible_flow.py:53-59): forward bit-identical
+    to pdec_curl_2d_fwd + pdec_advect_centered_2d_fwd; gradients (density loss + terms on the velocity, which enter through add_vy /
+    add_vx) equal the composition's up to the order of one float addition."""
+    ops = _ops()
+    B, ny, nx = shape
+    rng = np.random.RandomState(3 * ny + 7 * mode + pmode)
+    rho = rng.rand(B, ny, nx).astype(np.float32)
+    phi = (rng.randn(B, ny, nx) * 1.5).astype(np.float32)
+    wr = rng.randn(B, ny, nx).astype(np.float32)
+    wy, wx = rng.randn(B, ny + 1, nx).astype(np.float32), rng.randn(B, ny, nx + 1).astype(np.float32)
+    (r1, p1), (r2, p2) = [[torch.tensor(a).cuda().requires_grad_() for a in (rho, phi)] for _ in range(2)]
+    W = [torch.tensor(a).cuda() for a in (wr, wy, wx)]
+    o1, y1, x1 = ops.curl_advect(r1, p1, 0.8, pmode, mode, box)
+    y2, x2 = ops.curl_2d(p2, pmode)
+    o2 = ops.advect_centered(r2, y2, x2, 0.8, mode, box)
+    assert torch.equal(o1, o2) and torch.equal(y1, y2) and torch.equal(x1, x2)
+    ((o1 * W[0]).sum() + (y1 * W[1]).sum() + 0.5 * (x1 * W[2]).sum()).backward()
+    ((o2 * W[0]).sum() + (y2 * W[1]).sum() + 0.5 * (x2 * W[2]).sum()).backward()
+    assert torch.equal(r1.grad, r2.grad)
+    assert rel_err(p1.grad.cpu(), p2.grad.cpu()) < 2e-6
+    # only the density output used / only a velocity output used
+    r3, p3 = [torch.tensor(a).cuda().requires_grad_() for a in (rho, phi)]
+    o3, y3, x3 = ops.curl_advect(r3, p3, 0.8, pmode, mode, box)
+    (o3 * W[0]).sum().backward()
+    r4, p4 = [torch.tensor(a).cuda().requires_grad_() for a in (rho, phi)]
+    y4, x4 = ops.curl_2d(p4, pmode)
+    (ops.advect_centered(r4, y4, x4, 0.8, mode, box) * W[0]).sum().backward()
+    assert torch.equal(r3.grad, r4.grad) and torch.equal(p3.grad, p4.grad)
+    r5, p5 = [torch.tensor(a).cuda().requires_grad_() for a in (rho, phi)]
+    o5, y5, x5 = ops.curl_advect(r5, p5, 0.8, pmode, mode, box)
+    (y5 * W[1]).sum().backward()
+    p6 = torch.tensor(phi).cuda().requires_grad_()
+    y6, x6 = ops.curl_2d(p6, pmode)
+    (y6 * W[1]).sum().backward()
+    assert rel_err(p5.grad.cpu(), p6.grad.cpu()) < 2e-6 and float(r5.grad.abs().max()) == 0.0
+
+
 def test_total_force_loss_of_the_control_module_takes_the_fused_kernel():
     """IncompFlowControl.total_force_loss equivalent (control/incompressible_flow.py) on StaggeredGrids from the curl: same value as the
     oracle's force_loss on the golden notebook frame."""
