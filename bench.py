@@ -239,10 +239,17 @@ def main():
     ap.add_argument("--no-parity", action="store_true", help="skip the in-run oracle checks")
     args = ap.parse_args()
     t0 = time.time()
+    # stdout carries the ONE JSON line and nothing else: libraries that write to file descriptor 1 themselves (NCCL prints its version
+    # there at the first communicator) are sent to stderr for the length of the run
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(json_fd, "w")
     if args.impl == "reference":
         run_reference(args)
     else:
         run_b200(args)
+    sys.stdout.flush()
     if int(os.environ.get("RANK", "0")) == 0:
         print("bench.py wall %.1f s" % (time.time() - t0), file=sys.stderr)
 
