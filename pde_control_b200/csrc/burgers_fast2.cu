@@ -49,15 +49,8 @@ struct Unit2P {
                                       // CTA, which then finishes 5 us before the younger one and leaves the SM half empty for that long (per-warp timers,
                                       // scripts/diag/burgers_tail.py: CTAs 0..147 37 us, CTAs 148..295 42 us; one CTA: all warps 40 us).  14x2 51.2, 28x1 49.2, 24x1 51.4 us
 #endif
-#ifndef F2_WAVES
-#define F2_WAVES 1                    // CTAs per resident slot: > 1 lets the hardware scheduler balance the load (measured slower)
-#endif
-#ifndef F2_PIECES
-#define F2_PIECES 1                   // most ranges per warp (power of two)
-#endif
-#ifndef F2_PIECE_MIN
-#define F2_PIECE_MIN 4                // shortest range, in pairs
-#endif
+// Measured and dropped (profiles/r1k_burgers_summary.md, r2ab_burgers_walk.md): several shorter ranges per warp, more CTAs than resident
+// slots, floor / ceil parts in two accumulator rows, a second register-staged prefetch, a cp.async ring of 2-5 frames per warp.
 
 __device__ __forceinline__ float2 f2(float x, float y) { return make_float2(x, y); }
 __device__ __forceinline__ float2 sub2(float2 a, float2 b) { return __ffma2_rn(b, f2(-1.0f, -1.0f), a); }   // rn(a - b), one rounding
@@ -188,36 +181,19 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
             ordered = ordered && (lane == 0 || (cf > pf && cc > pc));
         }
     }
-#ifdef F2_SKIP_SCATTER
-    if (false) {
-#else
     if (__all_sync(PDEC_FULL_MASK, ordered)) {
-#endif
         // strictly increasing floor(xi) over the lanes: the in-domain targets of one warp instruction are distinct (floor targets
         // among themselves, ceil targets among themselves); out-of-domain lanes all hit the scratch words
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-#ifdef F2_SPLIT
-            // floor and ceil parts in two rows, both at the floor offset: two independent read-modify-writes per sample
-            float* af = ptr_off(sacc, S.offF[k]);
-            float* ac = ptr_off(sacc + F2_ROW, S.offF[k]);
-            const float a = *af, c = *ac;
-            *af = fmaf(-q[k], w1[k], a);
-            *ac = fmaf(-q[k], w0[k], c);
-            __syncwarp();
-#else
             float* af = ptr_off(sacc, S.offF[k]);
             *af = fmaf(-q[k], w1[k], *af);
             __syncwarp();
             float* ac = ptr_off(sacc, S.offC[k]);
             *ac = fmaf(-q[k], w0[k], *ac);
             __syncwarp();
-#endif
         }
     } else
-#ifdef F2_SKIP_SCATTER
-    if (false)
-#endif
     {
         // folded back-trace (a shock steeper than one cell per cell): lanes that share a floor index are ranked by lane id
         // (match_any) and take turns by rank -- same sums in a fixed order, as many rounds as the largest group
@@ -240,11 +216,7 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
                 }
                 __syncwarp();
                 if (inside && rankC == r) {
-#ifdef F2_SPLIT
-                    float* ac = ptr_off(sacc + F2_ROW, S.offF[k]);
-#else
                     float* ac = ptr_off(sacc, S.offC[k]);
-#endif
                     *ac = fmaf(-q[k], w0[k], *ac);
                 }
                 __syncwarp();
@@ -252,19 +224,8 @@ __device__ __forceinline__ void step2_adjoint(const Unit2P& p, const Step2& S, f
         }
     }
     // transpose of the gather (own four cells) plus the derivative through xi(u)
-#ifdef F2_SPLIT
-    // cell j = floor part of slot j + ceil part of slot j - 1 (for the lane's first cell that is the previous lane's last slot)
-    float* mine_c = mine_acc + F2_ROW;
-    const float cprev = lane > 0 ? mine_c[95] : 0.0f;
-    const float c0 = mine_c[0], c1 = mine_c[32], c2 = mine_c[64];
-    const float o0 = mine_acc[0] + cprev, o1 = mine_acc[32] + c0, o2 = mine_acc[64] + c1, o3 = mine_acc[96] + c2;
-    __syncwarp();                                                      // the neighbour's slot is read before its owner clears it
-    mine_acc[0] = 0.0f; mine_acc[32] = 0.0f; mine_acc[64] = 0.0f; mine_acc[96] = 0.0f;
-    mine_c[0] = 0.0f; mine_c[32] = 0.0f; mine_c[64] = 0.0f; mine_c[96] = 0.0f;
-#else
     const float o0 = mine_acc[0], o1 = mine_acc[32], o2 = mine_acc[64], o3 = mine_acc[96];
     mine_acc[0] = 0.0f; mine_acc[32] = 0.0f; mine_acc[64] = 0.0f; mine_acc[96] = 0.0f;
-#endif
     const float2 dt2 = f2(p.dt128, p.dt128);
     const float2 e01 = __fmul2_rn(f2(S.du[0], S.du[1]), dt2), e23 = __fmul2_rn(f2(S.du[2], S.du[3]), dt2);   // -du * dxi/du
     gin01 = __ffma2_rn(q01, e01, f2(o0, o1));
@@ -283,22 +244,15 @@ __device__ __forceinline__ float sgn(float d) { return (d > 0.0f) ? 1.0f : ((d <
 // the carry the first real pair needs); the first frame of the next row is requested during the segment's last pair.
 template <bool L1TERM, bool GSTRIDE, int PAD, int WARPS, int MINB>
 __global__ void __launch_bounds__(32 * WARPS, MINB) burgers_pair_loss_unit_kernel(Unit2P p, const float* __restrict__ s, float* __restrict__ grad_s,
-                                                                            float2* partials, int T, int B, int t0, int t1, long long per_warp, int pieces,
+                                                                            float2* partials, int T, int B, int t0, int t1, long long per_warp,
                                                                             long long gf4, unsigned* done_counter, float* __restrict__ losses, float inv_B) {
-#ifdef F2_SPLIT
-    __shared__ float smem[WARPS][3][F2_ROW];
-#else
     __shared__ float smem[WARPS][2][F2_ROW];
-#endif
     __shared__ float red2[WARPS], red1[WARPS];
     __shared__ unsigned s_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* su = smem[warp][0];
     float* sacc = smem[warp][1];
     for (int q = lane; q < F2_ROW; q += 32) { su[q] = 0.0f; sacc[q] = 0.0f; }
-#ifdef F2_SPLIT
-    for (int q = lane; q < F2_ROW; q += 32) sacc[F2_ROW + q] = 0.0f;
-#endif
     __syncwarp();
     float* mine = su + lane;
     float* mine_acc = sacc + lane;
@@ -317,14 +271,10 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) burgers_pair_loss_unit_kerne
     const float2 gl2v = f2(p.gl2, p.gl2);
     const int Cw = t1 - t0;                                            // pairs per row in the window
     const long long total = (long long)B * Cw;
-    // a warp's share = `pieces` ranges of per_warp pairs, piece k of warp w at ((k * warps) + w) * per_warp: rows that take the slow
-    // scatter path for all their pairs (shocks) are spread over several warps instead of landing on one
-    const long long n_warps = (long long)gridDim.x * WARPS;
     float2 acc2 = f2(0.0f, 0.0f);
     float acc1 = 0.0f;
-    const int npieces = F2_PIECES == 1 ? 1 : pieces;                   // the default build has no piece loop
-    for (int piece = 0; piece < npieces; ++piece) {
-        const long long P0 = ((long long)piece * n_warps + (long long)blockIdx.x * WARPS + warp) * per_warp;
+    do {                                                               // this warp's range: per_warp pairs from P0
+        const long long P0 = ((long long)blockIdx.x * WARPS + warp) * per_warp;
         const long long P1 = min(total, P0 + per_warp);
         if (P0 >= P1) break;
         int left = (int)(P1 - P0);                                     // real pairs of the range not yet handed to a row segment
@@ -388,11 +338,7 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) burgers_pair_loss_unit_kerne
                 off += f4;                                                                                                               \
                 if (GSTRIDE) goff += (size_t)gf4;                                                                                        \
             }
-#if defined(F2_SKIP_ADJ)
-#define F2_ADJOINT_CALL gin01 = gd01; gin23 = gd23;
-#else
 #define F2_ADJOINT_CALL step2_adjoint<PAD>(p, S, gd01, gd23, sacc, mine_acc, lane, gin01, gin23);      /* dL/dv = -gd */
-#endif
             bool in_b;                                                 // the row's last frame ended up in B (else in A); the other holds the next row's first
             while (true) {
                 F2_PAIR(A, Bq)
@@ -414,7 +360,7 @@ __global__ void __launch_bounds__(32 * WARPS, MINB) burgers_pair_loss_unit_kerne
             off = next_first;
             Bq = __ldcs(s4 + off + f4);
         }
-    }
+    } while (false);
 #ifdef F2_TIMING
     if (lane == 0) {
         unsigned long long t_end;
@@ -487,14 +433,10 @@ int pdec_burgers_pair_loss_unit(const float* s, float* grad_s, float2* partials,
     const bool lean = gl1 == 0.0f && !strided && pad_mode == PDEC_MODE_CONSTANT;
     const int warps = lean ? F2_WARPS_LEAN : F2_WARPS;
     // one range per resident warp (148 SMs x F2_MINB CTAs x warps), at least 4 pairs per range
-    long long grid = 148LL * (lean ? F2_MINB_LEAN : F2_MINB) * F2_WAVES;
+    long long grid = 148LL * (lean ? F2_MINB_LEAN : F2_MINB);
     if (grid * warps * 4 > total) grid = total / (4 * warps) > 0 ? total / (4 * warps) : 1;
     long long per_warp = (total + grid * warps - 1) / (grid * warps);
-    // several shorter ranges per warp when there is enough work (each range start costs one carry-only forward step)
-    int pieces = 1;
-    while (pieces < F2_PIECES && per_warp / (pieces * 2) >= F2_PIECE_MIN) pieces *= 2;
-    per_warp = (total + grid * warps * pieces - 1) / (grid * warps * pieces);
-#define F2_LAUNCH(L1, GS, PER, W, MB) burgers_pair_loss_unit_kernel<L1, GS, PER, W, MB><<<(unsigned)grid, 32 * W, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, pieces, gf4, done_counter, losses, invB)
+#define F2_LAUNCH(L1, GS, PER, W, MB) burgers_pair_loss_unit_kernel<L1, GS, PER, W, MB><<<(unsigned)grid, 32 * W, 0, st>>>(p, s, grad_s, partials, T, B, t0, t1, per_warp, gf4, done_counter, losses, invB)
 #define F2_PICK(L1, GS) do { if (pad_mode == PDEC_MODE_CIRCULAR) F2_LAUNCH(L1, GS, PDEC_MODE_CIRCULAR, F2_WARPS, F2_MINB); else if (pad_mode == PDEC_MODE_REPLICATE) F2_LAUNCH(L1, GS, PDEC_MODE_REPLICATE, F2_WARPS, F2_MINB); else F2_LAUNCH(L1, GS, PDEC_MODE_CONSTANT, F2_WARPS, F2_MINB); } while (0)
     if (lean) F2_LAUNCH(false, false, PDEC_MODE_CONSTANT, F2_WARPS_LEAN, F2_MINB_LEAN);
     else if (gl1 != 0.0f) { if (strided) F2_PICK(true, true); else F2_PICK(true, false); }
