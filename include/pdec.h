@@ -316,6 +316,15 @@ int pdec_poisson_direct_2d_supported(int ny, int nx);
 int pdec_poisson_direct_2d_setup(void* spectral, size_t spectral_bytes, int ny, int nx, int closed, void* stream);
 int pdec_poisson_direct_2d(const float* rhs, float* p, int B, int ny, int nx, const void* spectral, void* stream);
 
+/* The same exact solve on the tensor cores (tcgen05.mma kind::tf32, accumulators in tensor memory): every 128^3 product is three TF32
+ * products on exact hi / lo splits of both operands (A_hi B_hi + A_lo B_hi + A_hi B_lo, fp32 accumulation), so the result stays at
+ * fp32 rounding level.  Same arguments and meaning as pdec_poisson_direct_2d*, but its own spectral block (the constant matrices
+ * pre-split and laid out as tensor-core operands): pdec_poisson_direct_tc_2d_spectral_bytes() bytes, 16-byte aligned, filled by
+ * pdec_poisson_direct_tc_2d_setup.  Replaces the same reference class (SparseSciPy, PF/physics/pressuresolver/sparse.py:14-37). */
+size_t pdec_poisson_direct_tc_2d_spectral_bytes(void);
+int pdec_poisson_direct_tc_2d_setup(void* spectral, size_t spectral_bytes, int ny, int nx, int closed, void* stream);
+int pdec_poisson_direct_tc_2d(const float* rhs, float* p, int B, int ny, int nx, const void* spectral, void* stream);
+
 /* The stencil of a domain with obstacles from its cell mask (replaces the LaplaceMatrix op, PF/tf/cuda/src/laplace_op.cc:10-17, and
  * PoissonDomain's mask logic, solver_api.py:51-121): active [ny*nx] floats (1 fluid, 0 obstacle) -> code [ny*nx] bytes as
  * pdec_cg_poisson_2d_masked reads them, and the face masks fy [(ny+1)*nx], fx [ny*(nx+1)] that multiply the velocity before the

@@ -99,6 +99,9 @@ _SIGNATURES = {
     "pdec_poisson_direct_2d_supported": (_c.c_int, [_c.c_int, _c.c_int]),
     "pdec_poisson_direct_2d_setup": (_c.c_int, [_P, _c.c_size_t, _c.c_int, _c.c_int, _c.c_int, _P]),
     "pdec_poisson_direct_2d": (_c.c_int, [_P, _P, _c.c_int, _c.c_int, _c.c_int, _P, _P]),
+    "pdec_poisson_direct_tc_2d_spectral_bytes": (_c.c_size_t, []),
+    "pdec_poisson_direct_tc_2d_setup": (_c.c_int, [_P, _c.c_size_t, _c.c_int, _c.c_int, _c.c_int, _P]),
+    "pdec_poisson_direct_tc_2d": (_c.c_int, [_P, _P, _c.c_int, _c.c_int, _c.c_int, _P, _P]),
     "pdec_laplace_matrix_2d": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _P]),
     "pdec_cg_poisson_2d_masked": (_c.c_int, [_P, _P, _P, _P, _P, _P, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _c.c_int, _c.c_int,
                                               _P, _c.c_size_t, _P]),

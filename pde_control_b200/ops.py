@@ -517,27 +517,36 @@ def cg_poisson_raw(rhs, out, closed, accuracy, max_iterations, guess=None, itera
 _SPECTRAL = {}
 
 
-def _spectral_block(device, ny, nx, closed):
-    """Eigenvector matrices + reciprocal eigenvalue sums of the (ny, nx, closed) Poisson matrix, built once on the device."""
-    key = (device.index if device.index is not None else torch.cuda.current_device(), int(ny), int(nx), closed_code(closed))
+# PDEC_DIRECT_TENSOR_CORES=0 selects the fp32 FFMA kernel of the direct solver (A/B runs); default: the tcgen05 3 x TF32 kernel
+_DIRECT_TC = os.environ.get("PDEC_DIRECT_TENSOR_CORES", "1") != "0"
+
+
+def _spectral_block(device, ny, nx, closed, tensor_cores=None):
+    """Eigenvector matrices + reciprocal eigenvalue sums of the (ny, nx, closed) Poisson matrix, built once on the device (one block per
+    kernel flavour: plain fp32 matrices for the FFMA kernel; hi / lo TF32 splits in the tensor core's operand layout for the tcgen05 one)."""
+    tc = _DIRECT_TC if tensor_cores is None else bool(tensor_cores)
+    key = (device.index if device.index is not None else torch.cuda.current_device(), int(ny), int(nx), closed_code(closed), tc)
     blk = _SPECTRAL.get(key)
     if blk is None:
         L = _lib.lib()
-        nbytes = L.pdec_poisson_direct_2d_spectral_bytes()
+        name = "pdec_poisson_direct_tc_2d" if tc else "pdec_poisson_direct_2d"
+        nbytes = getattr(L, name + "_spectral_bytes")()
         blk = torch.empty(nbytes // 4, device=device, dtype=torch.float32)
         with torch.cuda.device(device):
-            _call("pdec_poisson_direct_2d_setup", _lib.ptr(blk), nbytes, int(ny), int(nx), closed_code(closed), _lib.stream_ptr())
+            _call(name + "_setup", _lib.ptr(blk), nbytes, int(ny), int(nx), closed_code(closed), _lib.stream_ptr())
         # built on the current stream; other streams (graph branches) only ever read it after this one has been joined
         torch.cuda.current_stream(device).synchronize()
         _SPECTRAL[key] = blk
     return blk
 
 
-def poisson_direct_raw(rhs, out, closed):
+def poisson_direct_raw(rhs, out, closed, tensor_cores=None):
     B, ny, nx = rhs.shape
-    blk = _spectral_block(rhs.device, ny, nx, closed)
+    tc = _DIRECT_TC if tensor_cores is None else bool(tensor_cores)
+    blk = _spectral_block(rhs.device, ny, nx, closed, tc)
     with torch.cuda.device(rhs.device):
-        _call("pdec_poisson_direct_2d", _lib.ptr(rhs), _lib.ptr(out), B, ny, nx, _lib.ptr(blk), _lib.stream_ptr())
+        _call("pdec_poisson_direct_tc_2d" if tc else "pdec_poisson_direct_2d", _lib.ptr(rhs), _lib.ptr(out), B, ny, nx, _lib.ptr(blk),
+              _lib.stream_ptr())
 
 
 class _PressureSolveDirect(torch.autograd.Function):

@@ -469,6 +469,51 @@ def test_controlled_variant_and_force_loss_vs_golden_and_oracle():
     assert rel_err(pc.grad.cpu(), po.grad) < 1e-3 and rel_err(rc.grad.cpu(), ro.grad) < 1e-3
 
 
+@pytest.mark.parametrize("closed", [False, True, (True, False, False, True), (False, True, True, True)])
+@pytest.mark.parametrize("B,ny,nx", [(5, 128, 128), (2, 64, 128), (3, 100, 90), (1, 37, 50), (2, 2, 3), (150, 16, 24)])
+def test_tensor_core_direct_solver_against_the_fp32_kernel_and_the_residual(closed, B, ny, nx):
+    """pdec_poisson_direct_tc_2d (tcgen05.mma kind::tf32, three products on hi / lo splits, accumulators in tensor memory) against
+    pdec_poisson_direct_2d (fp32 FFMA) on the same right-hand sides -- uniform and per-side boundaries, ragged sizes (zero padding), more
+    elements than SMs -- and, independently, A p == rhs through the oracle's stencil on the uniform domains.  Same bits twice in a row."""
+    ops = _ops()
+    rng = np.random.RandomState(ny * 7 + nx + B)
+    rhs = _smooth(rng, (B, ny, nx), 1.0, passes=2) if min(ny, nx) > 4 else rng.randn(B, ny, nx).astype(np.float32)
+    t = torch.tensor(rhs, device="cuda")
+    p_tc, p_tc2, p_ff = torch.empty_like(t), torch.empty_like(t), torch.empty_like(t)
+    ops.poisson_direct_raw(t, p_tc, closed, tensor_cores=True)
+    ops.poisson_direct_raw(t, p_ff, closed, tensor_cores=False)
+    ops.poisson_direct_raw(t, p_tc2, closed, tensor_cores=True)
+    assert torch.equal(p_tc, p_tc2)
+    scale = float(p_ff.abs().max())
+    assert float((p_tc - p_ff).abs().max()) < 2e-5 * scale
+    if isinstance(closed, bool):
+        bd = "closed" if closed else "open"
+        target = rhs - rhs.mean((1, 2), keepdims=True) if closed else rhs
+        resid = (F.laplace_apply(p_tc.cpu().double(), bd) - torch.tensor(target).double()).abs().max()
+        assert float(resid) < 4e-5 * max(1.0, scale)
+
+
+def test_tensor_core_direct_solver_c_abi_codes():
+    """Return codes of the tensor-core entry points: sizes beyond 128, too small or misaligned spectral block, null pointers, B = 0."""
+    ops = _ops()
+    from pde_control_b200 import _lib
+    L = _lib.lib()
+    n = L.pdec_poisson_direct_tc_2d_spectral_bytes()
+    assert n % 16 == 0 and n > 4 * 128 * 128 * 4
+    blk = torch.empty(n // 4 + 4, device="cuda")
+    st = _lib.stream_ptr()
+    assert L.pdec_poisson_direct_tc_2d_setup(_lib.ptr(blk), n, 129, 64, 0, st) == -2
+    assert L.pdec_poisson_direct_tc_2d_setup(_lib.ptr(blk), n - 16, 64, 64, 0, st) == -4
+    assert L.pdec_poisson_direct_tc_2d_setup(blk.data_ptr() + 4, n, 64, 64, 0, st) == -1
+    assert L.pdec_poisson_direct_tc_2d_setup(0, n, 64, 64, 0, st) == -1
+    assert L.pdec_poisson_direct_tc_2d_setup(_lib.ptr(blk), n, 64, 64, 0, st) == 0
+    x = torch.zeros(2, 64, 64, device="cuda")
+    assert L.pdec_poisson_direct_tc_2d(_lib.ptr(x), _lib.ptr(x), 0, 64, 64, _lib.ptr(blk), st) == 0
+    assert L.pdec_poisson_direct_tc_2d(0, _lib.ptr(x), 2, 64, 64, _lib.ptr(blk), st) == -1
+    assert L.pdec_poisson_direct_tc_2d(_lib.ptr(x), _lib.ptr(x), 2, 200, 64, _lib.ptr(blk), st) == -2
+    torch.cuda.synchronize()
+
+
 @pytest.mark.parametrize("closed", [False, True])
 @pytest.mark.parametrize("B,ny,nx", [(3, 128, 128), (2, 64, 128), (2, 100, 90), (1, 37, 50), (2, 16, 24)])
 def test_fused_projection_is_bit_identical_to_the_three_operator_composition(closed, B, ny, nx):
