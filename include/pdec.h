@@ -202,7 +202,8 @@ int pdec_advect_centered_2d_fwd(const float* rho, const float* vy, const float* 
 int pdec_advect_staggered_2d_fwd(const float* vy, const float* vx, float* ay, float* ax, int B, int ny, int nx, int mode,
                                  double dt, float lower_y, float lower_x, float size_y, float size_x, void* stream);
 /* adjoints (replace TF autodiff of gather_nd; native twin ResampleGradient, resample_gradient.cu.cc:138-226, which uses
- * float atomics): deterministic gather-transpose over a window bounded by the per-element maximum displacement.
+ * float atomics): every sample's shares are added to 64-bit fixed-point accumulators with integer atomics -- order-independent, so
+ * the result is bit-reproducible -- then converted and combined with the fixed face stencils of the velocity routes.
  * g_rho / g_vy / g_vx of the centred variant may be NULL (not wanted). */
 size_t pdec_advect_2d_workspace_bytes(int B, int ny, int nx);
 int pdec_advect_centered_2d_bwd(const float* rho, const float* vy, const float* vx, const float* g_out, float* g_rho,

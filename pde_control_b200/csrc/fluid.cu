@@ -10,11 +10,9 @@
 // reads/writes 128 contiguous bytes of a row; gathers go through the read-only L1 path (__ldg) -- at the
 // configured sizes all fields are L2 resident (128x128 x 64 = 4 MiB per field, L2 = 126 MB).
 //
-// Adjoint of the bilinear gather = deterministic GATHER-TRANSPOSE (no float atomics): pass A stores every
-// source sample's back-traced index coordinates (xi_y, xi_x) and its coordinate gradients, and reduces the
-// per-batch-element maximum displacement R (integer atomicMax: order independent); pass B lets every
-// DESTINATION cell collect  sum_s g[s] * hat(xi_y[s]-i) * hat(xi_x[s]-j)  over the window |s-d| <= R in a fixed
-// order.  hat(t) = max(0, 1-|t|) is the bilinear weight; extrapolation modes act on xi.
+// Adjoint of the bilinear gather = a scatter made ORDER-INDEPENDENT (no float atomics): pass A adds every sample's four weighted
+// shares of the output gradient to 64-bit fixed-point accumulators with integer atomics and stores the sample's coordinate
+// gradients; pass B converts the sums and brings the coordinate gradients to the velocity faces (fixed small stencils).
 #include "pdec_common.cuh"
 
 namespace pdec {
@@ -222,142 +220,84 @@ __global__ void __launch_bounds__(256) force_loss_seed_kernel(const float* __res
     }
 }
 
-// ---- adjoint pass A: coordinates, coordinate gradients, displacement bound ----------------------------
-// Effective coordinate for the transpose: 'constant' -> NaN marks "contributes nothing"; 'replicate' -> clamped.
-template <int MODE>
-__device__ __forceinline__ float effective_coord(float xi, int n) {
-    if (MODE == PDEC_MODE_CONSTANT) return (xi >= 0.0f && xi < (float)(n - 1)) ? xi : __int_as_float(0x7fc00000);
-    if (MODE == PDEC_MODE_REPLICATE) return fminf(fmaxf(xi, 0.0f), (float)(n - 1));
-    return xi;
+// ---- adjoint pass A: scatter of the output gradient through the sampling, coordinate gradients ----------------------------
+// The transpose of the bilinear sampling is a scatter to data-dependent cells.  Every sample adds its four weighted shares of g_out
+// to 64-bit FIXED-POINT accumulators with integer atomics (pdec_common.cuh: scale from max|g_out|, integer adds commute): the sums do
+// not depend on the order the atomics land in -- bit-reproducible, no float atomics, no bound on the displacement, one pass.
+// (Rounds 1-2a gathered instead: coordinates written out, then every cell summed hat weights over a window bounded by the largest
+// displacement; 2.2 x the time of this at 128 x 128 x 64, profiles/r2af_advection_adjoint.md.)
+constexpr int ADV_BITS = 40;                 // |share| <= max|g_out| -> below 2^40; 2^22 shares per cell still fit the 64-bit sum
+
+// max |g| of up to two arrays -> header[0], header[1] (bits of non-negative floats order like unsigned integers)
+__global__ void __launch_bounds__(256) advect_absmax_kernel(const float* __restrict__ g0, long long n0, const float* __restrict__ g1, long long n1,
+                                                            unsigned* __restrict__ header) {
+    float m0 = 0.0f, m1 = 0.0f;
+    for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < n0; q += (long long)gridDim.x * 256) {
+        const float v = fabsf(g0[q]);
+        if (v == v && v < 3.0e38f) m0 = fmaxf(m0, v);              // NaN / inf gradients do not set the scale
+    }
+    for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < n1; q += (long long)gridDim.x * 256) {
+        const float v = fabsf(g1[q]);
+        if (v == v && v < 3.0e38f) m1 = fmaxf(m1, v);
+    }
+    m0 = warp_max(m0); m1 = warp_max(m1);
+    __shared__ float sm[2][8];
+    if ((threadIdx.x & 31) == 0) { sm[0][threadIdx.x >> 5] = m0; sm[1][threadIdx.x >> 5] = m1; }
+    __syncthreads();
+    if (threadIdx.x < 8) {
+        m0 = sm[0][threadIdx.x]; m1 = sm[1][threadIdx.x];
+        for (int o = 4; o > 0; o >>= 1) { m0 = fmaxf(m0, __shfl_xor_sync(0xffu, m0, o)); m1 = fmaxf(m1, __shfl_xor_sync(0xffu, m1, o)); }
+        if (threadIdx.x == 0) {
+            atomicMax(header, __float_as_uint(m0));
+            if (g1 != nullptr) atomicMax(header + 1, __float_as_uint(m1));
+        }
+    }
 }
 
+__device__ __forceinline__ float fixed_value(unsigned long long acc, double inv_scale) { return (float)((double)(long long)acc * inv_scale); }
+
+// acc (may be null: field gradient not wanted) <- shares of g_out; GY / GX <- g_out * d(sample)/d(xi) * d(xi)/d(u): the gradient w.r.t.
+// the velocity (uy, ux) AT the sample point, brought to the faces by pass B
 template <int VARIANT, int FMODE, int VMODE>
-__global__ void __launch_bounds__(256) advect_bwd_prep_kernel(FluidGeo g, const float* __restrict__ field, const float* __restrict__ vy,
-                                                              const float* __restrict__ vx, const float* __restrict__ gout,
-                                                              float* __restrict__ XY, float* __restrict__ XX, float* __restrict__ GY,
-                                                              float* __restrict__ GX, int* __restrict__ rmax) {
+__global__ void __launch_bounds__(256) advect_bwd_scatter_kernel(FluidGeo g, const float* __restrict__ field, const float* __restrict__ vy,
+                                                                 const float* __restrict__ vx, const float* __restrict__ gout,
+                                                                 unsigned long long* __restrict__ acc, float* __restrict__ GY,
+                                                                 float* __restrict__ GX, const unsigned* __restrict__ header) {
     int ry, rx;
     variant_res<VARIANT>(g.ny, g.nx, ry, rx);
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     const size_t sy = (size_t)(g.ny + 1) * g.nx, sx = (size_t)g.ny * (g.nx + 1), sf = (size_t)ry * rx;
-    int dispy = 0, dispx = 0;
     __shared__ float s_py[8], s_px[32];
     block_points(ry, rx, (VARIANT == V_CENTERED) ? g.lo : g.clo[VARIANT - 1], (VARIANT == V_CENTERED) ? g.sz : g.csz[VARIANT - 1], s_py, s_px);
-    if (i < ry && j < rx) {
-        float xiy, xix, dy, dx;
-        backtrace<VARIANT, VMODE>(g, vy + b * sy, vx + b * sx, i, j, ry, rx, s_py[threadIdx.y], s_px[threadIdx.x], xiy, xix);
-        sample2d<FMODE, true>(field + b * sf, ry, rx, xiy, xix, dy, dx);
-        const float go = gout[b * sf + (size_t)i * rx + j];
-        const float *sz = (VARIANT == V_CENTERED) ? g.sz : g.csz[VARIANT - 1];
-        const size_t o = b * sf + (size_t)i * rx + j;
-        float ey = effective_coord<FMODE>(xiy, ry), ex = effective_coord<FMODE>(xix, rx);
-        if (FMODE == PDEC_MODE_CONSTANT && (ey != ey || ex != ex)) ey = ex = __int_as_float(0x7fc00000);
-        XY[o] = ey;
-        XX[o] = ex;
-        GY[o] = go * dy * (-(g.dt * (float)ry) / sz[0]);     // through xi = ((p - u*dt - lower)/size)*res - 0.5
-        GX[o] = go * dx * (-(g.dt * (float)rx) / sz[1]);
-        if (ey == ey) {
-            float ty = fabsf(ey - (float)i), tx = fabsf(ex - (float)j);
-            if (FMODE == PDEC_MODE_CIRCULAR) { ty = fminf(ty, (float)ry * 0.5f); tx = fminf(tx, (float)rx * 0.5f); }
-            dispy = (int)fminf(ty, 1.0e6f) + 1;               // window half-width that covers floor and ceil
-            dispx = (int)fminf(tx, 1.0e6f) + 1;
+    if (i >= ry || j >= rx) return;
+    float xiy, xix;
+    backtrace<VARIANT, VMODE>(g, vy + b * sy, vx + b * sx, i, j, ry, rx, s_py[threadIdx.y], s_px[threadIdx.x], xiy, xix);
+    int fy, cy, fx, cx;
+    float w0y, w1y, w0x, w1x;
+    interp_setup<FMODE>(xiy, ry, fy, cy, w0y, w1y);
+    interp_setup<FMODE>(xix, rx, fx, cx, w0x, w1x);
+    const float* f = field + b * sf;
+    const float s00 = __ldg(f + (size_t)fy * rx + fx), s01 = __ldg(f + (size_t)fy * rx + cx);
+    const float s10 = __ldg(f + (size_t)cy * rx + fx), s11 = __ldg(f + (size_t)cy * rx + cx);
+    const float dy = (s10 - s00) * w1x + (s11 - s01) * w0x;           // as sample2d<FMODE, true>
+    const float dx = (s01 * w1y + s11 * w0y) - (s00 * w1y + s10 * w0y);
+    const size_t o = b * sf + (size_t)i * rx + j;
+    const float go = gout[o];
+    const float *sz = (VARIANT == V_CENTERED) ? g.sz : g.csz[VARIANT - 1];
+    GY[o] = go * dy * (-(g.dt * (float)ry) / sz[0]);                  // through xi = ((p - u*dt - lower)/size)*res - 0.5
+    GX[o] = go * dx * (-(g.dt * (float)rx) / sz[1]);
+    if (acc != nullptr) {
+        const float scale = fixed_scale(header, ADV_BITS);
+        if (scale > 0.0f) {
+            // transpose of out = (s00 w1y + s10 w0y) w1x + (s01 w1y + s11 w0y) w0x; an out-of-domain 'constant' sample has both taps of
+            // an axis on one cell with weights w and -w: its two shares cancel exactly in fixed point, like its value is exactly +0
+            unsigned long long* a = acc + b * sf;
+            fixed_add(a + (size_t)fy * rx + fx, go * w1x * w1y, scale);
+            fixed_add(a + (size_t)cy * rx + fx, go * w1x * w0y, scale);
+            fixed_add(a + (size_t)fy * rx + cx, go * w0x * w1y, scale);
+            fixed_add(a + (size_t)cy * rx + cx, go * w0x * w0y, scale);
         }
     }
-    // block max -> one integer atomicMax per block (max is order independent: deterministic)
-    __shared__ int sm[2][8];
-    for (int o = 16; o > 0; o >>= 1) {
-        dispy = max(dispy, __shfl_xor_sync(PDEC_FULL_MASK, dispy, o));
-        dispx = max(dispx, __shfl_xor_sync(PDEC_FULL_MASK, dispx, o));
-    }
-    if (threadIdx.x == 0) { sm[0][threadIdx.y] = dispy; sm[1][threadIdx.y] = dispx; }
-    __syncthreads();
-    if (threadIdx.y == 0 && threadIdx.x < 8) {
-        dispy = sm[0][threadIdx.x];
-        dispx = sm[1][threadIdx.x];
-        for (int o = 4; o > 0; o >>= 1) {
-            dispy = max(dispy, __shfl_xor_sync(0xffu, dispy, o));
-            dispx = max(dispx, __shfl_xor_sync(0xffu, dispx, o));
-        }
-        if (threadIdx.x == 0) {
-            atomicMax(rmax + 2 * b, dispy);
-            atomicMax(rmax + 2 * b + 1, dispx);
-        }
-    }
-}
-
-__device__ __forceinline__ float hat(float t) { return fmaxf(0.0f, 1.0f - fabsf(t)); }
-
-// ---- adjoint pass B: gather-transpose of g over the bounded window ---------------------------------
-template <int MODE>
-__device__ __forceinline__ float gather_transpose(const float* __restrict__ XY, const float* __restrict__ XX, const float* __restrict__ G,
-                                                  int ry, int rx, int i, int j, int Ry, int Rx) {
-    float acc = 0.0f;
-    if (MODE == PDEC_MODE_CIRCULAR) {
-        Ry = min(Ry, ry / 2); Rx = min(Rx, rx / 2);
-        // a window that covers the whole ring visits every source ONCE: on an even ring -R and +R are the same cell
-        const int hy = 2 * Ry >= ry ? Ry - 1 : Ry, hx = 2 * Rx >= rx ? Rx - 1 : Rx;
-        for (int di = -Ry; di <= hy; ++di) {
-            const int a = map_index<MODE>(i + di, ry);
-            for (int dj = -Rx; dj <= hx; ++dj) {
-                const int c = map_index<MODE>(j + dj, rx);
-                const size_t o = (size_t)a * rx + c;
-                float ty = __ldg(XY + o) - (float)i, tx = __ldg(XX + o) - (float)j;
-                ty -= (float)ry * rintf(ty / (float)ry);
-                tx -= (float)rx * rintf(tx / (float)rx);
-                acc += __ldg(G + o) * (hat(ty) * hat(tx));
-            }
-        }
-        return acc;
-    }
-    const int a0 = max(i - Ry, 0), a1 = min(i + Ry, ry - 1), c0 = max(j - Rx, 0), c1 = min(j + Rx, rx - 1);
-    for (int a = a0; a <= a1; ++a) {
-        for (int c = c0; c <= c1; ++c) {
-            const size_t o = (size_t)a * rx + c;
-            const float wy = hat(__ldg(XY + o) - (float)i);      // NaN ('constant', outside) -> fmaxf(0, NaN) = 0
-            if (wy > 0.0f) {
-                const float wx = hat(__ldg(XX + o) - (float)j);
-                if (wx > 0.0f) acc += __ldg(G + o) * (wy * wx);
-            }
-        }
-    }
-    return acc;
-}
-
-// The same sums with the window staged in shared memory: for windows up to 2 cells (every benchmarked flow: max|v| dt / dx < 2) the block
-// loads the (8 + 2 Ry) x (32 + 2 Rx) tile of coordinates and gradients once, coalesced, instead of (2R+1)^2 x 3 scattered loads per thread
-// through L1 (ncu on the global version: 13 long-scoreboard stalls per issue).  Entries outside the grid carry NaN coordinates: weight 0, skipped
-// by the same tests, so the terms and their order -- and the bits of the sum -- are those of gather_transpose.  Block-cooperative: every
-// thread of the block must call it.
-constexpr int GT_R = 2, GT_H = 8 + 2 * GT_R, GT_W = 32 + 2 * GT_R;
-__device__ __forceinline__ float gather_transpose_tile(const float* __restrict__ XY, const float* __restrict__ XX, const float* __restrict__ G,
-                                                       int ry, int rx, int i, int j, int Ry, int Rx, float (*sm)[GT_H * GT_W]) {
-    const int W = 32 + 2 * Rx, H = 8 + 2 * Ry;
-    const int i0 = blockIdx.y * 8 - Ry, j0 = blockIdx.x * 32 - Rx;
-    const float nan = __int_as_float(0x7fc00000);
-    for (int q = threadIdx.y * 32 + threadIdx.x; q < H * W; q += 256) {
-        const int a = i0 + q / W, c = j0 + q % W;
-        const bool in = a >= 0 && a < ry && c >= 0 && c < rx;
-        const size_t o = (size_t)a * rx + c;
-        sm[0][q] = in ? __ldg(XY + o) : nan;
-        sm[1][q] = in ? __ldg(XX + o) : nan;
-        sm[2][q] = in ? __ldg(G + o) : 0.0f;
-    }
-    __syncthreads();
-    float acc = 0.0f;
-    if (i < ry && j < rx) {
-        for (int da = 0; da <= 2 * Ry; ++da) {
-            const int row = (threadIdx.y + da) * W + threadIdx.x;
-            for (int dc = 0; dc <= 2 * Rx; ++dc) {
-                const float wy = hat(sm[0][row + dc] - (float)i);
-                if (wy > 0.0f) {
-                    const float wx = hat(sm[1][row + dc] - (float)j);
-                    if (wx > 0.0f) acc += sm[2][row + dc] * (wy * wx);
-                }
-            }
-        }
-    }
-    __syncthreads();                         // the tile is reused by the next gather of the same kernel
-    return acc;
 }
 
 // transpose of "component brought to the other component's faces" (two nested 2-point lerps with pad mode)
@@ -410,26 +350,20 @@ __device__ __forceinline__ float cross_to_vy(const FluidGeo& g, const float* __r
     return acc;
 }
 
-// centred advection, pass B: g_rho (transpose), and the velocity gradient from the coordinate gradients
+// centred advection, pass B: g_rho out of the fixed-point sums, and the velocity gradient from the coordinate gradients
 template <int FMODE>
-__global__ void __launch_bounds__(256) advect_centered_bwd_kernel(FluidGeo g, const float* __restrict__ XY, const float* __restrict__ XX,
-                                                                  const float* __restrict__ GY, const float* __restrict__ GX,
-                                                                  const float* __restrict__ gout, const int* __restrict__ rmax,
+__global__ void __launch_bounds__(256) advect_centered_bwd_kernel(FluidGeo g, const unsigned long long* __restrict__ acc, const float* __restrict__ GY,
+                                                                  const float* __restrict__ GX, const unsigned* __restrict__ header,
                                                                   float* __restrict__ g_rho, float* g_vy, float* g_vx,
                                                                   const float* add_vy, const float* add_vx) {
     // add_vy / add_vx (optional, same shapes as g_vy / g_vx, may alias them): gradients that reached the velocity by other routes
     const int ny = g.ny, nx = g.nx;
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     const size_t sf = (size_t)ny * nx;
-    __shared__ float s_tile[3][GT_H * GT_W];
-    const int Ry = rmax[2 * b], Rx = rmax[2 * b + 1];
-    if (g_rho != nullptr) {
-        if (FMODE != PDEC_MODE_CIRCULAR && Ry <= GT_R && Rx <= GT_R) {
-            const float v = gather_transpose_tile(XY + b * sf, XX + b * sf, gout + b * sf, ny, nx, i, j, Ry, Rx, s_tile);
-            if (i < ny && j < nx) g_rho[b * sf + (size_t)i * nx + j] = v;
-        } else if (i < ny && j < nx) {
-            g_rho[b * sf + (size_t)i * nx + j] = gather_transpose<FMODE>(XY + b * sf, XX + b * sf, gout + b * sf, ny, nx, i, j, Ry, Rx);
-        }
+    if (g_rho != nullptr && i < ny && j < nx) {
+        const float scale = fixed_scale(header, ADV_BITS);
+        const size_t at = b * sf + (size_t)i * nx + j;
+        g_rho[at] = fixed_value(acc[at], scale > 0.0f ? 1.0 / (double)scale : 0.0);
     }
     // velocity at centres = vy[i+1]*wu + vy[i]*wl  ->  g_vy[i] = wu * GY[i-1] + wl * GY[i]
     if (g_vy != nullptr && i <= ny && j < nx) {
@@ -448,34 +382,28 @@ __global__ void __launch_bounds__(256) advect_centered_bwd_kernel(FluidGeo g, co
     }
 }
 
-// staggered self-advection, pass B.  W0 = {XY,XX,GY,GX} of the vy grid, W1 of the vx grid.
+// staggered self-advection, pass B: the field gradient out of the fixed-point sums plus the three velocity routes
 template <int VMODE>
-__global__ void __launch_bounds__(256) advect_staggered_bwd_kernel(FluidGeo g, const float* __restrict__ W0, const float* __restrict__ W1,
-                                                                   const float* __restrict__ g_ay, const float* __restrict__ g_ax,
-                                                                   const int* __restrict__ rmax0, const int* __restrict__ rmax1,
-                                                                   float* __restrict__ g_vy, float* __restrict__ g_vx, int accumulate,
-                                                                   int B) {
+__global__ void __launch_bounds__(256) advect_staggered_bwd_kernel(FluidGeo g, const unsigned long long* __restrict__ acc0, const unsigned long long* __restrict__ acc1,
+                                                                   const float* __restrict__ G0, const float* __restrict__ G1,
+                                                                   const unsigned* __restrict__ header, float* __restrict__ g_vy,
+                                                                   float* __restrict__ g_vx, int accumulate, int B) {
     const int ny = g.ny, nx = g.nx;
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     const size_t sy = (size_t)(ny + 1) * nx, sx = (size_t)ny * (nx + 1);
-    const float *XY0 = W0 + b * sy, *XX0 = W0 + (size_t)B * sy + b * sy, *GY0 = W0 + 2 * (size_t)B * sy + b * sy, *GX0 = W0 + 3 * (size_t)B * sy + b * sy;
-    const float *XY1 = W1 + b * sx, *XX1 = W1 + (size_t)B * sx + b * sx, *GY1 = W1 + 2 * (size_t)B * sx + b * sx, *GX1 = W1 + 3 * (size_t)B * sx + b * sx;
-    __shared__ float s_tile[3][GT_H * GT_W];
-    const bool tiled = VMODE != PDEC_MODE_CIRCULAR && rmax0[2 * b] <= GT_R && rmax0[2 * b + 1] <= GT_R && rmax1[2 * b] <= GT_R && rmax1[2 * b + 1] <= GT_R;
-    float t0 = 0.0f, t1 = 0.0f;
-    if (tiled) {
-        t0 = gather_transpose_tile(XY0, XX0, g_ay + b * sy, ny + 1, nx, i, j, rmax0[2 * b], rmax0[2 * b + 1], s_tile);
-        t1 = gather_transpose_tile(XY1, XX1, g_ax + b * sx, ny, nx + 1, i, j, rmax1[2 * b], rmax1[2 * b + 1], s_tile);
-    }
+    // G0 = {GY, GX} of the vy grid, G1 of the vx grid (arrays of B elements each)
+    const float *GY0 = G0 + b * sy, *GX0 = G0 + (size_t)B * sy + b * sy, *GY1 = G1 + b * sx, *GX1 = G1 + (size_t)B * sx + b * sx;
     if (i <= ny && j < nx) {
-        float v = tiled ? t0 : gather_transpose<VMODE>(XY0, XX0, g_ay + b * sy, ny + 1, nx, i, j, rmax0[2 * b], rmax0[2 * b + 1]);
+        const float scale = fixed_scale(header, ADV_BITS);
+        float v = fixed_value(acc0[b * sy + (size_t)i * nx + j], scale > 0.0f ? 1.0 / (double)scale : 0.0);
         v += __ldg(GY0 + (size_t)i * nx + j);               // uy = vy itself at vy faces
         v += cross_to_vy<VMODE>(g, GY1, i, j);              // vy averaged to vx faces
         float* p = g_vy + b * sy + (size_t)i * nx + j;
         *p = accumulate ? *p + v : v;
     }
     if (i < ny && j <= nx) {
-        float v = tiled ? t1 : gather_transpose<VMODE>(XY1, XX1, g_ax + b * sx, ny, nx + 1, i, j, rmax1[2 * b], rmax1[2 * b + 1]);
+        const float scale = fixed_scale(header + 1, ADV_BITS);
+        float v = fixed_value(acc1[b * sx + (size_t)i * (nx + 1) + j], scale > 0.0f ? 1.0 / (double)scale : 0.0);
         v += __ldg(GX1 + (size_t)i * (nx + 1) + j);
         v += cross_to_vx<VMODE>(g, GX0, i, j);
         float* p = g_vx + b * sx + (size_t)i * (nx + 1) + j;
@@ -834,9 +762,11 @@ extern "C" int pdec_advect_staggered_2d_fwd(const float* vy, const float* vx, fl
     return PDEC_OK;
 }
 
-// workspace layout for the advection adjoints: [ints: 4*B (rmax of two grids)] [pad to 256 B] [W0: 4 arrays B*(ny+1)*nx]
-// [W1: 4 arrays B*ny*(nx+1)]
+// workspace layout for the advection adjoints: [header: max|g_out| of the two grids, 256-byte multiple]
+// [fixed-point sums: u64 x B*(ny+1)*nx, then u64 x B*ny*(nx+1)] [GY, GX of the vy grid] [GY, GX of the vx grid]  (16 bytes per sample;
+// the centred variant uses one grid of B*ny*nx: sums, then GY, GX)
 static size_t ws_header(int B) { return (((size_t)4 * (B > 0 ? B : 1) * sizeof(int)) + 255) & ~(size_t)255; }
+static int absmax_blocks(long long n) { return (int)((n + 255) / 256 > 592 ? 592 : (n + 255) / 256); }
 
 extern "C" size_t pdec_advect_2d_workspace_bytes(int B, int ny, int nx) {
     const size_t b = B > 0 ? B : 1;
@@ -855,13 +785,15 @@ extern "C" int pdec_advect_centered_2d_bwd(const float* rho, const float* vy, co
     if (!rho || !vy || !vx || !g_out || !workspace) return PDEC_ERR_INVALID_ARGUMENT;
     if (workspace_bytes < pdec_advect_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
     cudaStream_t st = (cudaStream_t)stream;
-    int* rmax = reinterpret_cast<int*>(workspace);
-    float* W = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + ws_header(B));
+    unsigned* header = reinterpret_cast<unsigned*>(workspace);
     const size_t sf = (size_t)B * ny * nx;
-    if (cudaMemsetAsync(rmax, 0, 4 * (size_t)B * sizeof(int), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+    unsigned long long* acc = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(workspace) + ws_header(B));
+    float* G = reinterpret_cast<float*>(acc + sf);                     // GY, GX
+    if (cudaMemsetAsync(workspace, 0, ws_header(B) + (g_rho ? sf * sizeof(unsigned long long) : 0), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+    if (g_rho) advect_absmax_kernel<<<absmax_blocks((long long)sf), 256, 0, st>>>(g_out, (long long)sf, nullptr, 0, header);
 #define CALL(M)                                                                                                                     \
-    advect_bwd_prep_kernel<V_CENTERED, M, 0><<<tiles(ny, nx, B), kBlock, 0, st>>>(g, rho, vy, vx, g_out, W, W + sf, W + 2 * sf, W + 3 * sf, rmax); \
-    advect_centered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, W, W + sf, W + 2 * sf, W + 3 * sf, g_out, rmax, g_rho, g_vy, g_vx, accumulate_v ? g_vy : nullptr, accumulate_v ? g_vx : nullptr)
+    advect_bwd_scatter_kernel<V_CENTERED, M, 0><<<tiles(ny, nx, B), kBlock, 0, st>>>(g, rho, vy, vx, g_out, g_rho ? acc : nullptr, G, G + sf, header); \
+    advect_centered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, acc, G, G + sf, header, g_rho, g_vy, g_vx, accumulate_v ? g_vy : nullptr, accumulate_v ? g_vx : nullptr)
     MODE_SWITCH(mode, CALL);
 #undef CALL
     PDEC_CHECK_LAUNCH();
@@ -880,16 +812,18 @@ extern "C" int pdec_advect_staggered_2d_bwd(const float* vy, const float* vx, co
     if (!vy || !vx || !g_ay || !g_ax || !g_vy || !g_vx || !workspace) return PDEC_ERR_INVALID_ARGUMENT;
     if (workspace_bytes < pdec_advect_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
     cudaStream_t st = (cudaStream_t)stream;
-    int* rmax0 = reinterpret_cast<int*>(workspace);
-    int* rmax1 = rmax0 + 2 * (size_t)B;
-    float* W0 = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + ws_header(B));
+    unsigned* header = reinterpret_cast<unsigned*>(workspace);
     const size_t sy = (size_t)B * (ny + 1) * nx, sx = (size_t)B * ny * (nx + 1);
-    float* W1 = W0 + 4 * sy;
-    if (cudaMemsetAsync(rmax0, 0, 4 * (size_t)B * sizeof(int), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+    unsigned long long* acc0 = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(workspace) + ws_header(B));
+    unsigned long long* acc1 = acc0 + sy;
+    float* G0 = reinterpret_cast<float*>(acc1 + sx);                   // GY, GX of the vy grid
+    float* G1 = G0 + 2 * sy;                                           // GY, GX of the vx grid
+    if (cudaMemsetAsync(workspace, 0, ws_header(B) + (sy + sx) * sizeof(unsigned long long), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+    advect_absmax_kernel<<<absmax_blocks((long long)(sy > sx ? sy : sx)), 256, 0, st>>>(g_ay, (long long)sy, g_ax, (long long)sx, header);
 #define CALL(M)                                                                                                                              \
-    advect_bwd_prep_kernel<V_COMP_Y, M, M><<<tiles(ny + 1, nx, B), kBlock, 0, st>>>(g, vy, vy, vx, g_ay, W0, W0 + sy, W0 + 2 * sy, W0 + 3 * sy, rmax0); \
-    advect_bwd_prep_kernel<V_COMP_X, M, M><<<tiles(ny, nx + 1, B), kBlock, 0, st>>>(g, vx, vy, vx, g_ax, W1, W1 + sx, W1 + 2 * sx, W1 + 3 * sx, rmax1); \
-    advect_staggered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, W0, W1, g_ay, g_ax, rmax0, rmax1, g_vy, g_vx, accumulate, B)
+    advect_bwd_scatter_kernel<V_COMP_Y, M, M><<<tiles(ny + 1, nx, B), kBlock, 0, st>>>(g, vy, vy, vx, g_ay, acc0, G0, G0 + sy, header);      \
+    advect_bwd_scatter_kernel<V_COMP_X, M, M><<<tiles(ny, nx + 1, B), kBlock, 0, st>>>(g, vx, vy, vx, g_ax, acc1, G1, G1 + sx, header + 1);  \
+    advect_staggered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, acc0, acc1, G0, G1, header, g_vy, g_vx, accumulate, B)
     MODE_SWITCH(mode, CALL);
 #undef CALL
     PDEC_CHECK_LAUNCH();
@@ -936,15 +870,17 @@ extern "C" int pdec_curl_advect_2d_bwd(const float* rho, const float* vy, const 
     if (!rho || !vy || !vx || !g_out || !g_phi || !workspace) return PDEC_ERR_INVALID_ARGUMENT;
     if (workspace_bytes < pdec_advect_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
     cudaStream_t st = (cudaStream_t)stream;
-    int* rmax = reinterpret_cast<int*>(workspace);
-    float* W = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + ws_header(B));
+    unsigned* header = reinterpret_cast<unsigned*>(workspace);
     const size_t sf = (size_t)B * ny * nx;
-    float* t_vy = W + 4 * sf;                                          // B * (ny + 1) * nx
+    unsigned long long* acc = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(workspace) + ws_header(B));
+    float* G = reinterpret_cast<float*>(acc + sf);                     // GY, GX
+    float* t_vy = G + 2 * sf;                                          // B * (ny + 1) * nx
     float* t_vx = t_vy + (size_t)B * (ny + 1) * nx;                    // B * ny * (nx + 1)
-    if (cudaMemsetAsync(rmax, 0, 4 * (size_t)B * sizeof(int), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+    if (cudaMemsetAsync(workspace, 0, ws_header(B) + (g_rho ? sf * sizeof(unsigned long long) : 0), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+    if (g_rho) advect_absmax_kernel<<<absmax_blocks((long long)sf), 256, 0, st>>>(g_out, (long long)sf, nullptr, 0, header);
 #define CALL(M)                                                                                                                     \
-    advect_bwd_prep_kernel<V_CENTERED, M, 0><<<tiles(ny, nx, B), kBlock, 0, st>>>(g, rho, vy, vx, g_out, W, W + sf, W + 2 * sf, W + 3 * sf, rmax); \
-    advect_centered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, W, W + sf, W + 2 * sf, W + 3 * sf, g_out, rmax, g_rho, t_vy, t_vx, add_vy, add_vx)
+    advect_bwd_scatter_kernel<V_CENTERED, M, 0><<<tiles(ny, nx, B), kBlock, 0, st>>>(g, rho, vy, vx, g_out, g_rho ? acc : nullptr, G, G + sf, header); \
+    advect_centered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, acc, G, G + sf, header, g_rho, t_vy, t_vx, add_vy, add_vx)
     MODE_SWITCH(mode, CALL);
 #undef CALL
 #define CALL(M) curl_bwd_kernel<M><<<tiles(ny, nx, B), kBlock, 0, st>>>(t_vy, t_vx, g_phi, ny, nx)

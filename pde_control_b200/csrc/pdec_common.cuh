@@ -130,6 +130,22 @@ __device__ __forceinline__ void interp_setup(float xi, int n, int& fi, int& ci, 
     }
 }
 
+// ---- order-independent accumulation: 64-bit fixed point (resample.cu, the advection adjoints of fluid.cu) -------------------------
+// header[0] = bits of max|g| (non-negative floats order like their bit patterns; written with an integer atomicMax).
+// scale = 2^(bits - exponent of max|g|): every |contribution| <= max|g| maps below 2^bits; integer adds commute, so the sums do not
+// depend on the order the atomics land in: bit-reproducible without float atomics.
+__device__ __forceinline__ float fixed_scale(const unsigned* header, int bits) {
+    const float m = __uint_as_float(header[0]);
+    if (!(m > 0.0f)) return 0.0f;
+    int e;
+    frexpf(m, &e);                                                  // m = f * 2^e, f in [0.5, 1)
+    return ldexpf(1.0f, min(max(bits - e, -120), 120));
+}
+__device__ __forceinline__ void fixed_add(unsigned long long* cell, float v, float scale) {     // two's-complement add
+    const float sv = v * scale;
+    if (sv == sv && fabsf(sv) < 9.0e18f) atomicAdd(cell, (unsigned long long)__float2ll_rn(sv));
+}
+
 }  // namespace pdec
 
 #define PDEC_CHECK_LAUNCH()                                   \

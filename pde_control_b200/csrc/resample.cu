@@ -61,14 +61,6 @@ __global__ void __launch_bounds__(256) resample_absmax_kernel(const float* __res
     }
 }
 
-// scale = 2^(bits - exponent of max|g|): every |contribution| <= max|g| maps below 2^bits
-__device__ __forceinline__ float fixed_scale(const unsigned* header, int bits) {
-    const float m = __uint_as_float(header[0]);
-    if (!(m > 0.0f)) return 0.0f;
-    int e;
-    frexpf(m, &e);                                                  // m = f * 2^e, f in [0.5, 1)
-    return ldexpf(1.0f, min(max(bits - e, -120), 120));
-}
 
 template <int MODE, int RANK>
 __global__ void __launch_bounds__(256) resample_bwd_kernel(const float* __restrict__ data, const float* __restrict__ coords, const float* __restrict__ g_out,
