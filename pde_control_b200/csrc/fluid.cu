@@ -202,21 +202,36 @@ __global__ void __launch_bounds__(1024) force_loss_finish_kernel(const float* __
     if (threadIdx.x == 0) loss[0] = (float)(sh[0][0] / 2.0 / (double)B) + (float)(sh[1][0] / 2.0 / (double)B);
 }
 
-// seeds of the adjoint: g_a = resid * (g_loss / B) for both components, and the target's gradient -g_a (optional)
+// seeds of the adjoint: g_a = resid * (g_loss / B) for both components, the target's gradient -g_a (optional), and max|g_a| per
+// component into header[0], header[1] (the fixed-point scale of the adjoint that follows: saves its own reduction pass)
 __global__ void __launch_bounds__(256) force_loss_seed_kernel(const float* __restrict__ ry_, const float* __restrict__ rx_, const float* __restrict__ g_loss,
                                                               float inv_B, float* __restrict__ gy, float* __restrict__ gx, float* __restrict__ g_ty,
-                                                              float* __restrict__ g_tx, size_t n0, size_t n1) {
+                                                              float* __restrict__ g_tx, size_t n0, size_t n1, unsigned* __restrict__ header) {
     const float k = g_loss[0] * inv_B;
+    float m0 = 0.0f, m1 = 0.0f;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n0 + n1; i += (size_t)gridDim.x * blockDim.x) {
         if (i < n0) {
             const float v = ry_[i] * k;
             gy[i] = v;
             if (g_ty) g_ty[i] = -v;
+            const float a = fabsf(v);
+            if (a == a && a < 3.0e38f) m0 = fmaxf(m0, a);
         } else {
             const float v = rx_[i - n0] * k;
             gx[i - n0] = v;
             if (g_tx) g_tx[i - n0] = -v;
+            const float a = fabsf(v);
+            if (a == a && a < 3.0e38f) m1 = fmaxf(m1, a);
         }
+    }
+    m0 = warp_max(m0); m1 = warp_max(m1);
+    __shared__ float sm[2][8];
+    if ((threadIdx.x & 31) == 0) { sm[0][threadIdx.x >> 5] = m0; sm[1][threadIdx.x >> 5] = m1; }
+    __syncthreads();
+    if (threadIdx.x < 8) {
+        m0 = sm[0][threadIdx.x]; m1 = sm[1][threadIdx.x];
+        for (int o = 4; o > 0; o >>= 1) { m0 = fmaxf(m0, __shfl_xor_sync(0xffu, m0, o)); m1 = fmaxf(m1, __shfl_xor_sync(0xffu, m1, o)); }
+        if (threadIdx.x == 0) { atomicMax(header, __float_as_uint(m0)); atomicMax(header + 1, __float_as_uint(m1)); }
     }
 }
 
@@ -259,15 +274,14 @@ __device__ __forceinline__ float fixed_value(unsigned long long acc, double inv_
 // acc (may be null: field gradient not wanted) <- shares of g_out; GY / GX <- g_out * d(sample)/d(xi) * d(xi)/d(u): the gradient w.r.t.
 // the velocity (uy, ux) AT the sample point, brought to the faces by pass B
 template <int VARIANT, int FMODE, int VMODE>
-__global__ void __launch_bounds__(256) advect_bwd_scatter_kernel(FluidGeo g, const float* __restrict__ field, const float* __restrict__ vy,
-                                                                 const float* __restrict__ vx, const float* __restrict__ gout,
-                                                                 unsigned long long* __restrict__ acc, float* __restrict__ GY,
-                                                                 float* __restrict__ GX, const unsigned* __restrict__ header) {
+__device__ __forceinline__ void advect_bwd_scatter_body(const FluidGeo& g, const float* __restrict__ field, const float* __restrict__ vy,
+                                                        const float* __restrict__ vx, const float* __restrict__ gout,
+                                                        unsigned long long* __restrict__ acc, float* __restrict__ GY, float* __restrict__ GX,
+                                                        const unsigned* __restrict__ header, int b, float* s_py, float* s_px) {
     int ry, rx;
     variant_res<VARIANT>(g.ny, g.nx, ry, rx);
-    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
+    const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y;
     const size_t sy = (size_t)(g.ny + 1) * g.nx, sx = (size_t)g.ny * (g.nx + 1), sf = (size_t)ry * rx;
-    __shared__ float s_py[8], s_px[32];
     block_points(ry, rx, (VARIANT == V_CENTERED) ? g.lo : g.clo[VARIANT - 1], (VARIANT == V_CENTERED) ? g.sz : g.csz[VARIANT - 1], s_py, s_px);
     if (i >= ry || j >= rx) return;
     float xiy, xix;
@@ -298,6 +312,29 @@ __global__ void __launch_bounds__(256) advect_bwd_scatter_kernel(FluidGeo g, con
             fixed_add(a + (size_t)cy * rx + cx, go * w0x * w0y, scale);
         }
     }
+}
+
+template <int VARIANT, int FMODE, int VMODE>
+__global__ void __launch_bounds__(256) advect_bwd_scatter_kernel(FluidGeo g, const float* __restrict__ field, const float* __restrict__ vy,
+                                                                 const float* __restrict__ vx, const float* __restrict__ gout,
+                                                                 unsigned long long* __restrict__ acc, float* __restrict__ GY,
+                                                                 float* __restrict__ GX, const unsigned* __restrict__ header) {
+    __shared__ float s_py[8], s_px[32];
+    advect_bwd_scatter_body<VARIANT, FMODE, VMODE>(g, field, vy, vx, gout, acc, GY, GX, header, blockIdx.z, s_py, s_px);
+}
+
+// both components of the staggered self-advection in one launch: blockIdx.z < B -> the vy grid, else the vx grid (the tile grid covers
+// (ny + 1) x (nx + 1); blocks beyond a component's own extent leave at once)
+template <int M>
+__global__ void __launch_bounds__(256) advect_bwd_scatter_staggered_kernel(FluidGeo g, const float* __restrict__ vy, const float* __restrict__ vx,
+                                                                           const float* __restrict__ g_ay, const float* __restrict__ g_ax,
+                                                                           unsigned long long* __restrict__ acc0, unsigned long long* __restrict__ acc1,
+                                                                           float* __restrict__ G0, float* __restrict__ G1,
+                                                                           const unsigned* __restrict__ header, int B) {
+    __shared__ float s_py[8], s_px[32];
+    const size_t sy = (size_t)B * (g.ny + 1) * g.nx, sx = (size_t)B * g.ny * (g.nx + 1);
+    if ((int)blockIdx.z < B) advect_bwd_scatter_body<V_COMP_Y, M, M>(g, vy, vy, vx, g_ay, acc0, G0, G0 + sy, header, blockIdx.z, s_py, s_px);
+    else advect_bwd_scatter_body<V_COMP_X, M, M>(g, vx, vy, vx, g_ax, acc1, G1, G1 + sx, header + 1, (int)blockIdx.z - B, s_py, s_px);
 }
 
 // transpose of "component brought to the other component's faces" (two nested 2-point lerps with pad mode)
@@ -800,10 +837,10 @@ extern "C" int pdec_advect_centered_2d_bwd(const float* rho, const float* vy, co
     return PDEC_OK;
 }
 
-extern "C" int pdec_advect_staggered_2d_bwd(const float* vy, const float* vx, const float* g_ay, const float* g_ax, float* g_vy,
-                                            float* g_vx, int accumulate, int B, int ny, int nx, int mode, double dt, float lower_y,
-                                            float lower_x, float size_y, float size_x, void* workspace, size_t workspace_bytes,
-                                            void* stream) {
+// header_ready: the caller has cleared header + sums and put max|g_ay|, max|g_ax| into the header already
+static int advect_staggered_bwd_impl(const float* vy, const float* vx, const float* g_ay, const float* g_ax, float* g_vy, float* g_vx, int accumulate,
+                                     int B, int ny, int nx, int mode, double dt, float lower_y, float lower_x, float size_y, float size_x,
+                                     void* workspace, size_t workspace_bytes, void* stream, bool header_ready) {
     FluidGeo g;
     int rc = make_geo(g, B, ny, nx, dt, lower_y, lower_x, size_y, size_x);
     if (rc != PDEC_OK) return rc;
@@ -818,16 +855,30 @@ extern "C" int pdec_advect_staggered_2d_bwd(const float* vy, const float* vx, co
     unsigned long long* acc1 = acc0 + sy;
     float* G0 = reinterpret_cast<float*>(acc1 + sx);                   // GY, GX of the vy grid
     float* G1 = G0 + 2 * sy;                                           // GY, GX of the vx grid
-    if (cudaMemsetAsync(workspace, 0, ws_header(B) + (sy + sx) * sizeof(unsigned long long), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
-    advect_absmax_kernel<<<absmax_blocks((long long)(sy > sx ? sy : sx)), 256, 0, st>>>(g_ay, (long long)sy, g_ax, (long long)sx, header);
+    if (!header_ready) {
+        if (cudaMemsetAsync(workspace, 0, ws_header(B) + (sy + sx) * sizeof(unsigned long long), st) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+        advect_absmax_kernel<<<absmax_blocks((long long)(sy > sx ? sy : sx)), 256, 0, st>>>(g_ay, (long long)sy, g_ax, (long long)sx, header);
+    }
+    const bool one_launch = 2 * B <= 65535;                            // grid.z limit
 #define CALL(M)                                                                                                                              \
-    advect_bwd_scatter_kernel<V_COMP_Y, M, M><<<tiles(ny + 1, nx, B), kBlock, 0, st>>>(g, vy, vy, vx, g_ay, acc0, G0, G0 + sy, header);      \
-    advect_bwd_scatter_kernel<V_COMP_X, M, M><<<tiles(ny, nx + 1, B), kBlock, 0, st>>>(g, vx, vy, vx, g_ax, acc1, G1, G1 + sx, header + 1);  \
+    if (one_launch) advect_bwd_scatter_staggered_kernel<M><<<tiles(ny + 1, nx + 1, 2 * B), kBlock, 0, st>>>(g, vy, vx, g_ay, g_ax, acc0, acc1, G0, G1, header, B); \
+    else {                                                                                                                                   \
+        advect_bwd_scatter_kernel<V_COMP_Y, M, M><<<tiles(ny + 1, nx, B), kBlock, 0, st>>>(g, vy, vy, vx, g_ay, acc0, G0, G0 + sy, header);  \
+        advect_bwd_scatter_kernel<V_COMP_X, M, M><<<tiles(ny, nx + 1, B), kBlock, 0, st>>>(g, vx, vy, vx, g_ax, acc1, G1, G1 + sx, header + 1); \
+    }                                                                                                                                        \
     advect_staggered_bwd_kernel<M><<<tiles(ny + 1, nx + 1, B), kBlock, 0, st>>>(g, acc0, acc1, G0, G1, header, g_vy, g_vx, accumulate, B)
     MODE_SWITCH(mode, CALL);
 #undef CALL
     PDEC_CHECK_LAUNCH();
     return PDEC_OK;
+}
+
+extern "C" int pdec_advect_staggered_2d_bwd(const float* vy, const float* vx, const float* g_ay, const float* g_ax, float* g_vy,
+                                            float* g_vx, int accumulate, int B, int ny, int nx, int mode, double dt, float lower_y,
+                                            float lower_x, float size_y, float size_x, void* workspace, size_t workspace_bytes,
+                                            void* stream) {
+    return advect_staggered_bwd_impl(vy, vx, g_ay, g_ax, g_vy, g_vx, accumulate, B, ny, nx, mode, dt, lower_y, lower_x, size_y, size_x, workspace,
+                                     workspace_bytes, stream, false);
 }
 
 // ---- fused curl + density advection ----------------------------------------------------------------------
@@ -938,10 +989,14 @@ extern "C" int pdec_staggered_force_loss_bwd(const float* vy, const float* vx, c
     const size_t n0 = (size_t)B * (ny + 1) * nx, n1 = (size_t)B * ny * (nx + 1);
     size_t blocks = (n0 + n1 + 255) / 256;
     if (blocks > 148 * 16) blocks = 148 * 16;
-    force_loss_seed_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(resid_y, resid_x, g_loss, 1.0f / (float)B, seed_y, seed_x, g_ty, g_tx, n0, n1);
+    if (!workspace || ny < 2 || nx < 2) return PDEC_ERR_INVALID_ARGUMENT;
+    if (workspace_bytes < pdec_advect_2d_workspace_bytes(B, ny, nx)) return PDEC_ERR_WORKSPACE_TOO_SMALL;
+    if (cudaMemsetAsync(workspace, 0, ws_header(B) + (n0 + n1) * sizeof(unsigned long long), (cudaStream_t)stream) != cudaSuccess) return PDEC_ERR_CUDA_LAUNCH;
+    force_loss_seed_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(resid_y, resid_x, g_loss, 1.0f / (float)B, seed_y, seed_x, g_ty, g_tx, n0, n1,
+                                                                               reinterpret_cast<unsigned*>(workspace));
     PDEC_CHECK_LAUNCH();
-    return pdec_advect_staggered_2d_bwd(vy, vx, seed_y, seed_x, g_vy, g_vx, 0, B, ny, nx, mode, dt, lower_y, lower_x, size_y, size_x, workspace,
-                                        workspace_bytes, stream);
+    return advect_staggered_bwd_impl(vy, vx, seed_y, seed_x, g_vy, g_vx, 0, B, ny, nx, mode, dt, lower_y, lower_x, size_y, size_x, workspace,
+                                     workspace_bytes, stream, true);
 }
 
 extern "C" int pdec_mask_divergence_2d_fwd(const float* vy, const float* vx, float* div, int B, int ny, int nx, int closed, void* stream) {
