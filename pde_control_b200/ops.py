@@ -849,6 +849,126 @@ def _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, m
     return _Project.apply(vy, vx, closed_code(closed), b[2], b[3], accuracy, int(max_iterations), ga, int(gi))
 
 
+class _ProjectComposed(torch.autograd.Function):
+    """divergence_free (PF/physics/fluid.py:214-243) as ONE autograd node around the three launches (divergence, solve, gradient
+    subtraction): the backward hands the velocity gradient of the gradient subtraction to the divergence adjoint to accumulate into
+    (the kernels' `accumulate` flag) instead of leaving two sums per step to autograd.  Same kernels, same values as the three-node
+    composition (the order of the one float addition per face is the same: subtraction term first, divergence term added).
+    solver = ("direct",) or ("cg", accuracy, max_iterations, gradient_accuracy, max_gradient_iterations, stop_mode)."""
+
+    @staticmethod
+    def forward(ctx, vy, vx, closed, size_y, size_x, solver):
+        _req_cuda(vy, vx)
+        vy, vx = _c(vy), _c(vx)
+        B, ny1, nx = vy.shape
+        ny = ny1 - 1
+        dev = vy.device
+        div = torch.empty((B, ny, nx), device=dev, dtype=torch.float32)
+        p = torch.empty_like(div)
+        oy, ox = torch.empty_like(vy), torch.empty_like(vx)
+        iters = torch.zeros(B, device=dev, dtype=torch.int32)
+        with torch.cuda.device(dev):
+            _call("pdec_mask_divergence_2d_fwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(div), B, ny, nx, closed, _lib.stream_ptr())
+            if solver[0] == "direct":
+                poisson_direct_raw(div, p, closed)
+            else:
+                cg_poisson_raw(div, p, closed, solver[1], solver[2], None, iters, None, solver[5])
+            _call("pdec_subtract_pressure_gradient_2d_fwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(p), _lib.ptr(oy), _lib.ptr(ox), B, ny, nx,
+                  closed, size_y, size_x, _lib.stream_ptr())
+        ctx.cfg = (B, ny, nx, closed, size_y, size_x, solver)
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(iters)
+        return oy, ox, p, div, iters
+
+    @staticmethod
+    def backward(ctx, g_oy, g_ox, g_p, g_div, _gi):
+        B, ny, nx, closed, size_y, size_x, solver = ctx.cfg
+        if g_oy is None and g_ox is None and g_p is None and g_div is None:
+            return None, None, None, None, None, None
+        ref = next(t for t in (g_oy, g_ox, g_p, g_div) if t is not None)
+        dev = ref.device
+        g_vy = torch.empty((B, ny + 1, nx), device=dev, dtype=torch.float32)
+        g_vx = torch.empty((B, ny, nx + 1), device=dev, dtype=torch.float32)
+        with torch.cuda.device(dev):
+            if g_oy is None and g_ox is None:
+                g_vy.zero_(); g_vx.zero_()
+                g_pt = _c(g_p) if g_p is not None else None
+            else:
+                g_oy = _c(g_oy) if g_oy is not None else torch.zeros_like(g_vy)
+                g_ox = _c(g_ox) if g_ox is not None else torch.zeros_like(g_vx)
+                g_pt = torch.empty((B, ny, nx), device=dev, dtype=torch.float32)
+                _call("pdec_subtract_pressure_gradient_2d_bwd", _lib.ptr(g_oy), _lib.ptr(g_ox), _lib.ptr(g_vy), _lib.ptr(g_vx), _lib.ptr(g_pt), 0,
+                      B, ny, nx, closed, size_y, size_x, _lib.stream_ptr())
+                if g_p is not None:
+                    g_pt = g_pt + g_p
+            g_d = None
+            if g_pt is not None:
+                g_d = torch.empty_like(g_pt)
+                if solver[0] == "direct":
+                    poisson_direct_raw(g_pt, g_d, closed)
+                else:
+                    cg_poisson_raw(g_pt, g_d, closed, solver[3], solver[4], None, None, None, solver[5])
+            if g_div is not None:
+                g_d = _c(g_div) if g_d is None else g_d + g_div
+            if g_d is not None:
+                _call("pdec_mask_divergence_2d_bwd", _lib.ptr(g_d), _lib.ptr(g_vy), _lib.ptr(g_vx), 1, B, ny, nx, closed, _lib.stream_ptr())
+        return g_vy, g_vx, None, None, None, None
+
+
+class _AdvectPair(torch.autograd.Function):
+    """The two advections of IncompressibleFlow.step (PF/physics/fluid.py:102-103) -- density by the velocity, velocity by itself -- as
+    one autograd node: the centred adjoint accumulates its velocity gradient into the staggered adjoint's (accumulate_v) instead of two
+    separate sums.  Same kernels, same values as advect_centered + advect_staggered."""
+
+    @staticmethod
+    def forward(ctx, rho, vy, vx, dt, mode, box):
+        _req_cuda(rho, vy, vx)
+        rho, vy, vx = _c(rho), _c(vy), _c(vx)
+        B, ny, nx = rho.shape
+        assert vy.shape == (B, ny + 1, nx) and vx.shape == (B, ny, nx + 1), (rho.shape, vy.shape, vx.shape)
+        out, ay, ax = torch.empty_like(rho), torch.empty_like(vy), torch.empty_like(vx)
+        with torch.cuda.device(rho.device):
+            _call("pdec_advect_centered_2d_fwd", _lib.ptr(rho), _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(out), B, ny, nx, mode, dt, *box, _lib.stream_ptr())
+            _call("pdec_advect_staggered_2d_fwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(ay), _lib.ptr(ax), B, ny, nx, mode, dt, *box, _lib.stream_ptr())
+        ctx.save_for_backward(rho, vy, vx)
+        ctx.cfg = (dt, mode, box)
+        ctx.set_materialize_grads(False)
+        return out, ay, ax
+
+    @staticmethod
+    def backward(ctx, g_out, g_ay, g_ax):
+        rho, vy, vx = ctx.saved_tensors
+        dt, mode, box = ctx.cfg
+        B, ny, nx = rho.shape
+        if g_out is None and g_ay is None and g_ax is None:
+            return None, None, None, None, None, None
+        g_vy, g_vx = torch.empty_like(vy), torch.empty_like(vx)
+        g_rho = None
+        nbytes = _lib.lib().pdec_advect_2d_workspace_bytes(B, ny, nx)
+        ws = _lib.workspace(rho.device, nbytes)
+        with torch.cuda.device(rho.device):
+            if g_ay is None and g_ax is None:
+                have_v = False
+            else:
+                g_ay = _c(g_ay) if g_ay is not None else torch.zeros_like(vy)
+                g_ax = _c(g_ax) if g_ax is not None else torch.zeros_like(vx)
+                _call("pdec_advect_staggered_2d_bwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(g_ay), _lib.ptr(g_ax), _lib.ptr(g_vy), _lib.ptr(g_vx), 0,
+                      B, ny, nx, mode, dt, *box, _lib.ptr(ws), nbytes, _lib.stream_ptr())
+                have_v = True
+            if g_out is not None:
+                g_rho = torch.empty_like(rho)
+                _call("pdec_advect_centered_2d_bwd", _lib.ptr(rho), _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(_c(g_out)), _lib.ptr(g_rho), _lib.ptr(g_vy),
+                      _lib.ptr(g_vx), 1 if have_v else 0, B, ny, nx, mode, dt, *box, _lib.ptr(ws), nbytes, _lib.stream_ptr())
+            elif not have_v:
+                g_vy.zero_(); g_vx.zero_()
+        return g_rho, g_vy, g_vx, None, None, None
+
+
+def advect_pair(rho, vy, vx, dt, mode=MODE_REPLICATE, box=None):
+    """(advect_centered(rho, vy, vx), *advect_staggered(vy, vx)) as one autograd node."""
+    return _AdvectPair.apply(rho, vy, vx, float(dt), int(mode), _box(box, rho.shape[1], rho.shape[2]))
+
+
 def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
                     max_gradient_iterations=None, guess=None, slab=None, fused=None, direct=False, stop_mode=CG_STOP_PER_ELEMENT):
     """divergence_free (PF/physics/fluid.py:214-243) without obstacles -> (vy', vx', pressure, iterations, divergence).
@@ -860,15 +980,20 @@ def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000
     slab: a SlabSolver -> the pressure solve is decomposed over its process group.
     direct=True: the exact fast-diagonalisation solve instead of CG (pressure_solve_direct; iterations are reported as 0)."""
     ny, nx = vx.shape[1], vy.shape[2]
+    b4 = _box(box, ny, nx)
     if direct:
-        div = mask_divergence(vy, vx, closed)
-        p = pressure_solve_direct(div, closed)
-        oy, ox = subtract_pressure_gradient(vy, vx, p, closed, box)
-        return oy, ox, p, torch.zeros(vy.shape[0], device=vy.device, dtype=torch.int32), div
+        oy, ox, p, div, iters = _ProjectComposed.apply(vy, vx, closed_code(closed), b4[2], b4[3], ("direct",))
+        return oy, ox, p, iters, div
     if fused is None:
         fused = _FUSED_PROJECTION
     if fused and slab is None and guess is None and stop_mode == CG_STOP_PER_ELEMENT and _lib.lib().pdec_project_2d_supported(ny, nx):
         oy, ox, p, div, iters = _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations)
+        return oy, ox, p, iters, div
+    if slab is None and guess is None:
+        ga = accuracy if gradient_accuracy is None else gradient_accuracy
+        gi = max_iterations if max_gradient_iterations is None else max_gradient_iterations
+        oy, ox, p, div, iters = _ProjectComposed.apply(vy, vx, closed_code(closed), b4[2], b4[3],
+                                                       ("cg", accuracy, int(max_iterations), ga, int(gi), int(stop_mode)))
         return oy, ox, p, iters, div
     div = mask_divergence(vy, vx, closed)
     if slab is not None:
@@ -962,8 +1087,7 @@ def incompressible_step(rho, vy, vx, dt, closed, box=None, accuracy=1e-5, max_it
     Field modes follow Material.extrapolation_mode / vector_extrapolation_mode: open -> constant, closed -> replicate.
     direct=True: exact fast-diagonalisation pressure solve instead of CG (see divergence_free)."""
     mode = MODE_REPLICATE if closed else MODE_CONSTANT
-    rho2 = advect_centered(rho, vy, vx, dt, mode, box)
-    ay, ax = advect_staggered(vy, vx, dt, mode, box)
+    rho2, ay, ax = advect_pair(rho, vy, vx, dt, mode, box)
     if closed and conserve_density:
         rho2 = normalize_to(rho2, rho)
     oy, ox, p, iters, _ = divergence_free(ay, ax, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations,
