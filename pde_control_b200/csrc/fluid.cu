@@ -25,6 +25,7 @@ struct FluidGeo {
     float c_wu[2], c_wl[2];      // component c -> cell centres along axis c      (grid.py:112-120)
     float s_wu[2][2], s_wl[2][2];// component 1-c -> face centres of component c, [c][axis]
     float dt;
+    float gfac[3][2];            // [variant][axis]: d(xi)/d(u) = -(dt * resolution) / size of the variant's grid
 };
 
 enum { V_CENTERED = 0, V_COMP_Y = 1, V_COMP_X = 2 };
@@ -269,7 +270,6 @@ __global__ void __launch_bounds__(256) advect_absmax_kernel(const float* __restr
     }
 }
 
-__device__ __forceinline__ float fixed_value(unsigned long long acc, double inv_scale) { return (float)((double)(long long)acc * inv_scale); }
 
 // acc (may be null: field gradient not wanted) <- shares of g_out; GY / GX <- g_out * d(sample)/d(xi) * d(xi)/d(u): the gradient w.r.t.
 // the velocity (uy, ux) AT the sample point, brought to the faces by pass B
@@ -297,9 +297,9 @@ __device__ __forceinline__ void advect_bwd_scatter_body(const FluidGeo& g, const
     const float dx = (s01 * w1y + s11 * w0y) - (s00 * w1y + s10 * w0y);
     const size_t o = b * sf + (size_t)i * rx + j;
     const float go = gout[o];
-    const float *sz = (VARIANT == V_CENTERED) ? g.sz : g.csz[VARIANT - 1];
-    GY[o] = go * dy * (-(g.dt * (float)ry) / sz[0]);                  // through xi = ((p - u*dt - lower)/size)*res - 0.5
-    GX[o] = go * dx * (-(g.dt * (float)rx) / sz[1]);
+    const float *gf = g.gfac[VARIANT];                               // -(dt * res) / size per axis: through xi = ((p - u*dt - lower)/size)*res - 0.5
+    GY[o] = go * dy * gf[0];
+    GX[o] = go * dx * gf[1];
     if (acc != nullptr) {
         const float scale = fixed_scale(header, ADV_BITS);
         if (scale > 0.0f) {
@@ -398,9 +398,8 @@ __global__ void __launch_bounds__(256) advect_centered_bwd_kernel(FluidGeo g, co
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     const size_t sf = (size_t)ny * nx;
     if (g_rho != nullptr && i < ny && j < nx) {
-        const float scale = fixed_scale(header, ADV_BITS);
         const size_t at = b * sf + (size_t)i * nx + j;
-        g_rho[at] = fixed_value(acc[at], scale > 0.0f ? 1.0 / (double)scale : 0.0);
+        g_rho[at] = fixed_to_float(acc[at], fixed_inv_scale(header, ADV_BITS));
     }
     // velocity at centres = vy[i+1]*wu + vy[i]*wl  ->  g_vy[i] = wu * GY[i-1] + wl * GY[i]
     if (g_vy != nullptr && i <= ny && j < nx) {
@@ -431,16 +430,14 @@ __global__ void __launch_bounds__(256) advect_staggered_bwd_kernel(FluidGeo g, c
     // G0 = {GY, GX} of the vy grid, G1 of the vx grid (arrays of B elements each)
     const float *GY0 = G0 + b * sy, *GX0 = G0 + (size_t)B * sy + b * sy, *GY1 = G1 + b * sx, *GX1 = G1 + (size_t)B * sx + b * sx;
     if (i <= ny && j < nx) {
-        const float scale = fixed_scale(header, ADV_BITS);
-        float v = fixed_value(acc0[b * sy + (size_t)i * nx + j], scale > 0.0f ? 1.0 / (double)scale : 0.0);
+        float v = fixed_to_float(acc0[b * sy + (size_t)i * nx + j], fixed_inv_scale(header, ADV_BITS));
         v += __ldg(GY0 + (size_t)i * nx + j);               // uy = vy itself at vy faces
         v += cross_to_vy<VMODE>(g, GY1, i, j);              // vy averaged to vx faces
         float* p = g_vy + b * sy + (size_t)i * nx + j;
         *p = accumulate ? *p + v : v;
     }
     if (i < ny && j <= nx) {
-        const float scale = fixed_scale(header + 1, ADV_BITS);
-        float v = fixed_value(acc1[b * sx + (size_t)i * (nx + 1) + j], scale > 0.0f ? 1.0 / (double)scale : 0.0);
+        float v = fixed_to_float(acc1[b * sx + (size_t)i * (nx + 1) + j], fixed_inv_scale(header + 1, ADV_BITS));
         v += __ldg(GX1 + (size_t)i * (nx + 1) + j);
         v += cross_to_vx<VMODE>(g, GX0, i, j);
         float* p = g_vx + b * sx + (size_t)i * (nx + 1) + j;
@@ -712,6 +709,12 @@ static int make_geo(FluidGeo& g, int B, int ny, int nx, double dt, float lower_y
         g.inv[a] = exact_inv(g.sz[a]);
         for (int c = 0; c < 2; ++c) g.cinv[c][a] = exact_inv(g.csz[c][a]);
     }
+    for (int v = 0; v < 3; ++v)
+        for (int a = 0; a < 2; ++a) {
+            const int r = res[a] + ((v == 1 && a == 0) || (v == 2 && a == 1) ? 1 : 0);
+            const float size = v == 0 ? g.sz[a] : g.csz[v - 1][a];
+            g.gfac[v][a] = -(g.dt * (float)r) / size;                // the expression the kernels evaluated per thread
+        }
     for (int c = 0; c < 2; ++c) half_weights(g.clo[c][c], g.csz[c][c], res[c] + 1, g.lo[c], g.c_wu[c], g.c_wl[c]);
     for (int c = 0; c < 2; ++c) {
         const int d = 1 - c;   // the other component, padded by one cell on both sides along axis c

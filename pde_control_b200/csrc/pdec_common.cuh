@@ -134,13 +134,25 @@ __device__ __forceinline__ void interp_setup(float xi, int n, int& fi, int& ci, 
 // header[0] = bits of max|g| (non-negative floats order like their bit patterns; written with an integer atomicMax).
 // scale = 2^(bits - exponent of max|g|): every |contribution| <= max|g| maps below 2^bits; integer adds commute, so the sums do not
 // depend on the order the atomics land in: bit-reproducible without float atomics.
-__device__ __forceinline__ float fixed_scale(const unsigned* header, int bits) {
-    const float m = __uint_as_float(header[0]);
-    if (!(m > 0.0f)) return 0.0f;
-    int e;
-    frexpf(m, &e);                                                  // m = f * 2^e, f in [0.5, 1)
-    return ldexpf(1.0f, min(max(bits - e, -120), 120));
+__device__ __forceinline__ int fixed_shift(const unsigned* header, int bits, bool& valid) {
+    const unsigned u = header[0];                                   // bits of max|g|: a non-negative finite float
+    valid = u != 0u && u < 0x7f800000u;
+    const int e = (int)(u >> 23) - 126;                             // max|g| = f * 2^e, f in [0.5, 1) (as frexpf for normal numbers)
+    return min(max(bits - e, -120), 120);
 }
+__device__ __forceinline__ float fixed_scale(const unsigned* header, int bits) {
+    bool valid;
+    const int k = fixed_shift(header, bits, valid);
+    return valid ? __int_as_float((unsigned)(k + 127) << 23) : 0.0f;     // 2^k, exact
+}
+// 1 / scale = 2^-k (exact); 0 when there is nothing to convert
+__device__ __forceinline__ float fixed_inv_scale(const unsigned* header, int bits) {
+    bool valid;
+    const int k = fixed_shift(header, bits, valid);
+    return valid ? __int_as_float((unsigned)(127 - k) << 23) : 0.0f;
+}
+// fixed-point sum -> float: ONE rounding (integer -> float), then an exact power-of-two scaling
+__device__ __forceinline__ float fixed_to_float(unsigned long long acc, float inv_scale) { return __ll2float_rn((long long)acc) * inv_scale; }
 __device__ __forceinline__ void fixed_add(unsigned long long* cell, float v, float scale) {     // two's-complement add
     const float sv = v * scale;
     if (sv == sv && fabsf(sv) < 9.0e18f) atomicAdd(cell, (unsigned long long)__float2ll_rn(sv));

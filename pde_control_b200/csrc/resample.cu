@@ -111,10 +111,9 @@ __global__ void __launch_bounds__(256) resample_bwd_kernel(const float* __restri
 
 __global__ void __launch_bounds__(256) resample_unfix_kernel(const unsigned long long* __restrict__ acc, float* __restrict__ g_data, long long n,
                                                              const unsigned* __restrict__ header, int bits) {
-    const float scale = fixed_scale(header, bits);
-    const double inv = scale > 0.0f ? 1.0 / (double)scale : 0.0;
+    const float inv = fixed_inv_scale(header, bits);
     for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < n; q += (long long)gridDim.x * 256)
-        g_data[q] = (float)((double)(long long)acc[q] * inv);
+        g_data[q] = fixed_to_float(acc[q], inv);
 }
 
 }  // namespace pdec
