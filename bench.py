@@ -9,7 +9,8 @@ ONE JSON line on rank 0.  Its top level is BASELINE config 2 (the configuration 
 Burgers force loss + adjoint over s[33, 4096, 128] per GPU); `workloads` carries the rest of the target with the same keys each:
   fluid_config3               128 x 128, 16 projected steps + adjoint, B = 64: CG at the accuracy that HOLDS the parity tolerances (1e-7)
   fluid_config3_ref_accuracy  the same at the reference's default CG accuracy 1e-5
-  fluid_config3_direct        the same with the opt-in exact solver (physics.SparseSciPy)
+  fluid_config3_direct        the same with the opt-in exact solver (physics.SparseSciPy; tcgen05 tensor cores)
+  fluid_config3_chained       SparseSciPy() & SparseCG(1e-7): the exact solve as the CG's initial guess (the reference's solver chain)
   fluid_notebook              the IncompressibleFluidPDE path: potential -> curl -> advection + staggered force loss
   burgers_config1             B = 8 trajectory + control-loss gradient (latency-bound)
   config4        (N >= 2)     config 2 + the OP-network gradient all-reduce inside the timed region
@@ -114,7 +115,7 @@ def run_b200(args):
     subs = {}
     if world > 1 and want("config4"):
         subs["config4"] = measure(BurgersConfig4(dev, rank, world, base), args, proto, sampler, peak, peak_src, world, rank)
-    for key in ("fluid_config3", "fluid_config3_ref_accuracy", "fluid_config3_direct"):
+    for key in ("fluid_config3", "fluid_config3_ref_accuracy", "fluid_config3_direct", "fluid_config3_chained"):
         if want(key):
             wl = FluidConfig3(dev, rank, world, key)
             subs[key] = measure(wl, args, proto, sampler, peak, peak_src, world, rank)

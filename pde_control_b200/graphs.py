@@ -66,7 +66,7 @@ class GraphedFunction(object):
         return self.replay()
 
 
-def fluid_trajectory(steps, dt, closed, accuracy=1e-5, max_iterations=2000, box=None, loss=None, direct=False, groups=1):
+def fluid_trajectory(steps, dt, closed, accuracy=1e-5, max_iterations=2000, box=None, loss=None, direct=False, groups=1, guess=None):
     """fn(rho, vy, vx[, target]) for GraphedFunction: `steps` projected IncompressibleFlow steps (PF/physics/fluid.py:90-114); returns
     (loss, rho, vy, vx, cg_iterations [steps, B]) with loss = l2_loss(rho_final - target) (PF/math/nd.py:111-124) unless `loss` is given.
 
@@ -74,7 +74,8 @@ def fluid_trajectory(steps, dt, closed, accuracy=1e-5, max_iterations=2000, box=
     graph).  Batch elements never interact, but a CG launch lasts as long as its slowest element: with one launch per step for the whole
     batch every step waits for the slowest of all B elements, with sub-batches only for the slowest of its own group, and the groups drift
     apart instead of idling (64 one-CTA solves still fit the 148 SMs at once).  Per-element results are bit-identical; the loss is summed
-    group by group."""
+    group by group.
+    guess="direct": the solver chain SparseSciPy() & SparseCG(accuracy) (ops.divergence_free)."""
     from . import ops
     streams = []
 
@@ -82,7 +83,7 @@ def fluid_trajectory(steps, dt, closed, accuracy=1e-5, max_iterations=2000, box=
         iters = []
         for _ in range(steps):
             rho, vy, vx, _p, it = ops.incompressible_step(rho, vy, vx, dt, closed, box=box, accuracy=accuracy, max_iterations=max_iterations,
-                                                          direct=direct)
+                                                          direct=direct, guess=guess)
             iters.append(it)
         return rho, vy, vx, torch.stack(iters)
 

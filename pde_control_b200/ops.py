@@ -854,7 +854,7 @@ class _ProjectComposed(torch.autograd.Function):
     subtraction): the backward hands the velocity gradient of the gradient subtraction to the divergence adjoint to accumulate into
     (the kernels' `accumulate` flag) instead of leaving two sums per step to autograd.  Same kernels, same values as the three-node
     composition (the order of the one float addition per face is the same: subtraction term first, divergence term added).
-    solver = ("direct",) or ("cg", accuracy, max_iterations, gradient_accuracy, max_gradient_iterations, stop_mode)."""
+    solver = ("direct",) or ("cg" | "cg_from_direct", accuracy, max_iterations, gradient_accuracy, max_gradient_iterations, stop_mode)."""
 
     @staticmethod
     def forward(ctx, vy, vx, closed, size_y, size_x, solver):
@@ -871,6 +871,10 @@ class _ProjectComposed(torch.autograd.Function):
             _call("pdec_mask_divergence_2d_fwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(div), B, ny, nx, closed, _lib.stream_ptr())
             if solver[0] == "direct":
                 poisson_direct_raw(div, p, closed)
+            elif solver[0] == "cg_from_direct":                      # SparseSciPy() & SparseCG(...): the exact solve is the CG's initial guess
+                p0 = torch.empty_like(div)
+                poisson_direct_raw(div, p0, closed)
+                cg_poisson_raw(div, p, closed, solver[1], solver[2], p0, iters, None, solver[5])
             else:
                 cg_poisson_raw(div, p, closed, solver[1], solver[2], None, iters, None, solver[5])
             _call("pdec_subtract_pressure_gradient_2d_fwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(p), _lib.ptr(oy), _lib.ptr(ox), B, ny, nx,
@@ -906,6 +910,10 @@ class _ProjectComposed(torch.autograd.Function):
                 g_d = torch.empty_like(g_pt)
                 if solver[0] == "direct":
                     poisson_direct_raw(g_pt, g_d, closed)
+                elif solver[0] == "cg_from_direct":                  # the adjoint system is the same matrix: same chain
+                    g0 = torch.empty_like(g_pt)
+                    poisson_direct_raw(g_pt, g0, closed)
+                    cg_poisson_raw(g_pt, g_d, closed, solver[3], solver[4], g0, None, None, solver[5])
                 else:
                     cg_poisson_raw(g_pt, g_d, closed, solver[3], solver[4], None, None, None, solver[5])
             if g_div is not None:
@@ -978,7 +986,10 @@ def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000
     prologue / epilogue perturb the register allocation of the iteration loop by 9 instructions in 482, which costs more than the two
     stencil launches did inside a CUDA graph), so it is an option (PDEC_FUSED_PROJECTION=1 makes it the default), not the default.
     slab: a SlabSolver -> the pressure solve is decomposed over its process group.
-    direct=True: the exact fast-diagonalisation solve instead of CG (pressure_solve_direct; iterations are reported as 0)."""
+    direct=True: the exact fast-diagonalisation solve instead of CG (pressure_solve_direct; iterations are reported as 0).
+    guess="direct": the reference's solver chain `SparseSciPy() & SparseCG(...)` (solver_api.py:161-174): the exact solve is the initial
+    guess of a CG that runs to the usual stopping rule max|r| < accuracy -- forward and adjoint (same matrix).  At 1e-5 the guess already
+    satisfies the rule (0-1 iterations), at 1e-7 40-150 iterations remain instead of 320-480 (scripts/diag/cg_from_direct.py)."""
     ny, nx = vx.shape[1], vy.shape[2]
     b4 = _box(box, ny, nx)
     if direct:
@@ -989,11 +1000,15 @@ def divergence_free(vy, vx, closed, box=None, accuracy=1e-5, max_iterations=2000
     if fused and slab is None and guess is None and stop_mode == CG_STOP_PER_ELEMENT and _lib.lib().pdec_project_2d_supported(ny, nx):
         oy, ox, p, div, iters = _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations)
         return oy, ox, p, iters, div
-    if slab is None and guess is None:
+    from_direct = isinstance(guess, str) and guess == "direct"
+    if from_direct:
+        assert slab is None and direct_solver_supported(ny, nx), "guess='direct' needs a grid the direct solver takes (<= 128 x 128, one GPU)"
+    if slab is None and (guess is None or from_direct):
         ga = accuracy if gradient_accuracy is None else gradient_accuracy
         gi = max_iterations if max_gradient_iterations is None else max_gradient_iterations
         oy, ox, p, div, iters = _ProjectComposed.apply(vy, vx, closed_code(closed), b4[2], b4[3],
-                                                       ("cg", accuracy, int(max_iterations), ga, int(gi), int(stop_mode)))
+                                                       ("cg_from_direct" if from_direct else "cg", accuracy, int(max_iterations), ga, int(gi),
+                                                        int(stop_mode)))
         return oy, ox, p, iters, div
     div = mask_divergence(vy, vx, closed)
     if slab is not None:
@@ -1082,7 +1097,7 @@ def divergence_free_masked(vy, vx, masks, box=None, accuracy=1e-5, max_iteration
 
 
 def incompressible_step(rho, vy, vx, dt, closed, box=None, accuracy=1e-5, max_iterations=2000, gradient_accuracy=None,
-                        max_gradient_iterations=None, conserve_density=True, slab=None, direct=False, fused=None):
+                        max_gradient_iterations=None, conserve_density=True, slab=None, direct=False, fused=None, guess=None):
     """IncompressibleFlow.step (PF/physics/fluid.py:90-114), default flags, no obstacles / effects / buoyancy.
     Field modes follow Material.extrapolation_mode / vector_extrapolation_mode: open -> constant, closed -> replicate.
     direct=True: exact fast-diagonalisation pressure solve instead of CG (see divergence_free)."""
@@ -1091,5 +1106,5 @@ def incompressible_step(rho, vy, vx, dt, closed, box=None, accuracy=1e-5, max_it
     if closed and conserve_density:
         rho2 = normalize_to(rho2, rho)
     oy, ox, p, iters, _ = divergence_free(ay, ax, closed, box, accuracy, max_iterations, gradient_accuracy, max_gradient_iterations,
-                                         slab=slab, direct=direct, fused=fused)
+                                         slab=slab, direct=direct, fused=fused, guess=guess)
     return rho2, oy, ox, p, iters

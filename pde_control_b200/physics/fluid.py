@@ -257,9 +257,16 @@ def divergence_free(velocity, domain=None, obstacles=(), pressure_solver=None, r
     if isinstance(solver, _SolverChain):
         # solver1 & solver2 (solver_api.py:161-174; the reference's TF default is FourierSolver() & SparseCG()): the leading solvers turn
         # the divergence into an initial guess for the last one
-        div0 = ops.mask_divergence(vy, vx, _closed(domain)).detach()
-        for lead in solver.solvers[:-1]:
-            guess, _ = lead.solve(div0, domain, guess)
+        ny_, nx_ = int(vx.shape[1]), int(vy.shape[2])
+        if (len(solver.solvers) == 2 and isinstance(solver.solvers[0], SparseSciPy) and isinstance(solver.solvers[1], SparseCG)
+                and len(obstacles) == 0 and ops.direct_solver_supported(ny_, nx_)):
+            # SparseSciPy() & SparseCG(...): the exact solve as the CG's initial guess, in ONE autograd node -- the adjoint solve takes
+            # the same chain (same matrix) instead of a CG from zero
+            guess = "direct"
+        else:
+            div0 = ops.mask_divergence(vy, vx, _closed(domain)).detach()
+            for lead in solver.solvers[:-1]:
+                guess, _ = lead.solve(div0, domain, guess)
         solver = solver.solvers[-1]
     if isinstance(solver, FourierSolver):
         raise NotImplementedError("FourierSolver alone is exact on periodic domains only: chain it, FourierSolver() & SparseCG()")

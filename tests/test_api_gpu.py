@@ -265,6 +265,33 @@ def test_sparse_cg_stop_modes_and_solver_chain_through_divergence_free():
     assert int(res["chain"][1].max()) > 0
 
 
+@pytest.mark.parametrize("bd", ["open", "closed"])
+def test_direct_solver_chained_in_front_of_cg(bd):
+    """SparseSciPy() & SparseCG(accuracy) -- the reference's solver-chain idiom (solver_api.py:161-174) with the exact tensor-core solve as
+    the CG's initial guess: the CG still runs to the reference's stopping rule (so the result meets the same criterion as a CG from zero
+    and agrees with it within the tolerance), but needs a fraction of the iterations; the adjoint takes the same chain and agrees with the
+    adjoint of the plain CG."""
+    from pde_control_b200 import physics as P
+    rng = np.random.RandomState(5)
+    B, ny, nx = 3, 64, 48
+    dom = P.Domain([ny, nx], boundaries=P.CLOSED if bd == "closed" else P.OPEN)
+    vy = torch.tensor(rng.randn(B, ny + 1, nx, 1).astype(np.float32), device="cuda")
+    vx = torch.tensor(rng.randn(B, ny, nx + 1, 1).astype(np.float32), device="cuda")
+    wy, wx = torch.randn(B, ny + 1, nx, 1, device="cuda"), torch.randn(B, ny, nx + 1, 1, device="cuda")
+    res = {}
+    for name, solver in (("cg", P.SparseCG(accuracy=1e-7, max_iterations=5000)), ("chain", P.SparseSciPy() & P.SparseCG(accuracy=1e-7, max_iterations=5000))):
+        a, b = vy.clone().requires_grad_(), vx.clone().requires_grad_()
+        v = P.StaggeredGrid([a, b], box=dom.box, batch_size=B)
+        out, info = P.divergence_free(v, dom, pressure_solver=solver, return_info=True)
+        ((out.data[0].data * wy).sum() + (out.data[1].data * wx).sum()).backward()
+        res[name] = (out, info["iterations"], a.grad, b.grad, info["pressure"] if "pressure" in info else None)
+    it_cg, it_ch = res["cg"][1].cpu().numpy(), res["chain"][1].cpu().numpy()
+    assert it_ch.max() < it_cg.min() / 2, (it_cg, it_ch)
+    for k in (0, 1):
+        assert rel_err(res["chain"][0].data[k].data.detach().cpu(), res["cg"][0].data[k].data.detach().cpu()) < 1e-5
+    assert rel_err(res["chain"][2].cpu(), res["cg"][2].cpu()) < 1e-4 and rel_err(res["chain"][3].cpu(), res["cg"][3].cpu()) < 1e-4
+
+
 def test_periodic_burgers_takes_the_fft_diffusion_branch():
     """PERIODIC Burgers through World (circular advection kernel + FFT diffusion + GROW effect) vs the live reference."""
     from pde_control_b200.physics import World, Domain, BurgersVelocity, Burgers, PERIODIC, box, FieldEffect, CenteredGrid
