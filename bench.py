@@ -14,6 +14,7 @@ Burgers force loss + adjoint over s[33, 4096, 128] per GPU); `workloads` carries
   fluid_notebook              the IncompressibleFluidPDE path: potential -> curl -> advection + staggered force loss
   burgers_config1             B = 8 trajectory + control-loss gradient (latency-bound)
   config4        (N >= 2)     config 2 + the OP-network gradient all-reduce inside the timed region
+  config5_direct              2048 x 2048 projected steps + adjoint on one GPU with the exact solver (library GEMMs beyond 128 x 128)
   config5_slab   (N >= 2)     2048 x 2048 slab-decomposed projected steps + a solve checked against its fp64 residual
 Every workload: W untimed warm-up steps (at least 3), then the K-step loop repeated R times so that the timed region lasts >= 0.6 s
 (`timing.repeats`), CUDA events on the launching stream, barrier + synchronize on both sides of every repetition, max over ranks,
@@ -104,7 +105,7 @@ def run_b200(args):
     if sampler:
         sampler.start()
     from benchlib.burgers import BurgersConfig2, BurgersConfig1, BurgersConfig4
-    from benchlib.fluid import FluidConfig3, FluidNotebook, Config5Slab
+    from benchlib.fluid import FluidConfig3, FluidNotebook, Config5Slab, Config5Direct
     only = set(args.only.split(",")) if args.only else None
     want = lambda key: only is None or key in only
 
@@ -126,6 +127,11 @@ def run_b200(args):
         torch.cuda.empty_cache()
     if want("burgers_config1"):
         subs["burgers_config1"] = measure(BurgersConfig1(dev, rank, world), args, proto, sampler, peak, peak_src, world, rank)
+    if want("config5_direct"):
+        sub_args = argparse.Namespace(**vars(args))
+        sub_args.steps, sub_args.warmup = 3, 3
+        subs["config5_direct"] = measure(Config5Direct(dev, rank, world), sub_args, proto, sampler, peak, peak_src, world, rank)
+        torch.cuda.empty_cache()
     if world > 1 and want("config5_slab"):
         sub_args = argparse.Namespace(**vars(args))
         sub_args.steps, sub_args.warmup = 1, 1          # one 2-step trajectory of ~100 ms per "step"

@@ -493,6 +493,37 @@ def test_tensor_core_direct_solver_against_the_fp32_kernel_and_the_residual(clos
         assert float(resid) < 4e-5 * max(1.0, scale)
 
 
+@pytest.mark.parametrize("closed", [False, True, (True, False, False, True)])
+@pytest.mark.parametrize("B,ny,nx", [(2, 200, 160), (1, 512, 384)])
+def test_direct_solver_beyond_128_uses_library_gemms_and_matches_the_fp64_formula(closed, B, ny, nx):
+    """ops.poisson_direct_raw on grids the on-chip kernels do not take: p = Ey [(Ey^T rhs Ex) / (l_y + l_x)] Ex^T with fp32 library GEMMs,
+    against the same formula in fp64 (whose stencil residual is at 1e-11) and, on uniform domains, against A p == rhs; the differentiable
+    wrapper's gradient is the same solve."""
+    ops = _ops()
+    rng = np.random.RandomState(ny + nx)
+    rhs = _smooth(rng, (B, ny, nx), 1.0, passes=3)
+    t = torch.tensor(rhs, device="cuda", requires_grad=True)
+    p = ops.pressure_solve_direct(t, closed)
+    Ey, EyT, Ex, ExT, inv = ops._spectral_large(t.device, ny, nx, closed)
+    code = ops.closed_code(closed)
+    sides = (0xF if code == 1 else 0) if code < 0x10 else (code & 0xF)
+    Ey64, ly = ops._eig_1d(ny, sides & 3, t.device)
+    Ex64, lx = ops._eig_1d(nx, (sides >> 2) & 3, t.device)
+    assert float((Ey64.T @ Ey64 - torch.eye(ny, device="cuda", dtype=torch.float64)).abs().max()) < 1e-10      # orthonormal bases
+    lam = ly[:, None] + lx[None, :]
+    inv64 = torch.where(lam.abs() < 1e-9, torch.zeros_like(lam), 1.0 / lam)
+    p64 = Ey64 @ ((Ey64.T @ t.detach().double() @ Ex64) * inv64) @ Ex64.T
+    assert rel_err(p.detach().cpu(), p64.cpu()) < 2e-5
+    if isinstance(closed, bool):
+        bd = "closed" if closed else "open"
+        target = rhs - rhs.mean((1, 2), keepdims=True) if closed else rhs
+        assert float((F.laplace_apply(p64.cpu(), bd) - torch.tensor(target).double()).abs().max()) < 1e-6
+    w = torch.tensor(rng.randn(B, ny, nx).astype(np.float32), device="cuda")
+    (p * w).sum().backward()
+    g64 = Ey64 @ ((Ey64.T @ w.double() @ Ex64) * inv64) @ Ex64.T
+    assert rel_err(t.grad.cpu(), g64.cpu()) < 2e-5
+
+
 def test_tensor_core_direct_solver_c_abi_codes():
     """Return codes of the tensor-core entry points: sizes beyond 128, too small or misaligned spectral block, null pointers, B = 0."""
     ops = _ops()
