@@ -23,7 +23,7 @@ class BurgersConfig2(object):
     algorithmic_bytes_per_cell_update = 8.0     # read each frame once + write its gradient once
     dtype = "f32"
     dominant_kernel = "burgers_pair_loss_unit_kernel"
-    ncu_traffic_bytes = 129.0e6     # steady state: dram read 66.1 MB + write 62.9 MB per launch, profiles/r1k_burgers_summary.md
+    ncu_traffic_bytes = 130.4e6     # steady state: dram read 67.1 MB + write 63.3 MB per launch (ncu --set full, profiles/r2ac_burgers_summary.md)
     mode = 0                        # PDEC_MODE_CONSTANT: the reference's Burgers domain (OPEN boundaries -> 'constant' extrapolation)
     B, n, T = 4096, 128, 32
 
