@@ -247,15 +247,21 @@ constexpr int ADV_BITS = 40;                 // |share| <= max|g_out| -> below 2
 // max |g| of up to two arrays -> header[0], header[1] (bits of non-negative floats order like unsigned integers)
 __global__ void __launch_bounds__(256) advect_absmax_kernel(const float* __restrict__ g0, long long n0, const float* __restrict__ g1, long long n1,
                                                             unsigned* __restrict__ header) {
-    float m0 = 0.0f, m1 = 0.0f;
-    for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < n0; q += (long long)gridDim.x * 256) {
-        const float v = fabsf(g0[q]);
-        if (v == v && v < 3.0e38f) m0 = fmaxf(m0, v);              // NaN / inf gradients do not set the scale
-    }
-    for (long long q = (long long)blockIdx.x * 256 + threadIdx.x; q < n1; q += (long long)gridDim.x * 256) {
-        const float v = fabsf(g1[q]);
-        if (v == v && v < 3.0e38f) m1 = fmaxf(m1, v);
-    }
+    // NaN / inf gradients do not set the scale.  16 bytes per load where the array allows it (the max does not depend on the order)
+    auto scan = [&](const float* __restrict__ g, long long n) -> float {
+        float m = 0.0f;
+        auto take = [&](float x) { const float v = fabsf(x); if (v == v && v < 3.0e38f) m = fmaxf(m, v); };
+        const long long tid = (long long)blockIdx.x * 256 + threadIdx.x, step = (long long)gridDim.x * 256;
+        long long done = 0;
+        if ((reinterpret_cast<uintptr_t>(g) & 15) == 0) {
+            const float4* g4 = reinterpret_cast<const float4*>(g);
+            for (long long q = tid; q < n / 4; q += step) { const float4 v = g4[q]; take(v.x); take(v.y); take(v.z); take(v.w); }
+            done = (n / 4) * 4;
+        }
+        for (long long q = done + tid; q < n; q += step) take(g[q]);
+        return m;
+    };
+    float m0 = scan(g0, n0), m1 = g1 != nullptr ? scan(g1, n1) : 0.0f;
     m0 = warp_max(m0); m1 = warp_max(m1);
     __shared__ float sm[2][8];
     if ((threadIdx.x & 31) == 0) { sm[0][threadIdx.x >> 5] = m0; sm[1][threadIdx.x >> 5] = m1; }
@@ -806,7 +812,7 @@ extern "C" int pdec_advect_staggered_2d_fwd(const float* vy, const float* vx, fl
 // [fixed-point sums: u64 x B*(ny+1)*nx, then u64 x B*ny*(nx+1)] [GY, GX of the vy grid] [GY, GX of the vx grid]  (16 bytes per sample;
 // the centred variant uses one grid of B*ny*nx: sums, then GY, GX)
 static size_t ws_header(int B) { return (((size_t)4 * (B > 0 ? B : 1) * sizeof(int)) + 255) & ~(size_t)255; }
-static int absmax_blocks(long long n) { return (int)((n + 255) / 256 > 592 ? 592 : (n + 255) / 256); }
+static int absmax_blocks(long long n) { const long long b = (n / 4 + 255) / 256; return (int)(b > 148 * 8 ? 148 * 8 : (b < 1 ? 1 : b)); }
 
 extern "C" size_t pdec_advect_2d_workspace_bytes(int B, int ny, int nx) {
     const size_t b = B > 0 ? B : 1;
