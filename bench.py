@@ -16,6 +16,7 @@ Burgers force loss + adjoint over s[33, 4096, 128] per GPU); `workloads` carries
   config4        (N >= 2)     config 2 + the OP-network gradient all-reduce inside the timed region
   config5_direct              2048 x 2048 projected steps + adjoint on one GPU with the exact solver (library GEMMs beyond 128 x 128)
   config5_slab   (N >= 2)     2048 x 2048 slab-decomposed projected steps + a solve checked against its fp64 residual
+  config5_slab_chained (N >= 2)  the same with the solver chain: whole-domain exact solve as the guess, slab CG on the correction
 Every workload: W untimed warm-up steps (at least 3), then the K-step loop repeated R times so that the timed region lasts >= 0.6 s
 (`timing.repeats`), CUDA events on the launching stream, barrier + synchronize on both sides of every repetition, max over ranks,
 median repetition; `e2e` = the same through the public API with pinned HOST buffers copied in and results copied out every step;
@@ -58,7 +59,7 @@ def measure(wl, args, proto, sampler, peak, peak_src, world, rank, top=False):
         if hasattr(wl, "solve_parity"):
             wl.solve_parity()           # collective: every rank takes part
         return None
-    strong = getattr(wl, "key", "") == "config5_slab"
+    strong = getattr(wl, "key", "").startswith("config5_slab")
     units = wl.cell_updates * (1 if strong else world)
     res.update({"metric": METRIC, "value": units * K / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
                 "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
@@ -132,14 +133,15 @@ def run_b200(args):
         sub_args.steps, sub_args.warmup = 3, 3
         subs["config5_direct"] = measure(Config5Direct(dev, rank, world), sub_args, proto, sampler, peak, peak_src, world, rank)
         torch.cuda.empty_cache()
-    if world > 1 and want("config5_slab"):
-        sub_args = argparse.Namespace(**vars(args))
-        sub_args.steps, sub_args.warmup = 1, 1          # one 2-step trajectory of ~100 ms per "step"
-        wl = Config5Slab(dev, rank, world)
-        try:
-            subs["config5_slab"] = measure(wl, sub_args, proto, sampler, peak, peak_src, world, rank)
-        finally:
-            wl.close()
+    for key, chained in (("config5_slab", False), ("config5_slab_chained", True)):
+        if world > 1 and want(key):
+            sub_args = argparse.Namespace(**vars(args))
+            sub_args.steps, sub_args.warmup = 1, 1          # one 2-step trajectory per "step"
+            wl = Config5Slab(dev, rank, world, chained=chained)
+            try:
+                subs[key] = measure(wl, sub_args, proto, sampler, peak, peak_src, world, rank)
+            finally:
+                wl.close()
     if rank == 0:
         if sampler:
             sampler.summary(stop=True)

@@ -353,7 +353,10 @@ class Config5Slab(object):
     dtype = "f32"
     N, STEPS, HALO = 2048, 2, 4
 
-    def __init__(self, device, rank, world):
+    def __init__(self, device, rank, world, chained=False):
+        self.chained = chained
+        if chained:
+            self.key = "config5_slab_chained"
         import torch.distributed as dist
         from pde_control_b200 import ops, slab
         self.ops, self.dev, self.rank, self.world, self.dist = ops, device, rank, world, dist
@@ -382,7 +385,7 @@ class Config5Slab(object):
         leaves = [t.clone().requires_grad_(True) for t in self.local]
         s, its = tuple(leaves), []
         for _ in range(self.STEPS):
-            out = self.stepper.step(*s, 0.8, False, accuracy=1e-5, max_iterations=20000)
+            out = self.stepper.step(*s, 0.8, False, accuracy=1e-5, max_iterations=20000, chained=self.chained)
             s = out[:3]
             its.append(out[4])
         self.loss = ((s[0] - self.target) ** 2).sum() / 2
@@ -390,8 +393,10 @@ class Config5Slab(object):
         self.its = its
 
     def config(self):
-        return {"workload": "incompressible_flow 2048x2048 B=1 steps=%d OPEN fwd + adjoint, row slabs over %d GPUs, CG to 1e-5 (BASELINE config 5); "
-                            "ms_per_step = one %d-step trajectory" % (self.STEPS, self.world, self.STEPS),
+        return {"workload": "incompressible_flow 2048x2048 B=1 steps=%d OPEN fwd + adjoint, row slabs over %d GPUs, %s (BASELINE config 5); "
+                            "ms_per_step = one %d-step trajectory"
+                            % (self.STEPS, self.world, "solver chain: whole-domain exact solve (library GEMMs, every rank) as the guess, slab CG on the "
+                               "correction system to 1e-5" if self.chained else "CG to 1e-5", self.STEPS),
                 "resolution": [self.N, self.N], "steps": self.STEPS, "halo_rows": self.HALO,
                 "parallelism": "row slabs x%d: advection halos and the pressure halo over NVLink peer memory, slab CG with in-kernel exchange; "
                                "nothing replicated, no NCCL on the data path" % self.world, "scaling": "strong"}
@@ -410,7 +415,7 @@ class Config5Slab(object):
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        p, iters = slab._SlabSolve.apply(div, st, 0, 1e-5, 20000)
+        p, iters = (slab._SlabSolveChained if self.chained else slab._SlabSolve).apply(div, st, 0, 1e-5, 20000)
         e1.record()
         torch.cuda.synchronize()
         P, R = st.gather(p).double(), st.gather(div).double()
@@ -421,7 +426,7 @@ class Config5Slab(object):
         ms = e0.elapsed_time(e1)
         return {"checked": True, "against": "fp64 evaluation of A p - rhs of the gathered slab solve (rhs = divergence of the timed velocity)",
                 "iterations": k, "true_residual_inf": true_res, "rhs_inf": float(R.abs().max()),
-                "tolerance": {"true_residual_inf": 1e-3}, "ok": k > 0 and true_res < 1e-3, "ms_per_solve": ms, "us_per_iteration": ms * 1e3 / max(k, 1)}
+                "tolerance": {"true_residual_inf": 1e-3}, "ok": (k > 0 or self.chained) and true_res < 1e-3, "ms_per_solve": ms, "us_per_iteration": ms * 1e3 / max(k, 1)}
 
     def close(self):
         self.stepper.close()

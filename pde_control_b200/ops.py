@@ -908,6 +908,23 @@ def _project(vy, vx, closed, box, accuracy, max_iterations, gradient_accuracy, m
     return _Project.apply(vy, vx, closed_code(closed), b[2], b[3], accuracy, int(max_iterations), ga, int(gi))
 
 
+def _cg_from_direct(rhs, out, closed, accuracy, max_iterations, iters, stop_mode):
+    """out <- CG(rhs) started from the exact solve (the chain SparseSciPy() & SparseCG()).  OPEN sides somewhere: the CG kernel takes the
+    guess.  All sides closed: the matrix is singular (constants), and rounding leaves rhs - A p0 with a small mean no CG step can remove
+    (the stopping rule would never be met); so the CORRECTION system A d = (rhs - A p0) - mean is solved from zero and out = p0 + d --
+    the constant it drops is annihilated by the gradient that follows."""
+    p0 = torch.empty_like(rhs)
+    poisson_direct_raw(rhs, p0, closed)
+    if closed_code(closed) != 1:
+        cg_poisson_raw(rhs, out, closed, accuracy, max_iterations, p0, iters, None, stop_mode)
+        return
+    from .slab import laplace_rows
+    r = rhs - laplace_rows(p0, 0, rhs.shape[1], True)
+    r -= r.mean((1, 2), keepdim=True)
+    cg_poisson_raw(r, out, closed, accuracy, max_iterations, None, iters, None, stop_mode)
+    out += p0
+
+
 class _ProjectComposed(torch.autograd.Function):
     """divergence_free (PF/physics/fluid.py:214-243) as ONE autograd node around the three launches (divergence, solve, gradient
     subtraction): the backward hands the velocity gradient of the gradient subtraction to the divergence adjoint to accumulate into
@@ -931,9 +948,7 @@ class _ProjectComposed(torch.autograd.Function):
             if solver[0] == "direct":
                 poisson_direct_raw(div, p, closed)
             elif solver[0] == "cg_from_direct":                      # SparseSciPy() & SparseCG(...): the exact solve is the CG's initial guess
-                p0 = torch.empty_like(div)
-                poisson_direct_raw(div, p0, closed)
-                cg_poisson_raw(div, p, closed, solver[1], solver[2], p0, iters, None, solver[5])
+                _cg_from_direct(div, p, closed, solver[1], solver[2], iters, solver[5])
             else:
                 cg_poisson_raw(div, p, closed, solver[1], solver[2], None, iters, None, solver[5])
             _call("pdec_subtract_pressure_gradient_2d_fwd", _lib.ptr(vy), _lib.ptr(vx), _lib.ptr(p), _lib.ptr(oy), _lib.ptr(ox), B, ny, nx,
@@ -970,9 +985,7 @@ class _ProjectComposed(torch.autograd.Function):
                 if solver[0] == "direct":
                     poisson_direct_raw(g_pt, g_d, closed)
                 elif solver[0] == "cg_from_direct":                  # the adjoint system is the same matrix: same chain
-                    g0 = torch.empty_like(g_pt)
-                    poisson_direct_raw(g_pt, g0, closed)
-                    cg_poisson_raw(g_pt, g_d, closed, solver[3], solver[4], g0, None, None, solver[5])
+                    _cg_from_direct(g_pt, g_d, closed, solver[3], solver[4], None, solver[5])
                 else:
                     cg_poisson_raw(g_pt, g_d, closed, solver[3], solver[4], None, None, None, solver[5])
             if g_div is not None:

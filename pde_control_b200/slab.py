@@ -196,6 +196,53 @@ class _SlabSolve(torch.autograd.Function):
         return g_div, None, None, None, None
 
 
+def laplace_rows(p_full, r0, r1, closed):
+    """Rows [r0, r1) of A p for the whole-domain pressure p_full [B, ny, nx]: the 5-point operator of the pressure solve (a zero outside an
+    OPEN domain, one neighbour fewer on a CLOSED one: sparse.py:151-221 without obstacles), evaluated with torch slices."""
+    q = torch.nn.functional.pad(p_full, (1, 1, 1, 1), mode="replicate" if closed else "constant")
+    c = q[:, r0 + 1:r1 + 1, 1:-1]
+    return q[:, r0:r1, 1:-1] + q[:, r0 + 2:r1 + 2, 1:-1] + q[:, r0 + 1:r1 + 1, :-2] + q[:, r0 + 1:r1 + 1, 2:] - 4.0 * c
+
+
+class _SlabSolveChained(torch.autograd.Function):
+    """SparseSciPy() & SparseCG(accuracy) on slabs: every rank gathers the right-hand side (one all-gather), runs the exact solve of the
+    WHOLE domain (library GEMMs, ops.poisson_direct_raw), and the slab CG then solves the CORRECTION system A d = rhs - A p0 on the
+    slabs to the reference's stopping rule (its residual is the residual of the whole system); p = p0 + d.  At 2048 x 2048 the correction
+    needs 0-2 iterations instead of ~3000 (scripts/diag/cg_correction_large.py).  Backward = the same chain on the incoming gradient."""
+
+    @staticmethod
+    def _solve(rhs, stepper, closed_code, accuracy, max_iterations, iters):
+        from . import ops
+        lay = stepper.layout
+        full = stepper.gather(rhs)
+        p0 = torch.empty_like(full)
+        ops.poisson_direct_raw(full, p0, closed_code)
+        if closed_code:
+            # a closed domain's matrix is singular (constants): rounding leaves the correction's right-hand side with a small mean the CG
+            # could never remove -- it would run to max_iterations and drift.  Project it out (every rank holds the whole p0 and rhs).
+            r_full = full - laplace_rows(p0, 0, lay.ny, True)
+            r = (r_full[:, lay.r0:lay.r1] - r_full.mean((1, 2), keepdim=True)).contiguous()
+        else:
+            r = (rhs - laplace_rows(p0, lay.r0, lay.r1, False)).contiguous()
+        d = torch.empty_like(r)
+        ops.cg_poisson_slab_raw(r, d, closed_code, accuracy, max_iterations, ny_global=lay.ny, row0=lay.r0, comm=stepper.comm, iterations=iters)
+        return p0[:, lay.r0:lay.r1] + d
+
+    @staticmethod
+    def forward(ctx, div, stepper, closed_code, accuracy, max_iterations):
+        assert closed_code in (0, 1), "the chained slab solve covers uniformly open or closed domains"
+        iters = torch.zeros(div.shape[0], device=div.device, dtype=torch.int32)
+        p = _SlabSolveChained._solve(div.contiguous(), stepper, closed_code, accuracy, max_iterations, iters)
+        ctx.cfg = (stepper, closed_code, accuracy, max_iterations)
+        ctx.mark_non_differentiable(iters)
+        return p, iters
+
+    @staticmethod
+    def backward(ctx, g_p, _gi):
+        stepper, closed_code, accuracy, max_iterations = ctx.cfg
+        return _SlabSolveChained._solve(g_p.contiguous(), stepper, closed_code, accuracy, max_iterations, None), None, None, None, None
+
+
 class SlabStepper(object):
     """IncompressibleFlow.step (PF/physics/fluid.py:90-114; no obstacles / effects) on a row-slab decomposed domain."""
 
@@ -249,8 +296,9 @@ class SlabStepper(object):
         yhi = bool(bits & 2) and not self.layout.has_hi and hhi == 0
         return (ylo, yhi, bool(bits & 4), bool(bits & 8))
 
-    def step(self, rho, vy, vx, dt, closed, accuracy=1e-5, max_iterations=20000, conserve_density=True):
-        """Local slabs in, local slabs out: (rho', vy', vx', p, cg iterations)."""
+    def step(self, rho, vy, vx, dt, closed, accuracy=1e-5, max_iterations=20000, conserve_density=True, chained=False):
+        """Local slabs in, local slabs out: (rho', vy', vx', p, cg iterations).  chained=True: the solver chain SparseSciPy() & SparseCG
+        (_SlabSolveChained: whole-domain exact solve on every rank as the guess, slab CG on the correction)."""
         from . import ops
         from ._lib import MODE_CONSTANT, MODE_REPLICATE
         lay, H = self.layout, self.halo
@@ -279,7 +327,7 @@ class SlabStepper(object):
             rho2 = rho2 * (s_old / torch.clamp(s_new, min=1e-5))[:, None, None]
         # projection: divergence is local (the seam face is there), the solve is the slab CG, the gradient needs one halo row of p
         div = ops.mask_divergence(ay.contiguous(), ax.contiguous(), self._sides(closed, 0, 0))
-        p, iters = _SlabSolve.apply(div, self, ops.closed_code(closed), accuracy, int(max_iterations))
+        p, iters = (_SlabSolveChained if chained else _SlabSolve).apply(div, self, ops.closed_code(closed), accuracy, int(max_iterations))
         plo, phi = lay.halo_widths(1)
         p_h = self.ex.exchange(p, "p", 1)
         zy = ay.new_zeros((ay.shape[0], 1, ay.shape[2]))

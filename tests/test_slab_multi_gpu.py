@@ -125,6 +125,31 @@ def _step_worker(rank, world, port, out_dir):
         rel = lambda a, b: float((a - b).abs().max() / b.abs().max())
         out[closed] = dict(state=[rel(a, b.detach()) for a, b in zip(full, s)], grad=[rel(a, b) for a, b in zip(gfull, grads_ref)],
                            loss=(float(loss_all), float(loss_ref)), status=int(st.ex.status.item()), violations=int(st.halo_violations.item()))
+        # the same with the solver chain on the slabs (whole-domain exact solve as the guess, slab CG on the correction system)
+        loc2 = [t.detach().clone().requires_grad_(True) for t in st.scatter(*[g.detach() for g in glob])]
+        z, its = tuple(loc2), []
+        for _ in range(steps):
+            o = st.step(*z, dt, closed, accuracy=1e-7, max_iterations=8000, chained=True)
+            z = o[:3]
+            its.append(int(o[4].max()))
+        zy = z[1][:, :-1] if lay.has_hi else z[1]
+        loss2 = ((z[0] - tgt[:, lay.r0:lay.r1]) ** 2).sum() / (2 * B) + 0.1 * (zy ** 2).sum() / (2 * B) + 0.1 * (z[2] ** 2).sum() / (2 * B)
+        g2 = torch.autograd.grad(loss2, loc2)
+        full2 = [st.gather(z[0].detach()), st.gather(z[1].detach(), slab.YFACE), st.gather(z[2].detach())]
+        gfull2 = [st.gather_grad(g2[0]), st.gather_grad(g2[1], slab.YFACE), st.gather_grad(g2[2])]
+        torch.cuda.synchronize()
+        # its reference: the single-GPU trajectory with the EXACT solver.  (On the closed domain the fp32 CG cannot reach 1e-7 on the rough
+        # right-hand sides of the adjoint: it runs to max_iterations and ends 1e-3 off -- in the single-GPU step and in the plain slab CG
+        # alike, which is why those two agree with each other; the chain is compared with the exact answer instead.)
+        glob2 = [g.detach().clone().requires_grad_(True) for g in glob]
+        sd = tuple(glob2)
+        for _ in range(steps):
+            sd = ops.incompressible_step(*sd, dt, closed, direct=True)[:3]
+        loss_d = ((sd[0] - tgt) ** 2).sum() / (2 * B) + 0.1 * (sd[1] ** 2).sum() / (2 * B) + 0.1 * (sd[2] ** 2).sum() / (2 * B)
+        grads_d = torch.autograd.grad(loss_d, glob2)
+        out[closed].update(chained_state=[rel(a, b.detach()) for a, b in zip(full2, sd)], chained_grad=[rel(a, b) for a, b in zip(gfull2, grads_d)],
+                           cg_vs_exact_grad=[rel(a, b) for a, b in zip(grads_ref, grads_d)],
+                           chained_iterations=its, status2=int(st.ex.status.item()))
         st.close()
     if rank == 0:
         np.save(os.path.join(out_dir, "step.npy"), np.array([out], dtype=object), allow_pickle=True)
@@ -142,3 +167,6 @@ def test_two_gpu_slab_step_and_adjoint_match_the_single_gpu_step(tmp_path):
         assert abs(r["loss"][0] - r["loss"][1]) < 1e-4 * abs(r["loss"][1]), r
         assert max(r["state"]) < 1e-4, r          # sample coordinates of a haloed slab round differently from the global grid's: ~1e-6
         assert max(r["grad"]) < 1e-3, r           # both paths solve to 1e-7: at 1e-6 two CG implementations differ by 1.6e-3 in the gradient
+        # solver chain on the slabs: same results, a handful of correction iterations instead of hundreds
+        assert r["status2"] == 0 and max(r["chained_state"]) < 1e-4 and max(r["chained_grad"]) < 1e-3, r
+        assert max(r["chained_iterations"]) < 200, r
