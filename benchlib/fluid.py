@@ -52,8 +52,9 @@ class FluidConfig3(object):
         self.mean_it, self.max_it = float(its.mean()), int(its.max())
         self.sum_max_it = float(its.max(dim=1).values.sum())            # a CG launch lasts as long as its slowest batch element
         # per projected step: 3 advection kernels + divergence + solve + gradient subtraction forward (6), and in the adjoint
-        # subtraction^T + solve + divergence^T + 2 x (memset + prep + gather-transpose) (9); plus a few torch kernels for the loss
-        self.launches_per_step = self.STEPS * 15 + 6
+        # subtraction^T + solve + divergence^T + 2 x (max-reduction + scatter + conversion) (9); the chained variant runs two solver
+        # kernels per solve (+2); plus a few torch kernels for the loss
+        self.launches_per_step = self.STEPS * (17 if self.direct == "chain" else 15) + 6
 
     def step(self):
         self.graphed.replay()
