@@ -565,28 +565,29 @@ __global__ void __launch_bounds__(256) mask_divergence_bwd_kernel(const float* _
 // ---- pressure-gradient subtraction (fluid.py:240-242, staggered_grid.py:219-231) ---------------------
 __global__ void __launch_bounds__(256) subtract_gradient_fwd_kernel(const float* __restrict__ vy, const float* __restrict__ vx, const float* __restrict__ p,
                                                                     float* __restrict__ oy, float* __restrict__ ox, int ny, int nx, unsigned closed,
-                                                                    float dx0, float dxy, float dxx) {
+                                                                    float dx0, float dxy, float dxx, float iy, float ix) {
+    // iy / ix: exact reciprocal of dxy / dxx when that is a power of two (x / 2^k == x * 2^-k bit for bit), else 0 -> divide
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     const float* q = p + (size_t)b * ny * nx;
     if (i <= ny && j < nx) {
         const size_t o = (size_t)b * (ny + 1) * nx + (size_t)i * nx + j;
         const float m = face_mask_y(i, ny, closed);
         float gr = 0.0f;                                   // replicate pad: boundary-face gradient is 0
-        if (i >= 1 && i < ny) gr = (q[(size_t)i * nx + j] * dx0 - q[(size_t)(i - 1) * nx + j] * dx0) / dxy;
+        if (i >= 1 && i < ny) { const float d = q[(size_t)i * nx + j] * dx0 - q[(size_t)(i - 1) * nx + j] * dx0; gr = iy != 0.0f ? d * iy : d / dxy; }
         oy[o] = vy[o] * m - gr * m;
     }
     if (i < ny && j <= nx) {
         const size_t o = (size_t)b * ny * (nx + 1) + (size_t)i * (nx + 1) + j;
         const float m = face_mask_x(j, nx, closed);
         float gr = 0.0f;
-        if (j >= 1 && j < nx) gr = (q[(size_t)i * nx + j] * dx0 - q[(size_t)i * nx + j - 1] * dx0) / dxx;
+        if (j >= 1 && j < nx) { const float d = q[(size_t)i * nx + j] * dx0 - q[(size_t)i * nx + j - 1] * dx0; gr = ix != 0.0f ? d * ix : d / dxx; }
         ox[o] = vx[o] * m - gr * m;
     }
 }
 
 __global__ void __launch_bounds__(256) subtract_gradient_bwd_kernel(const float* __restrict__ g_oy, const float* __restrict__ g_ox, float* __restrict__ g_vy,
                                                                     float* __restrict__ g_vx, float* __restrict__ g_p, int ny, int nx, unsigned closed,
-                                                                    float dx0, float dxy, float dxx, int accumulate) {
+                                                                    float dx0, float dxy, float dxx, int accumulate, float iy, float ix) {
     const int j = blockIdx.x * 32 + threadIdx.x, i = blockIdx.y * 8 + threadIdx.y, b = blockIdx.z;
     const float* gy = g_oy + (size_t)b * (ny + 1) * nx;
     const float* gx = g_ox + (size_t)b * ny * (nx + 1);
@@ -603,10 +604,12 @@ __global__ void __launch_bounds__(256) subtract_gradient_bwd_kernel(const float*
     if (g_p != nullptr && i < ny && j < nx) {
         // interior faces only: face i (1..ny-1) contributes -g/dx to p[i] and +g/dx to p[i-1]
         float acc = 0.0f;
-        if (i >= 1) acc -= gy[(size_t)i * nx + j] / dxy;
-        if (i + 1 < ny) acc += gy[(size_t)(i + 1) * nx + j] / dxy;
-        if (j >= 1) acc -= gx[(size_t)i * (nx + 1) + j] / dxx;
-        if (j + 1 < nx) acc += gx[(size_t)i * (nx + 1) + j + 1] / dxx;
+        auto by = [&](float v) { return iy != 0.0f ? v * iy : v / dxy; };
+        auto bx = [&](float v) { return ix != 0.0f ? v * ix : v / dxx; };
+        if (i >= 1) acc -= by(gy[(size_t)i * nx + j]);
+        if (i + 1 < ny) acc += by(gy[(size_t)(i + 1) * nx + j]);
+        if (j >= 1) acc -= bx(gx[(size_t)i * (nx + 1) + j]);
+        if (j + 1 < nx) acc += bx(gx[(size_t)i * (nx + 1) + j + 1]);
         g_p[(size_t)b * ny * nx + (size_t)i * nx + j] = acc * dx0;
     }
 }
@@ -694,6 +697,12 @@ static void half_weights(float self_lower, float self_size, int self_res, float 
     wl = (float)(1.0 - w);
 }
 
+// 1 / v when v is a power of two (then x / v == x * (1 / v) bit for bit), else 0
+static float pow2_reciprocal(float v) {
+    int e;
+    return (v > 0.0f && frexpf(v, &e) == 0.5f && e > -100 && e < 100) ? 1.0f / v : 0.0f;
+}
+
 static int make_geo(FluidGeo& g, int B, int ny, int nx, double dt, float lower_y, float lower_x, float size_y, float size_x) {
     if (B < 0 || ny < 2 || nx < 2 || !(size_y > 0.0f) || !(size_x > 0.0f)) return PDEC_ERR_INVALID_ARGUMENT;
     if (B > 65535) return PDEC_ERR_UNSUPPORTED_SIZE;
@@ -710,7 +719,7 @@ static int make_geo(FluidGeo& g, int B, int ny, int nx, double dt, float lower_y
             g.clo[c][a] = lo_c;
             g.csz[c][a] = up_c - lo_c;
         }
-    auto exact_inv = [](float v) { int e; return (v > 0.0f && frexpf(v, &e) == 0.5f && e > -100 && e < 100) ? 1.0f / v : 0.0f; };
+    auto exact_inv = [](float v) { return pow2_reciprocal(v); };
     for (int a = 0; a < 2; ++a) {
         g.inv[a] = exact_inv(g.sz[a]);
         for (int c = 0; c < 2; ++c) g.cinv[c][a] = exact_inv(g.csz[c][a]);
@@ -1034,7 +1043,7 @@ extern "C" int pdec_subtract_pressure_gradient_2d_fwd(const float* vy, const flo
     if (!vy || !vx || !p || !vy_out || !vx_out) return PDEC_ERR_INVALID_ARGUMENT;
     const float dxy = (float)((double)size_y / ny), dxx = (float)((double)size_x / nx);
     subtract_gradient_fwd_kernel<<<tiles(ny + 1, nx + 1, B), kBlock, 0, (cudaStream_t)stream>>>(vy, vx, p, vy_out, vx_out, ny, nx, pdec_closed_sides(closed),
-                                                                                                 dxy, dxy, dxx);
+                                                                                                 dxy, dxy, dxx, pow2_reciprocal(dxy), pow2_reciprocal(dxx));
     PDEC_CHECK_LAUNCH();
     return PDEC_OK;
 }
@@ -1047,7 +1056,8 @@ extern "C" int pdec_subtract_pressure_gradient_2d_bwd(const float* g_vy_out, con
     if (!g_vy_out || !g_vx_out) return PDEC_ERR_INVALID_ARGUMENT;
     const float dxy = (float)((double)size_y / ny), dxx = (float)((double)size_x / nx);
     subtract_gradient_bwd_kernel<<<tiles(ny + 1, nx + 1, B), kBlock, 0, (cudaStream_t)stream>>>(g_vy_out, g_vx_out, g_vy, g_vx, g_p, ny, nx,
-                                                                                                 pdec_closed_sides(closed), dxy, dxy, dxx, accumulate_v);
+                                                                                                 pdec_closed_sides(closed), dxy, dxy, dxx, accumulate_v,
+                                                                                                 pow2_reciprocal(dxy), pow2_reciprocal(dxx));
     PDEC_CHECK_LAUNCH();
     return PDEC_OK;
 }
